@@ -1,0 +1,300 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the expANN query hot path on B200 (contract: see DESIGN.md §Measurement).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c4|c5]
+
+A "step" is one pass of the hot path over one batch of m synthetic queries against the HBM-resident base set.
+  value : QPS, device-resident queries in, merged 64-bit (dist,id) keys out (CUDA events, max over ranks)
+  e2e   : QPS through the reference-facing host-buffer call (expann_gpu_query at N=1), H2D of the queries and
+          D2H of ids inside the timed region
+  roofline : algorithmic bytes of the dominant kernel / its CUDA-event time (events recorded inside the library
+          around every scan launch on the launching stream)
+  cpu_baseline : the UNMODIFIED reference brute_force_engine (oracle/_ref) — or the C restatement when that
+          build is not usable on this host — timed on a bounded query sample with all host threads
+N > 1 (torchrun): the base set is sharded by contiguous row ranges (strong scaling: the same 1M-row base over
+N GPUs), every rank scans its shard for all queries, the per-rank [m][k] key lists are all-gathered over NCCL
+and merged by K7 on every rank.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (generator, variant, n, m, d, k, metric, description)
+    "c1": ("gauss", None, 56_000, 400, 128, 10, "l2", "config_synthetic.json shape 56000x128 gaussian, m=400 (L2-resident)"),
+    "c2": ("sift", "iid", 1_000_000, 10_000, 128, 10, "l2", "SIFT-shape synthetic 1Mx128 fp32 (u8-valued iid), 10k queries, brute-force L2 exact top-10"),
+    "c4": ("deep", None, 10_000_000, 10_000, 96, 10, "l2", "Deep-shape synthetic 10Mx96 fp32, 10k queries, sharded brute-force L2 top-10"),
+    "c5": ("gist", None, 1_000_000, 1_000, 960, 10, "ip", "GIST-shape synthetic 1Mx960 fp32, 1k queries, brute-force inner-product top-10"),
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:  # noqa: BLE001
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)"""
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_reference_qps(base, q, k, metric, budget_s=15.0):
+    """time the reference's own CPU brute force (oracle/_ref) on a bounded query sample, all host threads.
+    Returns (qps, cores, kind, sample description)."""
+    from oracle import pyoracle
+    threads = os.cpu_count() or 1
+    d = base.shape[1]
+    kind, eng = "port", None
+    if metric == "l2":
+        try:
+            ref = pyoracle.Reference(128 if d == 128 else None)
+            t0 = time.perf_counter()
+            eng = ref.bf(base)  # store_vector x n + build (not timed as query time)
+            kind = "reference"
+        except Exception:  # noqa: BLE001
+            eng = None
+    orc = pyoracle.Oracle() if eng is None else None
+
+    def run(qs):
+        t0 = time.perf_counter()
+        if eng is not None:
+            eng.query(qs, k, threads=threads)
+        else:
+            orc.bf_query(base, qs, k, metric=1 if metric == "ip" else 0, threads=threads)
+        return time.perf_counter() - t0
+
+    probe = q[:min(len(q), threads)]
+    t = run(probe)
+    per_q = t / len(probe)
+    msample = int(max(len(probe), min(len(q), budget_s / max(per_q, 1e-9))))
+    msample = max(threads, msample // threads * threads) if msample >= threads else msample
+    msample = min(msample, len(q))
+    t = run(q[:msample])
+    return msample / t, threads, kind, f"{msample} of {len(q)} queries, full {base.shape[0]}x{d} base, {threads} threads, {t:.1f}s"
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--qtile", type=int, default=0)
+    ap.add_argument("--m", type=int, default=0, help="override the query count")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    gen, variant, n, m, d, k, metric, desc = WORKLOADS[args.workload]
+    if args.m:
+        m = args.m
+    from expann_b200 import datasets
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        base, q = datasets.make(gen, n, m, d, variant=variant or "lowrank")
+        # each step = a bounded sample of the workload's queries on the full base
+        budget = max(4.0, 120.0 / max(1, args.steps + args.warmup))
+        vals = []
+        info = None
+        for i in range(args.warmup + args.steps):
+            qps, cores, kind, sample = cpu_reference_qps(base, q, k, metric, budget_s=budget)
+            if i >= args.warmup:
+                vals.append(qps)
+            info = (cores, kind, sample)
+        v = float(np.mean(vals))
+        out = {"impl": "reference", "metric": "QPS (exact brute-force top-%d)" % k, "value": v, "unit": "queries/s",
+               "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * m / v,
+               "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+               "config": {"workload": desc, "n": n, "m": m, "d": d, "k": k, "metric": metric},
+               "cpu_baseline": {"value": v, "unit": "queries/s", "cores": info[0], "kind": info[1], "sample": info[2]},
+               "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(out))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    import expann_b200
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: no CUDA device visible (there is no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+
+    base, q = datasets.make(gen, n, m, d, variant=variant or "lowrank")
+    rows_per = (n + world - 1) // world
+    lo, hi = rank * rows_per, min(n, (rank + 1) * rows_per)
+    eng = expann_b200.BruteForceEngine(metric=1 if metric == "ip" else 0, device=local_rank, qtile=args.qtile, id_offset=lo)
+    eng.store_many_vectors(base[lo:hi])
+    eng.build()
+
+    stream = torch.cuda.current_stream().cuda_stream
+    dq = torch.from_numpy(q).to(dev)
+    hq = torch.from_numpy(q).pin_memory()
+    local_keys = torch.empty((m, k), dtype=torch.int64, device=dev)
+    gathered = torch.empty((world, m, k), dtype=torch.int64, device=dev) if world > 1 else None
+    final_keys = torch.empty((m, k), dtype=torch.int64, device=dev)
+    ids_dev = torch.empty((m, k), dtype=torch.int64, device=dev)
+    ids_host = torch.empty((m, k), dtype=torch.int64).pin_memory()
+    dq_e2e = torch.empty_like(dq)
+
+    def step_device(qptr):
+        if world == 1:
+            eng.query_device(qptr, m, k, final_keys.data_ptr(), stream)
+        else:
+            eng.query_device(qptr, m, k, local_keys.data_ptr(), stream)
+            dist.all_gather_into_tensor(gathered, local_keys)
+            eng.merge_device(gathered.data_ptr(), m, world, k, k, m * k, k, final_keys.data_ptr(), stream)
+
+    def step_e2e():
+        if world == 1:
+            return eng.query_k_batch(q, k)[0]          # the C-ABI host call: H2D q, scan, merge, decode, D2H
+        dq_e2e.copy_(hq, non_blocking=True)
+        step_device(dq_e2e.data_ptr())
+        eng.decode_device(final_keys.data_ptr(), m, k, ids_dev.data_ptr(), 0, 0, stream)
+        ids_host.copy_(ids_dev, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return ids_host
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(args.warmup):
+        step_device(dq.data_ptr())
+    barrier()
+    st0 = eng.stats()
+    eng.set_timing(True)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms = timed(lambda: step_device(dq.data_ptr()), args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    st1 = eng.stats()
+    eng.set_timing(False)
+    # e2e leg (host buffers): its own warm-up, then K timed steps by wall clock bracketed by barriers
+    for _ in range(max(1, min(args.warmup, 2))):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e_s.item())
+
+    # correctness spot check on rank 0 (not timed): the keys decode to sorted unique ids
+    eng.decode_device(final_keys.data_ptr(), m, k, ids_dev.data_ptr(), 0, 0, stream)
+    torch.cuda.synchronize()
+    got = ids_dev[:4].cpu().numpy()
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        launches = sum(st1[x] - st0[x] for x in ("scan_launches", "merge_launches", "graph_launches", "aux_launches"))
+        hot_ms = (st1["hot_time_ns"] - st0["hot_time_ns"]) / 1e6 / max(1, st1["hot_timed_launches"] - st0["hot_timed_launches"])
+        qt = st1["last_qtile"]
+        passes = (m + qt - 1) // qt
+        alg_bytes = passes * (hi - lo) * d * 4
+        achieved = alg_bytes / (hot_ms * 1e-3) / 1e9
+        out = {"metric": "QPS (exact brute-force top-%d)" % k, "value": m * args.steps / (ms * 1e-3), "unit": "queries/s",
+               "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+               "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+               "config": {"workload": desc, "n": n, "m": m, "d": d, "k": k, "metric": metric, "qtile": int(qt),
+                          "nsplit": int(st1["last_nsplit"]), "rows_per_gpu": hi - lo,
+                          "l2": "base shard (%.0f MB) %s L2 (126 MB); no explicit flush" % ((hi - lo) * d * 4 / 1e6, "larger than" if (hi - lo) * d * 4 > 126e6 else "fits in"),
+                          "parallelism": "base rows sharded x%d, NCCL all-gather of [m][k] keys + K7 merge" % world if world > 1 else "single GPU"},
+               "e2e": {"value": m * args.steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(m * d * 4),
+                       "d2h_bytes_per_step": int(m * k * 8 + (m * k * 4 + m * 8 if world == 1 else 0)),
+                       "api": "expann_gpu_query (host buffers)" if world == 1 else "pinned H2D + query_device + all_gather + merge + decode + D2H"},
+               "gpu_launches": int(launches),
+               "roofline": {"bound": "hbm", "kernel": "scan_topk_f32_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                            "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                            "algorithmic_bytes_per_launch": int(alg_bytes), "kernel_ms_per_launch": hot_ms,
+                            "note": "algorithmic bytes = ceil(m/qtile) passes x shard bytes (SURVEY 8(d)); CTAs of one "
+                                    "wave share rows through L2, so DRAM traffic is lower than this figure"},
+               "clocks": clocks}
+        if not args.no_cpu and world == 1:
+            qps, cores, kind, sample = cpu_reference_qps(base, q, k, metric)
+            out["cpu_baseline"] = {"value": qps, "unit": "queries/s", "cores": cores, "kind": kind, "sample": sample}
+        out["check"] = {"first_ids": got[0].tolist()}
+        print(json.dumps(out))
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

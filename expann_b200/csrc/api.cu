@@ -1,0 +1,299 @@
+// C ABI of libexpann_gpu.so (declared in include/expann_gpu.h). Host-side state machine only; the kernels
+// live in scan_f32.cuh / merge_topk.cuh / graph_search.cuh / quant_scan.cuh.
+#include "engine.h"
+#include <algorithm>
+#include <cstring>
+#include <new>
+
+namespace expann {
+
+static thread_local std::string g_create_err;
+
+int fail(expann_gpu* h, int code, const std::string& msg) {
+	if (h) h->err = msg; else g_create_err = msg;
+	return code;
+}
+int cuda_fail(expann_gpu* h, cudaError_t e, const char* what) {
+	return fail(h, EXPANN_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+static cudaEvent_t get_event(expann_gpu* h) {
+	if (!h->event_pool.empty()) { cudaEvent_t e = h->event_pool.back(); h->event_pool.pop_back(); return e; }
+	cudaEvent_t e = nullptr;
+	cudaEventCreate(&e);
+	return e;
+}
+cudaEvent_t timing_begin(expann_gpu* h, cudaStream_t st) {
+	if (!h->timing) return nullptr;
+	cudaEvent_t e = get_event(h);
+	if (e) cudaEventRecord(e, st);
+	return e;
+}
+void timing_end(expann_gpu* h, cudaEvent_t start, cudaStream_t st) {
+	if (!start) return;
+	cudaEvent_t e = get_event(h);
+	if (e) cudaEventRecord(e, st);
+	h->timed.emplace_back(start, e);
+}
+static void timing_collect(expann_gpu* h) {
+	for (auto& pr : h->timed) {
+		float ms = 0.f;
+		if (pr.second && cudaEventSynchronize(pr.second) == cudaSuccess &&
+		    cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) {
+			h->stats.hot_time_ns += (uint64_t)((double)ms * 1e6);
+			h->stats.hot_timed_launches++;
+		}
+		if (pr.first) h->event_pool.push_back(pr.first);
+		if (pr.second) h->event_pool.push_back(pr.second);
+	}
+	h->timed.clear();
+}
+
+static size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct DeviceGuard {
+	int prev = -1;
+	explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); }
+	~DeviceGuard() { int cur; cudaGetDevice(&cur); if (prev >= 0 && cur != prev) cudaSetDevice(prev); }
+};
+
+// grow the HBM base buffer to hold `rows` rows (zero-filled so the d..d_pad padding columns stay 0)
+static int reserve_rows(expann_gpu* h, size_t rows) {
+	if (rows <= h->cap_rows) return EXPANN_OK;
+	size_t want = rows;
+	if (h->cap_rows) want = std::max(rows, h->cap_rows + h->cap_rows / 2);
+	float* nb = nullptr;
+	EXPANN_CUDA(h, cudaMalloc(&nb, want * h->d_pad * sizeof(float)));
+	cudaError_t e = cudaMemsetAsync(nb, 0, want * h->d_pad * sizeof(float), h->stream);
+	if (e == cudaSuccess && h->n)
+		e = cudaMemcpyAsync(nb, h->base, h->n * h->d_pad * sizeof(float), cudaMemcpyDeviceToDevice, h->stream);
+	if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+	if (e != cudaSuccess) { cudaFree(nb); return cuda_fail(h, e, "reserve_rows"); }
+	if (h->base) cudaFree(h->base);
+	h->base = nb;
+	h->cap_rows = want;
+	return EXPANN_OK;
+}
+
+static int upload_rows(expann_gpu* h, const float* rows, size_t n, cudaMemcpyKind kind, cudaStream_t st) {
+	if (int rc = reserve_rows(h, h->n + n)) return rc;
+	EXPANN_CUDA(h, cudaMemcpy2DAsync(h->base + h->n * h->d_pad, h->d_pad * sizeof(float), rows, h->d * sizeof(float),
+	                                 h->d * sizeof(float), n, kind, st));
+	EXPANN_CUDA(h, cudaStreamSynchronize(st));
+	h->n += n;
+	h->built = false;
+	return EXPANN_OK;
+}
+
+static int flush_staging(expann_gpu* h) {
+	if (!h->staged_rows) return EXPANN_OK;
+	size_t rows = h->staged_rows;
+	h->staged_rows = 0;
+	int rc = upload_rows(h, h->staging.data(), rows, cudaMemcpyHostToDevice, h->stream);
+	h->staging.clear();
+	return rc;
+}
+
+static int check_dim(expann_gpu* h, size_t d) {
+	if (d == 0) return fail(h, EXPANN_ERR_ARG, "d must be > 0");
+	if (h->d == 0) {
+		h->d = d;
+		h->d_pad = round_up(d, 32);
+	} else if (h->d != d)
+		return fail(h, EXPANN_ERR_ARG, "dimension mismatch with previously stored vectors");
+	return EXPANN_OK;
+}
+
+// pad device queries [m][d] -> [m][d_pad] when d is not a multiple of 32 floats
+static int padded_queries(expann_gpu* h, const float* d_q, size_t m, cudaStream_t st, const float** out) {
+	if (h->d == h->d_pad) { *out = d_q; return EXPANN_OK; }
+	EXPANN_CUDA(h, h->qpad.ensure(m * h->d_pad * sizeof(float)));
+	EXPANN_CUDA(h, cudaMemsetAsync(h->qpad.p, 0, m * h->d_pad * sizeof(float), st));
+	EXPANN_CUDA(h, cudaMemcpy2DAsync(h->qpad.p, h->d_pad * sizeof(float), d_q, h->d * sizeof(float), h->d * sizeof(float),
+	                                 m, cudaMemcpyDeviceToDevice, st));
+	h->stats.aux_launches += 2;
+	*out = h->qpad.as<float>();
+	return EXPANN_OK;
+}
+
+static int query_device_impl(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out,
+                             cudaStream_t st) {
+	(void)ef;
+	if (!h->built) return fail(h, EXPANN_ERR_STATE, "query before build()");
+	if (k == 0) return fail(h, EXPANN_ERR_ARG, "k must be > 0");
+	if (m == 0) return EXPANN_OK;
+	const float* qp = nullptr;
+	if (int rc = padded_queries(h, d_q, m, st, &qp)) return rc;
+	switch (h->cfg.engine) {
+	case EXPANN_ENGINE_BRUTE_FORCE:
+		return launch_scan_f32(h, qp, m, k, d_keys_out, st);
+	default:
+		return fail(h, EXPANN_ERR_UNSUPPORTED, "engine kind not implemented");
+	}
+}
+
+} // namespace expann
+
+using namespace expann;
+
+extern "C" {
+
+const char* expann_gpu_version(void) { return "expann_b200 0.1; sm_100a; kernels: scan_topk_f32 merge_topk decode_keys"; }
+
+int expann_gpu_create(const expann_gpu_cfg* cfg, expann_gpu_t** out) {
+	if (!cfg || !out) return fail(nullptr, EXPANN_ERR_ARG, "null argument");
+	*out = nullptr;
+	if (cfg->engine != EXPANN_ENGINE_BRUTE_FORCE) return fail(nullptr, EXPANN_ERR_UNSUPPORTED, "engine kind not implemented");
+	if (cfg->metric != EXPANN_METRIC_L2 && cfg->metric != EXPANN_METRIC_IP) return fail(nullptr, EXPANN_ERR_ARG, "bad metric");
+	int ndev = 0;
+	cudaError_t e = cudaGetDeviceCount(&ndev);
+	if (e != cudaSuccess || ndev == 0)
+		return fail(nullptr, EXPANN_ERR_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e) +
+		                                          " (this library has no CPU fallback)");
+	int dev = cfg->device;
+	if (dev < 0) cudaGetDevice(&dev);
+	if (dev >= ndev) return fail(nullptr, EXPANN_ERR_ARG, "device ordinal out of range");
+	cudaDeviceProp prop;
+	e = cudaGetDeviceProperties(&prop, dev);
+	if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaGetDeviceProperties");
+	if (prop.major != 10) return fail(nullptr, EXPANN_ERR_UNSUPPORTED, "device is not sm_100 (kernels are built for sm_100a only)");
+	expann_gpu* h = new (std::nothrow) expann_gpu();
+	if (!h) return fail(nullptr, EXPANN_ERR_ARG, "out of host memory");
+	h->cfg = *cfg;
+	h->device = dev;
+	DeviceGuard g(dev);
+	e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+	if (e != cudaSuccess) { delete h; return cuda_fail(nullptr, e, "cudaStreamCreate"); }
+	*out = h;
+	return EXPANN_OK;
+}
+
+void expann_gpu_destroy(expann_gpu_t* h) {
+	if (!h) return;
+	DeviceGuard g(h->device);
+	if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
+	timing_collect(h);
+	for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
+	if (h->base) cudaFree(h->base);
+	for (DevBuf* b : { &h->qpad, &h->partial, &h->keys, &h->ids, &h->dists, &h->counts, &h->h_q, &h->h_ids, &h->h_dists,
+	                   &h->h_counts })
+		b->release();
+	delete h;
+}
+
+const char* expann_gpu_last_error(const expann_gpu_t* h) { return h ? h->err.c_str() : g_create_err.c_str(); }
+
+int expann_gpu_add(expann_gpu_t* h, const float* rows, size_t n, size_t d) {
+	if (!h || (!rows && n)) return fail(h, EXPANN_ERR_ARG, "null argument");
+	if (int rc = check_dim(h, d)) return rc;
+	if (n == 0) return EXPANN_OK;
+	DeviceGuard g(h->device);
+	const size_t small = 4096; // rows; per-vector store_vector calls are batched on the host
+	if (n < small) {
+		h->staging.insert(h->staging.end(), rows, rows + n * d);
+		h->staged_rows += n;
+		h->built = false;
+		if (h->staging.size() * sizeof(float) >= (size_t)64 << 20) return flush_staging(h);
+		return EXPANN_OK;
+	}
+	if (int rc = flush_staging(h)) return rc;
+	return upload_rows(h, rows, n, cudaMemcpyHostToDevice, h->stream);
+}
+
+int expann_gpu_add_device(expann_gpu_t* h, const float* d_rows, size_t n, size_t d, void* stream) {
+	if (!h || (!d_rows && n)) return fail(h, EXPANN_ERR_ARG, "null argument");
+	if (int rc = check_dim(h, d)) return rc;
+	if (n == 0) return EXPANN_OK;
+	DeviceGuard g(h->device);
+	if (int rc = flush_staging(h)) return rc;
+	cudaStream_t st = (cudaStream_t)stream;
+	EXPANN_CUDA(h, cudaStreamSynchronize(st));
+	return upload_rows(h, d_rows, n, cudaMemcpyDeviceToDevice, h->stream);
+}
+
+int expann_gpu_build(expann_gpu_t* h) {
+	if (!h) return EXPANN_ERR_ARG;
+	DeviceGuard g(h->device);
+	if (int rc = flush_staging(h)) return rc;
+	if (h->n == 0) return fail(h, EXPANN_ERR_STATE, "build() on an empty engine (the reference asserts n > 0)");
+	if (h->n + h->cfg.id_offset > 0xFFFFFFFEull) return fail(h, EXPANN_ERR_UNSUPPORTED, "ids must fit 32 bits on device");
+	if (int rc = make_base_tensor_map(h)) return rc;
+	h->stats.n = h->n;
+	h->stats.d = h->d;
+	h->stats.d_pad = h->d_pad;
+	h->built = true;
+	return EXPANN_OK;
+}
+
+int expann_gpu_query_device(expann_gpu_t* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out,
+                            void* stream) {
+	if (!h || (m && (!d_q || !d_keys_out))) return fail(h, EXPANN_ERR_ARG, "null argument");
+	DeviceGuard g(h->device);
+	return query_device_impl(h, d_q, m, k, ef, d_keys_out, (cudaStream_t)stream);
+}
+
+int expann_gpu_query(expann_gpu_t* h, const float* q, size_t m, size_t k, size_t ef, uint64_t* ids_out, float* dist_out,
+                     uint64_t* counts_out) {
+	if (!h || (m && (!q || !ids_out))) return fail(h, EXPANN_ERR_ARG, "null argument");
+	if (!h->built) return fail(h, EXPANN_ERR_STATE, "query before build()");
+	if (k == 0) return fail(h, EXPANN_ERR_ARG, "k must be > 0");
+	if (m == 0) return EXPANN_OK;
+	DeviceGuard g(h->device);
+	cudaStream_t st = h->stream;
+	const size_t qbytes = m * h->d * sizeof(float), nk = m * k;
+	EXPANN_CUDA(h, h->h_q.ensure(qbytes));
+	EXPANN_CUDA(h, h->h_ids.ensure(nk * 8));
+	EXPANN_CUDA(h, h->h_dists.ensure(nk * 4));
+	EXPANN_CUDA(h, h->h_counts.ensure(m * 8));
+	EXPANN_CUDA(h, h->keys.ensure(nk * 8 + qbytes + 256)); // keys | raw queries
+	EXPANN_CUDA(h, h->ids.ensure(nk * 8));
+	EXPANN_CUDA(h, h->dists.ensure(nk * 4));
+	EXPANN_CUDA(h, h->counts.ensure(m * 8));
+	std::memcpy(h->h_q.p, q, qbytes);
+	float* d_q = reinterpret_cast<float*>(h->keys.as<uint8_t>() + round_up(nk * 8, 256));
+	EXPANN_CUDA(h, cudaMemcpyAsync(d_q, h->h_q.p, qbytes, cudaMemcpyHostToDevice, st));
+	if (int rc = query_device_impl(h, d_q, m, k, ef, h->keys.as<uint64_t>(), st)) return rc;
+	if (int rc = launch_decode(h, h->keys.as<uint64_t>(), m, k, 0, h->ids.as<uint64_t>(), h->dists.as<float>(),
+	                           h->counts.as<uint64_t>(), st))
+		return rc;
+	EXPANN_CUDA(h, cudaMemcpyAsync(h->h_ids.p, h->ids.p, nk * 8, cudaMemcpyDeviceToHost, st));
+	if (dist_out) EXPANN_CUDA(h, cudaMemcpyAsync(h->h_dists.p, h->dists.p, nk * 4, cudaMemcpyDeviceToHost, st));
+	if (counts_out) EXPANN_CUDA(h, cudaMemcpyAsync(h->h_counts.p, h->counts.p, m * 8, cudaMemcpyDeviceToHost, st));
+	EXPANN_CUDA(h, cudaStreamSynchronize(st));
+	std::memcpy(ids_out, h->h_ids.p, nk * 8);
+	if (dist_out) std::memcpy(dist_out, h->h_dists.p, nk * 4);
+	if (counts_out) std::memcpy(counts_out, h->h_counts.p, m * 8);
+	return EXPANN_OK;
+}
+
+int expann_gpu_merge_device(expann_gpu_t* h, const uint64_t* d_keys_in, size_t m, size_t nlists, size_t klist,
+                            size_t stride_q, size_t stride_s, size_t k, uint64_t* d_keys_out, void* stream) {
+	if (!h || (m && (!d_keys_in || !d_keys_out))) return fail(h, EXPANN_ERR_ARG, "null argument");
+	DeviceGuard g(h->device);
+	return launch_merge(h, d_keys_in, m, nlists, klist, stride_q, stride_s, k, 0, d_keys_out, (cudaStream_t)stream);
+}
+
+int expann_gpu_decode_device(expann_gpu_t* h, const uint64_t* d_keys, size_t m, size_t k, uint64_t* d_ids, float* d_dist,
+                             uint64_t* d_counts, void* stream) {
+	if (!h || (m && (!d_keys || !d_ids))) return fail(h, EXPANN_ERR_ARG, "null argument");
+	DeviceGuard g(h->device);
+	return launch_decode(h, d_keys, m, k, 0, d_ids, d_dist, d_counts, (cudaStream_t)stream);
+}
+
+int expann_gpu_set_timing(expann_gpu_t* h, int on) {
+	if (!h) return EXPANN_ERR_ARG;
+	DeviceGuard g(h->device);
+	timing_collect(h);
+	h->timing = on != 0;
+	return EXPANN_OK;
+}
+
+int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out) {
+	if (!h || !out) return EXPANN_ERR_ARG;
+	DeviceGuard g(h->device);
+	timing_collect(h);
+	*out = h->stats;
+	return EXPANN_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,76 @@
+// Internal handle behind the C ABI (include/expann_gpu.h). Not installed; nothing here crosses the boundary.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/expann_gpu.h"
+
+namespace expann {
+
+struct DevBuf {
+	void* p = nullptr;
+	size_t cap = 0;
+	bool host = false; // pinned host memory instead of device memory
+	cudaError_t ensure(size_t bytes) {
+		if (bytes <= cap) return cudaSuccess;
+		release();
+		size_t want = bytes + bytes / 4 + 256;
+		cudaError_t e = host ? cudaMallocHost(&p, want) : cudaMalloc(&p, want);
+		if (e != cudaSuccess) { p = nullptr; cap = 0; return e; }
+		cap = want;
+		return cudaSuccess;
+	}
+	void release() {
+		if (p) { if (host) cudaFreeHost(p); else cudaFree(p); }
+		p = nullptr; cap = 0;
+	}
+	template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+} // namespace expann
+
+struct expann_gpu {
+	expann_gpu_cfg cfg{};
+	int device = 0;
+	std::string err;
+	// base set: row-major float[n][d_pad] in HBM, d_pad = d rounded up to 32 floats (128 B rows-chunks for TMA)
+	size_t n = 0, d = 0, d_pad = 0, cap_rows = 0;
+	float* base = nullptr;
+	std::vector<float> staging; // small host adds are batched here (d floats per row) until flushed
+	size_t staged_rows = 0;
+	bool built = false;
+	CUtensorMap tmap_base{};
+	cudaStream_t stream = nullptr;
+	expann::DevBuf qpad, partial, keys, ids, dists, counts; // device work buffers (grow-only)
+	expann::DevBuf h_q, h_ids, h_dists, h_counts;            // pinned host staging for the host-pointer API
+	expann_gpu_stats_t stats{};
+	bool timing = false;
+	std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timed; // pending (start, stop) pairs of the dominant kernel
+	std::vector<cudaEvent_t> event_pool;
+	expann_gpu() { h_q.host = h_ids.host = h_dists.host = h_counts.host = true; }
+};
+
+namespace expann {
+int fail(expann_gpu* h, int code, const std::string& msg);
+// timing brackets around the dominant kernel (no-ops unless expann_gpu_set_timing(h, 1))
+cudaEvent_t timing_begin(expann_gpu* h, cudaStream_t st);
+void timing_end(expann_gpu* h, cudaEvent_t start, cudaStream_t st);
+int cuda_fail(expann_gpu* h, cudaError_t e, const char* what);
+// scan_f32.cu
+int launch_scan_f32(expann_gpu* h, const float* d_q_padded, size_t m, size_t k, uint64_t* d_keys_out,
+                    cudaStream_t st);
+int make_base_tensor_map(expann_gpu* h);
+// merge_topk.cu
+int launch_merge(expann_gpu* h, const uint64_t* in, size_t m, size_t nlists, size_t klist, size_t stride_q,
+                 size_t stride_s, size_t k, uint32_t id_add, uint64_t* out, cudaStream_t st);
+int launch_decode(expann_gpu* h, const uint64_t* keys, size_t m, size_t k, int kind, uint64_t* ids, float* dists,
+                  uint64_t* counts, cudaStream_t st);
+} // namespace expann
+
+#define EXPANN_CUDA(h, call)                                              \
+	do {                                                                  \
+		cudaError_t _e = (call);                                          \
+		if (_e != cudaSuccess) return expann::cuda_fail((h), _e, #call);  \
+	} while (0)

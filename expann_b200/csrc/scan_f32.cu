@@ -1,0 +1,112 @@
+// Host side of K1/K2: tensor-map construction and launch-shape selection for the fp32 scan.
+#include "engine.h"
+#include "scan_f32.cuh"
+#include <algorithm>
+#include <mutex>
+
+namespace expann {
+
+constexpr int SCAN_TR = 2, SCAN_NWARP = 8, SCAN_STAGES = 3;
+constexpr int SCAN_ROWS = 32 * SCAN_TR * SCAN_NWARP; // 512 rows per pipeline stage
+constexpr int SCAN_BOXR = SCAN_ROWS > 256 ? 256 : SCAN_ROWS;
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static encode_tiled_fn get_encode_tiled() {
+	static encode_tiled_fn fn = nullptr;
+	static std::once_flag once;
+	std::call_once(once, [] {
+		void* p = nullptr;
+		cudaDriverEntryPointQueryResult qres;
+		if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+		    qres == cudaDriverEntryPointSuccess)
+			fn = reinterpret_cast<encode_tiled_fn>(p);
+	});
+	return fn;
+}
+
+// 2D view of the base set: dim0 = d_pad floats (contiguous), dim1 = n rows; box = [32 floats][BOXR rows],
+// 128B swizzle (16-byte chunk c of row r lands at chunk c ^ (r & 7) of its 128-byte line).
+int make_base_tensor_map(expann_gpu* h) {
+	encode_tiled_fn enc = get_encode_tiled();
+	if (!enc) return fail(h, EXPANN_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+	cuuint64_t gdim[2] = { (cuuint64_t)h->d_pad, (cuuint64_t)h->n };
+	cuuint64_t gstride[1] = { (cuuint64_t)h->d_pad * 4 };
+	cuuint32_t box[2] = { 32, (cuuint32_t)SCAN_BOXR };
+	cuuint32_t estr[2] = { 1, 1 };
+	CUresult r = enc(&h->tmap_base, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, h->base, gdim, gstride, box, estr,
+	                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+	                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+	if (r != CUDA_SUCCESS) return fail(h, EXPANN_ERR_CUDA, "cuTensorMapEncodeTiled failed: " + std::to_string((int)r));
+	return EXPANN_OK;
+}
+
+template <int QT, int METRIC, int LPL>
+static int launch_inst(expann_gpu* h, const ScanParams& p, dim3 grid, cudaStream_t st) {
+	using Cfg = ScanCfg<QT, SCAN_TR, SCAN_NWARP, SCAN_STAGES, METRIC, LPL>;
+	auto kern = scan_topk_f32_kernel<QT, SCAN_TR, SCAN_NWARP, SCAN_STAGES, METRIC, LPL>;
+	const size_t smem = Cfg::smem_bytes(p.d_pad);
+	if (smem > 227 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "scan: d too large for the shared-memory query tile");
+	EXPANN_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	kern<<<grid, Cfg::THREADS, smem, st>>>(h->tmap_base, p);
+	EXPANN_CUDA(h, cudaGetLastError());
+	return EXPANN_OK;
+}
+
+template <int QT, int METRIC> static int launch_k(expann_gpu* h, const ScanParams& p, dim3 grid, cudaStream_t st) {
+	if (p.k <= 32) return launch_inst<QT, METRIC, 1>(h, p, grid, st);
+	if (p.k <= 128) return launch_inst<QT, METRIC, 4>(h, p, grid, st);
+	return fail(h, EXPANN_ERR_UNSUPPORTED, "scan: k > 128 not supported");
+}
+template <int QT> static int launch_m(expann_gpu* h, const ScanParams& p, dim3 grid, cudaStream_t st) {
+	return h->cfg.metric == EXPANN_METRIC_IP ? launch_k<QT, METRIC_IP>(h, p, grid, st)
+	                                          : launch_k<QT, METRIC_L2>(h, p, grid, st);
+}
+
+int launch_scan_f32(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st) {
+	int qt = h->cfg.qtile;
+	if (qt == 0) qt = m >= 8 ? 8 : (m >= 3 ? 4 : 1);
+	if (qt != 1 && qt != 4 && qt != 8) return fail(h, EXPANN_ERR_ARG, "qtile must be 0, 1, 4 or 8");
+	if (qt == 8 && (size_t)qt * h->d_pad * 4 > 64 * 1024) qt = 4; // keep the query tile + 3 stages within 227 KB
+	const uint32_t qtiles = (uint32_t)((m + qt - 1) / qt);
+	const uint32_t groups = (uint32_t)((h->n + SCAN_ROWS - 1) / SCAN_ROWS);
+	int dev_sms = 148;
+	cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, h->device);
+	// enough CTAs for ~16 waves when the work allows it, but never fewer than 8 row groups per split
+	uint32_t want = (uint32_t)((16u * dev_sms + qtiles - 1) / qtiles);
+	uint32_t max_split = std::max(1u, groups / 8u);
+	uint32_t nsplit = std::max(1u, std::min(want, max_split));
+	uint32_t gps = (groups + nsplit - 1) / nsplit;
+	nsplit = (groups + gps - 1) / gps;
+
+	ScanParams p{};
+	p.queries = d_q;
+	p.m = (uint32_t)m;
+	p.k = (uint32_t)k;
+	p.d_pad = (uint32_t)h->d_pad;
+	p.n = (uint32_t)h->n;
+	p.rows_per_split = gps * SCAN_ROWS;
+	p.nsplit = nsplit;
+	uint64_t* scan_out = d_keys_out;
+	const bool need_merge = nsplit > 1 || (uint32_t)h->cfg.id_offset != 0;
+	if (need_merge) {
+		EXPANN_CUDA(h, h->partial.ensure((size_t)m * nsplit * k * 8));
+		scan_out = h->partial.as<uint64_t>();
+	}
+	p.partial = scan_out;
+	dim3 grid(qtiles, nsplit);
+	cudaEvent_t t0 = timing_begin(h, st);
+	int rc = qt == 8 ? launch_m<8>(h, p, grid, st) : qt == 4 ? launch_m<4>(h, p, grid, st) : launch_m<1>(h, p, grid, st);
+	timing_end(h, t0, st);
+	if (rc) return rc;
+	h->stats.scan_launches++;
+	h->stats.last_nsplit = nsplit;
+	h->stats.last_qtile = qt;
+	if (need_merge)
+		return launch_merge(h, scan_out, m, nsplit, k, (size_t)nsplit * k, k, k, (uint32_t)h->cfg.id_offset, d_keys_out, st);
+	return EXPANN_OK;
+}
+
+} // namespace expann

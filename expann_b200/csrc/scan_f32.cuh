@@ -1,0 +1,258 @@
+// K1/K2 — exhaustive fp32 scan with fused top-k (sm_100a).
+//
+// Replaces the hot loop of brute_force_engine<T>::_query_k (reference src/brute_force_engine.h:29-46):
+//     for i in 0..n-1: d = dist2(v, all_entries[i]); keep the k smallest (d, i)
+// with dist2 = sum (a_i-b_i)^2 (src/vec.h:139-142; AVX form src/distance.h:86-148: sub_ps then fmadd_ps per
+// element — the same two roundings per element are used here) and, for the inner-product metric, key = -dot
+// (src/vec.h:109-111, src/distance.h:181-190; no reference engine ranks by it — "parity unpinned").
+//
+// Mapping to the machine
+//   * base rows are streamed HBM -> shared memory by TMA (cp.async.bulk.tensor.2d, 128B-swizzled boxes of
+//     [BOXR rows][32 floats]) through a STAGES-deep mbarrier ring filled by one producer thread; the NWARP
+//     consumer warps never issue a global load for the base set.
+//   * one CTA holds QT queries in shared memory (broadcast LDS.128) and scans one contiguous row range
+//     ("split"); grid = (query tiles, splits) with the query tile as the fast index so that CTAs resident at
+//     the same time walk the same rows (the base is then read from HBM ~once per resident wave, the rest
+//     are L2 hits).
+//   * lane l of consumer warp w owns TR rows of every 32*TR*NWARP-row group and keeps QT*TR running sums in
+//     registers; the swizzle makes the lane-per-row LDS.128 bank-conflict free. Packed FADD2/FFMA2
+//     (sub.f32x2 / fma.rn.f32x2) halve the issue slots per element.
+//   * top-k: each warp keeps, per query, a sorted WarpList in registers and a float threshold; a distance
+//     enters the (rare) insertion path only if d <= threshold. Warps are merged through shared memory at the
+//     end of the CTA and the split results by merge_topk (K7).
+#pragma once
+#include <cuda.h>
+#include "common.cuh"
+
+namespace expann {
+
+enum { METRIC_L2 = 0, METRIC_IP = 1 };
+
+struct ScanParams {
+	const float* queries; // [m][d_pad] device, zero padded
+	uint64_t* partial;    // [m][nsplit][k] keys (local row ids)
+	uint32_t m, k, d_pad;
+	uint32_t n;              // rows in this shard
+	uint32_t rows_per_split; // multiple of the stage row count
+	uint32_t nsplit;
+};
+
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+	return ((uint64_t)__float_as_uint(hi) << 32) | __float_as_uint(lo);
+}
+__device__ __forceinline__ uint64_t sub2(uint64_t a, uint64_t b) {
+	uint64_t r;
+	asm("sub.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+	return r;
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+	uint64_t r;
+	asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+	return r;
+}
+__device__ __forceinline__ ulonglong2 lds128(uint32_t addr) {
+	ulonglong2 v;
+	asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(addr));
+	return v;
+}
+__device__ __forceinline__ float sum2(uint64_t a) {
+	return __uint_as_float((uint32_t)a) + __uint_as_float((uint32_t)(a >> 32));
+}
+
+template <int QT, int TR, int NWARP, int STAGES, int METRIC, int LPL>
+struct ScanCfg {
+	static constexpr int ROWS = 32 * TR * NWARP;          // rows per stage
+	static constexpr int BOXR = ROWS > 256 ? 256 : ROWS;  // TMA box rows (<= 256)
+	static constexpr int NBOX = ROWS / BOXR;
+	static constexpr int STAGE_BYTES = ROWS * 128;
+	static constexpr int THREADS = 32 * (NWARP + 1);
+	static constexpr int KMAX = 32 * LPL;
+	// dynamic smem: [align 1024] stages | queries (QT*d_pad*4) | barriers
+	static size_t smem_bytes(uint32_t d_pad) {
+		size_t merge = (size_t)NWARP * QT * KMAX * 8; // reuses the stage area
+		size_t st = (size_t)STAGES * STAGE_BYTES;
+		if (merge > st) st = merge;
+		return 1024 + st + (size_t)QT * d_pad * 4 + 2 * STAGES * 8 + 64;
+	}
+};
+
+template <int QT, int TR, int NWARP, int STAGES, int METRIC, int LPL>
+__global__ void __launch_bounds__(32 * (NWARP + 1), 1)
+scan_topk_f32_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
+	using Cfg = ScanCfg<QT, TR, NWARP, STAGES, METRIC, LPL>;
+	extern __shared__ uint8_t smem_raw[];
+	uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+	size_t stage_area = (size_t)STAGES * Cfg::STAGE_BYTES;
+	{
+		size_t merge = (size_t)NWARP * QT * Cfg::KMAX * 8;
+		if (merge > stage_area) stage_area = merge;
+	}
+	float* qsm = (float*)(smem + stage_area);
+	uint64_t* full = (uint64_t*)(smem + stage_area + (size_t)QT * p.d_pad * 4);
+	uint64_t* empty = full + STAGES;
+
+	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+	const uint32_t q0 = blockIdx.x * QT;
+	const uint32_t split = blockIdx.y;
+	const uint32_t row_begin = split * p.rows_per_split;
+	uint32_t row_end = row_begin + p.rows_per_split;
+	if (row_end > p.n) row_end = p.n;
+	const uint32_t ngroups = row_begin < row_end ? (row_end - row_begin + Cfg::ROWS - 1) / Cfg::ROWS : 0;
+	const uint32_t nkc = p.d_pad / 32;
+	const uint32_t total = ngroups * nkc;
+
+	// ---- prologue: queries -> smem (zero rows for q >= m), barriers
+	for (uint32_t i = tid; i < QT * p.d_pad / 4; i += Cfg::THREADS) {
+		uint32_t q = (i * 4) / p.d_pad;
+		float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+		if (q0 + q < p.m) v = reinterpret_cast<const float4*>(p.queries + (size_t)q0 * p.d_pad)[i];
+		reinterpret_cast<float4*>(qsm)[i] = v;
+	}
+	if (tid == 0) {
+		for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NWARP); }
+		mbar_fence_init();
+	}
+	__syncthreads();
+
+	if (warp == NWARP) {
+		// ===================== TMA producer (one thread) =====================
+		if (lane == 0) {
+			tma_prefetch_desc(&tmap);
+			for (uint32_t it = 0; it < total; ++it) {
+				const uint32_t s = it % STAGES, use = it / STAGES;
+				if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
+				const uint32_t g = it / nkc, kc = it - g * nkc;
+				mbar_expect_tx(&full[s], Cfg::STAGE_BYTES);
+#pragma unroll
+				for (int h = 0; h < Cfg::NBOX; ++h)
+					tma_load_2d(smem + (size_t)s * Cfg::STAGE_BYTES + (size_t)h * Cfg::BOXR * 128, &tmap, (int)(kc * 32),
+					            (int)(row_begin + g * Cfg::ROWS + h * Cfg::BOXR), &full[s]);
+			}
+		}
+		return;
+	}
+
+	// ===================== consumers =====================
+	WarpList<LPL> list[QT];
+	float thr[QT];
+#pragma unroll
+	for (int q = 0; q < QT; ++q) { list[q].init(); thr[q] = __int_as_float(0x7f800000); }
+	// lane-per-row address inside a stage with the 128B-swizzle folded in: chunk c of the row is at
+	// rowoff ^ (c << 4) because rowoff already carries (lane & 7) << 4 in its low 7 bits.
+	const uint32_t smem_base = smem_u32(smem), q_base = smem_u32(qsm);
+	uint32_t rowoff[TR];
+#pragma unroll
+	for (int r = 0; r < TR; ++r) rowoff[r] = (uint32_t)(warp * 32 * TR + r * 32 + lane) * 128 + ((lane & 7) << 4);
+
+	uint32_t it = 0;
+	for (uint32_t g = 0; g < ngroups; ++g) {
+		uint64_t acc[QT][TR];
+#pragma unroll
+		for (int q = 0; q < QT; ++q)
+#pragma unroll
+			for (int r = 0; r < TR; ++r) acc[q][r] = 0ull;
+		for (uint32_t kc = 0; kc < nkc; ++kc, ++it) {
+			const uint32_t s = it % STAGES;
+			mbar_wait(&full[s], (it / STAGES) & 1);
+			const uint32_t sb = smem_base + s * Cfg::STAGE_BYTES;
+			const uint32_t qb = q_base + kc * 128;
+#pragma unroll
+			for (int c = 0; c < 8; ++c) {
+				ulonglong2 xv[TR];
+#pragma unroll
+				for (int r = 0; r < TR; ++r)
+					xv[r] = lds128(sb + (rowoff[r] ^ (c << 4)));
+#pragma unroll
+				for (int q = 0; q < QT; ++q) {
+					const ulonglong2 qv = lds128(qb + q * p.d_pad * 4 + c * 16);
+#pragma unroll
+					for (int r = 0; r < TR; ++r) {
+						if (METRIC == METRIC_L2) {
+							uint64_t d0 = sub2(qv.x, xv[r].x), d1 = sub2(qv.y, xv[r].y);
+							acc[q][r] = fma2(d0, d0, acc[q][r]);
+							acc[q][r] = fma2(d1, d1, acc[q][r]);
+						} else {
+							acc[q][r] = fma2(qv.x, xv[r].x, acc[q][r]);
+							acc[q][r] = fma2(qv.y, xv[r].y, acc[q][r]);
+						}
+					}
+				}
+			}
+			__syncwarp();
+			if (lane == 0) mbar_arrive(&empty[s]);
+		}
+		// ---- distances of this row group are complete: filter against the per-query thresholds
+		const uint32_t grow = row_begin + g * Cfg::ROWS + warp * 32 * TR + lane;
+		float dist[QT][TR];
+		bool any = false;
+#pragma unroll
+		for (int q = 0; q < QT; ++q)
+#pragma unroll
+			for (int r = 0; r < TR; ++r) {
+				float d = sum2(acc[q][r]);
+				if (METRIC == METRIC_IP) d = -d;
+				dist[q][r] = d;
+				any |= (d <= thr[q]) && (grow + r * 32 < row_end);
+			}
+		if (__any_sync(FULL, any)) {
+#pragma unroll
+			for (int q = 0; q < QT; ++q) {
+#pragma unroll
+				for (int r = 0; r < TR; ++r) {
+					unsigned mask = __ballot_sync(FULL, (dist[q][r] <= thr[q]) && (grow + r * 32 < row_end));
+					if (mask) {
+						uint64_t tk = list[q].at(p.k - 1);
+						while (mask) {
+							int src = __ffs(mask) - 1;
+							mask &= mask - 1;
+							float dv = __shfl_sync(FULL, dist[q][r], src);
+							uint64_t key = make_key(dv, grow - lane + src + r * 32);
+							if (key < tk) {
+								list[q].insert(key, lane);
+								tk = list[q].at(p.k - 1);
+							}
+						}
+						thr[q] = tk == KEY_EMPTY ? __int_as_float(0x7f800000) : key_dist(tk);
+					}
+				}
+			}
+		}
+	}
+
+	// ---- merge the NWARP warp lists of every query through shared memory (stage area is free now)
+	asm volatile("bar.sync 1, %0;" ::"n"(32 * NWARP) : "memory");
+	uint64_t* msm = (uint64_t*)smem; // [NWARP][QT][KMAX]
+#pragma unroll
+	for (int q = 0; q < QT; ++q)
+#pragma unroll
+		for (int s = 0; s < LPL; ++s) msm[((size_t)warp * QT + q) * Cfg::KMAX + s * 32 + lane] = list[q].e[s];
+	asm volatile("bar.sync 1, %0;" ::"n"(32 * NWARP) : "memory");
+	for (int q = warp; q < QT; q += NWARP) {
+		if (q0 + q >= p.m) continue;
+		WarpList<LPL> out;
+		out.init();
+		uint64_t tk = KEY_EMPTY;
+		for (int w = 0; w < NWARP; ++w) {
+#pragma unroll
+			for (int s = 0; s < LPL; ++s) {
+				uint64_t key = msm[((size_t)w * QT + q) * Cfg::KMAX + s * 32 + lane];
+				unsigned mask = __ballot_sync(FULL, key < tk);
+				while (mask) {
+					int src = __ffs(mask) - 1;
+					mask &= mask - 1;
+					uint64_t kk = shfl_u64(key, src);
+					if (kk < tk) {
+						out.insert(kk, lane);
+						tk = out.at(p.k - 1);
+					}
+				}
+			}
+		}
+		uint64_t* dst = p.partial + ((size_t)(q0 + q) * p.nsplit + split) * p.k;
+#pragma unroll
+		for (int s = 0; s < LPL; ++s)
+			if (s * 32 + lane < (int)p.k) dst[s * 32 + lane] = out.e[s];
+	}
+}
+
+} // namespace expann

@@ -1,0 +1,155 @@
+"""Python host mirror of the reference engine interface over the C ABI.
+
+Reference interface mirrored (same names, argument meaning, result order):
+  ann_engine<T,Derived>::name/param_list/store_vector/build/query_k      src/ann_engine.h:16-29
+  brute_force_engine<T>                                                  src/brute_force_engine.h:10-46
+  pybind AntitopoEngine.store_many_vectors/query_k_numpy/set_ef_search   src/pyrunner.cpp:55-91
+plus the batched entry (`query_k_batch`) the GPU needs; `query_k` is the m == 1 case of the same call.
+All compute happens in libexpann_gpu.so on the GPU; there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import ExpannError, METRIC_IP, METRIC_L2
+
+
+def _f32c(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+class GpuEngine:
+    """Owns one expann_gpu_t handle (one engine instance on one GPU)."""
+
+    _engine_kind = _lib.ENGINE_BRUTE_FORCE
+    _name = "GPU Engine"
+
+    def __init__(self, metric: int = METRIC_L2, device: int = -1, qtile: int = 0, id_offset: int = 0, **kw):
+        self._lib = _lib.load()
+        cfg = _lib.Cfg()
+        cfg.engine = self._engine_kind
+        cfg.metric = metric
+        cfg.device = device
+        cfg.qtile = qtile
+        cfg.id_offset = id_offset
+        cfg.M = kw.get("M", 0)
+        cfg.M0 = kw.get("M0", 0)
+        cfg.ef_search_mult = kw.get("ef_search_mult", 1)
+        cfg.use_compression = int(kw.get("use_compression", False))
+        h = C.c_void_p()
+        rc = self._lib.expann_gpu_create(C.byref(cfg), C.byref(h))
+        if rc != 0:
+            raise ExpannError(rc, self._lib.expann_gpu_last_error(None).decode())
+        self._h = h
+        self.metric = metric
+        self.qtile = qtile
+        self.id_offset = id_offset
+        self.ef_search = 0
+        self.d = None
+
+    # -- helpers
+    def _check(self, rc):
+        if rc != 0:
+            raise ExpannError(rc, self._lib.expann_gpu_last_error(self._h).decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.expann_gpu_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- ann_engine interface (src/ann_engine.h:16-29)
+    def name(self) -> str:
+        return self._name
+
+    def param_list(self) -> dict:
+        st = self.stats()
+        return {"metric": "ip" if self.metric == METRIC_IP else "l2", "qtile": str(st["last_qtile"] or self.qtile),
+                "batched": "1", "device": "B200"}
+
+    def store_vector(self, v) -> None:
+        v = _f32c(v).reshape(1, -1)
+        self.store_many_vectors(v)
+
+    def store_many_vectors(self, rows, take_norms: bool = False) -> None:
+        """src/pyrunner.cpp:70-81 (take_norms: L2-normalise on ingest, :78-79)"""
+        rows = _f32c(rows)
+        if rows.ndim != 2:
+            raise ValueError("rows must be [n][d]")
+        if take_norms:
+            rows = rows / np.linalg.norm(rows, axis=1, keepdims=True).astype(np.float32)
+            rows = _f32c(rows)
+        self.d = rows.shape[1]
+        self._check(self._lib.expann_gpu_add(self._h, rows.ctypes.data, rows.shape[0], rows.shape[1]))
+
+    def store_device_rows(self, ptr: int, n: int, d: int, stream: int = 0) -> None:
+        """rows already resident in HBM (e.g. a torch tensor's data_ptr())"""
+        self.d = d
+        self._check(self._lib.expann_gpu_add_device(self._h, ptr, n, d, stream))
+
+    def build(self) -> None:
+        self._check(self._lib.expann_gpu_build(self._h))
+
+    def set_ef_search(self, ef: int) -> None:
+        """src/antitopo_engine.h:189-195"""
+        self.ef_search = int(ef)
+
+    def query_k(self, v, k: int):
+        """one query -> list of ids, nearest first (src/ann_engine.h:26-28)"""
+        ids, _, counts = self.query_k_batch(_f32c(v).reshape(1, -1), k)
+        return [int(x) for x in ids[0, :int(counts[0])]]
+
+    query_k_numpy = query_k  # src/pyrunner.cpp:85-90
+
+    def query_k_batch(self, q, k: int, ef: int | None = None):
+        """m queries -> (ids [m][k] uint64 padded with UINT64_MAX, keys [m][k] float32 padded with +inf, counts [m])"""
+        q = _f32c(q)
+        if q.ndim != 2:
+            raise ValueError("q must be [m][d]")
+        m = q.shape[0]
+        ids = np.empty((m, k), np.uint64)
+        dists = np.empty((m, k), np.float32)
+        counts = np.empty(m, np.uint64)
+        if self.d is not None and q.shape[1] != self.d:
+            raise ValueError("query dimension mismatch")
+        self._check(self._lib.expann_gpu_query(self._h, q.ctypes.data, m, k, self.ef_search if ef is None else ef,
+                                               ids.ctypes.data, dists.ctypes.data, counts.ctypes.data))
+        return ids, dists, counts
+
+    # -- HBM-resident entry points (device pointers as ints, CUDA stream handle as int)
+    def query_device(self, q_ptr: int, m: int, k: int, keys_out_ptr: int, stream: int = 0, ef: int | None = None):
+        self._check(self._lib.expann_gpu_query_device(self._h, q_ptr, m, k, self.ef_search if ef is None else ef,
+                                                      keys_out_ptr, stream))
+
+    def merge_device(self, keys_in_ptr: int, m: int, nlists: int, klist: int, stride_q: int, stride_s: int, k: int,
+                     keys_out_ptr: int, stream: int = 0):
+        self._check(self._lib.expann_gpu_merge_device(self._h, keys_in_ptr, m, nlists, klist, stride_q, stride_s, k,
+                                                      keys_out_ptr, stream))
+
+    def decode_device(self, keys_ptr: int, m: int, k: int, ids_ptr: int, dist_ptr: int = 0, counts_ptr: int = 0,
+                      stream: int = 0):
+        self._check(self._lib.expann_gpu_decode_device(self._h, keys_ptr, m, k, ids_ptr, dist_ptr or None,
+                                                       counts_ptr or None, stream))
+
+    def set_timing(self, on: bool) -> None:
+        self._check(self._lib.expann_gpu_set_timing(self._h, int(on)))
+
+    def stats(self) -> dict:
+        st = _lib.Stats()
+        self._check(self._lib.expann_gpu_stats(self._h, C.byref(st)))
+        return {f: getattr(st, f) for f, _ in st._fields_ if f != "reserved"}
+
+
+class BruteForceEngine(GpuEngine):
+    """brute_force_engine<float> (src/brute_force_engine.h:10-46) on the GPU: exact k-NN by exhaustive scan,
+    results ordered by (distance asc, id asc)."""
+    _engine_kind = _lib.ENGINE_BRUTE_FORCE
+    _name = "Brute-Force Engine (B200)"

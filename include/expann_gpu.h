@@ -1,0 +1,97 @@
+/* libexpann_gpu.so — C ABI of the B200-native expANN query path.
+ *
+ * This is the drop-in boundary: every entry point replaces one member of the reference's
+ * compile-time engine interface  template<class T, class Derived> struct ann_engine  (reference
+ * src/ann_engine.h:16-29) or of the engines behind it. No C++ or torch types cross it: opaque handle, plain
+ * pointers, sizes, negative status codes. Host-pointer entry points are what a reference-side engine shim
+ * binds; the *_device entry points take HBM-resident buffers and a CUDA stream for
+ * callers that already own device memory (bench.py / the multi-GPU merge).
+ *
+ * One handle = one engine instance on one GPU = one host thread at a time (the reference engines are not
+ * re-entrant either: src/antitopo_engine.h:208-209). Distinct handles are independent.
+ */
+#ifndef EXPANN_GPU_H
+#define EXPANN_GPU_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct expann_gpu expann_gpu_t;
+
+enum { EXPANN_OK = 0, EXPANN_ERR_ARG = -1, EXPANN_ERR_CUDA = -2, EXPANN_ERR_STATE = -3, EXPANN_ERR_UNSUPPORTED = -4,
+       EXPANN_ERR_IO = -5 };
+enum { EXPANN_ENGINE_BRUTE_FORCE = 0, /* brute_force_engine<float>, src/brute_force_engine.h:10-46 */
+       EXPANN_ENGINE_GRAPH = 1,       /* antitopo_engine<float> query half, src/antitopo_engine.h:495-928 */
+       EXPANN_ENGINE_QUANT_SCAN = 2   /* quantizer.h compressed scan + fp32 rerank, src/quantizer.h:20-150 */ };
+enum { EXPANN_METRIC_L2 = 0, /* dist2, src/vec.h:139-142 */
+       EXPANN_METRIC_IP = 1  /* key = -dot, src/vec.h:109-111 (no reference engine ranks by it) */ };
+
+typedef struct expann_gpu_cfg {
+	int32_t engine;          /* EXPANN_ENGINE_* */
+	int32_t metric;          /* EXPANN_METRIC_* */
+	int32_t device;          /* CUDA ordinal; -1 = current device */
+	int32_t qtile;           /* queries per CTA in the scan: 0 = auto, else 1, 4 or 8 */
+	uint64_t id_offset;      /* global id of local row 0 (base-set sharding) */
+	/* graph engine (antitopo_engine_config, src/antitopo_engine.h:66-101) */
+	uint64_t M, M0, ef_search_mult;
+	int32_t use_compression; /* src/antitopo_engine.h:197-199: quantizer_simple<uint8_t> codes */
+	int32_t reserved[7];
+} expann_gpu_cfg;
+
+typedef struct expann_gpu_stats {
+	uint64_t n, d, d_pad;
+	uint64_t scan_launches, merge_launches, graph_launches, aux_launches; /* kernels launched so far */
+	uint64_t last_nsplit, last_qtile;
+	uint64_t distcomps; /* RECORD_STATS num_distcomps analogue (src/antitopo_engine.h:125-129), graph engine */
+	uint64_t hot_time_ns, hot_timed_launches; /* CUDA-event time of the dominant kernel, see expann_gpu_set_timing */
+	uint64_t reserved[6];
+} expann_gpu_stats_t;
+
+/* ann_engine() / Engine(config) constructor — src/ann_engine.h:17, src/bench_runner.h:33 */
+int expann_gpu_create(const expann_gpu_cfg* cfg, expann_gpu_t** out);
+void expann_gpu_destroy(expann_gpu_t* h);
+/* last error text of this handle (or of the failed create when h == NULL); never NULL */
+const char* expann_gpu_last_error(const expann_gpu_t* h);
+
+/* store_vector(const vec<T>&) × n — src/ann_engine.h:22-24, src/brute_force_engine.h:19-22. Rows are COPIED
+ * (the reference's engines copy too); `rows` is host memory, row-major [n][d]. d is fixed by the first call. */
+int expann_gpu_add(expann_gpu_t* h, const float* rows, size_t n, size_t d);
+/* same, rows already in HBM on the handle's device */
+int expann_gpu_add_device(expann_gpu_t* h, const float* d_rows, size_t n, size_t d, void* stream);
+/* build() — src/ann_engine.h:25, src/brute_force_engine.h:24-26 (the reference asserts n > 0; here n == 0
+ * returns EXPANN_ERR_STATE) */
+int expann_gpu_build(expann_gpu_t* h);
+
+/* query_k(const vec<T>&, size_t k) × m — src/ann_engine.h:26-28, src/brute_force_engine.h:29-46.
+ * q: host [m][d]. Outputs (host, caller-owned): ids_out [m][k] nearest first under (key asc, id asc), unused
+ * slots UINT64_MAX; dist_out [m][k] (may be NULL) the fp32 ranking key (dist2, or -dot), unused slots +inf;
+ * counts_out [m] (may be NULL) = min(k, n). ef: beam width for the graph engine (0 = k*ef_search_mult,
+ * src/antitopo_engine.h:858-859), ignored by scans. Includes H2D of q and D2H of the results. */
+int expann_gpu_query(expann_gpu_t* h, const float* q, size_t m, size_t k, size_t ef, uint64_t* ids_out,
+                     float* dist_out, uint64_t* counts_out);
+/* HBM-resident form: d_q device [m][d] (row stride d), d_keys_out device [m][k] 64-bit keys
+ * (orderable(dist) << 32 | local id + id_offset), asynchronous on `stream`. */
+int expann_gpu_query_device(expann_gpu_t* h, const float* d_q, size_t m, size_t k, size_t ef,
+                            uint64_t* d_keys_out, void* stream);
+/* K7: merge nlists key lists per query (list s of query q at d_keys_in + q*stride_q + s*stride_s, klist keys
+ * each) into the k smallest -> d_keys_out [m][k]. Used for the per-GPU lists gathered over NCCL. */
+int expann_gpu_merge_device(expann_gpu_t* h, const uint64_t* d_keys_in, size_t m, size_t nlists, size_t klist,
+                            size_t stride_q, size_t stride_s, size_t k, uint64_t* d_keys_out, void* stream);
+/* keys -> reference output form, all device pointers; d_dist / d_counts may be NULL */
+int expann_gpu_decode_device(expann_gpu_t* h, const uint64_t* d_keys, size_t m, size_t k, uint64_t* d_ids,
+                             float* d_dist, uint64_t* d_counts, void* stream);
+
+/* on != 0: bracket every launch of the engine's dominant kernel (scan / graph search) with CUDA events on the
+ * launching stream; expann_gpu_stats() then synchronises those events and reports the accumulated device time
+ * (total_query_time analogue of RECORD_STATS, src/antitopo_engine.h:125-129,920-926). */
+int expann_gpu_set_timing(expann_gpu_t* h, int on);
+int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
+/* library build info: "sm_100a;..." */
+const char* expann_gpu_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
