@@ -42,6 +42,7 @@ SYMBOLS = {
     "expann_gpu_decode_device": (C.c_int, [_vp, _vp, _sz, _sz, _vp, _vp, _vp, _vp]),
     "expann_gpu_set_timing": (C.c_int, [_vp, C.c_int]),
     "expann_gpu_stats": (C.c_int, [_vp, C.POINTER(Stats)]),
+    "expann_gpu_set_option": (C.c_int, [_vp, C.c_char_p, C.c_int64]),
     "expann_gpu_version": (C.c_char_p, []),
 }
 

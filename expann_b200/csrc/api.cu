@@ -288,6 +288,20 @@ int expann_gpu_set_timing(expann_gpu_t* h, int on) {
 	return EXPANN_OK;
 }
 
+int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
+	if (!h || !name) return EXPANN_ERR_ARG;
+	const std::string nm(name);
+	if (nm == "qtile") {
+		if (value != 0 && value != 1 && value != 4 && value != 8) return fail(h, EXPANN_ERR_ARG, "qtile must be 0, 1, 4 or 8");
+		h->cfg.qtile = (int32_t)value;
+	} else if (nm == "nsplit") {
+		if (value < 0) return fail(h, EXPANN_ERR_ARG, "nsplit must be >= 0");
+		h->opt_nsplit = (int)value;
+	} else
+		return fail(h, EXPANN_ERR_ARG, "unknown option: " + nm);
+	return EXPANN_OK;
+}
+
 int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out) {
 	if (!h || !out) return EXPANN_ERR_ARG;
 	DeviceGuard g(h->device);

@@ -46,6 +46,7 @@ struct expann_gpu {
 	expann::DevBuf qpad, partial, keys, ids, dists, counts; // device work buffers (grow-only)
 	expann::DevBuf h_q, h_ids, h_dists, h_counts;            // pinned host staging for the host-pointer API
 	expann_gpu_stats_t stats{};
+	int opt_nsplit = 0; // 0 = auto
 	bool timing = false;
 	std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timed; // pending (start, stop) pairs of the dominant kernel
 	std::vector<cudaEvent_t> event_pool;

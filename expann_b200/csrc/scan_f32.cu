@@ -78,6 +78,7 @@ int launch_scan_f32(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 	uint32_t want = (uint32_t)((16u * dev_sms + qtiles - 1) / qtiles);
 	uint32_t max_split = std::max(1u, groups / 8u);
 	uint32_t nsplit = std::max(1u, std::min(want, max_split));
+	if (h->opt_nsplit > 0) nsplit = std::min((uint32_t)h->opt_nsplit, groups);
 	uint32_t gps = (groups + nsplit - 1) / nsplit;
 	nsplit = (groups + gps - 1) / gps;
 

@@ -87,8 +87,8 @@ class GpuEngine:
         if take_norms:
             rows = rows / np.linalg.norm(rows, axis=1, keepdims=True).astype(np.float32)
             rows = _f32c(rows)
-        self.d = rows.shape[1]
         self._check(self._lib.expann_gpu_add(self._h, rows.ctypes.data, rows.shape[0], rows.shape[1]))
+        self.d = rows.shape[1]
 
     def store_device_rows(self, ptr: int, n: int, d: int, stream: int = 0) -> None:
         """rows already resident in HBM (e.g. a torch tensor's data_ptr())"""
@@ -141,6 +141,9 @@ class GpuEngine:
 
     def set_timing(self, on: bool) -> None:
         self._check(self._lib.expann_gpu_set_timing(self._h, int(on)))
+
+    def set_option(self, name: str, value: int) -> None:
+        self._check(self._lib.expann_gpu_set_option(self._h, name.encode(), int(value)))
 
     def stats(self) -> dict:
         st = _lib.Stats()

@@ -88,6 +88,9 @@ int expann_gpu_decode_device(expann_gpu_t* h, const uint64_t* d_keys, size_t m, 
  * (total_query_time analogue of RECORD_STATS, src/antitopo_engine.h:125-129,920-926). */
 int expann_gpu_set_timing(expann_gpu_t* h, int on);
 int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
+/* tuning knobs by name (the reference exposes its knobs as Engine::config members, src/bench_runner.h:133-172):
+ * "qtile" (0 auto | 1 | 4 | 8), "nsplit" (0 auto | forced row splits per scan). Unknown names: EXPANN_ERR_ARG. */
+int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value);
 /* library build info: "sm_100a;..." */
 const char* expann_gpu_version(void);
 
