@@ -118,7 +118,6 @@ static int padded_queries(expann_gpu* h, const float* d_q, size_t m, cudaStream_
 
 static int query_device_impl(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out,
                              cudaStream_t st) {
-	(void)ef;
 	if (!h->built) return fail(h, EXPANN_ERR_STATE, "query before build()");
 	if (k == 0) return fail(h, EXPANN_ERR_ARG, "k must be > 0");
 	if (m == 0) return EXPANN_OK;
@@ -127,6 +126,8 @@ static int query_device_impl(expann_gpu* h, const float* d_q, size_t m, size_t k
 	switch (h->cfg.engine) {
 	case EXPANN_ENGINE_BRUTE_FORCE:
 		return launch_scan_f32(h, qp, m, k, d_keys_out, st);
+	case EXPANN_ENGINE_GRAPH:
+		return launch_graph_search(h, qp, m, k, ef, d_keys_out, st);
 	default:
 		return fail(h, EXPANN_ERR_UNSUPPORTED, "engine kind not implemented");
 	}
@@ -143,7 +144,8 @@ const char* expann_gpu_version(void) { return "expann_b200 0.1; sm_100a; kernels
 int expann_gpu_create(const expann_gpu_cfg* cfg, expann_gpu_t** out) {
 	if (!cfg || !out) return fail(nullptr, EXPANN_ERR_ARG, "null argument");
 	*out = nullptr;
-	if (cfg->engine != EXPANN_ENGINE_BRUTE_FORCE) return fail(nullptr, EXPANN_ERR_UNSUPPORTED, "engine kind not implemented");
+	if (cfg->engine != EXPANN_ENGINE_BRUTE_FORCE && cfg->engine != EXPANN_ENGINE_GRAPH)
+		return fail(nullptr, EXPANN_ERR_UNSUPPORTED, "engine kind not implemented");
 	if (cfg->metric != EXPANN_METRIC_L2 && cfg->metric != EXPANN_METRIC_IP) return fail(nullptr, EXPANN_ERR_ARG, "bad metric");
 	int ndev = 0;
 	cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -175,6 +177,8 @@ void expann_gpu_destroy(expann_gpu_t* h) {
 	timing_collect(h);
 	for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
 	if (h->base) cudaFree(h->base);
+	for (DevBuf* b : { &h->g_bottom, &h->g_upper, &h->g_upper_idx, &h->g_upper_nl, &h->g_visited, &h->g_epoch, &h->g_codes })
+		b->release();
 	for (DevBuf* b : { &h->qpad, &h->partial, &h->keys, &h->ids, &h->dists, &h->counts, &h->h_q, &h->h_ids, &h->h_dists,
 	                   &h->h_counts })
 		b->release();
@@ -218,6 +222,8 @@ int expann_gpu_build(expann_gpu_t* h) {
 	if (h->n == 0) return fail(h, EXPANN_ERR_STATE, "build() on an empty engine (the reference asserts n > 0)");
 	if (h->n + h->cfg.id_offset > 0xFFFFFFFEull) return fail(h, EXPANN_ERR_UNSUPPORTED, "ids must fit 32 bits on device");
 	if (int rc = make_base_tensor_map(h)) return rc;
+	if (h->cfg.engine == EXPANN_ENGINE_GRAPH)
+		if (int rc = graph_finalize(h)) return rc;
 	h->stats.n = h->n;
 	h->stats.d = h->d;
 	h->stats.d_pad = h->d_pad;
@@ -280,6 +286,29 @@ int expann_gpu_decode_device(expann_gpu_t* h, const uint64_t* d_keys, size_t m, 
 	return launch_decode(h, d_keys, m, k, 0, d_ids, d_dist, d_counts, (cudaStream_t)stream);
 }
 
+int expann_gpu_load_index(expann_gpu_t* h, const char* path) {
+	if (!h || !path) return fail(h, EXPANN_ERR_ARG, "null argument");
+	if (h->cfg.engine != EXPANN_ENGINE_GRAPH) return fail(h, EXPANN_ERR_STATE, "load_index: not a graph engine");
+	DeviceGuard g(h->device);
+	std::vector<float> vectors;
+	size_t n = 0, d = 0;
+	if (int rc = graph_load_index(h, path, vectors, n, d)) return rc;
+	// like read_index in the reference (src/antitopo_engine.h:312-313,476-481): the file's vectors replace any stored ones
+	h->staging.clear();
+	h->staged_rows = 0;
+	h->n = 0;
+	h->d = 0;
+	if (int rc = check_dim(h, d)) return rc;
+	return upload_rows(h, vectors.data(), n, cudaMemcpyHostToDevice, h->stream);
+}
+
+int expann_gpu_set_graph(expann_gpu_t* h, size_t n, const uint32_t* nlayers, const uint64_t* offsets, const uint32_t* edges,
+                         uint64_t starting_vertex, uint64_t max_layer) {
+	if (!h || !nlayers || !offsets || !edges) return fail(h, EXPANN_ERR_ARG, "null argument");
+	if (h->cfg.engine != EXPANN_ENGINE_GRAPH) return fail(h, EXPANN_ERR_STATE, "set_graph: not a graph engine");
+	return graph_set_csr(h, n, nlayers, offsets, edges, starting_vertex, max_layer);
+}
+
 int expann_gpu_set_timing(expann_gpu_t* h, int on) {
 	if (!h) return EXPANN_ERR_ARG;
 	DeviceGuard g(h->device);
@@ -306,6 +335,7 @@ int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out) {
 	if (!h || !out) return EXPANN_ERR_ARG;
 	DeviceGuard g(h->device);
 	timing_collect(h);
+	if (h->cfg.engine == EXPANN_ENGINE_GRAPH) graph_read_distcomps(h);
 	*out = h->stats;
 	return EXPANN_OK;
 }

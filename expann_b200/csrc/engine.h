@@ -29,6 +29,14 @@ struct DevBuf {
 	template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+// host copy of the graph in the device layout (fixed-stride rows padded with 0xFFFFFFFF)
+struct HostGraph {
+	bool present = false;
+	size_t n = 0, m0s = 0, ms = 0;
+	uint32_t start = 0, max_layer = 0;
+	std::vector<uint32_t> bottom, upper, upper_idx, upper_nl;
+};
+
 } // namespace expann
 
 struct expann_gpu {
@@ -46,6 +54,11 @@ struct expann_gpu {
 	expann::DevBuf qpad, partial, keys, ids, dists, counts; // device work buffers (grow-only)
 	expann::DevBuf h_q, h_ids, h_dists, h_counts;            // pinned host staging for the host-pointer API
 	expann_gpu_stats_t stats{};
+	// graph engine
+	expann::HostGraph graph;
+	expann::DevBuf g_bottom, g_upper, g_upper_idx, g_upper_nl, g_visited, g_epoch, g_codes;
+	uint32_t g_ctas = 0;
+	size_t g_vis_stride = 0;
 	int opt_nsplit = 0; // 0 = auto
 	bool timing = false;
 	std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timed; // pending (start, stop) pairs of the dominant kernel
@@ -63,6 +76,13 @@ int cuda_fail(expann_gpu* h, cudaError_t e, const char* what);
 int launch_scan_f32(expann_gpu* h, const float* d_q_padded, size_t m, size_t k, uint64_t* d_keys_out,
                     cudaStream_t st);
 int make_base_tensor_map(expann_gpu* h);
+// graph.cu
+int graph_set_csr(expann_gpu* h, size_t n, const uint32_t* nlayers, const uint64_t* offsets, const uint32_t* edges,
+                  uint64_t start, uint64_t max_layer);
+int graph_load_index(expann_gpu* h, const char* path, std::vector<float>& vectors, size_t& n_out, size_t& d_out);
+int graph_finalize(expann_gpu* h);
+int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out, cudaStream_t st);
+int graph_read_distcomps(expann_gpu* h);
 // merge_topk.cu
 int launch_merge(expann_gpu* h, const uint64_t* in, size_t m, size_t nlists, size_t klist, size_t stride_q,
                  size_t stride_s, size_t k, uint32_t id_add, uint64_t* out, cudaStream_t st);

@@ -1,0 +1,205 @@
+// Host side of K5: graph hand-off (the reference's index file, or CSR arrays), HBM layout, launch.
+#include "engine.h"
+#include "graph_search.cuh"
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+
+namespace expann {
+
+__global__ void quantize_u8_kernel(const float* __restrict__ base, uint8_t* __restrict__ codes, size_t total) {
+	// quantizer_simple<uint8_t>::build (src/quantizer.h:132-141): code = uint8_t(x), i.e. truncation on [0,256)
+	size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	const size_t stride = (size_t)gridDim.x * blockDim.x;
+	for (; i < total; i += stride) codes[i] = (uint8_t)(uint32_t)base[i];
+}
+
+// CSR over (vertex, layer) pairs in vertex-major order -> fixed-stride device layout
+int graph_set_csr(expann_gpu* h, size_t n, const uint32_t* nlayers, const uint64_t* offsets, const uint32_t* edges,
+                  uint64_t start, uint64_t max_layer) {
+	HostGraph& g = h->graph;
+	if (n == 0 || start >= n) return fail(h, EXPANN_ERR_ARG, "graph: empty graph or bad starting vertex");
+	size_t maxb = 0, maxu = 0, urows = 0, li = 0;
+	for (size_t v = 0; v < n; ++v) {
+		if (nlayers[v] == 0) return fail(h, EXPANN_ERR_ARG, "graph: vertex without a bottom layer");
+		for (uint32_t l = 0; l < nlayers[v]; ++l, ++li) {
+			const size_t deg = (size_t)(offsets[li + 1] - offsets[li]);
+			if (l == 0) maxb = std::max(maxb, deg); else maxu = std::max(maxu, deg);
+		}
+		urows += nlayers[v] - 1;
+	}
+	if (maxb > GS_MAXNB || maxu > GS_MAXNB) return fail(h, EXPANN_ERR_UNSUPPORTED, "graph: vertex degree above 256");
+	g.n = n;
+	g.m0s = std::max<size_t>(4, (maxb + 3) / 4 * 4);
+	g.ms = std::max<size_t>(4, (maxu + 3) / 4 * 4);
+	g.start = (uint32_t)start;
+	g.max_layer = (uint32_t)max_layer;
+	g.bottom.assign(n * g.m0s, NO_VERTEX);
+	g.upper.assign(std::max<size_t>(1, urows) * g.ms, NO_VERTEX);
+	g.upper_idx.assign(n, NO_VERTEX);
+	g.upper_nl.assign(n, 1);
+	size_t urow = 0;
+	li = 0;
+	for (size_t v = 0; v < n; ++v) {
+		g.upper_nl[v] = nlayers[v];
+		if (nlayers[v] > 1) g.upper_idx[v] = (uint32_t)urow;
+		for (uint32_t l = 0; l < nlayers[v]; ++l, ++li) {
+			const uint32_t* e = edges + offsets[li];
+			const size_t deg = (size_t)(offsets[li + 1] - offsets[li]);
+			uint32_t* dst = l == 0 ? &g.bottom[v * g.m0s] : &g.upper[(urow + l - 1) * g.ms];
+			for (size_t j = 0; j < deg; ++j) {
+				if (e[j] >= n) return fail(h, EXPANN_ERR_ARG, "graph: edge to a vertex out of range");
+				dst[j] = e[j];
+			}
+		}
+		urow += nlayers[v] - 1;
+	}
+	g.present = true;
+	h->built = false;
+	return EXPANN_OK;
+}
+
+// reference index file, src/antitopo_engine.h:931-991 (writer) / :994-1074 (reader): raw little-endian dump.
+int graph_load_index(expann_gpu* h, const char* path, std::vector<float>& vectors, size_t& n_out, size_t& d_out) {
+	FILE* f = std::fopen(path, "rb");
+	if (!f) return fail(h, EXPANN_ERR_IO, std::string("cannot open index file ") + path);
+	auto rd = [&](void* p, size_t sz) { return std::fread(p, 1, sz, f) == sz; };
+	uint64_t start, M, M0, u64, max_layer, n = 0;
+	uint8_t b;
+	float fl;
+	bool ok = rd(&start, 8) && rd(&M, 8) && rd(&M0, 8) && rd(&u64, 8) /* ef_search_mult */ && rd(&b, 1);
+	if (ok && b) ok = rd(&u64, 8);                       // optional ef_search
+	ok = ok && rd(&u64, 8) && rd(&u64, 8)                // ef_construction, ortho_count
+	     && rd(&fl, 4) && rd(&fl, 4) && rd(&u64, 8)      // ortho_factor, ortho_bias, prune_overflow
+	     && rd(&b, 1) && rd(&b, 1)                       // use_compression, use_largest_direction_filtering
+	     && rd(&max_layer, 8) && rd(&n, 8);
+	size_t d = 0;
+	for (uint64_t i = 0; ok && i < n; ++i) {
+		uint64_t sz;
+		ok = rd(&sz, 8);
+		if (ok && i == 0) { d = sz; vectors.resize((size_t)n * d); }
+		ok = ok && sz == d && rd(vectors.data() + i * d, 4 * d);
+	}
+	uint64_t nv = 0;
+	ok = ok && rd(&nv, 8) && nv == n;
+	std::vector<uint32_t> nlayers(n), edges;
+	std::vector<uint64_t> offsets(1, 0);
+	std::vector<uint8_t> rec;
+	for (uint64_t v = 0; ok && v < n; ++v) {
+		uint64_t nl;
+		ok = rd(&nl, 8);
+		nlayers[v] = (uint32_t)nl;
+		for (uint64_t l = 0; ok && l < nl; ++l) {
+			uint64_t deg;
+			ok = rd(&deg, 8) && deg < (1u << 20);
+			if (!ok) break;
+			rec.resize(deg * 12); // {float len; size_t id} packed as written field by field
+			ok = rd(rec.data(), deg * 12);
+			for (uint64_t e = 0; ok && e < deg; ++e) {
+				uint64_t id;
+				std::memcpy(&id, rec.data() + e * 12 + 4, 8);
+				edges.push_back((uint32_t)id);
+			}
+			offsets.push_back(edges.size());
+		}
+	}
+	std::fclose(f);
+	if (!ok || n == 0) return fail(h, EXPANN_ERR_IO, std::string("malformed index file ") + path);
+	n_out = n;
+	d_out = d;
+	h->cfg.M = M;
+	h->cfg.M0 = M0;
+	return graph_set_csr(h, n, nlayers.data(), offsets.data(), edges.data(), start, max_layer);
+}
+
+int graph_finalize(expann_gpu* h) {
+	HostGraph& g = h->graph;
+	if (!g.present) return fail(h, EXPANN_ERR_STATE, "graph engine: no graph loaded (expann_gpu_load_index / expann_gpu_set_graph)");
+	if (g.n != h->n) return fail(h, EXPANN_ERR_STATE, "graph engine: graph and stored vectors disagree on n");
+	cudaStream_t st = h->stream;
+	EXPANN_CUDA(h, h->g_bottom.ensure(g.bottom.size() * 4));
+	EXPANN_CUDA(h, h->g_upper.ensure(g.upper.size() * 4));
+	EXPANN_CUDA(h, h->g_upper_idx.ensure(g.n * 4));
+	EXPANN_CUDA(h, h->g_upper_nl.ensure(g.n * 4));
+	EXPANN_CUDA(h, cudaMemcpyAsync(h->g_bottom.p, g.bottom.data(), g.bottom.size() * 4, cudaMemcpyHostToDevice, st));
+	EXPANN_CUDA(h, cudaMemcpyAsync(h->g_upper.p, g.upper.data(), g.upper.size() * 4, cudaMemcpyHostToDevice, st));
+	EXPANN_CUDA(h, cudaMemcpyAsync(h->g_upper_idx.p, g.upper_idx.data(), g.n * 4, cudaMemcpyHostToDevice, st));
+	EXPANN_CUDA(h, cudaMemcpyAsync(h->g_upper_nl.p, g.upper_nl.data(), g.n * 4, cudaMemcpyHostToDevice, st));
+	// resident warp slots: every SM holds GS_CTAS_PER_SM CTAs of GS_WARPS warps; one visited byte-array per slot
+	int sms = 148;
+	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+	h->g_ctas = (uint32_t)sms * 4;
+	const size_t slots = (size_t)h->g_ctas * GS_WARPS;
+	h->g_vis_stride = (g.n + 15) / 16 * 16;
+	EXPANN_CUDA(h, h->g_visited.ensure(slots * h->g_vis_stride));
+	EXPANN_CUDA(h, cudaMemsetAsync(h->g_visited.p, 0, slots * h->g_vis_stride, st));
+	EXPANN_CUDA(h, h->g_epoch.ensure(slots * 4 + 8));
+	EXPANN_CUDA(h, cudaMemsetAsync(h->g_epoch.p, 0, slots * 4 + 8, st));
+	if (h->cfg.use_compression) {
+		const size_t total = h->n * h->d_pad;
+		EXPANN_CUDA(h, h->g_codes.ensure(total));
+		quantize_u8_kernel<<<(unsigned)std::min<size_t>(65535, (total + 255) / 256), 256, 0, st>>>(h->base, h->g_codes.as<uint8_t>(), total);
+		EXPANN_CUDA(h, cudaGetLastError());
+		h->stats.aux_launches++;
+	}
+	EXPANN_CUDA(h, cudaStreamSynchronize(st));
+	return EXPANN_OK;
+}
+
+int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out, cudaStream_t st) {
+	if (ef == 0) ef = k * std::max<uint64_t>(1, h->cfg.ef_search_mult); // src/antitopo_engine.h:858-859
+	const size_t cap = std::max(k, ef);
+	if (cap > 256) return fail(h, EXPANN_ERR_UNSUPPORTED, "graph search: max(k, ef) above 256");
+	GraphParams p{};
+	p.base = h->base;
+	p.codes = h->cfg.use_compression ? h->g_codes.as<uint8_t>() : nullptr;
+	p.bottom = h->g_bottom.as<uint32_t>();
+	p.upper_idx = h->g_upper_idx.as<uint32_t>();
+	p.upper_nl = h->g_upper_nl.as<uint32_t>();
+	p.upper = h->g_upper.as<uint32_t>();
+	p.queries = d_q;
+	p.out_keys = d_keys_out;
+	p.visited = h->g_visited.as<uint8_t>();
+	p.epoch = h->g_epoch.as<uint32_t>();
+	p.distcomps = reinterpret_cast<unsigned long long*>(h->g_epoch.as<uint8_t>() + (size_t)h->g_ctas * GS_WARPS * 4);
+	p.n = (uint32_t)h->n;
+	p.vis_stride = (uint32_t)h->g_vis_stride;
+	p.d_pad = (uint32_t)h->d_pad;
+	p.m0s = (uint32_t)h->graph.m0s;
+	p.ms = (uint32_t)h->graph.ms;
+	p.m = (uint32_t)m;
+	p.k = (uint32_t)k;
+	p.ef = (uint32_t)ef;
+	p.start = h->graph.start;
+	p.max_layer = h->graph.max_layer;
+	p.id_add = (uint32_t)h->cfg.id_offset;
+	p.compressed = h->cfg.use_compression ? 1 : 0;
+	const size_t smem = ((size_t)h->d_pad * 5 + GS_MAXNB * 8) * GS_WARPS;
+	if (smem > 200 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "graph search: d too large");
+	const unsigned grid = (unsigned)std::min<size_t>(h->g_ctas, (m + GS_WARPS - 1) / GS_WARPS);
+	cudaEvent_t t0 = timing_begin(h, st);
+#define GS_LAUNCH(L)                                                                                              \
+	do {                                                                                                          \
+		EXPANN_CUDA(h, cudaFuncSetAttribute(graph_search_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+		graph_search_kernel<L><<<grid, 32 * GS_WARPS, smem, st>>>(p);                                            \
+	} while (0)
+	if (cap <= 32) GS_LAUNCH(1);
+	else if (cap <= 64) GS_LAUNCH(2);
+	else if (cap <= 128) GS_LAUNCH(4);
+	else GS_LAUNCH(8);
+#undef GS_LAUNCH
+	timing_end(h, t0, st);
+	EXPANN_CUDA(h, cudaGetLastError());
+	h->stats.graph_launches++;
+	return EXPANN_OK;
+}
+
+int graph_read_distcomps(expann_gpu* h) {
+	if (!h->g_epoch.p) return EXPANN_OK;
+	unsigned long long v = 0;
+	EXPANN_CUDA(h, cudaMemcpy(&v, h->g_epoch.as<uint8_t>() + (size_t)h->g_ctas * GS_WARPS * 4, 8, cudaMemcpyDeviceToHost));
+	h->stats.distcomps = v;
+	return EXPANN_OK;
+}
+
+} // namespace expann

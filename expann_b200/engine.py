@@ -156,3 +156,35 @@ class BruteForceEngine(GpuEngine):
     results ordered by (distance asc, id asc)."""
     _engine_kind = _lib.ENGINE_BRUTE_FORCE
     _name = "Brute-Force Engine (B200)"
+
+
+class GraphEngine(GpuEngine):
+    """Query half of antitopo_engine<float> (src/antitopo_engine.h:495-928) on the GPU: greedy descent through
+    the upper layers, beam search of width ef on the bottom layer (optionally over u8 codes with an fp32 rerank).
+    The graph comes from the reference's CPU build: `load_index(path)` reads the file written by serialize
+    (src/antitopo_engine.h:931-991); `set_graph(...)` takes the same graph as CSR arrays.
+    Constructor arguments mirror the pybind AntitopoEngine (src/pyrunner.cpp:55-62) where they matter for queries."""
+    _engine_kind = _lib.ENGINE_GRAPH
+    _name = "Anti-Topo Engine (B200 query path)"
+
+    def __init__(self, M: int = 0, M0: int = 0, ef_search_mult: int = 1, use_compression: bool = False, **kw):
+        super().__init__(M=M, M0=M0, ef_search_mult=ef_search_mult, use_compression=use_compression, **kw)
+        self.use_compression = use_compression
+        self.ef_search_mult = ef_search_mult
+
+    def load_index(self, path: str) -> None:
+        self._check(self._lib.expann_gpu_load_index(self._h, path.encode()))
+        self.d = None
+
+    def set_graph(self, nlayers, offsets, edges, starting_vertex: int, max_layer: int) -> None:
+        nl = np.ascontiguousarray(nlayers, np.uint32)
+        off = np.ascontiguousarray(offsets, np.uint64)
+        ed = np.ascontiguousarray(edges, np.uint32)
+        self._check(self._lib.expann_gpu_set_graph(self._h, nl.size, nl.ctypes.data, off.ctypes.data, ed.ctypes.data,
+                                                   int(starting_vertex), int(max_layer)))
+
+    def param_list(self) -> dict:
+        pl = super().param_list()
+        pl.update({"ef_search_mult": str(self.ef_search_mult), "use_compression": str(int(self.use_compression)),
+                   "ef_search": str(self.ef_search)})
+        return pl

@@ -60,6 +60,13 @@ const char* expann_gpu_last_error(const expann_gpu_t* h);
 int expann_gpu_add(expann_gpu_t* h, const float* rows, size_t n, size_t d);
 /* same, rows already in HBM on the handle's device */
 int expann_gpu_add_device(expann_gpu_t* h, const float* d_rows, size_t n, size_t d, void* stream);
+/* Graph hand-off (graph engine only). The reference builds its graph on the CPU (src/antitopo_engine.h:310-465)
+ * and dumps it with serialize (:931-991); load_index reads that file like deserialize (:994-1074): the file's
+ * vectors replace anything stored, exactly as read_index does (:312-313,476-481). set_graph takes the same graph
+ * as CSR arrays over (vertex, layer) pairs in vertex-major order: nlayers[n], offsets[sum(nlayers)+1], edges[]. */
+int expann_gpu_load_index(expann_gpu_t* h, const char* path);
+int expann_gpu_set_graph(expann_gpu_t* h, size_t n, const uint32_t* nlayers, const uint64_t* offsets,
+                         const uint32_t* edges, uint64_t starting_vertex, uint64_t max_layer);
 /* build() — src/ann_engine.h:25, src/brute_force_engine.h:24-26 (the reference asserts n > 0; here n == 0
  * returns EXPANN_ERR_STATE) */
 int expann_gpu_build(expann_gpu_t* h);

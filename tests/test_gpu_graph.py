@@ -1,0 +1,87 @@
+"""GPU parity: K5 graph beam search through the C ABI on reference-built graphs.
+Bar (north_star): recall@10 >= the reference's at every beam width on the SAME graph. On u8-valued data the
+arithmetic is exact, so result sets are also compared id for id and the distance-evaluation counter
+(RECORD_STATS num_distcomps, src/antitopo_engine.h:125-129) against the reference's."""
+import os
+
+import numpy as np
+import pytest
+
+from tests.util import GOLD, gold
+
+pytestmark = pytest.mark.gpu
+
+
+def recall(ids, truth):
+    return float(np.mean([len(set(a.tolist()) & set(b.tolist())) / len(b) for a, b in zip(ids, truth)]))
+
+
+@pytest.fixture(scope="module")
+def ex():
+    import expann_b200
+    return expann_b200
+
+
+@pytest.mark.parametrize("compressed", [False, True])
+def test_golden_index(ex, compressed):
+    g = gold("graph_u8_2000")
+    e = ex.GraphEngine(use_compression=compressed)
+    e.load_index(os.path.join(GOLD, "graph_u8_2000.index"))
+    e.build()
+    q = g["q"].astype(np.float32)
+    for ef in (10, 20, 40, 80):
+        e.set_ef_search(ef)
+        dc0 = e.stats()["distcomps"]
+        ids, dists, counts = e.query_k_batch(q, 10)
+        dc = e.stats()["distcomps"] - dc0
+        ref_ids = g[f"ids_comp_ef{ef}" if compressed else f"ids_ef{ef}"]
+        r_gpu, r_ref = recall(ids, g["truth"]), recall(ref_ids, g["truth"])
+        assert np.all(counts == 10)
+        assert r_gpu >= r_ref - 1e-9, (ef, r_gpu, r_ref)
+        for i in range(len(q)):
+            assert len(set(ids[i].tolist())) == 10                       # no duplicate ids (src/basic_bench.h:98-104)
+        assert np.all(np.diff(dists, axis=1) >= 0)
+        if not compressed:
+            # exact arithmetic + same algorithm: same result SETS up to distance ties at the k-th place
+            same = np.mean([set(a.tolist()) == set(b.tolist()) for a, b in zip(ids, ref_ids)])
+            assert same >= 0.9, (ef, same)
+            ref_dc = int(g[f"distcomps_ef{ef}"])
+            assert abs(dc - ref_dc) <= 0.02 * ref_dc, (ef, dc, ref_dc)
+    e.close()
+
+
+def test_live_reference_graph(ex, oracle, reference_128):
+    """build a graph with the unmodified reference on this host, hand it over as CSR arrays, compare recall"""
+    from expann_b200 import datasets
+    base, q = datasets.make("sift", 6000, 64, 128, seed=77, variant="lowrank")
+    G = reference_128.graph(M=12, M0=24, ef_construction=48)
+    G.store(base)
+    G.build()
+    path = "/tmp/expann_test_graph.index"
+    G.save(path)
+    og = oracle.graph_load(path)
+    truth, _, _ = oracle.bf_query(base, q, 10, threads=8)
+    e = ex.GraphEngine()
+    e.load_index(path)
+    e.build()
+    for ef in (10, 30, 60):
+        G.set_ef(ef)
+        rid, _ = G.query(q, 10)
+        e.set_ef_search(ef)
+        ids, dists, counts = e.query_k_batch(q, 10)
+        assert recall(ids, truth) >= recall(rid, truth) - 1e-9, ef
+        # the returned keys are the true fp32 distances of the returned ids
+        for i in (0, 17, 63):
+            ref = ((base[ids[i].astype(np.int64)] - q[i]) ** 2).sum(1, dtype=np.float64).astype(np.float32)
+            assert np.array_equal(ref, dists[i])
+    e.close()
+
+
+def test_graph_errors(ex):
+    e = ex.GraphEngine()
+    e.store_many_vectors(np.zeros((8, 32), np.float32))
+    with pytest.raises(ex.ExpannError):
+        e.build()  # no graph loaded
+    with pytest.raises(ex.ExpannError):
+        e.load_index("/nonexistent/file.index")
+    e.close()
