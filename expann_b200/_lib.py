@@ -17,7 +17,7 @@ METRIC_L2, METRIC_IP = 0, 1
 class Cfg(C.Structure):
     _fields_ = [("engine", C.c_int32), ("metric", C.c_int32), ("device", C.c_int32), ("qtile", C.c_int32),
                 ("id_offset", C.c_uint64), ("M", C.c_uint64), ("M0", C.c_uint64), ("ef_search_mult", C.c_uint64),
-                ("use_compression", C.c_int32), ("reserved", C.c_int32 * 7)]
+                ("use_compression", C.c_int32), ("quantizer", C.c_int32), ("reserved", C.c_int32 * 6)]
 
 
 class Stats(C.Structure):
@@ -42,6 +42,8 @@ SYMBOLS = {
     "expann_gpu_query_device": (C.c_int, [_vp, _vp, _sz, _sz, _sz, _vp, _vp]),
     "expann_gpu_merge_device": (C.c_int, [_vp, _vp, _sz, _sz, _sz, _sz, _sz, _sz, _vp, _vp]),
     "expann_gpu_decode_device": (C.c_int, [_vp, _vp, _sz, _sz, _vp, _vp, _vp, _vp]),
+    "expann_gpu_get_quantizer": (C.c_int, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "expann_gpu_pair_distances": (C.c_int, [C.c_int, C.c_int, _vp, _vp, _sz, _sz, _vp, _vp]),
     "expann_gpu_set_timing": (C.c_int, [_vp, C.c_int]),
     "expann_gpu_stats": (C.c_int, [_vp, C.POINTER(Stats)]),
     "expann_gpu_set_option": (C.c_int, [_vp, C.c_char_p, C.c_int64]),

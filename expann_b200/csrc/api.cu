@@ -128,6 +128,8 @@ static int query_device_impl(expann_gpu* h, const float* d_q, size_t m, size_t k
 		return launch_scan_f32(h, qp, m, k, d_keys_out, st);
 	case EXPANN_ENGINE_GRAPH:
 		return launch_graph_search(h, qp, m, k, ef, d_keys_out, st);
+	case EXPANN_ENGINE_QUANT_SCAN:
+		return launch_quant_scan(h, qp, m, k, d_keys_out, st);
 	default:
 		return fail(h, EXPANN_ERR_UNSUPPORTED, "engine kind not implemented");
 	}
@@ -144,8 +146,10 @@ const char* expann_gpu_version(void) { return "expann_b200 0.1; sm_100a; kernels
 int expann_gpu_create(const expann_gpu_cfg* cfg, expann_gpu_t** out) {
 	if (!cfg || !out) return fail(nullptr, EXPANN_ERR_ARG, "null argument");
 	*out = nullptr;
-	if (cfg->engine != EXPANN_ENGINE_BRUTE_FORCE && cfg->engine != EXPANN_ENGINE_GRAPH)
+	if (cfg->engine != EXPANN_ENGINE_BRUTE_FORCE && cfg->engine != EXPANN_ENGINE_GRAPH &&
+	    cfg->engine != EXPANN_ENGINE_QUANT_SCAN)
 		return fail(nullptr, EXPANN_ERR_UNSUPPORTED, "engine kind not implemented");
+	if (cfg->quantizer != 0 && cfg->quantizer != 1) return fail(nullptr, EXPANN_ERR_ARG, "bad quantizer");
 	if (cfg->metric != EXPANN_METRIC_L2 && cfg->metric != EXPANN_METRIC_IP) return fail(nullptr, EXPANN_ERR_ARG, "bad metric");
 	int ndev = 0;
 	cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -162,6 +166,7 @@ int expann_gpu_create(const expann_gpu_cfg* cfg, expann_gpu_t** out) {
 	expann_gpu* h = new (std::nothrow) expann_gpu();
 	if (!h) return fail(nullptr, EXPANN_ERR_ARG, "out of host memory");
 	h->cfg = *cfg;
+	h->quantizer = cfg->quantizer;
 	h->device = dev;
 	DeviceGuard g(dev);
 	e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
@@ -177,6 +182,7 @@ void expann_gpu_destroy(expann_gpu_t* h) {
 	timing_collect(h);
 	for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
 	if (h->base) cudaFree(h->base);
+	for (DevBuf* b : { &h->q_codes, &h->q_cnorm, &h->q_mm, &h->qq_codes, &h->qq_norm, &h->q_cand }) b->release();
 	for (DevBuf* b : { &h->g_bottom, &h->g_upper, &h->g_upper_idx, &h->g_upper_nl, &h->g_visited, &h->g_epoch, &h->g_codes })
 		b->release();
 	for (DevBuf* b : { &h->qpad, &h->partial, &h->keys, &h->ids, &h->dists, &h->counts, &h->h_q, &h->h_ids, &h->h_dists,
@@ -224,6 +230,8 @@ int expann_gpu_build(expann_gpu_t* h) {
 	if (int rc = make_base_tensor_map(h)) return rc;
 	if (h->cfg.engine == EXPANN_ENGINE_GRAPH)
 		if (int rc = graph_finalize(h)) return rc;
+	if (h->cfg.engine == EXPANN_ENGINE_QUANT_SCAN)
+		if (int rc = quant_finalize(h)) return rc;
 	h->stats.n = h->n;
 	h->stats.d = h->d;
 	h->stats.d_pad = h->d_pad;
@@ -309,6 +317,13 @@ int expann_gpu_set_graph(expann_gpu_t* h, size_t n, const uint32_t* nlayers, con
 	return graph_set_csr(h, n, nlayers, offsets, edges, starting_vertex, max_layer);
 }
 
+int expann_gpu_get_quantizer(const expann_gpu_t* h, float* scale, float* offset) {
+	if (!h || !scale || !offset) return EXPANN_ERR_ARG;
+	*scale = h->q_scale;
+	*offset = h->q_offset;
+	return EXPANN_OK;
+}
+
 int expann_gpu_set_timing(expann_gpu_t* h, int on) {
 	if (!h) return EXPANN_ERR_ARG;
 	DeviceGuard g(h->device);
@@ -323,6 +338,9 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 	if (nm == "qtile") {
 		if (value != 0 && value != 1 && value != 4 && value != 8) return fail(h, EXPANN_ERR_ARG, "qtile must be 0, 1, 4 or 8");
 		h->cfg.qtile = (int32_t)value;
+	} else if (nm == "kprime") {
+		if (value < 0 || value > 128) return fail(h, EXPANN_ERR_ARG, "kprime must be in 0..128");
+		h->opt_kprime = (int)value;
 	} else if (nm == "nsplit") {
 		if (value < 0) return fail(h, EXPANN_ERR_ARG, "nsplit must be >= 0");
 		h->opt_nsplit = (int)value;

@@ -54,6 +54,13 @@ struct expann_gpu {
 	expann::DevBuf qpad, partial, keys, ids, dists, counts; // device work buffers (grow-only)
 	expann::DevBuf h_q, h_ids, h_dists, h_counts;            // pinned host staging for the host-pointer API
 	expann_gpu_stats_t stats{};
+	// quantised scan engine (K6 + K4)
+	int quantizer = 0;       // 0 = quantizer_simple<uint8_t>, 1 = quantizer_ranged_q8
+	int opt_kprime = 0;      // 0 = auto
+	size_t dc_pad = 0;       // code row stride (d rounded up to 128)
+	float q_scale = 1.f, q_offset = 0.f;
+	expann::DevBuf q_codes, q_cnorm, q_mm, qq_codes, qq_norm, q_cand;
+	CUtensorMap tmap_codes{};
 	// graph engine
 	expann::HostGraph graph;
 	expann::DevBuf g_bottom, g_upper, g_upper_idx, g_upper_nl, g_visited, g_epoch, g_codes;
@@ -83,6 +90,9 @@ int graph_load_index(expann_gpu* h, const char* path, std::vector<float>& vector
 int graph_finalize(expann_gpu* h);
 int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out, cudaStream_t st);
 int graph_read_distcomps(expann_gpu* h);
+// quant.cu
+int quant_finalize(expann_gpu* h);
+int launch_quant_scan(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);
 // merge_topk.cu
 int launch_merge(expann_gpu* h, const uint64_t* in, size_t m, size_t nlists, size_t klist, size_t stride_q,
                  size_t stride_s, size_t k, uint32_t id_add, uint64_t* out, cudaStream_t st);

@@ -27,20 +27,25 @@ static encode_tiled_fn get_encode_tiled() {
 	return fn;
 }
 
-// 2D view of the base set: dim0 = d_pad floats (contiguous), dim1 = n rows; box = [32 floats][BOXR rows],
-// 128B swizzle (16-byte chunk c of row r lands at chunk c ^ (r & 7) of its 128-byte line).
-int make_base_tensor_map(expann_gpu* h) {
+// 2D tiled tensor map with 128B swizzle (16-byte chunk c of box row r lands at chunk c ^ (r & 7) of its line)
+int encode_tensor_map_2d(expann_gpu* h, CUtensorMap* out, int dtype_u8, void* base, uint64_t inner, uint64_t rows,
+                         uint64_t row_bytes, uint32_t box_inner, uint32_t box_rows) {
 	encode_tiled_fn enc = get_encode_tiled();
 	if (!enc) return fail(h, EXPANN_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
-	cuuint64_t gdim[2] = { (cuuint64_t)h->d_pad, (cuuint64_t)h->n };
-	cuuint64_t gstride[1] = { (cuuint64_t)h->d_pad * 4 };
-	cuuint32_t box[2] = { 32, (cuuint32_t)SCAN_BOXR };
+	cuuint64_t gdim[2] = { (cuuint64_t)inner, (cuuint64_t)rows };
+	cuuint64_t gstride[1] = { (cuuint64_t)row_bytes };
+	cuuint32_t box[2] = { box_inner, box_rows };
 	cuuint32_t estr[2] = { 1, 1 };
-	CUresult r = enc(&h->tmap_base, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, h->base, gdim, gstride, box, estr,
-	                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+	CUresult r = enc(out, dtype_u8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, gdim, gstride,
+	                 box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
 	                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 	if (r != CUDA_SUCCESS) return fail(h, EXPANN_ERR_CUDA, "cuTensorMapEncodeTiled failed: " + std::to_string((int)r));
 	return EXPANN_OK;
+}
+
+// base set: dim0 = d_pad floats (contiguous), dim1 = n rows; box = [32 floats][BOXR rows]
+int make_base_tensor_map(expann_gpu* h) {
+	return encode_tensor_map_2d(h, &h->tmap_base, 0, h->base, h->d_pad, h->n, h->d_pad * 4, 32, SCAN_BOXR);
 }
 
 template <int QT, int METRIC, int LPL>

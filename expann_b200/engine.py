@@ -39,6 +39,7 @@ class GpuEngine:
         cfg.M0 = kw.get("M0", 0)
         cfg.ef_search_mult = kw.get("ef_search_mult", 1)
         cfg.use_compression = int(kw.get("use_compression", False))
+        cfg.quantizer = int(kw.get("quantizer", 0))
         h = C.c_void_p()
         rc = self._lib.expann_gpu_create(C.byref(cfg), C.byref(h))
         if rc != 0:
@@ -188,3 +189,43 @@ class GraphEngine(GpuEngine):
         pl.update({"ef_search_mult": str(self.ef_search_mult), "use_compression": str(int(self.use_compression)),
                    "ef_search": str(self.ef_search)})
         return pl
+
+
+QUANT_SIMPLE_U8, QUANT_RANGED_Q8 = 0, 1
+
+
+class QuantScanEngine(GpuEngine):
+    """Exhaustive scan over 8-bit codes + fp32 rerank: quantizer_simple<uint8_t>
+    (src/quantizer.h:125-150; lossless on u8-valued data) or quantizer_ranged_q8 (src/quantizer.h:186-238, scored
+    with the sign-corrected int8 distance). The k' = `kprime` best codes are re-ranked with exact fp32 keys."""
+    _engine_kind = _lib.ENGINE_QUANT_SCAN
+    _name = "Quantized Scan Engine (B200)"
+
+    def __init__(self, quantizer: int = QUANT_SIMPLE_U8, kprime: int = 0, **kw):
+        super().__init__(quantizer=quantizer, **kw)
+        self.quantizer = quantizer
+        if kprime:
+            self.set_option("kprime", kprime)
+
+    def quantizer_params(self):
+        s, o = C.c_float(), C.c_float()
+        self._check(self._lib.expann_gpu_get_quantizer(self._h, C.byref(s), C.byref(o)))
+        return np.float32(s.value), np.float32(o.value)
+
+
+PAIR_F32_L2, PAIR_F32_DOT, PAIR_U8_COMPRESSED, PAIR_I8, PAIR_I16 = range(5)
+
+
+def pair_distances(kind: int, a, b, device: int = -1):
+    """distance primitives on explicit pairs (rows of a vs rows of b) computed on the GPU; see include/expann_gpu.h"""
+    lib = _lib.load()
+    ta = {0: np.float32, 1: np.float32, 2: np.float32, 3: np.int8, 4: np.int16}[kind]
+    tb = {0: np.float32, 1: np.float32, 2: np.uint8, 3: np.int8, 4: np.int16}[kind]
+    a, b = np.ascontiguousarray(a, ta), np.ascontiguousarray(b, tb)
+    n, d = a.shape
+    out = np.empty(n, np.float32 if kind <= 1 else np.int32)
+    rc = lib.expann_gpu_pair_distances(device, kind, a.ctypes.data, b.ctypes.data, n, d,
+                                       out.ctypes.data if kind <= 1 else None, out.ctypes.data if kind > 1 else None)
+    if rc != 0:
+        raise ExpannError(rc, "pair_distances failed")
+    return out

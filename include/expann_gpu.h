@@ -37,7 +37,9 @@ typedef struct expann_gpu_cfg {
 	/* graph engine (antitopo_engine_config, src/antitopo_engine.h:66-101) */
 	uint64_t M, M0, ef_search_mult;
 	int32_t use_compression; /* src/antitopo_engine.h:197-199: quantizer_simple<uint8_t> codes */
-	int32_t reserved[7];
+	int32_t quantizer;       /* QUANT_SCAN: 0 = quantizer_simple<uint8_t> (src/quantizer.h:125-150),
+	                            1 = quantizer_ranged_q8 (src/quantizer.h:186-238) */
+	int32_t reserved[6];
 } expann_gpu_cfg;
 
 typedef struct expann_gpu_stats {
@@ -90,13 +92,22 @@ int expann_gpu_merge_device(expann_gpu_t* h, const uint64_t* d_keys_in, size_t m
 int expann_gpu_decode_device(expann_gpu_t* h, const uint64_t* d_keys, size_t m, size_t k, uint64_t* d_ids,
                              float* d_dist, uint64_t* d_counts, void* stream);
 
+/* quantizer_ranged_q8 parameters fitted by build() (scale_factor / offset, src/quantizer.h:217-227) */
+int expann_gpu_get_quantizer(const expann_gpu_t* h, float* scale, float* offset);
+/* Distance primitives on explicit pairs, for parity tests of the reference kernels (host pointers, npairs x d):
+ * kind 0 fp32 sum (a-b)^2 (src/vec.h:139-142, src/distance.h:86-148) -> out_f; 1 fp32 dot (src/vec.h:109-111,
+ * src/distance.h:181-190) -> out_f; 2 float query vs u8 code, dist2_compressed (src/antitopo_engine.h:38-61) -> out_i;
+ * 3 int8 and 4 int16 squared distance in the mathematically correct form (src/distance.h:14-53 intend it) -> out_i. */
+int expann_gpu_pair_distances(int device, int kind, const void* a, const void* b, size_t npairs, size_t d,
+                              float* out_f, int32_t* out_i);
 /* on != 0: bracket every launch of the engine's dominant kernel (scan / graph search) with CUDA events on the
  * launching stream; expann_gpu_stats() then synchronises those events and reports the accumulated device time
  * (total_query_time analogue of RECORD_STATS, src/antitopo_engine.h:125-129,920-926). */
 int expann_gpu_set_timing(expann_gpu_t* h, int on);
 int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
 /* tuning knobs by name (the reference exposes its knobs as Engine::config members, src/bench_runner.h:133-172):
- * "qtile" (0 auto | 1 | 4 | 8), "nsplit" (0 auto | forced row splits per scan). Unknown names: EXPANN_ERR_ARG. */
+ * "qtile" (0 auto | 1 | 4 | 8), "nsplit" (0 auto | forced row splits per scan), "kprime" (QUANT_SCAN: survivors
+ * re-ranked in fp32, 0 auto = min(128, 10k)). Unknown names: EXPANN_ERR_ARG. */
 int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value);
 /* library build info: "sm_100a;..." */
 const char* expann_gpu_version(void);
