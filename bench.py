@@ -178,8 +178,8 @@ def main():
     dev = torch.device("cuda", local_rank)
 
     base, q = datasets.make(gen, n, m, d, variant=variant or "lowrank")
-    rows_per = (n + world - 1) // world
-    lo, hi = rank * rows_per, min(n, (rank + 1) * rows_per)
+    from expann_b200 import sharding
+    lo, hi = sharding.shard_range(n, world, rank)
     eng = expann_b200.BruteForceEngine(metric=1 if metric == "ip" else 0, device=local_rank, qtile=args.qtile, id_offset=lo)
     eng.store_many_vectors(base[lo:hi])
     eng.build()
@@ -188,7 +188,6 @@ def main():
     dq = torch.from_numpy(q).to(dev)
     hq = torch.from_numpy(q).pin_memory()
     local_keys = torch.empty((m, k), dtype=torch.int64, device=dev)
-    gathered = torch.empty((world, m, k), dtype=torch.int64, device=dev) if world > 1 else None
     final_keys = torch.empty((m, k), dtype=torch.int64, device=dev)
     ids_dev = torch.empty((m, k), dtype=torch.int64, device=dev)
     ids_host = torch.empty((m, k), dtype=torch.int64).pin_memory()
@@ -199,7 +198,7 @@ def main():
             eng.query_device(qptr, m, k, final_keys.data_ptr(), stream)
         else:
             eng.query_device(qptr, m, k, local_keys.data_ptr(), stream)
-            dist.all_gather_into_tensor(gathered, local_keys)
+            gathered = sharding.gather_keys(local_keys, world)   # NCCL all-gather -> [world][m][k]
             eng.merge_device(gathered.data_ptr(), m, world, k, k, m * k, k, final_keys.data_ptr(), stream)
 
     def step_e2e():
