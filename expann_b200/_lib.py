@@ -37,6 +37,8 @@ SYMBOLS = {
     "expann_gpu_add_device": (C.c_int, [_vp, _vp, _sz, _sz, _vp]),
     "expann_gpu_load_index": (C.c_int, [_vp, C.c_char_p]),
     "expann_gpu_set_graph": (C.c_int, [_vp, _sz, _vp, _vp, _vp, C.c_uint64, C.c_uint64]),
+    "expann_gpu_build_graph": (C.c_int, [_vp, C.c_uint64, C.c_uint64, C.c_uint64, C.c_float, C.c_float, C.c_uint64, C.c_uint64]),
+    "expann_gpu_save_index": (C.c_int, [_vp, C.c_char_p]),
     "expann_gpu_build": (C.c_int, [_vp]),
     "expann_gpu_query": (C.c_int, [_vp, _vp, _sz, _sz, _sz, _vp, _vp, _vp]),
     "expann_gpu_query_device": (C.c_int, [_vp, _vp, _sz, _sz, _sz, _vp, _vp]),

@@ -310,6 +310,23 @@ int expann_gpu_load_index(expann_gpu_t* h, const char* path) {
 	return upload_rows(h, vectors.data(), n, cudaMemcpyHostToDevice, h->stream);
 }
 
+int expann_gpu_build_graph(expann_gpu_t* h, uint64_t M, uint64_t M0, uint64_t K, float ortho_factor, float ortho_bias,
+                           uint64_t prune_overflow, uint64_t seed) {
+	if (!h) return EXPANN_ERR_ARG;
+	if (h->cfg.engine != EXPANN_ENGINE_GRAPH) return fail(h, EXPANN_ERR_STATE, "build_graph: not a graph engine");
+	DeviceGuard g(h->device);
+	if (int rc = flush_staging(h)) return rc;
+	return graph_build_gpu(h, M, M0, K, ortho_factor, ortho_bias, prune_overflow, seed);
+}
+
+int expann_gpu_save_index(expann_gpu_t* h, const char* path) {
+	if (!h || !path) return EXPANN_ERR_ARG;
+	if (h->cfg.engine != EXPANN_ENGINE_GRAPH) return fail(h, EXPANN_ERR_STATE, "save_index: not a graph engine");
+	DeviceGuard g(h->device);
+	if (int rc = flush_staging(h)) return rc;
+	return graph_save_index(h, path);
+}
+
 int expann_gpu_set_graph(expann_gpu_t* h, size_t n, const uint32_t* nlayers, const uint64_t* offsets, const uint32_t* edges,
                          uint64_t starting_vertex, uint64_t max_layer) {
 	if (!h || !nlayers || !offsets || !edges) return fail(h, EXPANN_ERR_ARG, "null argument");

@@ -35,6 +35,7 @@ struct HostGraph {
 	size_t n = 0, m0s = 0, ms = 0;
 	uint32_t start = 0, max_layer = 0;
 	std::vector<uint32_t> bottom, upper, upper_idx, upper_nl;
+	std::vector<float> bottom_len, upper_len; // edge lengths when known (GPU build), for the index writer
 };
 
 } // namespace expann
@@ -64,6 +65,8 @@ struct expann_gpu {
 	// graph engine
 	expann::HostGraph graph;
 	expann::DevBuf g_bottom, g_upper, g_upper_idx, g_upper_nl, g_visited, g_epoch, g_codes;
+	float build_ortho_factor = 0.5f, build_ortho_bias = 0.f;
+	uint64_t build_prune_overflow = 0, build_K = 0;
 	uint32_t g_ctas = 0;
 	size_t g_vis_stride = 0;
 	int opt_nsplit = 0; // 0 = auto
@@ -93,6 +96,10 @@ int graph_read_distcomps(expann_gpu* h);
 // quant.cu
 int quant_finalize(expann_gpu* h);
 int launch_quant_scan(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);
+// graph_build.cu
+int graph_build_gpu(expann_gpu* h, uint64_t M, uint64_t M0, uint64_t K, float ortho_factor, float ortho_bias,
+                    uint64_t prune_overflow, uint64_t seed);
+int graph_save_index(expann_gpu* h, const char* path);
 // merge_topk.cu
 int launch_merge(expann_gpu* h, const uint64_t* in, size_t m, size_t nlists, size_t klist, size_t stride_q,
                  size_t stride_s, size_t k, uint32_t id_add, uint64_t* out, cudaStream_t st);

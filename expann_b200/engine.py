@@ -177,6 +177,15 @@ class GraphEngine(GpuEngine):
         self._check(self._lib.expann_gpu_load_index(self._h, path.encode()))
         self.d = None
 
+    def build_graph(self, M: int = 16, M0: int = 32, K: int = 0, ortho_factor: float = 0.5, ortho_bias: float = 0.0,
+                    prune_overflow: int = 0, seed: int = 0) -> None:
+        """construct the graph on the GPU from the stored vectors (argument names follow antitopo_engine_config,
+        src/antitopo_engine.h:73-101; K plays the role of ef_construction: candidates per vertex)"""
+        self._check(self._lib.expann_gpu_build_graph(self._h, M, M0, K, ortho_factor, ortho_bias, prune_overflow, seed))
+
+    def save_index(self, path: str) -> None:
+        self._check(self._lib.expann_gpu_save_index(self._h, path.encode()))
+
     def set_graph(self, nlayers, offsets, edges, starting_vertex: int, max_layer: int) -> None:
         nl = np.ascontiguousarray(nlayers, np.uint32)
         off = np.ascontiguousarray(offsets, np.uint64)

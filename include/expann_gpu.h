@@ -69,6 +69,14 @@ int expann_gpu_add_device(expann_gpu_t* h, const float* d_rows, size_t n, size_t
 int expann_gpu_load_index(expann_gpu_t* h, const char* path);
 int expann_gpu_set_graph(expann_gpu_t* h, size_t n, const uint32_t* nlayers, const uint64_t* offsets,
                          const uint32_t* edges, uint64_t starting_vertex, uint64_t max_layer);
+/* GPU graph construction from the stored vectors: exact K-NN candidates (K1 scan), the
+ * reference's diversity prune (prune_edges, src/antitopo_engine.h:262-308: ortho_factor / ortho_bias /
+ * prune_overflow), reverse edges with lazy prune (:442-455), levels floor(-ln U / ln M) from mt19937(seed)
+ * (:159,323). K = 0 picks min(127, 2*M0). Batch construction: not bit-identical to the sequential insert.
+ * save_index writes the reference's serialize format (:931-991) so the reference can deserialize it (:994-1074). */
+int expann_gpu_build_graph(expann_gpu_t* h, uint64_t M, uint64_t M0, uint64_t K, float ortho_factor, float ortho_bias,
+                           uint64_t prune_overflow, uint64_t seed);
+int expann_gpu_save_index(expann_gpu_t* h, const char* path);
 /* build() — src/ann_engine.h:25, src/brute_force_engine.h:24-26 (the reference asserts n > 0; here n == 0
  * returns EXPANN_ERR_STATE) */
 int expann_gpu_build(expann_gpu_t* h);

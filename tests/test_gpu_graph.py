@@ -85,3 +85,38 @@ def test_graph_errors(ex):
     with pytest.raises(ex.ExpannError):
         e.load_index("/nonexistent/file.index")
     e.close()
+
+
+def test_gpu_built_graph_roundtrip(ex, oracle, reference_128):
+    """GPU graph construction + index writer (row 2): the graph built on the GPU is written in
+    the reference's serialize format, the UNMODIFIED reference deserializes it and searches it on the CPU; on that
+    same graph the GPU search must reach the reference's recall at every beam width, and the graph must be good."""
+    from expann_b200 import datasets
+    base, q = datasets.make("sift", 8000, 64, 128, seed=31, variant="lowrank")
+    truth, _, _ = oracle.bf_query(base, q, 10, threads=8)
+    e = ex.GraphEngine()
+    e.store_many_vectors(base)
+    e.build_graph(M=12, M0=24, K=48)
+    e.build()
+    path = "/tmp/expann_gpu_built.index"
+    e.save_index(path)
+    G = reference_128.graph(M=12, M0=24, ef_construction=48)
+    G.load(path, 128)
+    info = G.info()
+    assert info["n"] == 8000 and info["M0"] == 24
+    og = oracle.graph_load(path)
+    degs = np.array([len(og.neighbours(v, 0)) for v in range(0, 8000, 97)])
+    assert degs.max() <= 24 and degs.mean() >= 6
+    last = 0.0
+    for ef in (10, 20, 40, 80):
+        G.set_ef(ef)
+        rid, _ = G.query(q, 10)
+        e.set_ef_search(ef)
+        ids, dists, counts = e.query_k_batch(q, 10)
+        r_gpu, r_ref = recall(ids, truth), recall(rid, truth)
+        assert r_gpu >= r_ref - 1e-9, (ef, r_gpu, r_ref)
+        same = np.mean([set(a.tolist()) == set(b.tolist()) for a, b in zip(ids, rid)])
+        assert same >= 0.9, (ef, same)
+        last = r_gpu
+    assert last >= 0.95, last
+    e.close()
