@@ -123,7 +123,30 @@ def cpu_reference_qps(base, q, k, metric, budget_s=15.0):
     return msample / t, threads, kind, f"{msample} of {len(q)} queries, full {base.shape[0]}x{d} base, {threads} threads, {t:.1f}s"
 
 
+_REAL_STDOUT = None
+
+
+def protect_stdout():
+    """the reference's engines print to std::cout (e.g. "Total query time", src/antitopo_engine.h destructor path):
+    keep fd 1 clean for the ONE JSON line by pointing it at stderr for the whole run"""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, line)
+
+
 def main():
+    protect_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -133,6 +156,7 @@ def main():
     ap.add_argument("--qtile", type=int, default=0)
     ap.add_argument("--m", type=int, default=0, help="override the query count")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extras", action="store_true", help="skip the extra legs (graph engine sweep, BASELINE config 3)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -163,7 +187,7 @@ def main():
                "config": {"workload": desc, "n": n, "m": m, "d": d, "k": k, "metric": metric},
                "cpu_baseline": {"value": v, "unit": "queries/s", "cores": info[0], "kind": info[1], "sample": info[2]},
                "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(out))
+        emit(out)
         return 0
 
     import torch
@@ -288,8 +312,18 @@ def main():
             qps, cores, kind, sample = cpu_reference_qps(base, q, k, metric)
             out["cpu_baseline"] = {"value": qps, "unit": "queries/s", "cores": cores, "kind": kind, "sample": sample}
         out["check"] = {"first_ids": got[0].tolist()}
-        print(json.dumps(out))
     eng.close()
+    del eng
+    if rank == 0:
+        if world == 1 and args.workload == "c2" and not args.no_extras:
+            # BASELINE config 3 (graph engine, QPS at recall@10 >= 0.95) measured in the same run
+            try:
+                from tools import bench_extras
+                torch.cuda.empty_cache()
+                out["graph_c3"] = bench_extras.graph_c3(local_rank, max(2, args.steps), args.warmup, cpu=not args.no_cpu, peak_gbs=peak)
+            except Exception as ex:  # noqa: BLE001
+                out["graph_c3"] = {"error": repr(ex)[:300]}
+        emit(out)
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -1,0 +1,119 @@
+"""Extra bench legs reported next to the headline line (BASELINE.json configs 3 and 5). Not product code: may use
+oracle/ for the CPU baselines (bench.py's cpu_baseline leg)."""
+from __future__ import annotations
+
+import os
+import time
+
+import numpy as np
+
+
+def _recall(ids, truth, k):
+    return float(np.mean([len(set(a.tolist()) & set(b.tolist())) / k for a, b in zip(ids, truth)]))
+
+
+def graph_c3(device: int, steps: int, warmup: int, cpu: bool = True, n: int = 1_000_000, m: int = 10_000,
+             M0: int = 32, K: int = 64, peak_gbs: float = 6553.3) -> dict:
+    """C3: SIFT-shape (low-rank u8-valued) 1M x 128, graph engine, beam-width sweep; QPS at the smallest ef with
+    recall@10 >= 0.95. The graph is built on the GPU (expann_gpu_build_graph) and written in the reference's index
+    format; the CPU baseline searches THE SAME graph (reference deserialize / oracle loader)."""
+    import torch
+    import expann_b200
+    from expann_b200 import datasets
+    k, d = 10, 128
+    base, q = datasets.make("sift", n, m, d, variant="lowrank")
+    bf = expann_b200.BruteForceEngine(device=device)
+    bf.store_many_vectors(base)
+    bf.build()
+    truth = bf.query_k_batch(q, k)[0]
+    bf.close()
+    e = expann_b200.GraphEngine(device=device)
+    e.store_many_vectors(base)
+    t0 = time.perf_counter()
+    e.build_graph(M=M0 // 2, M0=M0, K=K)
+    build_s = time.perf_counter() - t0
+    e.build()
+    dq = torch.from_numpy(q).cuda(device)
+    keys = torch.empty((m, k), dtype=torch.int64, device=dq.device)
+    st = torch.cuda.current_stream().cuda_stream
+    sweep, chosen = [], None
+    for ef in (10, 20, 30, 40, 60, 80, 120, 200):
+        e.set_ef_search(ef)
+        ids = e.query_k_batch(q, k)[0]
+        rec = _recall(ids, truth, k)
+        for _ in range(max(1, warmup)):
+            e.query_device(dq.data_ptr(), m, k, keys.data_ptr(), st)
+        torch.cuda.synchronize()
+        s0 = e.stats()
+        e.set_timing(True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            e.query_device(dq.data_ptr(), m, k, keys.data_ptr(), st)
+        e1.record()
+        torch.cuda.synchronize()
+        s1 = e.stats()
+        e.set_timing(False)
+        ms = e0.elapsed_time(e1) / steps
+        kms = (s1["hot_time_ns"] - s0["hot_time_ns"]) / 1e6 / max(1, s1["hot_timed_launches"] - s0["hot_timed_launches"])
+        dcq = (s1["distcomps"] - s0["distcomps"]) / (steps * m)
+        row = {"ef": ef, "recall": rec, "qps": m / ms * 1e3, "ms_per_step": ms, "kernel_ms": kms, "distcomps_per_query": dcq,
+               "gather_GBs": dcq * d * 4 * m / (kms * 1e-3) / 1e9}
+        sweep.append(row)
+        if chosen is None and rec >= 0.95:
+            chosen = dict(row)
+            t1 = time.perf_counter()
+            for _ in range(steps):
+                e.query_k_batch(q, k)
+            chosen["e2e_qps"] = m * steps / (time.perf_counter() - t1)
+    out = {"workload": "SIFT-shape synthetic (low-rank, u8-valued) %dx%d, %d queries, graph engine M0=%d (GPU-built, K=%d), "
+                       "beam-width sweep" % (n, d, m, M0, K),
+           "metric": "QPS @ smallest ef with recall@10 >= 0.95", "graph_build_s": build_s, "sweep": sweep, "at_recall_0.95": chosen}
+    if chosen:
+        out["roofline"] = {"bound": "hbm", "kernel": "graph_search_kernel", "achieved": chosen["gather_GBs"], "peak": peak_gbs,
+                           "unit": "GB/s", "frac": chosen["gather_GBs"] / peak_gbs,
+                           "note": "algorithmic bytes = distance evaluations x d x 4 (random 512 B row gathers); latency-bound"}
+    if cpu and chosen:
+        path = "/tmp/expann_bench_c3.index"
+        e.save_index(path)
+        out["cpu_baseline"] = graph_cpu_baseline(path, q, truth, k, chosen["ef"])
+        try:
+            os.remove(path)
+        except OSError:
+            pass
+    e.close()
+    return out
+
+
+def graph_cpu_baseline(index_path: str, q, truth, k: int, ef: int, budget_s: float = 12.0) -> dict:
+    """the same graph searched on the host: (a) UNMODIFIED reference antitopo_engine, one thread (its _query_k is not
+    re-entrant); (b) the C restatement with one visited array per thread, all host threads."""
+    from oracle import pyoracle
+    threads = os.cpu_count() or 1
+    res = {}
+    og = pyoracle.Oracle().graph_load(index_path)
+    ms = min(len(q), 2000)
+    t0 = time.perf_counter()
+    ids, _ = og.query_mt(q[:ms], k, ef, threads=threads)
+    dt = time.perf_counter() - t0
+    msample = int(min(len(q), max(ms, ms * budget_s / max(dt, 1e-6))))
+    t0 = time.perf_counter()
+    ids, _ = og.query_mt(q[:msample], k, ef, threads=threads)
+    dt = time.perf_counter() - t0
+    res.update({"value": msample / dt, "unit": "queries/s", "cores": threads, "kind": "port",
+                "sample": f"{msample} queries, ef={ef}, same GPU-built graph, {dt:.1f}s", "recall": _recall(ids, truth[:msample], k)})
+    try:
+        ref = pyoracle.Reference(128)
+        G = ref.graph(M=16, M0=32)
+        G.load(index_path, q.shape[1])
+        G.set_ef(ef)
+        mr = min(len(q), 3000)
+        t0 = time.perf_counter()
+        rid, _ = G.query(q[:mr], k)
+        dt = time.perf_counter() - t0
+        res["reference_1thread"] = {"value": mr / dt, "unit": "queries/s", "cores": 1, "kind": "reference",
+                                    "sample": f"{mr} queries sequential (src/basic_bench.h:83-84 loop shape)",
+                                    "recall": _recall(rid, truth[:mr], k)}
+    except Exception as ex:  # noqa: BLE001
+        res["reference_1thread"] = {"unavailable": str(ex)[:200]}
+    return res
