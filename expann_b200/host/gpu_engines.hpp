@@ -1,0 +1,164 @@
+// C++ host side above the C ABI: engines with the reference's compile-time engine interface
+// (template<class T, class Derived> struct ann_engine: name / param_list / store_vector / build / query_k,
+// reference src/ann_engine.h:16-29) plus the nested `config` + `Engine(config)` constructor the harness needs
+// (src/bench_runner.h:33,116). Everything below forwards to include/expann_gpu.h; there is no CPU compute here.
+// Inside the reference tree the same classes derive from its own ann_engine and take its vec<T>.
+#pragma once
+#include <cstdint>
+#include <map>
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include "../../include/expann_gpu.h"
+
+namespace expann_host {
+
+using param_list_t = std::map<std::string, std::string>;
+using fvec = std::vector<float>; // stands in for vec<float> (src/vec.h:17-23): contiguous floats, .data()/.size()
+
+// CRTP dispatch, no virtual calls — the shape of src/ann_engine.h:16-29
+template <class Derived> struct gpu_engine_base {
+	std::string name() { return self()._name(); }
+	param_list_t param_list() { return self()._param_list(); }
+	void store_vector(const fvec& v) { self()._store_vector(v); }
+	void build() { self()._build(); }
+	const std::vector<size_t> query_k(const fvec& v, size_t k) { return self()._query_k(v, k); }
+
+	// GPU extension: all m queries in one call (queries row-major [m][d]); ids padded with SIZE_MAX
+	void query_k_batch(const float* q, size_t m, size_t k, std::vector<uint64_t>& ids, std::vector<float>* keys = nullptr,
+	                   std::vector<uint64_t>* counts = nullptr) {
+		ids.resize(m * k);
+		if (keys) keys->resize(m * k);
+		if (counts) counts->resize(m);
+		check(expann_gpu_query(h, q, m, k, ef_search, ids.data(), keys ? keys->data() : nullptr, counts ? counts->data() : nullptr));
+	}
+	void set_ef_search(size_t ef) { ef_search = ef; } // src/antitopo_engine.h:189-195
+	expann_gpu_stats_t stats() { expann_gpu_stats_t s; check(expann_gpu_stats(h, &s)); return s; }
+	~gpu_engine_base() { expann_gpu_destroy(h); }
+	gpu_engine_base() = default;
+	gpu_engine_base(const gpu_engine_base&) = delete;
+	gpu_engine_base& operator=(const gpu_engine_base&) = delete;
+
+protected:
+	expann_gpu_t* h = nullptr;
+	size_t dim = 0, ef_search = 0;
+	Derived& self() { return *static_cast<Derived*>(this); }
+	void create(const expann_gpu_cfg& c) {
+		if (expann_gpu_create(&c, &h) != EXPANN_OK) throw std::runtime_error(expann_gpu_last_error(nullptr));
+	}
+	void check(int rc) { if (rc != EXPANN_OK) throw std::runtime_error(expann_gpu_last_error(h)); }
+	void _store_vector(const fvec& v) { dim = v.size(); check(expann_gpu_add(h, v.data(), 1, v.size())); }
+	void _build() { check(expann_gpu_build(h)); }
+	std::vector<size_t> _query_k(const fvec& v, size_t k) {
+		std::vector<uint64_t> ids(k);
+		uint64_t cnt = 0;
+		check(expann_gpu_query(h, v.data(), 1, k, ef_search, ids.data(), nullptr, &cnt));
+		return std::vector<size_t>(ids.begin(), ids.begin() + cnt);
+	}
+	friend Derived;
+};
+
+// ---- brute_force_engine<T> (src/brute_force_engine.h:10-46) ---------------------------------------------
+struct gpu_brute_force_engine_config {
+	int device = 0;
+	int metric = EXPANN_METRIC_L2;
+};
+struct gpu_brute_force_engine : gpu_engine_base<gpu_brute_force_engine> {
+	using config = gpu_brute_force_engine_config;
+	explicit gpu_brute_force_engine(config c = config()) : conf(c) {
+		expann_gpu_cfg g{};
+		g.engine = EXPANN_ENGINE_BRUTE_FORCE;
+		g.metric = c.metric;
+		g.device = c.device;
+		create(g);
+	}
+	const std::string _name() { return "Brute-Force Engine (B200)"; }
+	const param_list_t _param_list() {
+		param_list_t pl;
+		pl["metric"] = conf.metric == EXPANN_METRIC_IP ? "ip" : "l2";
+		return pl;
+	}
+	config conf;
+};
+
+// ---- antitopo_engine<T> query path (src/antitopo_engine.h:103-1074); config mirrors antitopo_engine_config (:73-101)
+struct gpu_graph_engine_config {
+	size_t M = 16, M0 = 32, ef_search_mult = 1, ef_construction = 64 /* candidates per vertex of the GPU build */;
+	size_t ortho_count = 1;
+	float ortho_factor = 0.5f, ortho_bias = 0.f;
+	size_t prune_overflow = 0;
+	bool use_compression = false;
+	std::string index_filename;
+	bool read_index = false, write_index = false;
+	int device = 0;
+};
+struct gpu_graph_engine : gpu_engine_base<gpu_graph_engine> {
+	using config = gpu_graph_engine_config;
+	explicit gpu_graph_engine(config c) : conf(c) {
+		expann_gpu_cfg g{};
+		g.engine = EXPANN_ENGINE_GRAPH;
+		g.device = c.device;
+		g.M = c.M;
+		g.M0 = c.M0;
+		g.ef_search_mult = c.ef_search_mult;
+		g.use_compression = c.use_compression;
+		create(g);
+	}
+	void _store_vector(const fvec& v) {
+		if (conf.read_index) return; // src/antitopo_engine.h:312-313
+		gpu_engine_base<gpu_graph_engine>::_store_vector(v);
+	}
+	void _build() { // src/antitopo_engine.h:467-493
+		if (conf.read_index) check(expann_gpu_load_index(h, conf.index_filename.c_str()));
+		else check(expann_gpu_build_graph(h, conf.M, conf.M0, conf.ef_construction, conf.ortho_factor, conf.ortho_bias,
+		                                  conf.prune_overflow, 0));
+		if (conf.write_index && !conf.read_index) check(expann_gpu_save_index(h, conf.index_filename.c_str()));
+		check(expann_gpu_build(h));
+	}
+	const std::string _name() { return "Anti-Topo Engine (B200 query path)"; }
+	const param_list_t _param_list() { // src/antitopo_engine.h:211-238
+		param_list_t pl;
+		pl["M"] = std::to_string(conf.M);
+		pl["M0"] = std::to_string(conf.M0);
+		pl["ef_search_mult"] = std::to_string(conf.ef_search_mult);
+		pl["ef_construction"] = std::to_string(conf.ef_construction);
+		pl["ortho_count"] = std::to_string(conf.ortho_count);
+		pl["ortho_factor"] = std::to_string(conf.ortho_factor);
+		pl["ortho_bias"] = std::to_string(conf.ortho_bias);
+		pl["prune_overflow"] = std::to_string(conf.prune_overflow);
+		pl["use_compression"] = std::to_string(conf.use_compression);
+		pl["num_distcomps"] = std::to_string(stats().distcomps);
+		return pl;
+	}
+	config conf;
+};
+
+// ---- quantizer.h compressed scan + fp32 rerank (src/quantizer.h:20-238) ---------------------------------
+struct gpu_quant_scan_engine_config {
+	int device = 0;
+	int metric = EXPANN_METRIC_L2;
+	int quantizer = 0; // 0 quantizer_simple<uint8_t>, 1 quantizer_ranged_q8
+	size_t kprime = 0;
+};
+struct gpu_quant_scan_engine : gpu_engine_base<gpu_quant_scan_engine> {
+	using config = gpu_quant_scan_engine_config;
+	explicit gpu_quant_scan_engine(config c = config()) : conf(c) {
+		expann_gpu_cfg g{};
+		g.engine = EXPANN_ENGINE_QUANT_SCAN;
+		g.metric = c.metric;
+		g.device = c.device;
+		g.quantizer = c.quantizer;
+		create(g);
+		if (c.kprime) check(expann_gpu_set_option(h, "kprime", (int64_t)c.kprime));
+	}
+	const std::string _name() { return "Quantized Scan Engine (B200)"; }
+	const param_list_t _param_list() {
+		param_list_t pl;
+		pl["quantizer"] = conf.quantizer ? "ranged_q8" : "simple_u8";
+		pl["kprime"] = std::to_string(conf.kprime);
+		return pl;
+	}
+	config conf;
+};
+
+} // namespace expann_host
