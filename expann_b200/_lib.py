@@ -24,7 +24,8 @@ class Stats(C.Structure):
     _fields_ = [("n", C.c_uint64), ("d", C.c_uint64), ("d_pad", C.c_uint64), ("scan_launches", C.c_uint64),
                 ("merge_launches", C.c_uint64), ("graph_launches", C.c_uint64), ("aux_launches", C.c_uint64),
                 ("last_nsplit", C.c_uint64), ("last_qtile", C.c_uint64), ("distcomps", C.c_uint64),
-                ("hot_time_ns", C.c_uint64), ("hot_timed_launches", C.c_uint64), ("reserved", C.c_uint64 * 6)]
+                ("hot_time_ns", C.c_uint64), ("hot_timed_launches", C.c_uint64), ("tc_launches", C.c_uint64),
+                ("tc_fallbacks", C.c_uint64), ("tc_mode", C.c_uint64), ("reserved", C.c_uint64 * 3)]
 
 
 # every symbol include/expann_gpu.h declares: name -> (restype, argtypes)

@@ -182,6 +182,8 @@ void expann_gpu_destroy(expann_gpu_t* h) {
 	timing_collect(h);
 	for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
 	if (h->base) cudaFree(h->base);
+	for (DevBuf* b : { &h->tc_xb, &h->tc_xn, &h->tc_stats, &h->tc_qstats, &h->tc_qb, &h->tc_qn, &h->tc_thr, &h->tc_cnt, &h->tc_cand })
+		b->release();
 	for (DevBuf* b : { &h->q_codes, &h->q_cnorm, &h->q_mm, &h->qq_codes, &h->qq_norm, &h->q_cand }) b->release();
 	for (DevBuf* b : { &h->g_bottom, &h->g_upper, &h->g_upper_idx, &h->g_upper_nl, &h->g_visited, &h->g_epoch, &h->g_codes })
 		b->release();
@@ -232,7 +234,9 @@ int expann_gpu_build(expann_gpu_t* h) {
 		if (int rc = graph_finalize(h)) return rc;
 	if (h->cfg.engine == EXPANN_ENGINE_QUANT_SCAN)
 		if (int rc = quant_finalize(h)) return rc;
+	if (int rc = tc_finalize(h)) return rc;
 	h->stats.n = h->n;
+	h->stats.tc_mode = h->tc_mode;
 	h->stats.d = h->d;
 	h->stats.d_pad = h->d_pad;
 	h->built = true;
@@ -358,6 +362,11 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 	} else if (nm == "kprime") {
 		if (value < 0 || value > 128) return fail(h, EXPANN_ERR_ARG, "kprime must be in 0..128");
 		h->opt_kprime = (int)value;
+	} else if (nm == "tc") {
+		h->opt_tc = value != 0;
+	} else if (nm == "tc_min_batch") {
+		if (value < 1) return fail(h, EXPANN_ERR_ARG, "tc_min_batch must be >= 1");
+		h->opt_tc_min_batch = (int)value;
 	} else if (nm == "nsplit") {
 		if (value < 0) return fail(h, EXPANN_ERR_ARG, "nsplit must be >= 0");
 		h->opt_nsplit = (int)value;

@@ -55,6 +55,13 @@ struct expann_gpu {
 	expann::DevBuf qpad, partial, keys, ids, dists, counts; // device work buffers (grow-only)
 	expann::DevBuf h_q, h_ids, h_dists, h_counts;            // pinned host staging for the host-pointer API
 	expann_gpu_stats_t stats{};
+	// tensor-core candidate filter (K3)
+	int opt_tc = 1, opt_tc_min_batch = 512;
+	int tc_mode = 0; // 0 off, 1 bf16-exact single GEMM, 2 two-term bf16 split
+	uint32_t tc_kd = 0;
+	float tc_xmin = 0.f, tc_xmax = 0.f, tc_xnorm_max = 0.f;
+	expann::DevBuf tc_xb, tc_xn, tc_stats, tc_qstats, tc_qb, tc_qn, tc_thr, tc_cnt, tc_cand;
+	CUtensorMap tmap_xb{};
 	// quantised scan engine (K6 + K4)
 	int quantizer = 0;       // 0 = quantizer_simple<uint8_t>, 1 = quantizer_ranged_q8
 	int opt_kprime = 0;      // 0 = auto
@@ -93,6 +100,9 @@ int graph_load_index(expann_gpu* h, const char* path, std::vector<float>& vector
 int graph_finalize(expann_gpu* h);
 int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out, cudaStream_t st);
 int graph_read_distcomps(expann_gpu* h);
+// tc.cu
+int tc_finalize(expann_gpu* h);
+int launch_scan_tc(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);
 // quant.cu
 int quant_finalize(expann_gpu* h);
 int launch_quant_scan(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);

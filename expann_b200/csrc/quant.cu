@@ -128,6 +128,7 @@ int launch_quant_scan(expann_gpu* h, const float* d_q, size_t m, size_t k, uint6
 	r.m = (uint32_t)m;
 	r.k = (uint32_t)k;
 	r.kp = (uint32_t)kp;
+	r.cand_stride = (uint32_t)kp;
 	r.d_pad = (uint32_t)h->d_pad;
 	r.id_add = (uint32_t)h->cfg.id_offset;
 	r.metric = ip ? 1 : 0;

@@ -36,7 +36,7 @@ struct RerankParams {
 	const float* queries;   // [m][d_pad]
 	const uint64_t* cand;   // [m][kp] keys whose low 32 bits are local ids (KEY_EMPTY = none)
 	uint64_t* out_keys;     // [m][k]
-	uint32_t m, k, kp, d_pad, id_add;
+	uint32_t m, k, kp, cand_stride, d_pad, id_add; // kp entries are read from each query's cand_stride-strided list
 	int metric;
 };
 
@@ -52,7 +52,7 @@ template <int LPL> __global__ void __launch_bounds__(128) rerank_kernel(const Re
 	for (uint32_t i = lane; i < p.d_pad; i += 32) qsm[i] = p.queries[(size_t)q * p.d_pad + i];
 	int cnt = 0;
 	for (uint32_t j0 = 0; j0 < p.kp; j0 += 32) {
-		const uint64_t key = j0 + lane < p.kp ? p.cand[(size_t)q * p.kp + j0 + lane] : KEY_EMPTY;
+		const uint64_t key = j0 + lane < p.kp ? p.cand[(size_t)q * p.cand_stride + j0 + lane] : KEY_EMPTY;
 		const bool ok = key != KEY_EMPTY;
 		const unsigned mk = __ballot_sync(FULL, ok);
 		if (ok) ids[cnt + __popc(mk & ((1u << lane) - 1))] = key_id(key);
@@ -74,7 +74,7 @@ template <int LPL> __global__ void __launch_bounds__(128) rerank_kernel(const Re
 // ---- quantizers ------------------------------------------------------------------------------------------
 // quantizer_simple<uint8_t>::build (src/quantizer.h:132-141): code = uint8_t(x) (truncation on [0,256)); also
 // emits sum c^2 per row. One warp per row; dst row stride dc (zero padded).
-__global__ void quant_simple_u8_kernel(const float* __restrict__ src, size_t src_stride, uint32_t d, uint8_t* __restrict__ dst,
+static __global__ void quant_simple_u8_kernel(const float* __restrict__ src, size_t src_stride, uint32_t d, uint8_t* __restrict__ dst,
                                        uint32_t dc, int32_t* __restrict__ norm, size_t n) {
 	const size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const int lane = threadIdx.x & 31;
@@ -93,7 +93,7 @@ __global__ void quant_simple_u8_kernel(const float* __restrict__ src, size_t src
 
 // quantizer_ranged_q8 (src/quantizer.h:186-238): global min/max -> scale = 128/(max-min), offset = -scale*min;
 // code = clamp(round(scale*x+offset), 0, 127), a negative pre-clamp value becomes 127 (size_t wrap, :196-205).
-__global__ void minmax_kernel(const float* __restrict__ src, size_t src_stride, uint32_t d, size_t n, float* mm /*[2]*/) {
+static __global__ void minmax_kernel(const float* __restrict__ src, size_t src_stride, uint32_t d, size_t n, float* mm /*[2]*/) {
 	float mx = 1.17549435e-38f /* FLT_MIN, src/quantizer.h:210 */, mn = 3.402823466e+38f;
 	const size_t total = n * d;
 	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -109,7 +109,7 @@ __global__ void minmax_kernel(const float* __restrict__ src, size_t src_stride, 
 		atomicMin(reinterpret_cast<unsigned*>(mm) + 1, f32_orderable(mn));
 	}
 }
-__global__ void quant_ranged_q8_kernel(const float* __restrict__ src, size_t src_stride, uint32_t d, uint8_t* __restrict__ dst,
+static __global__ void quant_ranged_q8_kernel(const float* __restrict__ src, size_t src_stride, uint32_t d, uint8_t* __restrict__ dst,
                                        uint32_t dc, int32_t* __restrict__ norm, size_t n, float scale, float offset) {
 	const size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const int lane = threadIdx.x & 31;
@@ -131,7 +131,7 @@ __global__ void quant_ranged_q8_kernel(const float* __restrict__ src, size_t src
 
 // ---- explicit-pair distance primitives (parity tests of SURVEY §8(a) a2-a8): one warp per pair ----------
 enum { PAIR_F32_L2 = 0, PAIR_F32_DOT = 1, PAIR_U8_COMPRESSED = 2, PAIR_I8 = 3, PAIR_I16 = 4 };
-__global__ void pair_distance_kernel(int kind, const void* __restrict__ a, const void* __restrict__ b, size_t npairs,
+static __global__ void pair_distance_kernel(int kind, const void* __restrict__ a, const void* __restrict__ b, size_t npairs,
                                      uint32_t d, float* __restrict__ out_f, int32_t* __restrict__ out_i) {
 	const size_t pr = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const int lane = threadIdx.x & 31;

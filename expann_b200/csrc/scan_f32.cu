@@ -43,6 +43,19 @@ int encode_tensor_map_2d(expann_gpu* h, CUtensorMap* out, int dtype_u8, void* ba
 	return EXPANN_OK;
 }
 
+int encode_tensor_map_bf16(expann_gpu* h, CUtensorMap* out, void* base, uint64_t inner, uint64_t rows, uint32_t box_rows) {
+	encode_tiled_fn enc = get_encode_tiled();
+	if (!enc) return fail(h, EXPANN_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+	cuuint64_t gdim[2] = { (cuuint64_t)inner, (cuuint64_t)rows };
+	cuuint64_t gstride[1] = { (cuuint64_t)inner * 2 };
+	cuuint32_t box[2] = { 64, box_rows };
+	cuuint32_t estr[2] = { 1, 1 };
+	CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+	                 CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+	if (r != CUDA_SUCCESS) return fail(h, EXPANN_ERR_CUDA, "cuTensorMapEncodeTiled(bf16) failed: " + std::to_string((int)r));
+	return EXPANN_OK;
+}
+
 // base set: dim0 = d_pad floats (contiguous), dim1 = n rows; box = [32 floats][BOXR rows]
 int make_base_tensor_map(expann_gpu* h) {
 	return encode_tensor_map_2d(h, &h->tmap_base, 0, h->base, h->d_pad, h->n, h->d_pad * 4, 32, SCAN_BOXR);
@@ -70,7 +83,15 @@ template <int QT> static int launch_m(expann_gpu* h, const ScanParams& p, dim3 g
 	                                          : launch_k<QT, METRIC_L2>(h, p, grid, st);
 }
 
+int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);
+
+// path selection: the tensor-core filter (K3) for large batches when build() prepared its operands, else the SIMT scan
 int launch_scan_f32(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st) {
+	if (h->tc_mode && h->opt_tc && m >= (size_t)h->opt_tc_min_batch && k <= 128) return launch_scan_tc(h, d_q, m, k, d_keys_out, st);
+	return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st);
+}
+
+int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st) {
 	int qt = h->cfg.qtile;
 	if (qt == 0) qt = m >= 8 ? 8 : (m >= 3 ? 4 : 1);
 	if (qt != 1 && qt != 4 && qt != 8) return fail(h, EXPANN_ERR_ARG, "qtile must be 0, 1, 4 or 8");

@@ -1,0 +1,213 @@
+// Host side of K3: operand preparation at build(), chunked filter launches with threshold refresh, fp32 re-rank.
+//
+// Why the result is exact. Let a'(x) be the tensor-core value and e >= |a'(x) - a'_true(x)| the error bound of the
+// operand format (0 for bf16-exact integer data; eps_rel*|q|*max|x| for the two-term split). After any prefix of
+// the rows, let A_k be the k-th smallest a' seen. k seen rows have a'_true <= A_k + e, hence the final k-th true
+// value D_k <= A_k + e, and every row of the true top-k has a' <= D_k + e <= A_k + 2e =: thr. Rows are processed
+// in chunks of doubling size; each chunk is filtered with the thr of the rows before it (first chunk: +inf) and
+// thr only decreases, so the buffers always hold the true top-k. K4 then recomputes the survivors with the same
+// fp32 diff-form arithmetic as the SIMT scan and orders them by (key, id). A buffer overflow (adversarial row order)
+// is detected and the batch is redone by the SIMT scan.
+#include "engine.h"
+#include "rerank.cuh"
+#include "tc_filter.cuh"
+#include "tc_prep.cuh"
+#include <algorithm>
+#include <cmath>
+
+namespace expann {
+
+int encode_tensor_map_bf16(expann_gpu* h, CUtensorMap* out, void* base, uint64_t inner, uint64_t rows, uint32_t box_rows);
+int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);
+
+constexpr uint32_t TC_CAP = 4096, TC_FIRST_ROWS = 2048, TC_PAD = 256, TC_QBATCH = 16384;
+constexpr int TC_NSTAGE_EXACT = 4, TC_NSTAGE_SPLIT = 3;
+
+static size_t tc_smem_bytes(uint32_t kd, int nstage) {
+	return 1024 + (size_t)(kd / TC_BK) * TC_A_KB_BYTES + (size_t)nstage * TC_B_STAGE_BYTES + (1 + 2 * nstage + 4) * 8 + 16;
+}
+
+static int read_stats(expann_gpu* h, DevBuf& buf, TcStats* out, cudaStream_t st) {
+	EXPANN_CUDA(h, cudaMemcpyAsync(out, buf.p, sizeof(TcStats), cudaMemcpyDeviceToHost, st));
+	EXPANN_CUDA(h, cudaStreamSynchronize(st));
+	return EXPANN_OK;
+}
+static int reset_stats(expann_gpu* h, DevBuf& buf, cudaStream_t st) {
+	EXPANN_CUDA(h, buf.ensure(sizeof(TcStats)));
+	const TcStats init = { f32_orderable(3.4e38f), f32_orderable(-3.4e38f), 0u, f32_orderable(0.f) };
+	EXPANN_CUDA(h, cudaMemcpyAsync(buf.p, &init, sizeof(init), cudaMemcpyHostToDevice, st));
+	return EXPANN_OK;
+}
+
+// build(): decide the operand format from the base values and materialise the bf16 operand + ||x||^2
+int tc_finalize(expann_gpu* h) {
+	h->tc_mode = 0;
+	if (!h->opt_tc || h->cfg.engine != EXPANN_ENGINE_BRUTE_FORCE) return EXPANN_OK;
+	cudaStream_t st = h->stream;
+	const uint32_t seg = (uint32_t)((h->d + 63) / 64 * 64);
+	if (tc_smem_bytes(3 * seg, TC_NSTAGE_SPLIT) > 227 * 1024) return EXPANN_OK; // d too large for the resident query tile
+	const size_t n_pad = (h->n + TC_BN - 1) / TC_BN * TC_BN;
+	EXPANN_CUDA(h, h->tc_xn.ensure(n_pad * 4));
+	for (int mode = 1; mode <= 2; ++mode) {
+		const uint32_t kd = mode == 1 ? seg : 3 * seg;
+		EXPANN_CUDA(h, h->tc_xb.ensure(h->n * (size_t)kd * 2));
+		if (int rc = reset_stats(h, h->tc_stats, st)) return rc;
+		tc_convert_kernel<<<(unsigned)((h->n + 7) / 8), 256, 0, st>>>(h->base, h->d_pad, (uint32_t)h->d, h->n,
+		                                                             h->tc_xb.as<__nv_bfloat16>(), kd, mode, 0, h->tc_xn.as<float>(),
+		                                                             h->tc_stats.as<TcStats>());
+		EXPANN_CUDA(h, cudaGetLastError());
+		h->stats.aux_launches++;
+		TcStats s;
+		if (int rc = read_stats(h, h->tc_stats, &s, st)) return rc;
+		h->tc_xmin = f32_from_orderable(s.vmin);
+		h->tc_xmax = f32_from_orderable(s.vmax);
+		h->tc_xnorm_max = std::sqrt(f32_from_orderable(s.nmax));
+		h->tc_kd = kd;
+		h->tc_mode = mode;
+		if (mode == 1 && !s.inexact) break; // integer, bf16-exact base: single GEMM, error bound 0
+	}
+	if (n_pad > h->n) {
+		tc_fill_kernel<<<(unsigned)((n_pad - h->n + 255) / 256), 256, 0, st>>>(h->tc_xn.as<float>(), h->n, n_pad, nanf(""));
+		h->stats.aux_launches++;
+	}
+	if (h->cfg.metric == EXPANN_METRIC_IP) { // a' = -dot: no norm term
+		EXPANN_CUDA(h, cudaMemsetAsync(h->tc_xn.p, 0, h->n * 4, st));
+	}
+	EXPANN_CUDA(h, cudaStreamSynchronize(st));
+	return encode_tensor_map_bf16(h, &h->tmap_xb, h->tc_xb.p, h->tc_kd, h->n, TC_BN);
+}
+
+template <int NSTAGE>
+static int launch_filter(expann_gpu* h, const CUtensorMap& tq, const TcParams& p, dim3 grid, cudaStream_t st) {
+	const size_t smem = tc_smem_bytes(p.kd, NSTAGE);
+	EXPANN_CUDA(h, cudaFuncSetAttribute(tc_filter_kernel<NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	tc_filter_kernel<NSTAGE><<<grid, TC_THREADS, smem, st>>>(tq, h->tmap_xb, p);
+	EXPANN_CUDA(h, cudaGetLastError());
+	return EXPANN_OK;
+}
+
+static int tc_batch(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st, bool* fell_back) {
+	*fell_back = false;
+	const uint32_t kd = h->tc_kd;
+	const bool ip = h->cfg.metric == EXPANN_METRIC_IP;
+	EXPANN_CUDA(h, h->tc_qb.ensure(m * (size_t)kd * 2));
+	EXPANN_CUDA(h, h->tc_qn.ensure(m * 4));
+	EXPANN_CUDA(h, h->tc_thr.ensure(m * 4));
+	EXPANN_CUDA(h, h->tc_cnt.ensure(m * 4 + 16));
+	EXPANN_CUDA(h, h->tc_cand.ensure(m * (size_t)TC_CAP * 8));
+	uint32_t* flags = h->tc_cnt.as<uint32_t>() + m;
+	if (int rc = reset_stats(h, h->tc_qstats, st)) return rc;
+	tc_convert_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(d_q, h->d_pad, (uint32_t)h->d, m, h->tc_qb.as<__nv_bfloat16>(), kd,
+	                                                          h->tc_mode, 1, h->tc_qn.as<float>(), h->tc_qstats.as<TcStats>());
+	EXPANN_CUDA(h, cudaGetLastError());
+	h->stats.aux_launches++;
+	float eps_rel = 0.f, eps_abs = 0.f;
+	if (h->tc_mode == 1) {
+		// exact only if the queries are bf16-exact integers too and no intermediate can leave the 2^24 integer range
+		TcStats s;
+		if (int rc = read_stats(h, h->tc_qstats, &s, st)) return rc;
+		const float lo = std::min(h->tc_xmin, f32_from_orderable(s.vmin)), hi = std::max(h->tc_xmax, f32_from_orderable(s.vmax));
+		const float amax = std::max(std::fabs(lo), std::fabs(hi));
+		const double lim = 16777216.0, dd = (double)h->d;
+		const bool exact = !s.inexact && amax <= 256.f && dd * (hi - lo) * (hi - lo) < lim && dd * amax * amax < lim;
+		if (!exact) { *fell_back = true; return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st); }
+	} else {
+		eps_rel = 1.0f / 16384.0f;                                        // two-term bf16 split: < 2^-15 per product, doubled
+		eps_abs = 1e-6f * (h->tc_xnorm_max * h->tc_xnorm_max + 1e-30f);   // fp32 rounding of ||x||^2 and of the final fma
+	}
+	CUtensorMap tq;
+	if (int rc = encode_tensor_map_bf16(h, &tq, h->tc_qb.p, kd, m, TC_BM)) return rc;
+	EXPANN_CUDA(h, cudaMemsetAsync(h->tc_cnt.p, 0, m * 4 + 16, st));
+	tc_fill_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(h->tc_thr.as<float>(), 0, m, INFINITY);
+	h->stats.aux_launches++;
+	int sms = 148;
+	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+	const uint32_t qblocks = (uint32_t)((m + TC_BM - 1) / TC_BM);
+	const uint32_t total_tiles = (uint32_t)((h->n + TC_BN - 1) / TC_BN);
+	TcParams p{};
+	p.xn = h->tc_xn.as<float>();
+	p.thr = h->tc_thr.as<float>();
+	p.cand = h->tc_cand.as<uint64_t>();
+	p.cnt = h->tc_cnt.as<uint32_t>();
+	p.cap = TC_CAP;
+	p.m = (uint32_t)m;
+	p.n = (uint32_t)h->n;
+	p.kd = kd;
+	p.scale = ip ? -1.f : -2.f;
+	uint32_t tile0 = 0, chunk_tiles = TC_FIRST_ROWS / TC_BN;
+	while (tile0 < total_tiles) {
+		const uint32_t nt = std::min(chunk_tiles, total_tiles - tile0);
+		const bool last = tile0 + nt >= total_tiles;
+		// row splits: aim at >= 4 CTAs per SM-slot overall, each CTA with a few tiles to amortise the resident query tile
+		uint32_t rsplit = std::max(1u, std::min(nt, (uint32_t)((4u * sms + qblocks - 1) / qblocks)));
+		p.tile0 = tile0;
+		p.ntiles = nt;
+		p.tiles_per_cta = (nt + rsplit - 1) / rsplit;
+		rsplit = (nt + p.tiles_per_cta - 1) / p.tiles_per_cta;
+		dim3 grid(qblocks, rsplit);
+		cudaEvent_t t0 = timing_begin(h, st);
+		int rc = h->tc_mode == 1 ? launch_filter<TC_NSTAGE_EXACT>(h, tq, p, grid, st) : launch_filter<TC_NSTAGE_SPLIT>(h, tq, p, grid, st);
+		timing_end(h, t0, st);
+		if (rc) return rc;
+		h->stats.tc_launches++;
+		const unsigned sb = (unsigned)((m + 3) / 4);
+		if (k <= 32)
+			tc_select_kernel<1><<<sb, 128, 0, st>>>(p.cand, p.cnt, TC_CAP, p.m, (uint32_t)k, h->tc_qn.as<float>(), eps_rel, eps_abs,
+			                                        h->tc_xnorm_max, h->tc_thr.as<float>(), flags, last ? 1 : 0, TC_PAD);
+		else
+			tc_select_kernel<4><<<sb, 128, 0, st>>>(p.cand, p.cnt, TC_CAP, p.m, (uint32_t)k, h->tc_qn.as<float>(), eps_rel, eps_abs,
+			                                        h->tc_xnorm_max, h->tc_thr.as<float>(), flags, last ? 1 : 0, TC_PAD);
+		EXPANN_CUDA(h, cudaGetLastError());
+		h->stats.aux_launches++;
+		tile0 += nt;
+		if (tile0 >= 2 * (TC_FIRST_ROWS / TC_BN)) chunk_tiles *= 2; // 2048, 2048, 4096, 8192, ...
+	}
+	// K4: exact fp32 keys of the survivors, (key, id) order, truncate to k
+	RerankParams r{};
+	r.base = h->base;
+	r.queries = d_q;
+	r.cand = h->tc_cand.as<uint64_t>();
+	r.cand_stride = TC_CAP;
+	r.out_keys = d_keys_out;
+	r.m = (uint32_t)m;
+	r.k = (uint32_t)k;
+	r.kp = TC_PAD;
+	r.d_pad = (uint32_t)h->d_pad;
+	r.id_add = (uint32_t)h->cfg.id_offset;
+	r.metric = ip ? 1 : 0;
+	const size_t smem = ((size_t)h->d_pad * 4 + GS_MAXNB * 8) * 4;
+	const unsigned blocks = (unsigned)((m + 3) / 4);
+	if (k <= 32) {
+		EXPANN_CUDA(h, cudaFuncSetAttribute(rerank_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		rerank_kernel<1><<<blocks, 128, smem, st>>>(r);
+	} else {
+		EXPANN_CUDA(h, cudaFuncSetAttribute(rerank_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		rerank_kernel<4><<<blocks, 128, smem, st>>>(r);
+	}
+	EXPANN_CUDA(h, cudaGetLastError());
+	h->stats.aux_launches++;
+	// overflow check (needs the flag on the host): redo the batch with the SIMT scan if any buffer overflowed
+	uint32_t unsafe = 0;
+	EXPANN_CUDA(h, cudaMemcpyAsync(&unsafe, flags, 4, cudaMemcpyDeviceToHost, st));
+	EXPANN_CUDA(h, cudaStreamSynchronize(st));
+	if (unsafe) {
+		*fell_back = true;
+		h->stats.tc_fallbacks++;
+		return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st);
+	}
+	return EXPANN_OK;
+}
+
+// entry used by the brute-force engine for large batches
+int launch_scan_tc(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st) {
+	for (size_t q0 = 0; q0 < m; q0 += TC_QBATCH) {
+		const size_t mb = std::min<size_t>(TC_QBATCH, m - q0);
+		bool fb = false;
+		if (int rc = tc_batch(h, d_q + q0 * h->d_pad, mb, k, d_keys_out + q0 * k, st, &fb)) return rc;
+	}
+	h->stats.last_qtile = TC_BM;
+	h->stats.last_nsplit = 0;
+	return EXPANN_OK;
+}
+
+} // namespace expann

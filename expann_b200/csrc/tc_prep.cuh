@@ -1,0 +1,123 @@
+// Operand preparation and threshold maintenance for K3 (tc_filter.cuh).
+#pragma once
+#include <cuda_bf16.h>
+#include "common.cuh"
+
+namespace expann {
+
+// per-launch statistics of converted values: [0] min (orderable), [1] max (orderable), [2] non-integer/non-bf16 flag,
+// [3] max row norm^2 (orderable)
+struct TcStats { uint32_t vmin, vmax, inexact, nmax; };
+
+// fp32 rows -> bf16 operand rows (one warp per row).
+//   mode 1 (exact): dst[kd] = bf16(x), zero padded
+//   mode 2 (split): seg = kd/3; base rows [xh | xl | xh], query rows [qh | qh | ql] with x = xh + xl (+ residual)
+// also: norm2[row] = sum x^2 (fp32), value statistics for the exactness decision.
+__global__ void tc_convert_kernel(const float* __restrict__ src, size_t src_stride, uint32_t d, size_t rows,
+                                  __nv_bfloat16* __restrict__ dst, uint32_t kd, int mode, int is_query,
+                                  float* __restrict__ norm2, TcStats* __restrict__ stats) {
+	const size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	const int lane = threadIdx.x & 31;
+	if (row >= rows) return;
+	const float* x = src + row * src_stride;
+	__nv_bfloat16* o = dst + row * kd;
+	const uint32_t seg = mode == 2 ? kd / 3 : kd;
+	float s = 0.f, mn = 3.4e38f, mx = -3.4e38f;
+	uint32_t bad = 0;
+	for (uint32_t i = lane; i < seg; i += 32) {
+		const float v = i < d ? x[i] : 0.f;
+		const __nv_bfloat16 h = __float2bfloat16_rn(v);
+		const float hf = __bfloat162float(h);
+		if (mode == 2) {
+			const __nv_bfloat16 l = __float2bfloat16_rn(v - hf);
+			o[i] = h;
+			o[seg + i] = is_query ? h : l;
+			o[2 * seg + i] = is_query ? l : h;
+		} else
+			o[i] = h;
+		if (i < d) {
+			s = fmaf(v, v, s);
+			mn = fminf(mn, v);
+			mx = fmaxf(mx, v);
+			bad |= (hf != v) || (v != rintf(v));
+		}
+	}
+#pragma unroll
+	for (int of = 16; of >= 1; of >>= 1) {
+		s += __shfl_xor_sync(FULL, s, of);
+		mn = fminf(mn, __shfl_xor_sync(FULL, mn, of));
+		mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, of));
+		bad |= __shfl_xor_sync(FULL, bad, of);
+	}
+	if (lane == 0) {
+		if (norm2) norm2[row] = s;
+		if (stats) {
+			atomicMin(&stats->vmin, f32_orderable(mn));
+			atomicMax(&stats->vmax, f32_orderable(mx));
+			if (bad) atomicOr(&stats->inexact, 1u);
+			atomicMax(&stats->nmax, f32_orderable(s));
+		}
+	}
+}
+
+__global__ void tc_fill_kernel(float* p, size_t from, size_t to, float v) {
+	const size_t i = from + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < to) p[i] = v;
+}
+
+// After a chunk of rows: per query, k-th smallest a' among the buffered candidates -> new threshold
+//   thr = a'_k + 2*eps(q)   (every true top-k row has a' <= thr, see tc.cu), buffer compacted to a' <= thr.
+// flags[0] counts queries whose buffer overflowed (result not guaranteed -> caller falls back to the SIMT scan).
+// final != 0: additionally pads the buffer with KEY_EMPTY up to `pad` entries for the re-rank kernel and flags
+// queries with more than `pad` survivors.
+template <int LPL>
+__global__ void __launch_bounds__(128) tc_select_kernel(uint64_t* __restrict__ cand, uint32_t* __restrict__ cnt, uint32_t cap,
+                                                         uint32_t m, uint32_t k, const float* __restrict__ qnorm2, float eps_rel,
+                                                         float eps_abs, float xnorm_max, float* __restrict__ thr,
+                                                         uint32_t* __restrict__ flags, int final, uint32_t pad) {
+	const int lane = threadIdx.x & 31;
+	const uint32_t q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (q >= m) return;
+	uint64_t* buf = cand + (size_t)q * cap;
+	uint32_t c = cnt[q];
+	if (c > cap) {
+		if (lane == 0) atomicAdd(flags, 1u);
+		c = cap;
+	}
+	WarpList<LPL> best;
+	best.init();
+	uint64_t tk = KEY_EMPTY;
+	for (uint32_t i0 = 0; i0 < c; i0 += 32) {
+		const uint64_t key = i0 + lane < c ? buf[i0 + lane] : KEY_EMPTY;
+		unsigned mask = __ballot_sync(FULL, key < tk);
+		while (mask) {
+			const int src = __ffs(mask) - 1;
+			mask &= mask - 1;
+			const uint64_t kk = shfl_u64(key, src);
+			if (kk < tk) { best.insert(kk, lane); tk = best.at(k - 1); }
+		}
+	}
+	float t = __int_as_float(0x7f800000);
+	if (tk != KEY_EMPTY) {
+		const float eps = eps_rel * sqrtf(qnorm2[q]) * xnorm_max + eps_abs;
+		t = key_dist(tk) + 2.f * eps;
+		if (eps > 0.f) t = nextafterf(t, __int_as_float(0x7f800000)); // round the bound up
+	}
+	// compact in place (reads run ahead of writes)
+	uint32_t w = 0;
+	for (uint32_t i0 = 0; i0 < c; i0 += 32) {
+		const uint64_t key = i0 + lane < c ? buf[i0 + lane] : KEY_EMPTY;
+		const bool keep = key != KEY_EMPTY && key_dist(key) <= t;
+		const unsigned mk = __ballot_sync(FULL, keep);
+		__syncwarp();
+		if (keep) buf[w + __popc(mk & ((1u << lane) - 1))] = key;
+		w += __popc(mk);
+	}
+	if (final) {
+		for (uint32_t i = w + lane; i < pad; i += 32) buf[i] = KEY_EMPTY;
+		if (w > pad && lane == 0) atomicAdd(flags, 1u);
+	}
+	if (lane == 0) { cnt[q] = w; thr[q] = t; }
+}
+
+} // namespace expann

@@ -48,7 +48,9 @@ typedef struct expann_gpu_stats {
 	uint64_t last_nsplit, last_qtile;
 	uint64_t distcomps; /* RECORD_STATS num_distcomps analogue (src/antitopo_engine.h:125-129), graph engine */
 	uint64_t hot_time_ns, hot_timed_launches; /* CUDA-event time of the dominant kernel, see expann_gpu_set_timing */
-	uint64_t reserved[6];
+	uint64_t tc_launches, tc_fallbacks;       /* tensor-core filter launches; batches redone by the SIMT scan */
+	uint64_t tc_mode;                         /* 0 off, 1 bf16-exact, 2 two-term bf16 split (decided by build()) */
+	uint64_t reserved[3];
 } expann_gpu_stats_t;
 
 /* ann_engine() / Engine(config) constructor — src/ann_engine.h:17, src/bench_runner.h:33 */
@@ -114,7 +116,8 @@ int expann_gpu_pair_distances(int device, int kind, const void* a, const void* b
 int expann_gpu_set_timing(expann_gpu_t* h, int on);
 int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
 /* tuning knobs by name (the reference exposes its knobs as Engine::config members, src/bench_runner.h:133-172):
- * "qtile" (0 auto | 1 | 4 | 8), "nsplit" (0 auto | forced row splits per scan), "kprime" (QUANT_SCAN: survivors
+ * "qtile" (0 auto | 1 | 4 | 8), "nsplit" (0 auto | forced row splits per scan), "tc" (0/1: tensor-core candidate filter for large
+ * batches, must be set before build()), "tc_min_batch" (default 512), "kprime" (QUANT_SCAN: survivors
  * re-ranked in fp32, 0 auto = min(128, 10k)). Unknown names: EXPANN_ERR_ARG. */
 int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value);
 /* library build info: "sm_100a;..." */

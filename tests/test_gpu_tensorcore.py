@@ -1,0 +1,92 @@
+"""GPU parity: K3 tensor-core candidate filter (tcgen05) + K4 fp32 rerank must give the SAME answer as the exact scan.
+Large query batches (m >= tc_min_batch) take this path; smaller ones the SIMT scan."""
+import numpy as np
+import pytest
+
+from tests.util import assert_topk_parity
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ex():
+    import expann_b200
+    return expann_b200
+
+
+def run(ex, base, q, k, metric=0, tc=1, id_offset=0):
+    e = ex.BruteForceEngine(metric=metric, id_offset=id_offset)
+    e.set_option("tc", tc)
+    e.store_many_vectors(base)
+    e.build()
+    out = e.query_k_batch(q, k)
+    st = e.stats()
+    e.close()
+    return out + (st,)
+
+
+@pytest.mark.parametrize("metric", [0, 1])
+def test_exact_mode_u8_bit_identical(ex, oracle, metric):
+    rng = np.random.default_rng(1 + metric)
+    base = rng.integers(0, 256, (20011, 128)).astype(np.float32)   # ragged n (not a multiple of the 256-row tile)
+    q = rng.integers(0, 256, (777, 128)).astype(np.float32)        # ragged m (not a multiple of the 128-query tile)
+    ids, dists, counts, st = run(ex, base, q, 10, metric=metric)
+    assert st["tc_mode"] == 1 and st["tc_launches"] > 0 and st["tc_fallbacks"] == 0
+    oi, od, oc = oracle.bf_query(base, q, 10, metric=metric, threads=16)
+    assert np.array_equal(counts, oc)
+    assert_topk_parity(ids, dists, oi, od, base, q, exact=True, tag=f"tc exact metric{metric}")
+    # and identical to the SIMT path of the same library
+    ids2, dists2, _, st2 = run(ex, base, q, 10, metric=metric, tc=0)
+    assert st2["tc_launches"] == 0
+    assert np.array_equal(ids, ids2) and np.array_equal(dists, dists2)
+
+
+@pytest.mark.parametrize("d", [128, 96, 20])
+def test_split_mode_real_valued(ex, oracle, d):
+    rng = np.random.default_rng(d)
+    base = rng.standard_normal((30000, d)).astype(np.float32)
+    q = rng.standard_normal((600, d)).astype(np.float32)
+    for metric in (0, 1):
+        ids, dists, counts, st = run(ex, base, q, 10, metric=metric)
+        assert st["tc_mode"] == 2 and st["tc_launches"] > 0 and st["tc_fallbacks"] == 0
+        oi, od, oc = oracle.bf_query(base, q, 10, metric=metric, threads=16)
+        swaps = assert_topk_parity(ids, dists, oi, od, base, q, metric="ip" if metric else "l2", tag=f"tc split d{d}")
+        assert swaps <= 4
+
+
+def test_k100_and_duplicates(ex, oracle):
+    rng = np.random.default_rng(5)
+    pool = rng.integers(0, 256, (300, 64)).astype(np.float32)
+    base = pool[rng.integers(0, 300, 9000)]                       # heavy exact duplicates: ties broken by id
+    q = rng.integers(0, 256, (520, 64)).astype(np.float32)
+    for k in (1, 10, 100):
+        ids, dists, counts, st = run(ex, base, q, k)
+        assert st["tc_launches"] > 0
+        oi, od, _ = oracle.bf_query(base, q, k, threads=16)
+        assert_topk_parity(ids, dists, oi, od, base, q, exact=True, tag=f"k{k}")
+
+
+def test_adversarial_order_falls_back(ex, oracle):
+    """rows sorted from far to near: every row beats the running threshold, the candidate buffers overflow, the
+    batch is redone by the SIMT scan — the answer must still be exact"""
+    rng = np.random.default_rng(6)
+    base = rng.integers(0, 256, (40000, 32)).astype(np.float32)
+    c = np.rint(base.mean(0))
+    order = np.argsort(-((base - c) ** 2).sum(1))
+    base = np.ascontiguousarray(base[order])
+    q = np.ascontiguousarray(np.tile(c, (512, 1)) + rng.integers(-2, 3, (512, 32))).astype(np.float32)
+    ids, dists, counts, st = run(ex, base, q, 10)
+    oi, od, _ = oracle.bf_query(base, q, 10, threads=16)
+    assert_topk_parity(ids, dists, oi, od, base, q, exact=True, tag="adversarial")
+    assert st["tc_launches"] > 0
+
+
+def test_shard_offset_and_small_batches(ex, oracle):
+    rng = np.random.default_rng(7)
+    base = rng.integers(0, 256, (5000, 128)).astype(np.float32)
+    q = rng.integers(0, 256, (600, 128)).astype(np.float32)
+    ids, dists, _, st = run(ex, base, q, 10, id_offset=1000)
+    oi, od, _ = oracle.bf_query(base, q, 10, threads=16)
+    assert np.array_equal(ids, oi + np.uint64(1000)) and np.array_equal(dists, od)
+    ids, dists, _, st = run(ex, base, q[:100], 10)      # below tc_min_batch: SIMT path
+    assert st["tc_launches"] == 0 and np.array_equal(ids, oi[:100])
