@@ -31,6 +31,25 @@ __device__ __forceinline__ void gather_negdot_f32(const float* __restrict__ base
 	__syncwarp();
 }
 
+// Ranking key of one row with the SAME association as scan_topk_f32_kernel (scan_f32.cuh): two running sums, even
+// elements in one and odd elements in the other (the packed f32x2 accumulator of the scan), added at the end. With
+// this the tensor-core path (K3 filter + this re-rank) returns bit-identical keys to the SIMT scan on any data.
+__device__ __forceinline__ float scan_order_key(const float* __restrict__ row, const float* qsm, uint32_t d_pad, int metric) {
+	float lo = 0.f, hi = 0.f;
+	for (uint32_t i = 0; i < d_pad; i += 4) {
+		const float4 x = ldg128f(row + i);
+		const float4 q = *reinterpret_cast<const float4*>(qsm + i);
+		if (metric == 0) {
+			const float d0 = q.x - x.x, d1 = q.y - x.y, d2 = q.z - x.z, d3 = q.w - x.w;
+			lo = fmaf(d0, d0, lo); hi = fmaf(d1, d1, hi); lo = fmaf(d2, d2, lo); hi = fmaf(d3, d3, hi);
+		} else {
+			lo = fmaf(q.x, x.x, lo); hi = fmaf(q.y, x.y, hi); lo = fmaf(q.z, x.z, lo); hi = fmaf(q.w, x.w, hi);
+		}
+	}
+	const float s = lo + hi;
+	return metric == 0 ? s : -s;
+}
+
 struct RerankParams {
 	const float* base;      // [n][d_pad]
 	const float* queries;   // [m][d_pad]
@@ -38,6 +57,7 @@ struct RerankParams {
 	uint64_t* out_keys;     // [m][k]
 	uint32_t m, k, kp, cand_stride, d_pad, id_add; // kp entries are read from each query's cand_stride-strided list
 	int metric;
+	int scan_order; // 1: scan_order_key (lane per candidate) instead of the 8-lane team reduction
 };
 
 template <int LPL> __global__ void __launch_bounds__(128) rerank_kernel(const RerankParams p) {
@@ -59,7 +79,10 @@ template <int LPL> __global__ void __launch_bounds__(128) rerank_kernel(const Re
 		cnt += __popc(mk);
 	}
 	__syncwarp();
-	if (p.metric == 0) gather_dist_f32(p.base, p.d_pad, qsm, ids, dist, cnt, lane);
+	if (p.scan_order) {
+		for (int i = lane; i < cnt; i += 32) dist[i] = scan_order_key(p.base + (size_t)ids[i] * p.d_pad, qsm, p.d_pad, p.metric);
+		__syncwarp();
+	} else if (p.metric == 0) gather_dist_f32(p.base, p.d_pad, qsm, ids, dist, cnt, lane);
 	else gather_negdot_f32(p.base, p.d_pad, qsm, ids, dist, cnt, lane);
 	WarpList<LPL> fin;
 	fin.init();

@@ -11,9 +11,11 @@
 #include "engine.h"
 #include "rerank.cuh"
 #include "tc_filter.cuh"
+#include "tc_filter2.cuh"
 #include "tc_prep.cuh"
 #include <algorithm>
 #include <cmath>
+#include <cstring>
 
 namespace expann {
 
@@ -22,10 +24,15 @@ int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, ui
 
 constexpr uint32_t TC_CAP = 4096, TC_FIRST_ROWS = 2048, TC_PAD = 256, TC_QBATCH = 16384;
 constexpr int TC_NSTAGE_EXACT = 4, TC_NSTAGE_SPLIT = 3;
+// second form (tc_filter2.cuh): per-(query, split) candidate buffers of TC2_CAP keys, TC_PAD survivors per query
+constexpr uint32_t TC2_CAP = 512;
+constexpr int TC2_NSTAGE = 6;
 
 static size_t tc_smem_bytes(uint32_t kd, int nstage) {
 	return 1024 + (size_t)(kd / TC_BK) * TC_A_KB_BYTES + (size_t)nstage * TC_B_STAGE_BYTES + (1 + 2 * nstage + 4) * 8 + 16;
 }
+
+static float __uint_as_float_host(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
 
 static int read_stats(expann_gpu* h, DevBuf& buf, TcStats* out, cudaStream_t st) {
 	EXPANN_CUDA(h, cudaMemcpyAsync(out, buf.p, sizeof(TcStats), cudaMemcpyDeviceToHost, st));
@@ -74,6 +81,7 @@ int tc_finalize(expann_gpu* h) {
 		EXPANN_CUDA(h, cudaMemsetAsync(h->tc_xn.p, 0, h->n * 4, st));
 	}
 	EXPANN_CUDA(h, cudaStreamSynchronize(st));
+	if (int rc = encode_tensor_map_bf16(h, &h->tmap_xb128, h->tc_xb.p, h->tc_kd, h->n, TC2_TN)) return rc;
 	return encode_tensor_map_bf16(h, &h->tmap_xb, h->tc_xb.p, h->tc_kd, h->n, TC_BN);
 }
 
@@ -175,6 +183,7 @@ static int tc_batch(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 	r.d_pad = (uint32_t)h->d_pad;
 	r.id_add = (uint32_t)h->cfg.id_offset;
 	r.metric = ip ? 1 : 0;
+	r.scan_order = 1;
 	const size_t smem = ((size_t)h->d_pad * 4 + GS_MAXNB * 8) * 4;
 	const unsigned blocks = (unsigned)((m + 3) / 4);
 	if (k <= 32) {
@@ -198,15 +207,147 @@ static int tc_batch(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 	return EXPANN_OK;
 }
 
+
+template <int NQB>
+static int launch_filter2(expann_gpu* h, const CUtensorMap& tq, const Tc2Params& p, dim3 grid, cudaStream_t st) {
+	const size_t smem = Tc2Cfg<NQB>::smem_bytes(p.kd, TC2_NSTAGE);
+	EXPANN_CUDA(h, cudaFuncSetAttribute(tc_filter2_kernel<NQB, TC2_NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	tc_filter2_kernel<NQB, TC2_NSTAGE><<<grid, Tc2Cfg<NQB>::THREADS, smem, st>>>(tq, h->tmap_xb128, p);
+	EXPANN_CUDA(h, cudaGetLastError());
+	return EXPANN_OK;
+}
+
+// row splits of the second form: whole waves of CTAs (>= 97 % of the SM slots of the last wave used), as few
+// splits as that allows (every split warms its own bound up), at least 8 tiles per CTA
+static uint32_t tc2_pick_rsplit(uint32_t qblocks, uint32_t ntiles, int sms) {
+	const uint32_t max_split = std::max(1u, std::min(64u, ntiles / 8u));
+	uint32_t best = 1;
+	double best_eff = 0.0;
+	for (uint32_t w = 1; w <= 24; ++w) {
+		uint32_t rs = (uint32_t)((uint64_t)sms * w / qblocks);
+		if (rs < 1) continue;
+		if (rs > max_split) rs = max_split;
+		const uint32_t ctas = qblocks * rs;
+		const double eff = (double)ctas / (double)((ctas + sms - 1) / sms * sms);
+		if (eff > best_eff + 1e-9) { best_eff = eff; best = rs; }
+		if (eff >= 0.97 || rs == max_split) break;
+	}
+	return best;
+}
+
+// second form of K3 (k <= 16): ONE filter launch with in-kernel bounds, one select launch, one re-rank launch
+static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st, bool* fell_back) {
+	*fell_back = false;
+	const uint32_t kd = h->tc_kd;
+	const bool ip = h->cfg.metric == EXPANN_METRIC_IP;
+	const int nqb = Tc2Cfg<2>::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024 && m > TC_BM ? 2 : 1;
+	int sms = 148;
+	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+	const uint32_t qblocks = (uint32_t)((m + TC_BM * nqb - 1) / (TC_BM * nqb));
+	const uint32_t ntiles = (uint32_t)((h->n + TC2_TN - 1) / TC2_TN);
+	uint32_t rsplit = tc2_pick_rsplit(qblocks, ntiles, sms);
+	const uint32_t tiles_per_cta = (ntiles + rsplit - 1) / rsplit;
+	rsplit = (ntiles + tiles_per_cta - 1) / tiles_per_cta;
+	EXPANN_CUDA(h, h->tc_qb.ensure(m * (size_t)kd * 2));
+	EXPANN_CUDA(h, h->tc_qn.ensure(m * 4));
+	EXPANN_CUDA(h, h->tc_gthr.ensure(m * 4));
+	EXPANN_CUDA(h, h->tc_cnt.ensure(m * (size_t)rsplit * 4 + 16));
+	EXPANN_CUDA(h, h->tc_cand.ensure(m * (size_t)rsplit * TC2_CAP * 8));
+	EXPANN_CUDA(h, h->tc_sel.ensure(m * (size_t)TC_PAD * 8 + 16));
+	uint32_t* flags = reinterpret_cast<uint32_t*>(h->tc_sel.as<uint64_t>() + m * (size_t)TC_PAD);
+	if (int rc = reset_stats(h, h->tc_qstats, st)) return rc;
+	tc_convert_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(d_q, h->d_pad, (uint32_t)h->d, m, h->tc_qb.as<__nv_bfloat16>(), kd,
+	                                                          h->tc_mode, 1, h->tc_qn.as<float>(), h->tc_qstats.as<TcStats>());
+	EXPANN_CUDA(h, cudaGetLastError());
+	h->stats.aux_launches++;
+	float eps_rel = 0.f, eps_abs = 0.f;
+	if (h->tc_mode == 1) {
+		TcStats s;
+		if (int rc = read_stats(h, h->tc_qstats, &s, st)) return rc;
+		const float lo = std::min(h->tc_xmin, f32_from_orderable(s.vmin)), hi = std::max(h->tc_xmax, f32_from_orderable(s.vmax));
+		const float amax = std::max(std::fabs(lo), std::fabs(hi));
+		const double lim = 16777216.0, dd = (double)h->d;
+		const bool exact = !s.inexact && amax <= 256.f && dd * (hi - lo) * (hi - lo) < lim && dd * amax * amax < lim;
+		if (!exact) { *fell_back = true; return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st); }
+	} else {
+		eps_rel = 1.0f / 16384.0f;
+		eps_abs = 1e-6f * (h->tc_xnorm_max * h->tc_xnorm_max + 1e-30f);
+	}
+	CUtensorMap tq;
+	if (int rc = encode_tensor_map_bf16(h, &tq, h->tc_qb.p, kd, m, TC_BM)) return rc;
+	EXPANN_CUDA(h, cudaMemsetAsync(flags, 0, 16, st));
+	tc_fill_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(h->tc_gthr.as<float>(), 0, m, __uint_as_float_host(f32_orderable(INFINITY)));
+	h->stats.aux_launches++;
+	Tc2Params p{};
+	p.xn = h->tc_xn.as<float>();
+	p.qn = h->tc_qn.as<float>();
+	p.gthr = h->tc_gthr.as<uint32_t>();
+	p.cand = h->tc_cand.as<uint64_t>();
+	p.cnt = h->tc_cnt.as<uint32_t>();
+	p.cap = TC2_CAP;
+	p.m = (uint32_t)m;
+	p.n = (uint32_t)h->n;
+	p.kd = kd;
+	p.k = (uint32_t)k;
+	p.ntiles = ntiles;
+	p.tiles_per_cta = tiles_per_cta;
+	p.rsplit = rsplit;
+	p.scale = ip ? -1.f : -2.f;
+	p.eps_rel = eps_rel;
+	p.eps_abs = eps_abs;
+	p.xnorm_max = h->tc_xnorm_max;
+	dim3 grid(qblocks, rsplit);
+	cudaEvent_t t0 = timing_begin(h, st);
+	int rc = nqb == 2 ? launch_filter2<2>(h, tq, p, grid, st) : launch_filter2<1>(h, tq, p, grid, st);
+	timing_end(h, t0, st);
+	if (rc) return rc;
+	h->stats.tc_launches++;
+	h->stats.last_qtile = TC_BM * nqb;
+	h->stats.last_nsplit = rsplit;
+	tc_select2_kernel<1><<<(unsigned)((m + 3) / 4), 128, 0, st>>>(p.cand, p.cnt, TC2_CAP, rsplit, p.m, p.k, p.qn, eps_rel, eps_abs,
+	                                                             h->tc_xnorm_max, h->tc_sel.as<uint64_t>(), TC_PAD, flags);
+	EXPANN_CUDA(h, cudaGetLastError());
+	h->stats.aux_launches++;
+	RerankParams r{};
+	r.base = h->base;
+	r.queries = d_q;
+	r.cand = h->tc_sel.as<uint64_t>();
+	r.cand_stride = TC_PAD;
+	r.out_keys = d_keys_out;
+	r.m = (uint32_t)m;
+	r.k = (uint32_t)k;
+	r.kp = TC_PAD;
+	r.d_pad = (uint32_t)h->d_pad;
+	r.id_add = (uint32_t)h->cfg.id_offset;
+	r.metric = ip ? 1 : 0;
+	r.scan_order = 1;
+	const size_t smem = ((size_t)h->d_pad * 4 + GS_MAXNB * 8) * 4;
+	EXPANN_CUDA(h, cudaFuncSetAttribute(rerank_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	rerank_kernel<1><<<(unsigned)((m + 3) / 4), 128, smem, st>>>(r);
+	EXPANN_CUDA(h, cudaGetLastError());
+	h->stats.aux_launches++;
+	uint32_t unsafe = 0;
+	EXPANN_CUDA(h, cudaMemcpyAsync(&unsafe, flags, 4, cudaMemcpyDeviceToHost, st));
+	EXPANN_CUDA(h, cudaStreamSynchronize(st));
+	if (unsafe) {
+		*fell_back = true;
+		h->stats.tc_fallbacks++;
+		return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st);
+	}
+	return EXPANN_OK;
+}
+
 // entry used by the brute-force engine for large batches
 int launch_scan_tc(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st) {
 	for (size_t q0 = 0; q0 < m; q0 += TC_QBATCH) {
 		const size_t mb = std::min<size_t>(TC_QBATCH, m - q0);
 		bool fb = false;
-		if (int rc = tc_batch(h, d_q + q0 * h->d_pad, mb, k, d_keys_out + q0 * k, st, &fb)) return rc;
+		const bool v2 = k <= TC2_KK && !h->opt_tc_v1;
+		if (int rc = v2 ? tc_batch2(h, d_q + q0 * h->d_pad, mb, k, d_keys_out + q0 * k, st, &fb)
+		                : tc_batch(h, d_q + q0 * h->d_pad, mb, k, d_keys_out + q0 * k, st, &fb))
+			return rc;
+		if (!v2 && !fb) { h->stats.last_qtile = TC_BM; h->stats.last_nsplit = 0; }
 	}
-	h->stats.last_qtile = TC_BM;
-	h->stats.last_nsplit = 0;
 	return EXPANN_OK;
 }
 

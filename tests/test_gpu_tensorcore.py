@@ -14,9 +14,10 @@ def ex():
     return expann_b200
 
 
-def run(ex, base, q, k, metric=0, tc=1, id_offset=0):
+def run(ex, base, q, k, metric=0, tc=1, id_offset=0, v1=0):
     e = ex.BruteForceEngine(metric=metric, id_offset=id_offset)
     e.set_option("tc", tc)
+    e.set_option("tc_v1", v1)   # 1: force the chunked first form of K3 (otherwise used for k > 16 only)
     e.store_many_vectors(base)
     e.build()
     out = e.query_k_batch(q, k)
@@ -90,3 +91,40 @@ def test_shard_offset_and_small_batches(ex, oracle):
     assert np.array_equal(ids, oi + np.uint64(1000)) and np.array_equal(dists, od)
     ids, dists, _, st = run(ex, base, q[:100], 10)      # below tc_min_batch: SIMT path
     assert st["tc_launches"] == 0 and np.array_equal(ids, oi[:100])
+
+
+def test_first_form_still_exact(ex, oracle):
+    """the chunked (host-refreshed threshold) form of K3 stays available for k > 16; force it for k = 10"""
+    rng = np.random.default_rng(8)
+    base = rng.integers(0, 256, (20011, 128)).astype(np.float32)
+    q = rng.integers(0, 256, (777, 128)).astype(np.float32)
+    ids, dists, counts, st = run(ex, base, q, 10, v1=1)
+    assert st["tc_launches"] > 1 and st["tc_fallbacks"] == 0
+    oi, od, _ = oracle.bf_query(base, q, 10, threads=16)
+    assert_topk_parity(ids, dists, oi, od, base, q, exact=True, tag="tc v1")
+
+
+@pytest.mark.parametrize("k", [1, 10, 16])
+def test_second_form_many_splits(ex, k):
+    """larger case: several row splits and query blocks, shared bounds between splits; must equal the SIMT scan of the
+    same library bit for bit (which the other tests pin to the oracle)"""
+    rng = np.random.default_rng(9)
+    base = rng.integers(0, 256, (300_001, 128)).astype(np.float32)
+    q = rng.integers(0, 256, (1300, 128)).astype(np.float32)
+    ids, dists, counts, st = run(ex, base, q, k)
+    assert st["tc_launches"] == 1 and st["tc_fallbacks"] == 0 and st["last_nsplit"] > 1
+    ids2, dists2, counts2, st2 = run(ex, base, q, k, tc=0)
+    assert st2["tc_launches"] == 0
+    assert np.array_equal(ids, ids2) and np.array_equal(dists, dists2) and np.array_equal(counts, counts2)
+
+
+def test_second_form_real_valued_splits(ex):
+    rng = np.random.default_rng(10)
+    base = rng.standard_normal((150_000, 96)).astype(np.float32)
+    base /= np.linalg.norm(base, axis=1, keepdims=True)
+    q = rng.standard_normal((700, 96)).astype(np.float32)
+    for metric in (0, 1):
+        ids, dists, _, st = run(ex, base, q, 10, metric=metric)
+        assert st["tc_mode"] == 2 and st["tc_launches"] == 1 and st["tc_fallbacks"] == 0
+        ids2, dists2, _, _ = run(ex, base, q, 10, metric=metric, tc=0)
+        assert np.array_equal(ids, ids2) and np.array_equal(dists, dists2)
