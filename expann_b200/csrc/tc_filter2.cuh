@@ -50,12 +50,88 @@ __device__ __forceinline__ float4 lds128f(const float* p) {
 	return v;
 }
 
+
+// per-thread (= per-query) filter state of the epilogue
+struct Tc2Thread {
+	float v[TC2_KK]; // ascending; the first 16-k slots hold -inf for good, so v[15] is the k-th smallest a' seen
+	float thr, slack;
+	uint32_t cnt, cap;
+	uint64_t* cbuf;
+};
+__device__ __forceinline__ void tc2_event(Tc2Thread& t, float aj, uint32_t row) {
+	if (t.cnt < t.cap) t.cbuf[t.cnt] = make_key(aj, row);
+	++t.cnt;
+#pragma unroll
+	for (int i = TC2_KK - 1; i >= 1; --i) t.v[i] = fminf(t.v[i], fmaxf(t.v[i - 1], aj));
+	t.v[0] = fminf(t.v[0], aj);
+	t.thr = fminf(t.thr, __fadd_ru(t.v[TC2_KK - 1], t.slack));
+}
+// 32 accumulator columns of one query: a' = xn + scale * dot, one min tree, and — only when some a' <= thr — the
+// compact slow path (values parked in shared memory so that the walk over them is a rolled loop, not 32 code copies)
+__device__ __forceinline__ void tc2_chunk(Tc2Thread& t, const uint32_t (&d)[32], const float* xs_c, float scale, float* sc, uint32_t row_c) {
+	float a[32];
+#pragma unroll
+	for (int j4 = 0; j4 < 8; ++j4) {
+		const float4 x4 = lds128f(xs_c + j4 * 4);
+		a[j4 * 4 + 0] = fmaf(scale, __uint_as_float(d[j4 * 4 + 0]), x4.x);
+		a[j4 * 4 + 1] = fmaf(scale, __uint_as_float(d[j4 * 4 + 1]), x4.y);
+		a[j4 * 4 + 2] = fmaf(scale, __uint_as_float(d[j4 * 4 + 2]), x4.z);
+		a[j4 * 4 + 3] = fmaf(scale, __uint_as_float(d[j4 * 4 + 3]), x4.w);
+	}
+	// min over the 32 values (NaN = padded row: ignored by min and by the compares)
+	float mn[11];
+#pragma unroll
+	for (int j = 0; j < 10; ++j) mn[j] = min3f(a[3 * j], a[3 * j + 1], a[3 * j + 2]);
+	mn[10] = fminf(a[30], a[31]);
+	const float m0 = min3f(mn[0], mn[1], mn[2]), m1 = min3f(mn[3], mn[4], mn[5]), m2 = min3f(mn[6], mn[7], mn[8]);
+	const float mall = min3f(min3f(m0, m1, m2), mn[9], mn[10]);
+	if (mall <= t.thr) {
+		// rare: park the 32 values in this lane's scratch column and build the hit mask without branches, then visit
+		// only the set bits (usually one). thr tightens while we go, hence the second compare.
+		const uint32_t sca = smem_u32(sc);
+		uint32_t mask = 0;
+#pragma unroll
+		for (int j = 0; j < 32; ++j) {
+			asm volatile("st.shared.f32 [%0], %1;" ::"r"(sca + j * 128), "f"(a[j]) : "memory");
+			mask |= a[j] <= t.thr ? 1u << j : 0u;
+		}
+		while (mask) {
+			const int j = __ffs(mask) - 1;
+			mask &= mask - 1;
+			float aj;
+			asm volatile("ld.shared.f32 %0, [%1];" : "=f"(aj) : "r"(sca + j * 128) : "memory");
+			if (aj <= t.thr) tc2_event(t, aj, row_c + j);
+		}
+	}
+}
+__device__ __forceinline__ void tc_ld32_nowait(uint32_t taddr, uint32_t (&v)[32]) {
+	asm volatile(
+	    "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+	    "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+	    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+	      "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+	      "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+	      "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+	    : "r"(taddr)
+	    : "memory");
+}
+// the wait names the loaded registers as in/out operands so that no use of them can be scheduled above it
+__device__ __forceinline__ void tc_wait_ld(uint32_t (&v)[32]) {
+	asm volatile("tcgen05.wait::ld.sync.aligned;"
+	             : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]), "+r"(v[9]),
+	               "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]), "+r"(v[17]), "+r"(v[18]),
+	               "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]),
+	               "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+	             :
+	             : "memory");
+}
+
 template <int NQB> struct Tc2Cfg {
 	static constexpr int EPI_WARPS = 4 * NQB;
 	static constexpr int THREADS = 32 * (EPI_WARPS + 2);
 	static constexpr int TMEM_COLS = 2 * NQB * TC2_TN; // 256 or 512
 	static size_t smem_bytes(uint32_t kd, int nstage) {
-		return 1024 + (size_t)NQB * (kd / TC_BK) * TC_A_KB_BYTES + (size_t)nstage * TC2_B_STAGE_BYTES + (size_t)EPI_WARPS * TC2_TN * 4 +
+		return 1024 + (size_t)NQB * (kd / TC_BK) * TC_A_KB_BYTES + (size_t)nstage * TC2_B_STAGE_BYTES + (size_t)EPI_WARPS * (TC2_TN * 4 + 4096) +
 		       (size_t)(1 + 2 * nstage + 4) * 8 + 16;
 	}
 };
@@ -70,7 +146,8 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 	uint8_t* smA = smem;                                            // [NQB][nkb][128 q][64 bf16]
 	uint8_t* smB = smA + (size_t)NQB * nkb * TC_A_KB_BYTES;         // [NSTAGE][128 rows][64 bf16]
 	float* xs_all = reinterpret_cast<float*>(smB + (size_t)NSTAGE * TC2_B_STAGE_BYTES); // [EPI_WARPS][128]
-	uint64_t* bars = reinterpret_cast<uint64_t*>(xs_all + Cfg::EPI_WARPS * TC2_TN);
+	float* sc_all = xs_all + Cfg::EPI_WARPS * TC2_TN;                                  // [EPI_WARPS][32][32]
+	uint64_t* bars = reinterpret_cast<uint64_t*>(sc_all + Cfg::EPI_WARPS * 1024);
 	uint64_t* a_full = bars;
 	uint64_t* full = bars + 1;
 	uint64_t* empty = full + NSTAGE;
@@ -157,69 +234,55 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 		const uint32_t qg = q0 + qb * TC_BM + quad * 32 + lane;
 		const bool qvalid = qg < p.m;
 		const float INF = __int_as_float(0x7f800000);
-		float slack = 0.f;
-		if (qvalid && (p.eps_rel > 0.f || p.eps_abs > 0.f)) slack = 2.f * (p.eps_rel * sqrtf(p.qn[qg]) * p.xnorm_max + p.eps_abs);
-		float v[TC2_KK]; // ascending; the first 16-k slots hold -inf for good, so v[15] is the k-th smallest a' seen
+		Tc2Thread t;
+		t.slack = 0.f;
+		if (qvalid && (p.eps_rel > 0.f || p.eps_abs > 0.f)) t.slack = 2.f * (p.eps_rel * sqrtf(p.qn[qg]) * p.xnorm_max + p.eps_abs);
 #pragma unroll
-		for (int j = 0; j < TC2_KK; ++j) v[j] = j < TC2_KK - (int)p.k ? -INF : INF;
-		float thr = qvalid ? INF : -INF, pub = thr; // invalid lanes never append and never publish
-		uint32_t cnt = 0;
-		uint64_t* cbuf = p.cand + ((size_t)(qvalid ? qg : 0) * p.rsplit + split) * p.cap;
+		for (int j = 0; j < TC2_KK; ++j) t.v[j] = j < TC2_KK - (int)p.k ? -INF : INF;
+		t.thr = qvalid ? INF : -INF; // invalid lanes never append and never publish
+		float pub = t.thr;
+		t.cnt = 0;
+		t.cap = p.cap;
+		t.cbuf = p.cand + ((size_t)(qvalid ? qg : 0) * p.rsplit + split) * p.cap;
 		float* xs = xs_all + warp * TC2_TN;
+		float* sc = sc_all + warp * 1024 + lane; // slow-path scratch: value j of this lane at sc[j * 32]
 		float4 xnext = make_float4(0.f, 0.f, 0.f, 0.f);
 		if (my_tiles) xnext = __ldg(reinterpret_cast<const float4*>(p.xn + (size_t)t_begin * TC2_TN) + lane);
+		uint32_t gnext = f32_orderable(INF); // bound of the other splits, fetched one tile ahead (any stale value is valid)
 		for (uint32_t lt = 0; lt < my_tiles; ++lt) {
 			const uint32_t acc = lt & 1;
 			const uint32_t row0 = (t_begin + lt) * TC2_TN;
-			if (qvalid) thr = fminf(thr, f32_from_orderable(__ldcg(p.gthr + qg)));
+			if (qvalid) {
+				t.thr = fminf(t.thr, f32_from_orderable(gnext));
+				gnext = __ldcg(p.gthr + qg);
+			}
 			__syncwarp();
-			reinterpret_cast<float4*>(xs)[lane] = xnext;
+			asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(xs) + lane * 16), "f"(xnext.x), "f"(xnext.y), "f"(xnext.z), "f"(xnext.w) : "memory");
 			__syncwarp();
 			if (lt + 1 < my_tiles) xnext = __ldg(reinterpret_cast<const float4*>(p.xn + (size_t)(row0 + TC2_TN)) + lane);
 			mbar_wait(&tm_full[acc], (lt >> 1) & 1);
 			tc_fence_after();
 			const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + (acc * NQB + qb) * TC2_TN;
-#pragma unroll 1
-			for (int c = 0; c < TC2_TN / 32; ++c) {
-				uint32_t d[32];
-				tc_ld32(tbase + c * 32, d);
-				float a[32];
-#pragma unroll
-				for (int j4 = 0; j4 < 8; ++j4) {
-					const float4 x4 = lds128f(xs + c * 32 + j4 * 4);
-					a[j4 * 4 + 0] = fmaf(p.scale, __uint_as_float(d[j4 * 4 + 0]), x4.x);
-					a[j4 * 4 + 1] = fmaf(p.scale, __uint_as_float(d[j4 * 4 + 1]), x4.y);
-					a[j4 * 4 + 2] = fmaf(p.scale, __uint_as_float(d[j4 * 4 + 2]), x4.z);
-					a[j4 * 4 + 3] = fmaf(p.scale, __uint_as_float(d[j4 * 4 + 3]), x4.w);
-				}
-				// min over the 32 values (NaN = padded row: ignored by min and by the compare below)
-				float mn[11];
-#pragma unroll
-				for (int j = 0; j < 10; ++j) mn[j] = min3f(a[3 * j], a[3 * j + 1], a[3 * j + 2]);
-				mn[10] = fminf(a[30], a[31]);
-				const float m0 = min3f(mn[0], mn[1], mn[2]), m1 = min3f(mn[3], mn[4], mn[5]), m2 = min3f(mn[6], mn[7], mn[8]);
-				const float mall = min3f(min3f(m0, m1, m2), mn[9], mn[10]);
-				if (mall <= thr) {
-#pragma unroll
-					for (int j = 0; j < 32; ++j) {
-						const float aj = a[j];
-						if (aj <= thr) {
-							if (cnt < p.cap) cbuf[cnt] = make_key(aj, row0 + c * 32 + j);
-							++cnt;
-#pragma unroll
-							for (int i = TC2_KK - 1; i >= 1; --i) v[i] = fminf(v[i], fmaxf(v[i - 1], aj));
-							v[0] = fminf(v[0], aj);
-							thr = fminf(thr, __fadd_ru(v[TC2_KK - 1], slack));
-						}
-					}
-				}
-			}
+			// 4 chunks of 32 columns; the TMEM load of chunk c+1 is in flight while chunk c is filtered
+			uint32_t dA[32], dB[32];
+			tc_ld32_nowait(tbase, dA);
+			tc_wait_ld(dA);
+			tc_ld32_nowait(tbase + 32, dB);
+			tc2_chunk(t, dA, xs, p.scale, sc, row0);
+			tc_wait_ld(dB);
+			tc_ld32_nowait(tbase + 64, dA);
+			tc2_chunk(t, dB, xs + 32, p.scale, sc, row0 + 32);
+			tc_wait_ld(dA);
+			tc_ld32_nowait(tbase + 96, dB);
+			tc2_chunk(t, dA, xs + 64, p.scale, sc, row0 + 64);
+			tc_wait_ld(dB);
 			tc_fence_before();
 			__syncwarp();
-			if (lane == 0) mbar_arrive(&tm_empty[acc]);
-			if (thr < pub) { atomicMin(p.gthr + qg, f32_orderable(thr)); pub = thr; }
+			if (lane == 0) mbar_arrive(&tm_empty[acc]); // the accumulators are in registers now: release them early
+			tc2_chunk(t, dB, xs + 96, p.scale, sc, row0 + 96);
+			if (t.thr < pub) { atomicMin(p.gthr + qg, f32_orderable(t.thr)); pub = t.thr; }
 		}
-		if (qvalid) p.cnt[(size_t)qg * p.rsplit + split] = cnt;
+		if (qvalid) p.cnt[(size_t)qg * p.rsplit + split] = t.cnt;
 	}
 	tc_fence_before();
 	__syncthreads();
