@@ -39,6 +39,17 @@ WORKLOADS = {
 }
 
 
+def tensor_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            j = json.load(open(p))
+            return float(j["bf16_tflops"]), float(j.get("bf16_tflops_sustained", j["bf16_tflops"])), "measured (MEASURED_PEAKS.json, cuBLAS bf16)"
+        except Exception:  # noqa: BLE001
+            pass
+    return 1590.0, 1400.0, "fallback (B200_PROFILING.md)"
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -121,6 +132,40 @@ def cpu_reference_qps(base, q, k, metric, budget_s=15.0):
     msample = min(msample, len(q))
     t = run(q[:msample])
     return msample / t, threads, kind, f"{msample} of {len(q)} queries, full {base.shape[0]}x{d} base, {threads} threads, {t:.1f}s"
+
+
+def scan_hbm_leg(eng, torch, dq, k, n_rows, d, stream, peak, peak_src, steps):
+    """HBM-bound regime of the path: ONE pass of the streaming fp32 scan (K1) over the base for a tile of 8 queries
+    (the brute_force_engine per-query loop, src/brute_force_engine.h:29-46, batched 8 wide). L2 is flushed between
+    iterations (256 MB write) so every pass streams the base from DRAM."""
+    m8 = 8
+    keys = torch.empty((m8, k), dtype=torch.int64, device=dq.device)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dq.device)
+    for _ in range(3):
+        eng.query_device(dq.data_ptr(), m8, k, keys.data_ptr(), stream)
+    torch.cuda.synchronize()
+    s0 = eng.stats()
+    eng.set_timing(True)
+    whole = []
+    for _ in range(max(5, steps)):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        eng.query_device(dq.data_ptr(), m8, k, keys.data_ptr(), stream)
+        e1.record()
+        torch.cuda.synchronize()
+        whole.append(e0.elapsed_time(e1))
+    s1 = eng.stats()
+    eng.set_timing(False)
+    hot_ms = (s1["hot_time_ns"] - s0["hot_time_ns"]) / 1e6 / max(1, s1["hot_timed_launches"] - s0["hot_timed_launches"])
+    alg = n_rows * d * 4
+    call_ms = float(np.median(whole))
+    return {"workload": "one pass of the fp32 scan over the %dx%d base for 8 queries (L2 flushed between passes)" % (n_rows, d),
+            "qps": m8 / (call_ms * 1e-3), "ms_per_pass_call": call_ms, "qtile": int(s1["last_qtile"]), "nsplit": int(s1["last_nsplit"]),
+            "roofline": {"bound": "hbm", "kernel": "scan_topk_f32_kernel", "achieved": alg / (hot_ms * 1e-3) / 1e9, "peak": peak,
+                         "unit": "GB/s", "frac": alg / (hot_ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": int(alg), "kernel_ms_per_launch": hot_ms,
+                         "frac_whole_call": alg / (call_ms * 1e-3) / 1e9 / peak}}
 
 
 _REAL_STDOUT = None
@@ -285,16 +330,38 @@ def main():
 
     if rank == 0:
         peak, peak_src = peaks()
-        launches = sum(st1[x] - st0[x] for x in ("scan_launches", "merge_launches", "graph_launches", "aux_launches"))
+        launches = sum(st1[x] - st0[x] for x in ("scan_launches", "merge_launches", "graph_launches", "aux_launches", "tc_launches"))
         hot_ms = (st1["hot_time_ns"] - st0["hot_time_ns"]) / 1e6 / max(1, st1["hot_timed_launches"] - st0["hot_timed_launches"])
         qt = st1["last_qtile"]
-        passes = (m + qt - 1) // qt
-        alg_bytes = passes * (hi - lo) * d * 4
-        achieved = alg_bytes / (hot_ms * 1e-3) / 1e9
+        used_tc = st1["tc_launches"] > st0["tc_launches"] and st1["tc_fallbacks"] == st0["tc_fallbacks"]
+        if used_tc:
+            # K3: bf16 tcgen05 GEMM of a'(q,x) over the whole shard; flops = 2 * m * n_shard * kd (kd = operand row length:
+            # d rounded up to 64 in the bf16-exact mode, 3x that in the two-term split mode)
+            seg = (d + 63) // 64 * 64
+            kd = seg if st1["tc_mode"] == 1 else 3 * seg
+            flops = 2.0 * m * (hi - lo) * kd
+            achieved = flops / (hot_ms * 1e-3) / 1e12
+            tpeak, tpeak_sus, tsrc = tensor_peaks()
+            roof = {"bound": "tensor", "kernel": "tc_filter2_kernel (tcgen05.mma bf16, fp32 accumulate in TMEM)", "achieved": achieved,
+                    "peak": tpeak, "unit": "TFLOP/s", "frac": achieved / tpeak, "frac_of_sustained_peak": achieved / tpeak_sus,
+                    "traffic": None, "peak_source": tsrc, "algorithmic_flops_per_launch": flops, "kernel_ms_per_launch": hot_ms,
+                    "tc_mode": "bf16-exact" if st1["tc_mode"] == 1 else "two-term bf16 split", "kd": kd,
+                    "note": "flops = 2*m*n*kd of the candidate filter; survivors (about k per query) are re-ranked in fp32 by K4. "
+                            "peak = cuBLAS bf16 burst figure; frac_of_sustained_peak uses the seconds-long figure"}
+        else:
+            passes = (m + qt - 1) // qt
+            alg_bytes = passes * (hi - lo) * d * 4
+            achieved = alg_bytes / (hot_ms * 1e-3) / 1e9
+            roof = {"bound": "hbm", "kernel": "scan_topk_f32_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": int(alg_bytes), "kernel_ms_per_launch": hot_ms,
+                    "note": "algorithmic bytes = ceil(m/qtile) passes x shard bytes (SURVEY 8(d)); CTAs of one "
+                            "wave share rows through L2, so DRAM traffic is lower than this figure"}
         out = {"metric": "QPS (exact brute-force top-%d)" % k, "value": m * args.steps / (ms * 1e-3), "unit": "queries/s",
                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                "config": {"workload": desc, "n": n, "m": m, "d": d, "k": k, "metric": metric, "qtile": int(qt),
+                          "path": "K3 tcgen05 filter + K4 fp32 rerank" if used_tc else "K1 fp32 SIMT scan",
                           "nsplit": int(st1["last_nsplit"]), "rows_per_gpu": hi - lo,
                           "l2": "base shard (%.0f MB) %s L2 (126 MB); no explicit flush" % ((hi - lo) * d * 4 / 1e6, "larger than" if (hi - lo) * d * 4 > 126e6 else "fits in"),
                           "parallelism": "base rows sharded x%d, NCCL all-gather of [m][k] keys + K7 merge" % world if world > 1 else "single GPU"},
@@ -302,16 +369,17 @@ def main():
                        "d2h_bytes_per_step": int(m * k * 8 + (m * k * 4 + m * 8 if world == 1 else 0)),
                        "api": "expann_gpu_query (host buffers)" if world == 1 else "pinned H2D + query_device + all_gather + merge + decode + D2H"},
                "gpu_launches": int(launches),
-               "roofline": {"bound": "hbm", "kernel": "scan_topk_f32_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                            "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                            "algorithmic_bytes_per_launch": int(alg_bytes), "kernel_ms_per_launch": hot_ms,
-                            "note": "algorithmic bytes = ceil(m/qtile) passes x shard bytes (SURVEY 8(d)); CTAs of one "
-                                    "wave share rows through L2, so DRAM traffic is lower than this figure"},
+               "roofline": roof,
                "clocks": clocks}
         if not args.no_cpu and world == 1:
             qps, cores, kind, sample = cpu_reference_qps(base, q, k, metric)
             out["cpu_baseline"] = {"value": qps, "unit": "queries/s", "cores": cores, "kind": kind, "sample": sample}
         out["check"] = {"first_ids": got[0].tolist()}
+        if world == 1 and not args.no_extras:
+            try:
+                out["scan_hbm"] = scan_hbm_leg(eng, torch, dq, k, hi - lo, d, stream, peak, peak_src, args.steps)
+            except Exception as ex:  # noqa: BLE001
+                out["scan_hbm"] = {"error": repr(ex)[:300]}
     eng.close()
     del eng
     if rank == 0:

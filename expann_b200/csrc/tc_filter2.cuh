@@ -39,6 +39,11 @@ struct Tc2Params {
 __device__ __forceinline__ uint32_t tc2_instr_desc() { // kind::f16, bf16 x bf16 -> fp32, K-major A and B, M = 128, N = 128
 	return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC2_TN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
 }
+__device__ __forceinline__ bool elect_one() {
+	uint32_t pred;
+	asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.b32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+	return pred != 0;
+}
 __device__ __forceinline__ float min3f(float a, float b, float c) {
 	float r;
 	asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
@@ -66,42 +71,60 @@ __device__ __forceinline__ void tc2_event(Tc2Thread& t, float aj, uint32_t row) 
 	t.v[0] = fminf(t.v[0], aj);
 	t.thr = fminf(t.thr, __fadd_ru(t.v[TC2_KK - 1], t.slack));
 }
-// 32 accumulator columns of one query: a' = xn + scale * dot, one min tree, and — only when some a' <= thr — the
-// compact slow path (values parked in shared memory so that the walk over them is a rolled loop, not 32 code copies)
-__device__ __forceinline__ void tc2_chunk(Tc2Thread& t, const uint32_t (&d)[32], const float* xs_c, float scale, float* sc, uint32_t row_c) {
-	float a[32];
+__device__ __forceinline__ uint64_t pack_b64(uint32_t lo, uint32_t hi) {
+	uint64_t r;
+	asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+	return r;
+}
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) {
+	asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c) {
+	uint64_t r;
+	asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+	return r;
+}
+// 32 accumulator columns of one query: a'[j] = xn[j] + scale * dot[j] (packed FFMA2; bit-identical to fmaf per element)
+__device__ __forceinline__ void tc2_values(const uint32_t (&d)[32], const float* xs_c, uint64_t scale2, float (&a)[32]) {
 #pragma unroll
 	for (int j4 = 0; j4 < 8; ++j4) {
 		const float4 x4 = lds128f(xs_c + j4 * 4);
-		a[j4 * 4 + 0] = fmaf(scale, __uint_as_float(d[j4 * 4 + 0]), x4.x);
-		a[j4 * 4 + 1] = fmaf(scale, __uint_as_float(d[j4 * 4 + 1]), x4.y);
-		a[j4 * 4 + 2] = fmaf(scale, __uint_as_float(d[j4 * 4 + 2]), x4.z);
-		a[j4 * 4 + 3] = fmaf(scale, __uint_as_float(d[j4 * 4 + 3]), x4.w);
+		const uint64_t r0 = fma_f32x2(scale2, pack_b64(d[j4 * 4 + 0], d[j4 * 4 + 1]), pack_b64(__float_as_uint(x4.x), __float_as_uint(x4.y)));
+		const uint64_t r1 = fma_f32x2(scale2, pack_b64(d[j4 * 4 + 2], d[j4 * 4 + 3]), pack_b64(__float_as_uint(x4.z), __float_as_uint(x4.w)));
+		unpack_f32x2(r0, a[j4 * 4 + 0], a[j4 * 4 + 1]);
+		unpack_f32x2(r1, a[j4 * 4 + 2], a[j4 * 4 + 3]);
 	}
-	// min over the 32 values (NaN = padded row: ignored by min and by the compares)
+}
+// pass 1 of a chunk: only the minimum of its 32 values (NaN = padded row: ignored by min and by every compare)
+__device__ __forceinline__ float tc2_chunk_min(const uint32_t (&d)[32], const float* xs_c, uint64_t scale2) {
+	float a[32];
+	tc2_values(d, xs_c, scale2, a);
 	float mn[11];
 #pragma unroll
 	for (int j = 0; j < 10; ++j) mn[j] = min3f(a[3 * j], a[3 * j + 1], a[3 * j + 2]);
 	mn[10] = fminf(a[30], a[31]);
 	const float m0 = min3f(mn[0], mn[1], mn[2]), m1 = min3f(mn[3], mn[4], mn[5]), m2 = min3f(mn[6], mn[7], mn[8]);
-	const float mall = min3f(min3f(m0, m1, m2), mn[9], mn[10]);
-	if (mall <= t.thr) {
-		// rare: park the 32 values in this lane's scratch column and build the hit mask without branches, then visit
-		// only the set bits (usually one). thr tightens while we go, hence the second compare.
-		const uint32_t sca = smem_u32(sc);
-		uint32_t mask = 0;
+	return min3f(min3f(m0, m1, m2), mn[9], mn[10]);
+}
+// pass 2 (rare): a chunk known to hold some a' <= thr. The values are parked in this lane's scratch column and the hit
+// mask is built without branches; only the set bits (usually one) are visited. thr tightens while we go, hence the
+// second compare.
+__device__ __forceinline__ void tc2_chunk_hits(Tc2Thread& t, const uint32_t (&d)[32], const float* xs_c, uint64_t scale2, float* sc, uint32_t row_c) {
+	float a[32];
+	tc2_values(d, xs_c, scale2, a);
+	const uint32_t sca = smem_u32(sc);
+	uint32_t mask = 0;
 #pragma unroll
-		for (int j = 0; j < 32; ++j) {
-			asm volatile("st.shared.f32 [%0], %1;" ::"r"(sca + j * 128), "f"(a[j]) : "memory");
-			mask |= a[j] <= t.thr ? 1u << j : 0u;
-		}
-		while (mask) {
-			const int j = __ffs(mask) - 1;
-			mask &= mask - 1;
-			float aj;
-			asm volatile("ld.shared.f32 %0, [%1];" : "=f"(aj) : "r"(sca + j * 128) : "memory");
-			if (aj <= t.thr) tc2_event(t, aj, row_c + j);
-		}
+	for (int j = 0; j < 32; ++j) {
+		asm volatile("st.shared.f32 [%0], %1;" ::"r"(sca + j * 128), "f"(a[j]) : "memory");
+		mask |= a[j] <= t.thr ? 1u << j : 0u;
+	}
+	while (mask) {
+		const int j = __ffs(mask) - 1;
+		mask &= mask - 1;
+		float aj;
+		asm volatile("ld.shared.f32 %0, [%1];" : "=f"(aj) : "r"(sca + j * 128) : "memory");
+		if (aj <= t.thr) tc2_event(t, aj, row_c + j);
 	}
 }
 __device__ __forceinline__ void tc_ld32_nowait(uint32_t taddr, uint32_t (&v)[32]) {
@@ -179,30 +202,38 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 	const uint32_t tmem_base = *tmem_slot;
 
 	if (warp == Cfg::EPI_WARPS) {
-		// ===================== TMA producer (one thread) =====================
-		if (lane == 0 && my_tiles) {
-			tma_prefetch_desc(&tmap_q);
-			tma_prefetch_desc(&tmap_x);
-			mbar_expect_tx(a_full, NQB * nkb * TC_A_KB_BYTES);
-			for (int qb = 0; qb < NQB; ++qb)
-				for (uint32_t kb = 0; kb < nkb; ++kb)
-					tma_load_2d(smA + ((size_t)qb * nkb + kb) * TC_A_KB_BYTES, &tmap_q, (int)(kb * TC_BK), (int)(q0 + qb * TC_BM), a_full);
+		// ===================== TMA producer =====================
+		// The whole warp walks the loop converged and one elected lane issues: ptxas then emits the uniform-datapath
+		// instructions (UTMALDG, UTCHMMA, UTCBAR) directly instead of an ELECT / BRA.U.ANY loop around each of them.
+		if (my_tiles) {
+			if (elect_one()) {
+				tma_prefetch_desc(&tmap_q);
+				tma_prefetch_desc(&tmap_x);
+				mbar_expect_tx(a_full, NQB * nkb * TC_A_KB_BYTES);
+				for (int qb = 0; qb < NQB; ++qb)
+					for (uint32_t kb = 0; kb < nkb; ++kb)
+						tma_load_2d(smA + ((size_t)qb * nkb + kb) * TC_A_KB_BYTES, &tmap_q, (int)(kb * TC_BK), (int)(q0 + qb * TC_BM), a_full);
+			}
+			__syncwarp();
 			uint32_t it = 0;
 			for (uint32_t lt = 0; lt < my_tiles; ++lt) {
 				const uint32_t row = (t_begin + lt) * TC2_TN;
 				for (uint32_t kb = 0; kb < nkb; ++kb, ++it) {
 					const uint32_t s = it % NSTAGE, use = it / NSTAGE;
 					if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
-					mbar_expect_tx(&full[s], TC2_B_STAGE_BYTES);
-					tma_load_2d(smB + (size_t)s * TC2_B_STAGE_BYTES, &tmap_x, (int)(kb * TC_BK), (int)row, &full[s]);
+					if (elect_one()) {
+						mbar_expect_tx(&full[s], TC2_B_STAGE_BYTES);
+						tma_load_2d(smB + (size_t)s * TC2_B_STAGE_BYTES, &tmap_x, (int)(kb * TC_BK), (int)row, &full[s]);
+					}
+					__syncwarp();
 				}
 			}
 		}
 	} else if (warp == Cfg::EPI_WARPS + 1) {
-		// ===================== MMA issuer (one thread) =====================
-		if (lane == 0 && my_tiles) {
+		// ===================== MMA issuer (converged warp, one elected lane issues) =====================
+		if (my_tiles) {
 			const uint32_t idesc = tc2_instr_desc();
-			const uint32_t a_addr = smem_u32(smA), b_addr = smem_u32(smB);
+			const uint64_t a_desc0 = tc_smem_desc(smem_u32(smA)), b_desc0 = tc_smem_desc(smem_u32(smB));
 			mbar_wait(a_full, 0);
 			tc_fence_after();
 			uint32_t it = 0;
@@ -213,19 +244,22 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 					const uint32_t s = it % NSTAGE;
 					mbar_wait(&full[s], (it / NSTAGE) & 1);
 					tc_fence_after();
+					if (elect_one()) {
+						// descriptors: the start-address field counts 16-byte units, so a k step of 16 bf16 (32 B) adds 2
+						const uint64_t bd0 = b_desc0 + (uint64_t)((s * TC2_B_STAGE_BYTES) >> 4);
 #pragma unroll
-					for (int qb = 0; qb < NQB; ++qb) {
-						const uint32_t d_tmem = tmem_base + (acc * NQB + qb) * TC2_TN;
+						for (int qb = 0; qb < NQB; ++qb) {
+							const uint32_t d_tmem = tmem_base + (acc * NQB + qb) * TC2_TN;
+							const uint64_t ad0 = a_desc0 + (uint64_t)(((qb * nkb + kb) * TC_A_KB_BYTES) >> 4);
 #pragma unroll
-						for (int k = 0; k < TC_BK / TC_UMMA_K; ++k) {
-							const uint64_t ad = tc_smem_desc(a_addr + (qb * nkb + kb) * TC_A_KB_BYTES + k * TC_UMMA_K * 2);
-							const uint64_t bd = tc_smem_desc(b_addr + s * TC2_B_STAGE_BYTES + k * TC_UMMA_K * 2);
-							tc_mma(d_tmem, ad, bd, idesc, (kb | (uint32_t)k) != 0 ? 1u : 0u);
+							for (int k = 0; k < TC_BK / TC_UMMA_K; ++k)
+								tc_mma(d_tmem, ad0 + 2 * k, bd0 + 2 * k, idesc, (kb | (uint32_t)k) != 0 ? 1u : 0u);
 						}
+						tc_commit(&empty[s]);                        // stage reusable once these MMAs have read it
+						if (kb + 1 == nkb) tc_commit(&tm_full[acc]); // both query blocks' accumulators of this tile complete
 					}
-					tc_commit(&empty[s]); // stage reusable once these MMAs have read it
+					__syncwarp();
 				}
-				tc_commit(&tm_full[acc]); // both query blocks' accumulators of this tile complete
 			}
 		}
 	} else {
@@ -248,6 +282,7 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 		float* sc = sc_all + warp * 1024 + lane; // slow-path scratch: value j of this lane at sc[j * 32]
 		float4 xnext = make_float4(0.f, 0.f, 0.f, 0.f);
 		if (my_tiles) xnext = __ldg(reinterpret_cast<const float4*>(p.xn + (size_t)t_begin * TC2_TN) + lane);
+		const uint64_t scale2 = pack_b64(__float_as_uint(p.scale), __float_as_uint(p.scale));
 		uint32_t gnext = f32_orderable(INF); // bound of the other splits, fetched one tile ahead (any stale value is valid)
 		for (uint32_t lt = 0; lt < my_tiles; ++lt) {
 			const uint32_t acc = lt & 1;
@@ -263,23 +298,34 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 			mbar_wait(&tm_full[acc], (lt >> 1) & 1);
 			tc_fence_after();
 			const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + (acc * NQB + qb) * TC2_TN;
-			// 4 chunks of 32 columns; the TMEM load of chunk c+1 is in flight while chunk c is filtered
+			// pass 1, branch-free: the minimum of each of the 4 chunks of 32 columns (two TMEM loads in flight)
 			uint32_t dA[32], dB[32];
 			tc_ld32_nowait(tbase, dA);
-			tc_wait_ld(dA);
 			tc_ld32_nowait(tbase + 32, dB);
-			tc2_chunk(t, dA, xs, p.scale, sc, row0);
-			tc_wait_ld(dB);
-			tc_ld32_nowait(tbase + 64, dA);
-			tc2_chunk(t, dB, xs + 32, p.scale, sc, row0 + 32);
 			tc_wait_ld(dA);
-			tc_ld32_nowait(tbase + 96, dB);
-			tc2_chunk(t, dA, xs + 64, p.scale, sc, row0 + 64);
 			tc_wait_ld(dB);
+			const float mn0 = tc2_chunk_min(dA, xs, scale2);
+			tc_ld32_nowait(tbase + 64, dA);
+			const float mn1 = tc2_chunk_min(dB, xs + 32, scale2);
+			tc_ld32_nowait(tbase + 96, dB);
+			tc_wait_ld(dA);
+			tc_wait_ld(dB);
+			const float mn2 = tc2_chunk_min(dA, xs + 64, scale2);
+			const float mn3 = tc2_chunk_min(dB, xs + 96, scale2);
+			const uint32_t hm = (mn0 <= t.thr ? 1u : 0u) | (mn1 <= t.thr ? 2u : 0u) | (mn2 <= t.thr ? 4u : 0u) | (mn3 <= t.thr ? 8u : 0u);
+			// pass 2, rare: chunks in which some lane has a candidate are read again from TMEM (warp-collective load)
+			if (__any_sync(FULL, hm != 0)) {
+#pragma unroll 1
+				for (int c = 0; c < 4; ++c) {
+					if (!__any_sync(FULL, (hm >> c) & 1u)) continue;
+					tc_ld32_nowait(tbase + c * 32, dA);
+					tc_wait_ld(dA);
+					if ((hm >> c) & 1u) tc2_chunk_hits(t, dA, xs + c * 32, scale2, sc, row0 + c * 32);
+				}
+			}
 			tc_fence_before();
 			__syncwarp();
-			if (lane == 0) mbar_arrive(&tm_empty[acc]); // the accumulators are in registers now: release them early
-			tc2_chunk(t, dB, xs + 96, p.scale, sc, row0 + 96);
+			if (lane == 0) mbar_arrive(&tm_empty[acc]);
 			if (t.thr < pub) { atomicMin(p.gthr + qg, f32_orderable(t.thr)); pub = t.thr; }
 		}
 		if (qvalid) p.cnt[(size_t)qg * p.rsplit + split] = t.cnt;
