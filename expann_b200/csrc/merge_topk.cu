@@ -20,7 +20,10 @@ int launch_merge(expann_gpu* h, const uint64_t* in, size_t m, size_t nlists, siz
 	p.out_keys = out;
 	const int wpb = 4;
 	dim3 grid((unsigned)((m + wpb - 1) / wpb));
-	if (k <= 32) merge_topk_kernel<1><<<grid, wpb * 32, 0, st>>>(p);
+	if (nlists * klist >= 512 && m <= 4096) { // few queries, many lists: one block per query
+		if (k <= 32) merge_topk_block_kernel<1><<<(unsigned)m, 256, 0, st>>>(p);
+		else merge_topk_block_kernel<4><<<(unsigned)m, 256, 0, st>>>(p);
+	} else if (k <= 32) merge_topk_kernel<1><<<grid, wpb * 32, 0, st>>>(p);
 	else merge_topk_kernel<4><<<grid, wpb * 32, 0, st>>>(p);
 	EXPANN_CUDA(h, cudaGetLastError());
 	h->stats.merge_launches++;

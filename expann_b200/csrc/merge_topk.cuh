@@ -54,6 +54,62 @@ template <int LPL> __global__ void __launch_bounds__(128) merge_topk_kernel(cons
 	}
 }
 
+
+// Same merge with one 256-thread block per query: 8 warps each take every 8th 32-key slice, their lists meet in shared
+// memory and warp 0 merges those. For a few queries with many row splits (small-batch scans: 8 queries x 148 lists) the
+// one-warp kernel above is a chain of dependent L2 round trips (51 us measured for 218 lists).
+template <int LPL> __global__ void __launch_bounds__(256) merge_topk_block_kernel(const MergeParams p) {
+	__shared__ uint64_t sm[8][32 * LPL];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const uint32_t q = blockIdx.x;
+	WarpList<LPL> out;
+	out.init();
+	uint64_t tk = KEY_EMPTY;
+	const uint64_t* base = p.in + (size_t)q * p.stride_q;
+	const uint32_t total = p.nlists * p.klist;
+	for (uint32_t i0 = warp * 32; i0 < total; i0 += 256) {
+		const uint32_t i = i0 + lane;
+		uint64_t key = KEY_EMPTY;
+		if (i < total) {
+			const uint32_t s = i / p.klist, j = i - s * p.klist;
+			key = base[(size_t)s * p.stride_s + j];
+		}
+		unsigned mask = __ballot_sync(FULL, key < tk);
+		while (mask) {
+			const int src = __ffs(mask) - 1;
+			mask &= mask - 1;
+			const uint64_t kk = shfl_u64(key, src);
+			if (kk < tk) { out.insert(kk, lane); tk = out.at(p.k - 1); }
+		}
+	}
+#pragma unroll
+	for (int s = 0; s < LPL; ++s) sm[warp][s * 32 + lane] = out.e[s];
+	__syncthreads();
+	if (warp != 0) return;
+	for (int w = 1; w < 8; ++w) {
+#pragma unroll
+		for (int s = 0; s < LPL; ++s) {
+			const uint64_t key = sm[w][s * 32 + lane];
+			unsigned mask = __ballot_sync(FULL, key < tk);
+			while (mask) {
+				const int src = __ffs(mask) - 1;
+				mask &= mask - 1;
+				const uint64_t kk = shfl_u64(key, src);
+				if (kk < tk) { out.insert(kk, lane); tk = out.at(p.k - 1); }
+			}
+		}
+	}
+#pragma unroll
+	for (int s = 0; s < LPL; ++s) {
+		const uint32_t j = s * 32 + lane;
+		if (j < p.k) {
+			uint64_t key = out.e[s];
+			if (key != KEY_EMPTY) key += p.id_add;
+			p.out_keys[(size_t)q * p.k + j] = key;
+		}
+	}
+}
+
 // keys -> (ids, dists, counts). kind 0: fp32 keys (dist = decoded float), 1: int32 scores (dist = (float)score)
 __global__ void decode_keys_kernel(const uint64_t* keys, uint32_t m, uint32_t k, uint64_t id_offset, int kind,
                                    int negate, uint64_t* ids, float* dists, uint64_t* counts) {

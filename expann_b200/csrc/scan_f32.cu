@@ -95,18 +95,31 @@ int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, ui
 	int qt = h->cfg.qtile;
 	if (qt == 0) qt = m >= 8 ? 8 : (m >= 3 ? 4 : 1);
 	if (qt != 1 && qt != 4 && qt != 8) return fail(h, EXPANN_ERR_ARG, "qtile must be 0, 1, 4 or 8");
-	if (qt == 8 && (size_t)qt * h->d_pad * 4 > 64 * 1024) qt = 4; // keep the query tile + 3 stages within 227 KB
+	// keep stages + query tile + mailboxes within 227 KB (d = 960: 8 queries do not fit, 4 do)
+	auto fits = [&](int t) {
+		const uint32_t dp = (uint32_t)h->d_pad;
+		const size_t b = t == 8 ? ScanCfg<8, SCAN_TR, SCAN_NWARP, SCAN_STAGES, 0, 1>::smem_bytes(dp)
+		               : t == 4 ? ScanCfg<4, SCAN_TR, SCAN_NWARP, SCAN_STAGES, 0, 1>::smem_bytes(dp)
+		                        : ScanCfg<1, SCAN_TR, SCAN_NWARP, SCAN_STAGES, 0, 1>::smem_bytes(dp);
+		return b <= 227 * 1024;
+	};
+	if (qt == 8 && !fits(8)) qt = 4;
+	if (qt == 4 && !fits(4)) qt = 1;
 	const uint32_t qtiles = (uint32_t)((m + qt - 1) / qt);
 	const uint32_t groups = (uint32_t)((h->n + SCAN_ROWS - 1) / SCAN_ROWS);
 	int dev_sms = 148;
 	cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, h->device);
-	// enough CTAs for ~16 waves when the work allows it, but never fewer than 8 row groups per split
-	uint32_t want = (uint32_t)((16u * dev_sms + qtiles - 1) / qtiles);
-	uint32_t max_split = std::max(1u, groups / 8u);
+	// whole waves of CTAs (1 CTA per SM): W = ceil(qtiles / SMs) waves, as many row splits as fit in them; every split
+	// keeps at least 2 row groups. A small batch (qtiles == 1) is exactly one CTA per SM, each streaming 1/SMs of the rows.
+	const uint32_t waves = std::max(1u, (qtiles + dev_sms - 1) / (uint32_t)dev_sms);
+	const uint32_t want = std::max(1u, (uint32_t)((uint64_t)dev_sms * waves / qtiles));
+	const uint32_t max_split = std::max(1u, groups / 2u);
 	uint32_t nsplit = std::max(1u, std::min(want, max_split));
 	if (h->opt_nsplit > 0) nsplit = std::min((uint32_t)h->opt_nsplit, groups);
-	uint32_t gps = (groups + nsplit - 1) / nsplit;
-	nsplit = (groups + gps - 1) / gps;
+	// rows per split: even share rounded up to 64 rows (TMA box coordinates are arbitrary rows; the last row group of a
+	// split is partial and masked)
+	uint32_t rps = (uint32_t)(((h->n + nsplit - 1) / nsplit + 63) / 64 * 64);
+	nsplit = (uint32_t)((h->n + rps - 1) / rps);
 
 	ScanParams p{};
 	p.queries = d_q;
@@ -114,7 +127,7 @@ int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, ui
 	p.k = (uint32_t)k;
 	p.d_pad = (uint32_t)h->d_pad;
 	p.n = (uint32_t)h->n;
-	p.rows_per_split = gps * SCAN_ROWS;
+	p.rows_per_split = rps;
 	p.nsplit = nsplit;
 	uint64_t* scan_out = d_keys_out;
 	const bool need_merge = nsplit > 1 || (uint32_t)h->cfg.id_offset != 0;

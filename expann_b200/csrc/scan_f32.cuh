@@ -17,9 +17,13 @@
 //   * lane l of consumer warp w owns TR rows of every 32*TR*NWARP-row group and keeps QT*TR running sums in
 //     registers; the swizzle makes the lane-per-row LDS.128 bank-conflict free. Packed FADD2/FFMA2
 //     (sub.f32x2 / fma.rn.f32x2) halve the issue slots per element.
-//   * top-k: each warp keeps, per query, a sorted WarpList in registers and a float threshold; a distance
-//     enters the (rare) insertion path only if d <= threshold. Warps are merged through shared memory at the
-//     end of the CTA and the split results by merge_topk (K7).
+//   * top-k: ONE sorted WarpList per (CTA, query), owned by consumer warp q (QT <= NWARP), and a CTA-wide bound
+//     thr[q] (its k-th distance) in shared memory. After every row group a lane posts the rows with d <= thr[q]
+//     into query q's shared-memory mailbox; two named barriers bracket the owners' drain of the mailboxes, which
+//     tightens thr[q] for all warps. One list per CTA instead of one per warp divides the warm-up insertions
+//     (k * ln(rows/k) per list) by ~NWARP — at 8 queries per pass they were half of all issued instructions.
+//     A full mailbox is handled by extra post/drain rounds (far-to-near sorted data). The split results are
+//     merged by merge_topk (K7).
 #pragma once
 #include <cuda.h>
 #include "common.cuh"
@@ -55,8 +59,34 @@ __device__ __forceinline__ ulonglong2 lds128(uint32_t addr) {
 	asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(addr));
 	return v;
 }
+__device__ __forceinline__ uint32_t lds_u32(const void* p) {
+	uint32_t v;
+	asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
+	return v;
+}
+__device__ __forceinline__ void sts_u32(void* p, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory"); }
+__device__ __forceinline__ uint64_t lds_u64(const void* p) {
+	uint64_t v;
+	asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(smem_u32(p)) : "memory");
+	return v;
+}
+__device__ __forceinline__ void sts_u64(void* p, uint64_t v) { asm volatile("st.shared.u64 [%0], %1;" ::"r"(smem_u32(p)), "l"(v) : "memory"); }
+__device__ __forceinline__ uint32_t atom_inc_shared(void* p) {
+	uint32_t v;
+	asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(v) : "r"(smem_u32(p)) : "memory");
+	return v;
+}
 __device__ __forceinline__ float sum2(uint64_t a) {
 	return __uint_as_float((uint32_t)a) + __uint_as_float((uint32_t)(a >> 32));
+}
+
+// Rendezvous of the consumer warps on an mbarrier (one arrival per warp) instead of bar.sync: measured on B200, a
+// bar.sync issued while TMA boxes are in flight into this CTA's shared memory costs about one DRAM round trip (the
+// one-query scan spent 56 % of its time in the two per-group bar.syncs), the mbarrier rendezvous does not.
+__device__ __forceinline__ void consumer_rendezvous(uint64_t* bar, uint32_t n, int lane) {
+	__syncwarp();
+	if (lane == 0) mbar_arrive(bar);
+	mbar_wait(bar, n & 1);
 }
 
 template <int QT, int TR, int NWARP, int STAGES, int METRIC, int LPL>
@@ -67,12 +97,11 @@ struct ScanCfg {
 	static constexpr int STAGE_BYTES = ROWS * 128;
 	static constexpr int THREADS = 32 * (NWARP + 1);
 	static constexpr int KMAX = 32 * LPL;
-	// dynamic smem: [align 1024] stages | queries (QT*d_pad*4) | barriers
+	static constexpr int MB_CAP = 128; // mailbox entries per query and round
+	// dynamic smem: [align 1024] stages | queries (QT*d_pad*4) | mailboxes (QT*MB_CAP*8) | counts, bounds, flags | barriers
 	static size_t smem_bytes(uint32_t d_pad) {
-		size_t merge = (size_t)NWARP * QT * KMAX * 8; // reuses the stage area
-		size_t st = (size_t)STAGES * STAGE_BYTES;
-		if (merge > st) st = merge;
-		return 1024 + st + (size_t)QT * d_pad * 4 + 2 * STAGES * 8 + 64;
+		return 1024 + (size_t)STAGES * STAGE_BYTES + (size_t)QT * d_pad * 4 + (size_t)QT * MB_CAP * 8 + (size_t)QT * 8 + 16 +
+		       (2 * STAGES + 1) * 8 + 64;
 	}
 };
 
@@ -82,14 +111,16 @@ scan_topk_f32_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams 
 	using Cfg = ScanCfg<QT, TR, NWARP, STAGES, METRIC, LPL>;
 	extern __shared__ uint8_t smem_raw[];
 	uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-	size_t stage_area = (size_t)STAGES * Cfg::STAGE_BYTES;
-	{
-		size_t merge = (size_t)NWARP * QT * Cfg::KMAX * 8;
-		if (merge > stage_area) stage_area = merge;
-	}
+	static_assert(QT <= NWARP, "one owner warp per query of the tile");
+	const size_t stage_area = (size_t)STAGES * Cfg::STAGE_BYTES;
 	float* qsm = (float*)(smem + stage_area);
-	uint64_t* full = (uint64_t*)(smem + stage_area + (size_t)QT * p.d_pad * 4);
+	uint64_t* mbox = (uint64_t*)(smem + stage_area + (size_t)QT * p.d_pad * 4); // [QT][MB_CAP]
+	uint32_t* mb_cnt = (uint32_t*)(mbox + QT * Cfg::MB_CAP);                     // [QT]
+	float* thr_s = (float*)(mb_cnt + QT);                                        // [QT]
+	uint32_t* ovf_s = (uint32_t*)(thr_s + QT);                                   // [2] mailbox-overflow flag per round parity
+	uint64_t* full = (uint64_t*)(ovf_s + 4);
 	uint64_t* empty = full + STAGES;
+	uint64_t* csync = empty + STAGES; // consumer-warp rendezvous (see cta_rendezvous)
 
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 	const uint32_t q0 = blockIdx.x * QT;
@@ -108,8 +139,11 @@ scan_topk_f32_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams 
 		if (q0 + q < p.m) v = reinterpret_cast<const float4*>(p.queries + (size_t)q0 * p.d_pad)[i];
 		reinterpret_cast<float4*>(qsm)[i] = v;
 	}
+	if (tid < QT) { mb_cnt[tid] = 0; thr_s[tid] = __int_as_float(0x7f800000); }
 	if (tid == 0) {
+		ovf_s[0] = ovf_s[1] = 0;
 		for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NWARP); }
+		mbar_init(csync, NWARP);
 		mbar_fence_init();
 	}
 	__syncthreads();
@@ -133,10 +167,10 @@ scan_topk_f32_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams 
 	}
 
 	// ===================== consumers =====================
-	WarpList<LPL> list[QT];
-	float thr[QT];
-#pragma unroll
-	for (int q = 0; q < QT; ++q) { list[q].init(); thr[q] = __int_as_float(0x7f800000); }
+	WarpList<LPL> list; // the CTA's list of query `warp` (owner warps: warp < QT)
+	list.init();
+	uint64_t tk = KEY_EMPTY;
+	uint32_t round = 0, nsync = 0;
 	// lane-per-row address inside a stage with the 128B-swizzle folded in: chunk c of the row is at
 	// rowoff ^ (c << 4) because rowoff already carries (lane & 7) << 4 in its low 7 bits.
 	const uint32_t smem_base = smem_u32(smem), q_base = smem_u32(qsm);
@@ -181,77 +215,83 @@ scan_topk_f32_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams 
 			__syncwarp();
 			if (lane == 0) mbar_arrive(&empty[s]);
 		}
-		// ---- distances of this row group are complete: filter against the per-query thresholds
+		// ---- distances of this row group are complete: post candidates, owners drain, bounds tighten
 		const uint32_t grow = row_begin + g * Cfg::ROWS + warp * 32 * TR + lane;
 		float dist[QT][TR];
-		bool any = false;
+		uint32_t pend = 0; // bit q*TR+r: (query q, my row r) still has to be posted
 #pragma unroll
-		for (int q = 0; q < QT; ++q)
+		for (int q = 0; q < QT; ++q) {
+			const float tq = __uint_as_float(lds_u32(thr_s + q));
 #pragma unroll
 			for (int r = 0; r < TR; ++r) {
 				float d = sum2(acc[q][r]);
 				if (METRIC == METRIC_IP) d = -d;
 				dist[q][r] = d;
-				any |= (d <= thr[q]) && (grow + r * 32 < row_end);
+				if (d <= tq && grow + r * 32 < row_end) pend |= 1u << (q * TR + r);
 			}
-		if (__any_sync(FULL, any)) {
+		}
+		for (;;) {
+			uint32_t* ovf = ovf_s + (round & 1);
+			if (pend) {
 #pragma unroll
-			for (int q = 0; q < QT; ++q) {
+				for (int q = 0; q < QT; ++q)
 #pragma unroll
-				for (int r = 0; r < TR; ++r) {
-					unsigned mask = __ballot_sync(FULL, (dist[q][r] <= thr[q]) && (grow + r * 32 < row_end));
-					if (mask) {
-						uint64_t tk = list[q].at(p.k - 1);
+					for (int r = 0; r < TR; ++r)
+						if (pend & (1u << (q * TR + r))) {
+							const uint32_t slot = atom_inc_shared(mb_cnt + q);
+							if (slot < (uint32_t)Cfg::MB_CAP) {
+								sts_u64(mbox + q * Cfg::MB_CAP + slot, make_key(dist[q][r], grow + r * 32));
+								pend &= ~(1u << (q * TR + r));
+							} else
+								sts_u32(ovf, 1u);
+						}
+			}
+			consumer_rendezvous(csync, nsync++, lane); // all posts of this round are in
+			const uint32_t again = lds_u32(ovf);
+			if (tid == 0) sts_u32(ovf_s + ((round + 1) & 1), 0u);
+			if (warp < QT) {
+				const uint32_t c = min(lds_u32(mb_cnt + warp), (uint32_t)Cfg::MB_CAP);
+				if (c) {
+					for (uint32_t i0 = 0; i0 < c; i0 += 32) {
+						const uint64_t key = i0 + lane < c ? lds_u64(mbox + warp * Cfg::MB_CAP + i0 + lane) : KEY_EMPTY;
+						unsigned mask = __ballot_sync(FULL, key < tk);
 						while (mask) {
-							int src = __ffs(mask) - 1;
+							const int src = __ffs(mask) - 1;
 							mask &= mask - 1;
-							float dv = __shfl_sync(FULL, dist[q][r], src);
-							uint64_t key = make_key(dv, grow - lane + src + r * 32);
-							if (key < tk) {
-								list[q].insert(key, lane);
-								tk = list[q].at(p.k - 1);
+							const uint64_t kk = shfl_u64(key, src);
+							if (kk < tk) {
+								list.insert(kk, lane);
+								tk = list.at(p.k - 1);
 							}
 						}
-						thr[q] = tk == KEY_EMPTY ? __int_as_float(0x7f800000) : key_dist(tk);
+					}
+					__syncwarp();
+					if (lane == 0) {
+						sts_u32(mb_cnt + warp, 0u);
+						sts_u32(thr_s + warp, tk == KEY_EMPTY ? 0x7f800000u : __float_as_uint(key_dist(tk)));
 					}
 				}
+			}
+			consumer_rendezvous(csync, nsync++, lane); // bounds and empty mailboxes visible
+			++round;
+			if (!again) break;
+			// a mailbox was full: rows not yet posted are checked against the tightened bounds and posted again
+#pragma unroll
+			for (int q = 0; q < QT; ++q) {
+				const float tq = __uint_as_float(lds_u32(thr_s + q));
+#pragma unroll
+				for (int r = 0; r < TR; ++r)
+					if (!(dist[q][r] <= tq)) pend &= ~(1u << (q * TR + r));
 			}
 		}
 	}
 
-	// ---- merge the NWARP warp lists of every query through shared memory (stage area is free now)
-	asm volatile("bar.sync 1, %0;" ::"n"(32 * NWARP) : "memory");
-	uint64_t* msm = (uint64_t*)smem; // [NWARP][QT][KMAX]
-#pragma unroll
-	for (int q = 0; q < QT; ++q)
-#pragma unroll
-		for (int s = 0; s < LPL; ++s) msm[((size_t)warp * QT + q) * Cfg::KMAX + s * 32 + lane] = list[q].e[s];
-	asm volatile("bar.sync 1, %0;" ::"n"(32 * NWARP) : "memory");
-	for (int q = warp; q < QT; q += NWARP) {
-		if (q0 + q >= p.m) continue;
-		WarpList<LPL> out;
-		out.init();
-		uint64_t tk = KEY_EMPTY;
-		for (int w = 0; w < NWARP; ++w) {
-#pragma unroll
-			for (int s = 0; s < LPL; ++s) {
-				uint64_t key = msm[((size_t)w * QT + q) * Cfg::KMAX + s * 32 + lane];
-				unsigned mask = __ballot_sync(FULL, key < tk);
-				while (mask) {
-					int src = __ffs(mask) - 1;
-					mask &= mask - 1;
-					uint64_t kk = shfl_u64(key, src);
-					if (kk < tk) {
-						out.insert(kk, lane);
-						tk = out.at(p.k - 1);
-					}
-				}
-			}
-		}
-		uint64_t* dst = p.partial + ((size_t)(q0 + q) * p.nsplit + split) * p.k;
+	// ---- the owner warp of each query writes the CTA's list for this split
+	if (warp < QT && q0 + warp < p.m) {
+		uint64_t* dst = p.partial + ((size_t)(q0 + warp) * p.nsplit + split) * p.k;
 #pragma unroll
 		for (int s = 0; s < LPL; ++s)
-			if (s * 32 + lane < (int)p.k) dst[s * 32 + lane] = out.e[s];
+			if (s * 32 + lane < (int)p.k) dst[s * 32 + lane] = list.e[s];
 	}
 }
 
