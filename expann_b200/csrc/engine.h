@@ -52,7 +52,7 @@ struct expann_gpu {
 	bool built = false;
 	CUtensorMap tmap_base{};
 	cudaStream_t stream = nullptr;
-	expann::DevBuf qpad, partial, keys, ids, dists, counts; // device work buffers (grow-only)
+	expann::DevBuf qpad, partial, keys, ids, dists, counts, scan_cnt; // device work buffers (grow-only)
 	expann::DevBuf h_q, h_ids, h_dists, h_counts;            // pinned host staging for the host-pointer API
 	expann_gpu_stats_t stats{};
 	// tensor-core candidate filter (K3)

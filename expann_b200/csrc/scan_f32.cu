@@ -67,7 +67,12 @@ static int launch_inst(expann_gpu* h, const ScanParams& p, dim3 grid, cudaStream
 	auto kern = scan_topk_f32_kernel<QT, SCAN_TR, SCAN_NWARP, SCAN_STAGES, METRIC, LPL>;
 	const size_t smem = Cfg::smem_bytes(p.d_pad);
 	if (smem > 227 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "scan: d too large for the shared-memory query tile");
-	EXPANN_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	static thread_local int attr_dev = -1, attr_smem = 0; // per instantiation: set once per device / size, not per launch
+	if (attr_dev != h->device || attr_smem < (int)smem) {
+		EXPANN_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		attr_dev = h->device;
+		attr_smem = (int)smem;
+	}
 	kern<<<grid, Cfg::THREADS, smem, st>>>(h->tmap_base, p);
 	EXPANN_CUDA(h, cudaGetLastError());
 	return EXPANN_OK;
@@ -134,6 +139,13 @@ int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, ui
 	if (need_merge) {
 		EXPANN_CUDA(h, h->partial.ensure((size_t)m * nsplit * k * 8));
 		scan_out = h->partial.as<uint64_t>();
+		if (h->scan_cnt.cap < m * 4) { // tickets of the fused merge: zero once, the kernel leaves them zero
+			EXPANN_CUDA(h, h->scan_cnt.ensure(m * 4));
+			EXPANN_CUDA(h, cudaMemsetAsync(h->scan_cnt.p, 0, h->scan_cnt.cap, st));
+		}
+		p.final_out = d_keys_out;
+		p.counters = h->scan_cnt.as<uint32_t>();
+		p.id_add = (uint32_t)h->cfg.id_offset;
 	}
 	p.partial = scan_out;
 	dim3 grid(qtiles, nsplit);
@@ -144,9 +156,7 @@ int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, ui
 	h->stats.scan_launches++;
 	h->stats.last_nsplit = nsplit;
 	h->stats.last_qtile = qt;
-	if (need_merge)
-		return launch_merge(h, scan_out, m, nsplit, k, (size_t)nsplit * k, k, k, (uint32_t)h->cfg.id_offset, d_keys_out, st);
-	return EXPANN_OK;
+	return EXPANN_OK; // split merge is fused into the scan (last writer of each query)
 }
 
 } // namespace expann

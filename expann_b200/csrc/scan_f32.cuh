@@ -39,6 +39,11 @@ struct ScanParams {
 	uint32_t n;              // rows in this shard
 	uint32_t rows_per_split; // multiple of the stage row count
 	uint32_t nsplit;
+	// fused split merge (nsplit > 1 or id_add != 0): the owner warp that writes the LAST list of a query (ticket on
+	// counters[q], self-resetting) merges the nsplit lists into final_out[q][k] with id_add added to the ids
+	uint64_t* final_out;
+	uint32_t* counters;
+	uint32_t id_add;
 };
 
 __device__ __forceinline__ uint64_t pack2(float lo, float hi) {
@@ -286,12 +291,50 @@ scan_topk_f32_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams 
 		}
 	}
 
-	// ---- the owner warp of each query writes the CTA's list for this split
+	// ---- the owner warp of each query writes the CTA's list for this split; the last writer of a query merges
 	if (warp < QT && q0 + warp < p.m) {
-		uint64_t* dst = p.partial + ((size_t)(q0 + warp) * p.nsplit + split) * p.k;
+		const uint32_t qg = q0 + warp;
+		uint64_t* dst = p.partial + ((size_t)qg * p.nsplit + split) * p.k;
 #pragma unroll
 		for (int s = 0; s < LPL; ++s)
 			if (s * 32 + lane < (int)p.k) dst[s * 32 + lane] = list.e[s];
+		if (p.final_out) {
+			__threadfence();
+			__syncwarp();
+			uint32_t ticket = 0;
+			if (lane == 0) ticket = atomicAdd(p.counters + qg, 1u);
+			ticket = __shfl_sync(FULL, ticket, 0);
+			if (ticket == p.nsplit - 1) {
+				__threadfence();
+				const uint64_t* src = p.partial + (size_t)qg * p.nsplit * p.k;
+				const uint32_t total = p.nsplit * p.k;
+				WarpList<LPL> out;
+				out.init();
+				uint64_t ok = KEY_EMPTY;
+				for (uint32_t i0 = 0; i0 < total; i0 += 256) {
+					uint64_t kk[8]; // 8 independent loads in flight per lane
+#pragma unroll
+					for (int u = 0; u < 8; ++u) {
+						const uint32_t i = i0 + u * 32 + lane;
+						kk[u] = i < total ? __ldcg(src + i) : KEY_EMPTY;
+					}
+#pragma unroll
+					for (int u = 0; u < 8; ++u) {
+						unsigned mask = __ballot_sync(FULL, kk[u] < ok);
+						while (mask) {
+							const int sl = __ffs(mask) - 1;
+							mask &= mask - 1;
+							const uint64_t c = shfl_u64(kk[u], sl);
+							if (c < ok) { out.insert(c, lane); ok = out.at(p.k - 1); }
+						}
+					}
+				}
+#pragma unroll
+				for (int s = 0; s < LPL; ++s)
+					if (s * 32 + lane < (int)p.k) p.final_out[(size_t)qg * p.k + s * 32 + lane] = out.e[s] == KEY_EMPTY ? KEY_EMPTY : out.e[s] + p.id_add;
+				if (lane == 0) p.counters[qg] = 0;
+			}
+		}
 	}
 }
 
