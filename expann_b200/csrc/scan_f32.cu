@@ -92,7 +92,13 @@ int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, ui
 
 // path selection: the tensor-core filter (K3) for large batches when build() prepared its operands, else the SIMT scan
 int launch_scan_f32(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st) {
-	if (h->tc_mode && h->opt_tc && m >= (size_t)h->opt_tc_min_batch && k <= 128) return launch_scan_tc(h, d_q, m, k, d_keys_out, st);
+	if (h->tc_mode && h->opt_tc && k <= 128) {
+		// second form of K3 (k <= 16, single launch) pays from tc_min_batch queries on; the chunked first form (k <= 128)
+		// has ~10 launches and host round trips per batch and only pays for large batches
+		const bool second = k <= 16 && !h->opt_tc_v1;
+		const size_t need = second ? (size_t)h->opt_tc_min_batch : std::max<size_t>((size_t)h->opt_tc_min_batch, 512);
+		if (m >= need) return launch_scan_tc(h, d_q, m, k, d_keys_out, st);
+	}
 	return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st);
 }
 

@@ -211,7 +211,12 @@ static int tc_batch(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 template <int NQB>
 static int launch_filter2(expann_gpu* h, const CUtensorMap& tq, const Tc2Params& p, dim3 grid, cudaStream_t st) {
 	const size_t smem = Tc2Cfg<NQB>::smem_bytes(p.kd, TC2_NSTAGE);
-	EXPANN_CUDA(h, cudaFuncSetAttribute(tc_filter2_kernel<NQB, TC2_NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	static thread_local int f_dev = -1, f_smem = 0;
+	if (f_dev != h->device || f_smem < (int)smem) {
+		EXPANN_CUDA(h, cudaFuncSetAttribute(tc_filter2_kernel<NQB, TC2_NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		f_dev = h->device;
+		f_smem = (int)smem;
+	}
 	tc_filter2_kernel<NQB, TC2_NSTAGE><<<grid, Tc2Cfg<NQB>::THREADS, smem, st>>>(tq, h->tmap_xb128, p);
 	EXPANN_CUDA(h, cudaGetLastError());
 	return EXPANN_OK;
@@ -220,7 +225,7 @@ static int launch_filter2(expann_gpu* h, const CUtensorMap& tq, const Tc2Params&
 // row splits of the second form: whole waves of CTAs (>= 97 % of the SM slots of the last wave used), as few
 // splits as that allows (every split warms its own bound up), at least 8 tiles per CTA
 static uint32_t tc2_pick_rsplit(uint32_t qblocks, uint32_t ntiles, int sms) {
-	const uint32_t max_split = std::max(1u, std::min(64u, ntiles / 8u));
+	const uint32_t max_split = std::max(1u, std::min((uint32_t)TC2_MAX_SPLIT, ntiles / 8u));
 	uint32_t best = 1;
 	double best_eff = 0.0;
 	for (uint32_t w = 1; w <= 24; ++w) {
@@ -255,27 +260,24 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	EXPANN_CUDA(h, h->tc_cand.ensure(m * (size_t)rsplit * TC2_CAP * 8));
 	EXPANN_CUDA(h, h->tc_sel.ensure(m * (size_t)TC_PAD * 8 + 16));
 	uint32_t* flags = reinterpret_cast<uint32_t*>(h->tc_sel.as<uint64_t>() + m * (size_t)TC_PAD);
-	if (int rc = reset_stats(h, h->tc_qstats, st)) return rc;
+	EXPANN_CUDA(h, h->tc_qstats.ensure(sizeof(TcStats)));
+	EXPANN_CUDA(h, cudaMemsetAsync(flags, 0, 16, st));
+	tc_stats_init_kernel<<<1, 1, 0, st>>>(h->tc_qstats.as<TcStats>());
 	tc_convert_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(d_q, h->d_pad, (uint32_t)h->d, m, h->tc_qb.as<__nv_bfloat16>(), kd,
 	                                                          h->tc_mode, 1, h->tc_qn.as<float>(), h->tc_qstats.as<TcStats>());
 	EXPANN_CUDA(h, cudaGetLastError());
-	h->stats.aux_launches++;
+	h->stats.aux_launches += 2;
 	float eps_rel = 0.f, eps_abs = 0.f;
 	if (h->tc_mode == 1) {
-		TcStats s;
-		if (int rc = read_stats(h, h->tc_qstats, &s, st)) return rc;
-		const float lo = std::min(h->tc_xmin, f32_from_orderable(s.vmin)), hi = std::max(h->tc_xmax, f32_from_orderable(s.vmax));
-		const float amax = std::max(std::fabs(lo), std::fabs(hi));
-		const double lim = 16777216.0, dd = (double)h->d;
-		const bool exact = !s.inexact && amax <= 256.f && dd * (hi - lo) * (hi - lo) < lim && dd * amax * amax < lim;
-		if (!exact) { *fell_back = true; return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st); }
+		// exact only if the queries are bf16-exact integers too: checked on the device, a violation raises flags[0]
+		tc_check_exact_kernel<<<1, 1, 0, st>>>(h->tc_qstats.as<TcStats>(), h->tc_xmin, h->tc_xmax, (float)h->d, flags);
+		h->stats.aux_launches++;
 	} else {
 		eps_rel = 1.0f / 16384.0f;
 		eps_abs = 1e-6f * (h->tc_xnorm_max * h->tc_xnorm_max + 1e-30f);
 	}
 	CUtensorMap tq;
 	if (int rc = encode_tensor_map_bf16(h, &tq, h->tc_qb.p, kd, m, TC_BM)) return rc;
-	EXPANN_CUDA(h, cudaMemsetAsync(flags, 0, 16, st));
 	tc_fill_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(h->tc_gthr.as<float>(), 0, m, __uint_as_float_host(f32_orderable(INFINITY)));
 	h->stats.aux_launches++;
 	Tc2Params p{};
@@ -304,8 +306,12 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	h->stats.tc_launches++;
 	h->stats.last_qtile = TC_BM * nqb;
 	h->stats.last_nsplit = rsplit;
-	tc_select2_kernel<1><<<(unsigned)((m + 3) / 4), 128, 0, st>>>(p.cand, p.cnt, TC2_CAP, rsplit, p.m, p.k, p.qn, eps_rel, eps_abs,
-	                                                             h->tc_xnorm_max, h->tc_sel.as<uint64_t>(), TC_PAD, flags);
+	if (rsplit > 32) // many cold splits per query: one block per query
+		tc_select2_block_kernel<1><<<(unsigned)m, 256, 0, st>>>(p.cand, p.cnt, TC2_CAP, rsplit, p.m, p.k, p.qn, eps_rel, eps_abs,
+		                                                        h->tc_xnorm_max, h->tc_sel.as<uint64_t>(), TC_PAD, flags);
+	else
+		tc_select2_kernel<1><<<(unsigned)((m + 3) / 4), 128, 0, st>>>(p.cand, p.cnt, TC2_CAP, rsplit, p.m, p.k, p.qn, eps_rel, eps_abs,
+		                                                             h->tc_xnorm_max, h->tc_sel.as<uint64_t>(), TC_PAD, flags);
 	EXPANN_CUDA(h, cudaGetLastError());
 	h->stats.aux_launches++;
 	RerankParams r{};
@@ -322,7 +328,12 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	r.metric = ip ? 1 : 0;
 	r.scan_order = 1;
 	const size_t smem = ((size_t)h->d_pad * 4 + GS_MAXNB * 8) * 4;
-	EXPANN_CUDA(h, cudaFuncSetAttribute(rerank_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	static thread_local int rr_dev = -1, rr_smem = 0;
+	if (rr_dev != h->device || rr_smem < (int)smem) {
+		EXPANN_CUDA(h, cudaFuncSetAttribute(rerank_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		rr_dev = h->device;
+		rr_smem = (int)smem;
+	}
 	rerank_kernel<1><<<(unsigned)((m + 3) / 4), 128, smem, st>>>(r);
 	EXPANN_CUDA(h, cudaGetLastError());
 	h->stats.aux_launches++;

@@ -18,6 +18,7 @@
 // and hands those rows to the fp32 re-rank (K4). See tc.cu for why this is exact.
 #pragma once
 #include "tc_filter.cuh"
+#include "tc_prep.cuh"
 
 namespace expann {
 
@@ -341,32 +342,66 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 // Per query: exact k-th smallest key over the buffers of all its splits -> t = a'_k + 2*eps; survivors (a' <= t) are
 // written to out[q][pad] (KEY_EMPTY padded) for the fp32 re-rank. flags[0] counts queries whose result is not
 // guaranteed (a buffer overflowed, or more than `pad` survivors): the caller redoes the batch with the SIMT scan.
+// One warp per query. The per-split counts become an exclusive prefix in shared memory, and both passes walk the
+// FLAT index space of all buffered keys (binary search of the prefix per key, 4 independent loads in flight per lane):
+// with up to 296 splits a split-by-split walk is a chain of dependent L2 round trips (180 us measured at 148 splits).
+constexpr int TC2_MAX_SPLIT = 296;
+
+__device__ __forceinline__ uint64_t tc2_flat_key(const uint64_t* __restrict__ qbuf, const uint32_t* pre, uint32_t rsplit, uint32_t cap,
+                                                 uint32_t i, uint32_t total) {
+	if (i >= total) return KEY_EMPTY;
+	uint32_t lo = 0, hi = rsplit; // largest s with pre[s] <= i
+	while (hi - lo > 1) {
+		const uint32_t mid = (lo + hi) >> 1;
+		if (pre[mid] <= i) lo = mid; else hi = mid;
+	}
+	return __ldg(qbuf + (size_t)lo * cap + (i - pre[lo]));
+}
+
 template <int LPL>
 __global__ void __launch_bounds__(128) tc_select2_kernel(const uint64_t* __restrict__ cand, const uint32_t* __restrict__ cnt, uint32_t cap,
                                                           uint32_t rsplit, uint32_t m, uint32_t k, const float* __restrict__ qnorm2,
                                                           float eps_rel, float eps_abs, float xnorm_max, uint64_t* __restrict__ out,
                                                           uint32_t pad, uint32_t* __restrict__ flags) {
-	const int lane = threadIdx.x & 31;
-	const uint32_t q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	__shared__ uint32_t pre_s[4][TC2_MAX_SPLIT + 8];
+	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+	const uint32_t q = blockIdx.x * (blockDim.x >> 5) + wib;
 	if (q >= m) return;
+	uint32_t* pre = pre_s[wib];
 	const uint64_t* qbuf = cand + (size_t)q * rsplit * cap;
 	const uint32_t* qcnt = cnt + (size_t)q * rsplit;
+	uint32_t total = 0;
+	bool over = false;
+	for (uint32_t s0 = 0; s0 < rsplit; s0 += 32) {
+		const uint32_t s = s0 + lane;
+		uint32_t c = s < rsplit ? qcnt[s] : 0u;
+		if (c > cap) { over = true; c = cap; }
+		uint32_t incl = c;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			const uint32_t up = __shfl_up_sync(FULL, incl, o);
+			if (lane >= o) incl += up;
+		}
+		if (s < rsplit) pre[s] = total + incl - c;
+		total += __shfl_sync(FULL, incl, 31);
+	}
+	over = __any_sync(FULL, over);
+	__syncwarp();
 	WarpList<LPL> best;
 	best.init();
 	uint64_t tk = KEY_EMPTY;
-	bool over = false;
-	for (uint32_t s = 0; s < rsplit; ++s) {
-		uint32_t c = qcnt[s];
-		if (c > cap) { over = true; c = cap; }
-		const uint64_t* buf = qbuf + (size_t)s * cap;
-		for (uint32_t i0 = 0; i0 < c; i0 += 32) {
-			const uint64_t key = i0 + lane < c ? buf[i0 + lane] : KEY_EMPTY;
-			unsigned mask = __ballot_sync(FULL, key < tk);
+	for (uint32_t i0 = 0; i0 < total; i0 += 128) {
+		uint64_t kk[4];
+#pragma unroll
+		for (int u = 0; u < 4; ++u) kk[u] = tc2_flat_key(qbuf, pre, rsplit, cap, i0 + u * 32 + lane, total);
+#pragma unroll
+		for (int u = 0; u < 4; ++u) {
+			unsigned mask = __ballot_sync(FULL, kk[u] < tk);
 			while (mask) {
 				const int src = __ffs(mask) - 1;
 				mask &= mask - 1;
-				const uint64_t kk = shfl_u64(key, src);
-				if (kk < tk) { best.insert(kk, lane); tk = best.at(k - 1); }
+				const uint64_t c = shfl_u64(kk[u], src);
+				if (c < tk) { best.insert(c, lane); tk = best.at(k - 1); }
 			}
 		}
 	}
@@ -377,20 +412,159 @@ __global__ void __launch_bounds__(128) tc_select2_kernel(const uint64_t* __restr
 	}
 	uint64_t* o = out + (size_t)q * pad;
 	uint32_t w = 0;
-	for (uint32_t s = 0; s < rsplit; ++s) {
-		const uint32_t c = min(qcnt[s], cap);
-		const uint64_t* buf = qbuf + (size_t)s * cap;
-		for (uint32_t i0 = 0; i0 < c; i0 += 32) {
-			const uint64_t key = i0 + lane < c ? buf[i0 + lane] : KEY_EMPTY;
-			const bool keep = key != KEY_EMPTY && key_dist(key) <= t;
+	for (uint32_t i0 = 0; i0 < total; i0 += 128) {
+		uint64_t kk[4];
+#pragma unroll
+		for (int u = 0; u < 4; ++u) kk[u] = tc2_flat_key(qbuf, pre, rsplit, cap, i0 + u * 32 + lane, total);
+#pragma unroll
+		for (int u = 0; u < 4; ++u) {
+			const bool keep = kk[u] != KEY_EMPTY && key_dist(kk[u]) <= t;
 			const unsigned mk = __ballot_sync(FULL, keep);
 			const uint32_t pos = w + __popc(mk & ((1u << lane) - 1));
-			if (keep && pos < pad) o[pos] = key;
+			if (keep && pos < pad) o[pos] = kk[u];
 			w += __popc(mk);
 		}
 	}
 	for (uint32_t i = w + lane; i < pad; i += 32) o[i] = KEY_EMPTY;
 	if ((over || w > pad) && lane == 0) atomicAdd(flags, 1u);
+}
+
+
+// Block-per-query form of the select for launches with many row splits (small batches: every split warms up cold in
+// the same wave, ~k*ln(rows/k) keys each, 148 splits -> ~10^4 keys per query). 8 warps take contiguous eighths of the
+// flat key space (the split index advances incrementally), their lists meet in shared memory, warp 0 derives t, and
+// the second pass appends the survivors through a shared counter.
+template <int LPL>
+__global__ void __launch_bounds__(256) tc_select2_block_kernel(const uint64_t* __restrict__ cand, const uint32_t* __restrict__ cnt, uint32_t cap,
+                                                                uint32_t rsplit, uint32_t m, uint32_t k, const float* __restrict__ qnorm2,
+                                                                float eps_rel, float eps_abs, float xnorm_max, uint64_t* __restrict__ out,
+                                                                uint32_t pad, uint32_t* __restrict__ flags) {
+	__shared__ uint32_t pre[TC2_MAX_SPLIT + 8];
+	__shared__ uint64_t lists[8][32 * LPL];
+	__shared__ float t_s;
+	__shared__ uint32_t w_s, over_s;
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const uint32_t q = blockIdx.x;
+	const uint64_t* qbuf = cand + (size_t)q * rsplit * cap;
+	const uint32_t* qcnt = cnt + (size_t)q * rsplit;
+	if (warp == 0) {
+		uint32_t total = 0;
+		bool over = false;
+		for (uint32_t s0 = 0; s0 < rsplit; s0 += 32) {
+			const uint32_t s = s0 + lane;
+			uint32_t c = s < rsplit ? qcnt[s] : 0u;
+			if (c > cap) { over = true; c = cap; }
+			uint32_t incl = c;
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) {
+				const uint32_t up = __shfl_up_sync(FULL, incl, o);
+				if (lane >= o) incl += up;
+			}
+			if (s < rsplit) pre[s] = total + incl - c;
+			total += __shfl_sync(FULL, incl, 31);
+		}
+		over = __any_sync(FULL, over);
+		if (lane == 0) { pre[rsplit] = total; w_s = 0; over_s = over ? 1u : 0u; }
+	}
+	__syncthreads();
+	const uint32_t total = pre[rsplit];
+	const uint32_t per = (total + 7) / 8, i_begin = min(total, warp * per), i_end = min(total, i_begin + per);
+	// lane-private cursor into the prefix: flat indices of a lane only grow
+	auto fetch = [&](uint32_t i, uint32_t& sp) -> uint64_t {
+		if (i >= i_end) return KEY_EMPTY;
+		while (pre[sp + 1] <= i) ++sp;
+		return __ldg(qbuf + (size_t)sp * cap + (i - pre[sp]));
+	};
+	uint32_t sp0 = 0;
+	{ // split of this warp's first index
+		uint32_t lo = 0, hi = rsplit;
+		while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (pre[mid] <= i_begin) lo = mid; else hi = mid; }
+		sp0 = lo;
+	}
+	WarpList<LPL> best;
+	best.init();
+	uint64_t tk = KEY_EMPTY;
+	uint32_t sp = sp0;
+	for (uint32_t i0 = i_begin; i0 < i_end; i0 += 128) {
+		uint64_t kk[4];
+#pragma unroll
+		for (int u = 0; u < 4; ++u) kk[u] = fetch(i0 + u * 32 + lane, sp);
+#pragma unroll
+		for (int u = 0; u < 4; ++u) {
+			unsigned mask = __ballot_sync(FULL, kk[u] < tk);
+			while (mask) {
+				const int src = __ffs(mask) - 1;
+				mask &= mask - 1;
+				const uint64_t c = shfl_u64(kk[u], src);
+				if (c < tk) { best.insert(c, lane); tk = best.at(k - 1); }
+			}
+		}
+	}
+#pragma unroll
+	for (int s = 0; s < LPL; ++s) lists[warp][s * 32 + lane] = best.e[s];
+	__syncthreads();
+	if (warp == 0) {
+		for (int w = 1; w < 8; ++w) {
+#pragma unroll
+			for (int s = 0; s < LPL; ++s) {
+				const uint64_t key = lists[w][s * 32 + lane];
+				unsigned mask = __ballot_sync(FULL, key < tk);
+				while (mask) {
+					const int src = __ffs(mask) - 1;
+					mask &= mask - 1;
+					const uint64_t c = shfl_u64(key, src);
+					if (c < tk) { best.insert(c, lane); tk = best.at(k - 1); }
+				}
+			}
+		}
+		if (lane == 0) {
+			float t = __int_as_float(0x7f800000);
+			if (tk != KEY_EMPTY) t = __fadd_ru(key_dist(tk), 2.f * (eps_rel * sqrtf(qnorm2[q]) * xnorm_max + eps_abs));
+			t_s = t;
+		}
+	}
+	__syncthreads();
+	const float t = t_s;
+	uint64_t* o = out + (size_t)q * pad;
+	sp = sp0;
+	for (uint32_t i0 = i_begin; i0 < i_end; i0 += 128) {
+		uint64_t kk[4];
+#pragma unroll
+		for (int u = 0; u < 4; ++u) kk[u] = fetch(i0 + u * 32 + lane, sp);
+#pragma unroll
+		for (int u = 0; u < 4; ++u) {
+			const bool keep = kk[u] != KEY_EMPTY && key_dist(kk[u]) <= t;
+			const unsigned mk = __ballot_sync(FULL, keep);
+			if (mk) {
+				uint32_t base = 0;
+				if (lane == 0) base = atomicAdd(&w_s, (uint32_t)__popc(mk));
+				base = __shfl_sync(FULL, base, 0);
+				const uint32_t pos = base + __popc(mk & ((1u << lane) - 1));
+				if (keep && pos < pad) o[pos] = kk[u];
+			}
+		}
+	}
+	__syncthreads();
+	const uint32_t w = w_s;
+	for (uint32_t i = w + threadIdx.x; i < pad; i += 256) o[i] = KEY_EMPTY;
+	if ((over_s || w > pad) && threadIdx.x == 0) atomicAdd(flags, 1u);
+}
+
+// exactness of the bf16 single-GEMM mode for THIS query batch, decided on the device (no host round trip): the queries
+// must be bf16-exact integers too and no partial sum may leave the 2^24 integer range; otherwise flags[0] is raised and
+// the caller redoes the batch with the SIMT scan.
+__global__ void tc_check_exact_kernel(const TcStats* __restrict__ qs, float xmin, float xmax, float d, uint32_t* __restrict__ flags) {
+	const float lo = fminf(xmin, f32_from_orderable(qs->vmin)), hi = fmaxf(xmax, f32_from_orderable(qs->vmax));
+	const float amax = fmaxf(fabsf(lo), fabsf(hi));
+	const double lim = 16777216.0;
+	const bool exact = !qs->inexact && amax <= 256.f && (double)d * (hi - lo) * (hi - lo) < lim && (double)d * amax * amax < lim;
+	if (!exact) atomicAdd(flags, 1u);
+}
+__global__ void tc_stats_init_kernel(TcStats* s) {
+	s->vmin = f32_orderable(3.4e38f);
+	s->vmax = f32_orderable(-3.4e38f);
+	s->inexact = 0u;
+	s->nmax = f32_orderable(0.f);
 }
 
 } // namespace expann

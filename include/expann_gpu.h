@@ -117,7 +117,7 @@ int expann_gpu_set_timing(expann_gpu_t* h, int on);
 int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
 /* tuning knobs by name (the reference exposes its knobs as Engine::config members, src/bench_runner.h:133-172):
  * "qtile" (0 auto | 1 | 4 | 8), "nsplit" (0 auto | forced row splits per scan), "tc" (0/1: tensor-core candidate filter for large
- * batches, must be set before build()), "tc_min_batch" (default 512), "kprime" (QUANT_SCAN: survivors
+ * batches, must be set before build()), "tc_min_batch" (default 16: measured crossover with the SIMT scan on 1M x 128), "kprime" (QUANT_SCAN: survivors
  * re-ranked in fp32, 0 auto = min(128, 10k)). Unknown names: EXPANN_ERR_ARG. */
 int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value);
 /* library build info: "sm_100a;..." */

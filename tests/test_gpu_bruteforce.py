@@ -15,6 +15,7 @@ def ex():
 
 def run_bf(ex, base, q, k, metric=0, qtile=0, id_offset=0, chunked=False):
     e = ex.BruteForceEngine(metric=metric, qtile=qtile, id_offset=id_offset)
+    e.set_option("tc", 0)  # this file pins the SIMT scan (K1/K2); the tensor-core path has tests/test_gpu_tensorcore.py
     if chunked:  # mix of single-vector store_vector calls and bulk adds
         e.store_vector(base[0])
         e.store_many_vectors(base[1:7])
