@@ -201,6 +201,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--engine", default="auto", choices=["auto", "bf", "quant"],
+                    help="bf: exact brute force (K1/K3+K4); quant: quantizer compressed scan + fp32 rerank (K6+K4); auto: quant for c5")
     ap.add_argument("--qtile", type=int, default=0)
     ap.add_argument("--m", type=int, default=0, help="override the query count")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
@@ -252,7 +254,12 @@ def main():
     base, q = datasets.make(gen, n, m, d, variant=variant or "lowrank")
     from expann_b200 import sharding
     lo, hi = sharding.shard_range(n, world, rank)
-    eng = expann_b200.BruteForceEngine(metric=1 if metric == "ip" else 0, device=local_rank, qtile=args.qtile, id_offset=lo)
+    use_quant = args.engine == "quant" or (args.engine == "auto" and args.workload == "c5")
+    if use_quant:   # BASELINE config 5: quantizer_ranged_q8 codes (src/quantizer.h:186-238) scanned with K6, k' = 100 survivors re-ranked in fp32
+        eng = expann_b200.QuantScanEngine(quantizer=1, kprime=100, metric=1 if metric == "ip" else 0, device=local_rank,
+                                          qtile=args.qtile, id_offset=lo)
+    else:
+        eng = expann_b200.BruteForceEngine(metric=1 if metric == "ip" else 0, device=local_rank, qtile=args.qtile, id_offset=lo)
     eng.store_many_vectors(base[lo:hi])
     eng.build()
 
@@ -353,9 +360,9 @@ def main():
                             "peak = cuBLAS bf16 burst figure; frac_of_sustained_peak uses the seconds-long figure"}
         else:
             passes = (m + qt - 1) // qt
-            alg_bytes = passes * (hi - lo) * d * 4
+            alg_bytes = passes * (hi - lo) * d * (1 if use_quant else 4)
             achieved = alg_bytes / (hot_ms * 1e-3) / 1e9
-            roof = {"bound": "hbm", "kernel": "scan_topk_f32_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            roof = {"bound": "hbm", "kernel": "scan_topk_u8_kernel" if use_quant else "scan_topk_f32_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": int(alg_bytes), "kernel_ms_per_launch": hot_ms,
                     "note": "algorithmic bytes = ceil(m/qtile) passes x shard bytes (SURVEY 8(d)); CTAs of one "
@@ -364,7 +371,8 @@ def main():
                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                "config": {"workload": desc, "n": n, "m": m, "d": d, "k": k, "metric": metric, "qtile": int(qt),
-                          "path": "K3 tcgen05 filter + K4 fp32 rerank" if used_tc else "K1 fp32 SIMT scan",
+                          "path": "K6 8-bit code scan (dp4a) + K4 fp32 rerank of 100 survivors" if use_quant else
+                                  ("K3 tcgen05 filter + K4 fp32 rerank" if used_tc else "K1 fp32 SIMT scan"),
                           "nsplit": int(st1["last_nsplit"]), "rows_per_gpu": hi - lo,
                           "l2": "base shard (%.0f MB) %s L2 (126 MB); no explicit flush" % ((hi - lo) * d * 4 / 1e6, "larger than" if (hi - lo) * d * 4 > 126e6 else "fits in"),
                           "parallelism": "base rows sharded x%d, NCCL all-gather of [m][k] keys + K7 merge" % world if world > 1 else "single GPU"},
@@ -378,7 +386,21 @@ def main():
             qps, cores, kind, sample = cpu_reference_qps(base, q, k, metric)
             out["cpu_baseline"] = {"value": qps, "unit": "queries/s", "cores": cores, "kind": kind, "sample": sample}
         out["check"] = {"first_ids": got[0].tolist()}
-        if world == 1 and not args.no_extras:
+        if use_quant and world == 1:
+            # quality of the compressed scan: recall@10 against the exact fp32 scan of the same library (not timed)
+            try:
+                ex = expann_b200.BruteForceEngine(metric=1 if metric == "ip" else 0, device=local_rank)
+                ex.store_many_vectors(base)
+                ex.build()
+                msub = min(m, 1000)
+                eids = ex.query_k_batch(q[:msub], k)[0]
+                ex.close()
+                qids = eng.query_k_batch(q[:msub], k)[0]
+                hit = sum(len(set(a.tolist()) & set(b.tolist())) for a, b in zip(qids, eids))
+                out["check"]["recall_at_k_vs_exact"] = hit / float(msub * k)
+            except Exception as exn:  # noqa: BLE001
+                out["check"]["recall_error"] = repr(exn)[:200]
+        if world == 1 and not args.no_extras and not use_quant:
             try:
                 out["scan_hbm"] = scan_hbm_leg(eng, torch, dq, k, hi - lo, d, stream, peak, peak_src, args.steps)
             except Exception as ex:  # noqa: BLE001
