@@ -182,7 +182,7 @@ void expann_gpu_destroy(expann_gpu_t* h) {
 	timing_collect(h);
 	for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
 	if (h->base) cudaFree(h->base);
-	for (DevBuf* b : { &h->tc_xb, &h->tc_xn, &h->tc_stats, &h->tc_qstats, &h->tc_qb, &h->tc_qn, &h->tc_thr, &h->tc_cnt, &h->tc_cand, &h->tc_gthr, &h->tc_sel, &h->scan_cnt })
+	for (DevBuf* b : { &h->tc_xb, &h->tc_xn, &h->tc_stats, &h->tc_qstats, &h->tc_qb, &h->tc_qn, &h->tc_thr, &h->tc_cnt, &h->tc_cand, &h->tc_gthr, &h->tc_sel, &h->tc_xx, &h->scan_cnt })
 		b->release();
 	for (DevBuf* b : { &h->q_codes, &h->q_cnorm, &h->q_mm, &h->qq_codes, &h->qq_norm, &h->q_cand }) b->release();
 	for (DevBuf* b : { &h->g_bottom, &h->g_upper, &h->g_upper_idx, &h->g_upper_nl, &h->g_visited, &h->g_epoch, &h->g_codes })

@@ -43,15 +43,16 @@ int encode_tensor_map_2d(expann_gpu* h, CUtensorMap* out, int dtype_u8, void* ba
 	return EXPANN_OK;
 }
 
-int encode_tensor_map_bf16(expann_gpu* h, CUtensorMap* out, void* base, uint64_t inner, uint64_t rows, uint32_t box_rows) {
+int encode_tensor_map_bf16(expann_gpu* h, CUtensorMap* out, void* base, uint64_t inner, uint64_t rows, uint32_t box_rows,
+                           uint32_t box_inner) {
 	encode_tiled_fn enc = get_encode_tiled();
 	if (!enc) return fail(h, EXPANN_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
 	cuuint64_t gdim[2] = { (cuuint64_t)inner, (cuuint64_t)rows };
 	cuuint64_t gstride[1] = { (cuuint64_t)inner * 2 };
-	cuuint32_t box[2] = { 64, box_rows };
+	cuuint32_t box[2] = { box_inner, box_rows };
 	cuuint32_t estr[2] = { 1, 1 };
 	CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-	                 CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+	                 box_inner == 16 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 	if (r != CUDA_SUCCESS) return fail(h, EXPANN_ERR_CUDA, "cuTensorMapEncodeTiled(bf16) failed: " + std::to_string((int)r));
 	return EXPANN_OK;
 }

@@ -19,7 +19,8 @@
 
 namespace expann {
 
-int encode_tensor_map_bf16(expann_gpu* h, CUtensorMap* out, void* base, uint64_t inner, uint64_t rows, uint32_t box_rows);
+int encode_tensor_map_bf16(expann_gpu* h, CUtensorMap* out, void* base, uint64_t inner, uint64_t rows, uint32_t box_rows,
+                           uint32_t box_inner = 64);
 int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);
 
 constexpr uint32_t TC_CAP = 4096, TC_FIRST_ROWS = 2048, TC_PAD = 256, TC_QBATCH = 16384;
@@ -59,9 +60,11 @@ int tc_finalize(expann_gpu* h) {
 		const uint32_t kd = mode == 1 ? seg : 3 * seg;
 		EXPANN_CUDA(h, h->tc_xb.ensure(h->n * (size_t)kd * 2));
 		if (int rc = reset_stats(h, h->tc_stats, st)) return rc;
+		EXPANN_CUDA(h, h->tc_xx.ensure(h->n * 32));
 		tc_convert_kernel<<<(unsigned)((h->n + 7) / 8), 256, 0, st>>>(h->base, h->d_pad, (uint32_t)h->d, h->n,
 		                                                             h->tc_xb.as<__nv_bfloat16>(), kd, mode, 0, h->tc_xn.as<float>(),
-		                                                             h->tc_stats.as<TcStats>());
+		                                                             h->tc_stats.as<TcStats>(), 1.f, h->tc_xx.as<__nv_bfloat16>(),
+		                                                             h->cfg.metric == EXPANN_METRIC_IP ? 0 : 1);
 		EXPANN_CUDA(h, cudaGetLastError());
 		h->stats.aux_launches++;
 		TcStats s;
@@ -82,6 +85,7 @@ int tc_finalize(expann_gpu* h) {
 	}
 	EXPANN_CUDA(h, cudaStreamSynchronize(st));
 	if (int rc = encode_tensor_map_bf16(h, &h->tmap_xb128, h->tc_xb.p, h->tc_kd, h->n, TC2_TN)) return rc;
+	if (int rc = encode_tensor_map_bf16(h, &h->tmap_xx, h->tc_xx.p, 16, h->n, TC2_TN, 16)) return rc;
 	return encode_tensor_map_bf16(h, &h->tmap_xb, h->tc_xb.p, h->tc_kd, h->n, TC_BN);
 }
 
@@ -208,16 +212,16 @@ static int tc_batch(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 }
 
 
-template <int NQB>
+template <int NQB, int NSTAGE>
 static int launch_filter2(expann_gpu* h, const CUtensorMap& tq, const Tc2Params& p, dim3 grid, cudaStream_t st) {
-	const size_t smem = Tc2Cfg<NQB>::smem_bytes(p.kd, TC2_NSTAGE);
+	const size_t smem = Tc2Cfg<NQB>::smem_bytes(p.kd, NSTAGE);
 	static thread_local int f_dev = -1, f_smem = 0;
 	if (f_dev != h->device || f_smem < (int)smem) {
-		EXPANN_CUDA(h, cudaFuncSetAttribute(tc_filter2_kernel<NQB, TC2_NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		EXPANN_CUDA(h, cudaFuncSetAttribute(tc_filter2_kernel<NQB, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 		f_dev = h->device;
 		f_smem = (int)smem;
 	}
-	tc_filter2_kernel<NQB, TC2_NSTAGE><<<grid, Tc2Cfg<NQB>::THREADS, smem, st>>>(tq, h->tmap_xb128, p);
+	tc_filter2_kernel<NQB, NSTAGE><<<grid, Tc2Cfg<NQB>::THREADS, smem, st>>>(tq, h->tmap_xb128, h->tmap_xx, p);
 	EXPANN_CUDA(h, cudaGetLastError());
 	return EXPANN_OK;
 }
@@ -264,7 +268,7 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	EXPANN_CUDA(h, cudaMemsetAsync(flags, 0, 16, st));
 	tc_stats_init_kernel<<<1, 1, 0, st>>>(h->tc_qstats.as<TcStats>());
 	tc_convert_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(d_q, h->d_pad, (uint32_t)h->d, m, h->tc_qb.as<__nv_bfloat16>(), kd,
-	                                                          h->tc_mode, 1, h->tc_qn.as<float>(), h->tc_qstats.as<TcStats>());
+	                                                          h->tc_mode, 1, h->tc_qn.as<float>(), h->tc_qstats.as<TcStats>(), ip ? -1.f : -2.f);
 	EXPANN_CUDA(h, cudaGetLastError());
 	h->stats.aux_launches += 2;
 	float eps_rel = 0.f, eps_abs = 0.f;
@@ -300,7 +304,11 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	p.xnorm_max = h->tc_xnorm_max;
 	dim3 grid(qblocks, rsplit);
 	cudaEvent_t t0 = timing_begin(h, st);
-	int rc = nqb == 2 ? launch_filter2<2>(h, tq, p, grid, st) : launch_filter2<1>(h, tq, p, grid, st);
+	// ring depth: 6 slots of 20 KB when they fit beside the resident query tile(s), else 4 (split mode, d up to 128)
+	const bool deep = Tc2Cfg<1>::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024;
+	int rc = nqb == 2 ? launch_filter2<2, TC2_NSTAGE>(h, tq, p, grid, st)
+	         : deep   ? launch_filter2<1, TC2_NSTAGE>(h, tq, p, grid, st)
+	                  : launch_filter2<1, 4>(h, tq, p, grid, st);
 	timing_end(h, t0, st);
 	if (rc) return rc;
 	h->stats.tc_launches++;

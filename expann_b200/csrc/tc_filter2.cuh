@@ -1,8 +1,12 @@
 // K3 (second form) — single-launch tensor-core candidate filter for k <= 16 (sm_100a: tcgen05.mma + TMEM + TMA).
 //
-// Same arithmetic as tc_filter.cuh:  a'(q,x) = ||x||^2 + scale * q.x  on bf16 operands with fp32 accumulation in TMEM
-// (a' = dist2(q,x) - ||q||^2, src/vec.h:139-142; scale = -2, or -1 with ||x||^2 := 0 for the inner product), but the
-// filter threshold is maintained INSIDE the kernel instead of by a host loop over row chunks:
+// Same quantity as tc_filter.cuh:  a'(q,x) = ||x||^2 + scale * q.x  on bf16 operands with fp32 accumulation in TMEM
+// (a' = dist2(q,x) - ||q||^2, src/vec.h:139-142; scale = -2, or -1 with ||x||^2 := 0 for the inner product), but
+//   * the WHOLE of a' comes out of the tensor core: the query operand is pre-scaled (exact, a power of two) and
+//     ||x||^2 enters through one extra K=16 MMA step per tile, [1 1 1 0..] x [xn_hi xn_mid xn_lo 0..] (three bf16 terms
+//     = 24 bits; operand rows of 32 bytes, 32B-swizzle descriptors, see tc_convert_kernel) — the epilogue is
+//     tcgen05.ld + a min tree, no FMA and no norm loads;
+//   * the filter threshold is maintained INSIDE the kernel instead of by a host loop over row chunks:
 //   * one CTA owns NQB blocks of 128 queries (A operand resident in shared memory) and one contiguous row range
 //     ("split"); B streams through an NSTAGE ring of [128 rows][64 bf16] 128B-swizzled TMA boxes that both query
 //     blocks consume, so a row tile is fetched from L2 once per 128*NQB queries (the L2->SM path, ~42 B/clk/SM, is
@@ -23,7 +27,9 @@
 namespace expann {
 
 constexpr int TC2_TN = 128;                         // rows per tile (UMMA N)
-constexpr int TC2_B_STAGE_BYTES = TC2_TN * TC_BK * 2; // 16 KB
+constexpr int TC2_B_STAGE_BYTES = TC2_TN * TC_BK * 2; // 16 KB k-block of B
+constexpr int TC2_X_BYTES = TC2_TN * 32;              // 4 KB: [128 rows][16 bf16] norm terms of the tile
+constexpr int TC2_STAGE_BYTES = TC2_B_STAGE_BYTES + TC2_X_BYTES; // ring slot: k-block + (last k-block only) norm terms
 constexpr int TC2_KK = 16;                          // per-thread sorted values (k <= 16)
 
 struct Tc2Params {
@@ -39,6 +45,15 @@ struct Tc2Params {
 
 __device__ __forceinline__ uint32_t tc2_instr_desc() { // kind::f16, bf16 x bf16 -> fp32, K-major A and B, M = 128, N = 128
 	return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC2_TN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+}
+// K-major operand tile with 32-byte rows (K = 16 bf16 = one UMMA_K step), 32B swizzle: 8-row groups are 256 B apart
+__device__ __forceinline__ uint64_t tc_smem_desc_sw32(uint32_t saddr) {
+	uint64_t d = (uint64_t)((saddr >> 4) & 0x3FFF);
+	d |= (uint64_t)1 << 16;
+	d |= (uint64_t)(256 >> 4) << 32;
+	d |= (uint64_t)1 << 46;
+	d |= (uint64_t)6 << 61;
+	return d;
 }
 __device__ __forceinline__ bool elect_one() {
 	uint32_t pred;
@@ -85,47 +100,32 @@ __device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c
 	asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
 	return r;
 }
-// 32 accumulator columns of one query: a'[j] = xn[j] + scale * dot[j] (packed FFMA2; bit-identical to fmaf per element)
-__device__ __forceinline__ void tc2_values(const uint32_t (&d)[32], const float* xs_c, uint64_t scale2, float (&a)[32]) {
-#pragma unroll
-	for (int j4 = 0; j4 < 8; ++j4) {
-		const float4 x4 = lds128f(xs_c + j4 * 4);
-		const uint64_t r0 = fma_f32x2(scale2, pack_b64(d[j4 * 4 + 0], d[j4 * 4 + 1]), pack_b64(__float_as_uint(x4.x), __float_as_uint(x4.y)));
-		const uint64_t r1 = fma_f32x2(scale2, pack_b64(d[j4 * 4 + 2], d[j4 * 4 + 3]), pack_b64(__float_as_uint(x4.z), __float_as_uint(x4.w)));
-		unpack_f32x2(r0, a[j4 * 4 + 0], a[j4 * 4 + 1]);
-		unpack_f32x2(r1, a[j4 * 4 + 2], a[j4 * 4 + 3]);
-	}
-}
-// pass 1 of a chunk: only the minimum of its 32 values (NaN = padded row: ignored by min and by every compare)
-__device__ __forceinline__ float tc2_chunk_min(const uint32_t (&d)[32], const float* xs_c, uint64_t scale2) {
-	float a[32];
-	tc2_values(d, xs_c, scale2, a);
+// pass 1 of a chunk: only the minimum of its 32 accumulator columns (= a' values of one query)
+__device__ __forceinline__ float tc2_chunk_min(const uint32_t (&d)[32]) {
 	float mn[11];
 #pragma unroll
-	for (int j = 0; j < 10; ++j) mn[j] = min3f(a[3 * j], a[3 * j + 1], a[3 * j + 2]);
-	mn[10] = fminf(a[30], a[31]);
+	for (int j = 0; j < 10; ++j) mn[j] = min3f(__uint_as_float(d[3 * j]), __uint_as_float(d[3 * j + 1]), __uint_as_float(d[3 * j + 2]));
+	mn[10] = fminf(__uint_as_float(d[30]), __uint_as_float(d[31]));
 	const float m0 = min3f(mn[0], mn[1], mn[2]), m1 = min3f(mn[3], mn[4], mn[5]), m2 = min3f(mn[6], mn[7], mn[8]);
 	return min3f(min3f(m0, m1, m2), mn[9], mn[10]);
 }
 // pass 2 (rare): a chunk known to hold some a' <= thr. The values are parked in this lane's scratch column and the hit
 // mask is built without branches; only the set bits (usually one) are visited. thr tightens while we go, hence the
-// second compare.
-__device__ __forceinline__ void tc2_chunk_hits(Tc2Thread& t, const uint32_t (&d)[32], const float* xs_c, uint64_t scale2, float* sc, uint32_t row_c) {
-	float a[32];
-	tc2_values(d, xs_c, scale2, a);
+// second compare. Rows >= n (zero-filled by TMA: a' = 0) are masked here.
+__device__ __forceinline__ void tc2_chunk_hits(Tc2Thread& t, const uint32_t (&d)[32], float* sc, uint32_t row_c, uint32_t n) {
 	const uint32_t sca = smem_u32(sc);
 	uint32_t mask = 0;
 #pragma unroll
 	for (int j = 0; j < 32; ++j) {
-		asm volatile("st.shared.f32 [%0], %1;" ::"r"(sca + j * 128), "f"(a[j]) : "memory");
-		mask |= a[j] <= t.thr ? 1u << j : 0u;
+		asm volatile("st.shared.b32 [%0], %1;" ::"r"(sca + j * 128), "r"(d[j]) : "memory");
+		mask |= __uint_as_float(d[j]) <= t.thr ? 1u << j : 0u;
 	}
 	while (mask) {
 		const int j = __ffs(mask) - 1;
 		mask &= mask - 1;
 		float aj;
 		asm volatile("ld.shared.f32 %0, [%1];" : "=f"(aj) : "r"(sca + j * 128) : "memory");
-		if (aj <= t.thr) tc2_event(t, aj, row_c + j);
+		if (aj <= t.thr && row_c + j < n) tc2_event(t, aj, row_c + j);
 	}
 }
 __device__ __forceinline__ void tc_ld32_nowait(uint32_t taddr, uint32_t (&v)[32]) {
@@ -155,22 +155,23 @@ template <int NQB> struct Tc2Cfg {
 	static constexpr int THREADS = 32 * (EPI_WARPS + 2);
 	static constexpr int TMEM_COLS = 2 * NQB * TC2_TN; // 256 or 512
 	static size_t smem_bytes(uint32_t kd, int nstage) {
-		return 1024 + (size_t)NQB * (kd / TC_BK) * TC_A_KB_BYTES + (size_t)nstage * TC2_B_STAGE_BYTES + (size_t)EPI_WARPS * (TC2_TN * 4 + 4096) +
+		return 1024 + (size_t)NQB * (kd / TC_BK) * TC_A_KB_BYTES + 4096 + (size_t)nstage * TC2_STAGE_BYTES + (size_t)EPI_WARPS * 4096 +
 		       (size_t)(1 + 2 * nstage + 4) * 8 + 16;
 	}
 };
 
 template <int NQB, int NSTAGE>
 __global__ void __launch_bounds__(32 * (4 * NQB + 2), 1)
-tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x, const Tc2Params p) {
+tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
+                  const __grid_constant__ CUtensorMap tmap_xx, const Tc2Params p) {
 	using Cfg = Tc2Cfg<NQB>;
 	extern __shared__ uint8_t tc_smem_raw[];
 	uint8_t* smem = (uint8_t*)(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
 	const uint32_t nkb = p.kd / TC_BK;
 	uint8_t* smA = smem;                                            // [NQB][nkb][128 q][64 bf16]
-	uint8_t* smB = smA + (size_t)NQB * nkb * TC_A_KB_BYTES;         // [NSTAGE][128 rows][64 bf16]
-	float* xs_all = reinterpret_cast<float*>(smB + (size_t)NSTAGE * TC2_B_STAGE_BYTES); // [EPI_WARPS][128]
-	float* sc_all = xs_all + Cfg::EPI_WARPS * TC2_TN;                                  // [EPI_WARPS][32][32]
+	uint8_t* smOnes = smA + (size_t)NQB * nkb * TC_A_KB_BYTES;      // [128 q][16 bf16] = [1 1 1 0 0 0 0 0 | 1 1 1 0 0 0 0 0]
+	uint8_t* smB = smOnes + 4096;                                   // [NSTAGE]{[128 rows][64 bf16] k-block, [128 rows][16 bf16] norm terms}
+	float* sc_all = reinterpret_cast<float*>(smB + (size_t)NSTAGE * TC2_STAGE_BYTES);  // [EPI_WARPS][32][32]
 	uint64_t* bars = reinterpret_cast<uint64_t*>(sc_all + Cfg::EPI_WARPS * 1024);
 	uint64_t* a_full = bars;
 	uint64_t* full = bars + 1;
@@ -193,6 +194,9 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 		for (int s = 0; s < 2; ++s) { mbar_init(&tm_full[s], 1); mbar_init(&tm_empty[s], Cfg::EPI_WARPS); }
 		mbar_fence_init();
 	}
+	for (int i = tid; i < 128 * 16; i += Cfg::THREADS) // the constant A rows of the norm step
+		reinterpret_cast<__nv_bfloat16*>(smOnes)[i] = __float2bfloat16_rn((i & 7) < 3 ? 1.f : 0.f);
+	fence_proxy_async(); // generic-proxy writes -> visible to the tensor core (async proxy)
 	if (warp == Cfg::EPI_WARPS + 1) {
 		asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(Cfg::TMEM_COLS) : "memory");
 		asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -210,6 +214,7 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 			if (elect_one()) {
 				tma_prefetch_desc(&tmap_q);
 				tma_prefetch_desc(&tmap_x);
+				tma_prefetch_desc(&tmap_xx);
 				mbar_expect_tx(a_full, NQB * nkb * TC_A_KB_BYTES);
 				for (int qb = 0; qb < NQB; ++qb)
 					for (uint32_t kb = 0; kb < nkb; ++kb)
@@ -223,8 +228,10 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 					const uint32_t s = it % NSTAGE, use = it / NSTAGE;
 					if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
 					if (elect_one()) {
-						mbar_expect_tx(&full[s], TC2_B_STAGE_BYTES);
-						tma_load_2d(smB + (size_t)s * TC2_B_STAGE_BYTES, &tmap_x, (int)(kb * TC_BK), (int)row, &full[s]);
+						const bool last = kb + 1 == nkb; // the tile's norm terms travel with its last k-block
+						mbar_expect_tx(&full[s], TC2_B_STAGE_BYTES + (last ? TC2_X_BYTES : 0));
+						tma_load_2d(smB + (size_t)s * TC2_STAGE_BYTES, &tmap_x, (int)(kb * TC_BK), (int)row, &full[s]);
+						if (last) tma_load_2d(smB + (size_t)s * TC2_STAGE_BYTES + TC2_B_STAGE_BYTES, &tmap_xx, 0, (int)row, &full[s]);
 					}
 					__syncwarp();
 				}
@@ -232,9 +239,12 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 		}
 	} else if (warp == Cfg::EPI_WARPS + 1) {
 		// ===================== MMA issuer (converged warp, one elected lane issues) =====================
+		// (A second issuer warp taking every other tile was tried: +3 %, and it needs 2*nkb <= NSTAGE or the parity
+		// waits alias — not kept.)
 		if (my_tiles) {
 			const uint32_t idesc = tc2_instr_desc();
 			const uint64_t a_desc0 = tc_smem_desc(smem_u32(smA)), b_desc0 = tc_smem_desc(smem_u32(smB));
+			const uint64_t ones_desc = tc_smem_desc_sw32(smem_u32(smOnes)), x_desc0 = tc_smem_desc_sw32(smem_u32(smB) + TC2_B_STAGE_BYTES);
 			mbar_wait(a_full, 0);
 			tc_fence_after();
 			uint32_t it = 0;
@@ -247,7 +257,8 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 					tc_fence_after();
 					if (elect_one()) {
 						// descriptors: the start-address field counts 16-byte units, so a k step of 16 bf16 (32 B) adds 2
-						const uint64_t bd0 = b_desc0 + (uint64_t)((s * TC2_B_STAGE_BYTES) >> 4);
+						const uint64_t bd0 = b_desc0 + (uint64_t)((s * TC2_STAGE_BYTES) >> 4);
+						const bool last = kb + 1 == nkb;
 #pragma unroll
 						for (int qb = 0; qb < NQB; ++qb) {
 							const uint32_t d_tmem = tmem_base + (acc * NQB + qb) * TC2_TN;
@@ -255,6 +266,8 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 #pragma unroll
 							for (int k = 0; k < TC_BK / TC_UMMA_K; ++k)
 								tc_mma(d_tmem, ad0 + 2 * k, bd0 + 2 * k, idesc, (kb | (uint32_t)k) != 0 ? 1u : 0u);
+							if (last) // + ||x||^2: [1 1 1 0..] x [xn_hi xn_mid xn_lo 0..], 32-byte operand rows
+								tc_mma(d_tmem, ones_desc, x_desc0 + (uint64_t)((s * TC2_STAGE_BYTES) >> 4), idesc, 1u);
 						}
 						tc_commit(&empty[s]);                        // stage reusable once these MMAs have read it
 						if (kb + 1 == nkb) tc_commit(&tm_full[acc]); // both query blocks' accumulators of this tile complete
@@ -279,11 +292,7 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 		t.cnt = 0;
 		t.cap = p.cap;
 		t.cbuf = p.cand + ((size_t)(qvalid ? qg : 0) * p.rsplit + split) * p.cap;
-		float* xs = xs_all + warp * TC2_TN;
 		float* sc = sc_all + warp * 1024 + lane; // slow-path scratch: value j of this lane at sc[j * 32]
-		float4 xnext = make_float4(0.f, 0.f, 0.f, 0.f);
-		if (my_tiles) xnext = __ldg(reinterpret_cast<const float4*>(p.xn + (size_t)t_begin * TC2_TN) + lane);
-		const uint64_t scale2 = pack_b64(__float_as_uint(p.scale), __float_as_uint(p.scale));
 		uint32_t gnext = f32_orderable(INF); // bound of the other splits, fetched one tile ahead (any stale value is valid)
 		for (uint32_t lt = 0; lt < my_tiles; ++lt) {
 			const uint32_t acc = lt & 1;
@@ -292,10 +301,6 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 				t.thr = fminf(t.thr, f32_from_orderable(gnext));
 				gnext = __ldcg(p.gthr + qg);
 			}
-			__syncwarp();
-			asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(xs) + lane * 16), "f"(xnext.x), "f"(xnext.y), "f"(xnext.z), "f"(xnext.w) : "memory");
-			__syncwarp();
-			if (lt + 1 < my_tiles) xnext = __ldg(reinterpret_cast<const float4*>(p.xn + (size_t)(row0 + TC2_TN)) + lane);
 			mbar_wait(&tm_full[acc], (lt >> 1) & 1);
 			tc_fence_after();
 			const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + (acc * NQB + qb) * TC2_TN;
@@ -305,14 +310,14 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 			tc_ld32_nowait(tbase + 32, dB);
 			tc_wait_ld(dA);
 			tc_wait_ld(dB);
-			const float mn0 = tc2_chunk_min(dA, xs, scale2);
+			const float mn0 = tc2_chunk_min(dA);
 			tc_ld32_nowait(tbase + 64, dA);
-			const float mn1 = tc2_chunk_min(dB, xs + 32, scale2);
+			const float mn1 = tc2_chunk_min(dB);
 			tc_ld32_nowait(tbase + 96, dB);
 			tc_wait_ld(dA);
 			tc_wait_ld(dB);
-			const float mn2 = tc2_chunk_min(dA, xs + 64, scale2);
-			const float mn3 = tc2_chunk_min(dB, xs + 96, scale2);
+			const float mn2 = tc2_chunk_min(dA);
+			const float mn3 = tc2_chunk_min(dB);
 			const uint32_t hm = (mn0 <= t.thr ? 1u : 0u) | (mn1 <= t.thr ? 2u : 0u) | (mn2 <= t.thr ? 4u : 0u) | (mn3 <= t.thr ? 8u : 0u);
 			// pass 2, rare: chunks in which some lane has a candidate are read again from TMEM (warp-collective load)
 			if (__any_sync(FULL, hm != 0)) {
@@ -321,7 +326,7 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 					if (!__any_sync(FULL, (hm >> c) & 1u)) continue;
 					tc_ld32_nowait(tbase + c * 32, dA);
 					tc_wait_ld(dA);
-					if ((hm >> c) & 1u) tc2_chunk_hits(t, dA, xs + c * 32, scale2, sc, row0 + c * 32);
+					if ((hm >> c) & 1u) tc2_chunk_hits(t, dA, sc, row0 + c * 32, p.n);
 				}
 			}
 			tc_fence_before();
@@ -557,7 +562,8 @@ __global__ void tc_check_exact_kernel(const TcStats* __restrict__ qs, float xmin
 	const float lo = fminf(xmin, f32_from_orderable(qs->vmin)), hi = fmaxf(xmax, f32_from_orderable(qs->vmax));
 	const float amax = fmaxf(fabsf(lo), fabsf(hi));
 	const double lim = 16777216.0;
-	const bool exact = !qs->inexact && amax <= 256.f && (double)d * (hi - lo) * (hi - lo) < lim && (double)d * amax * amax < lim;
+	// the accumulator runs through sum (-2 q_i) x_i (+ ||x||^2): every partial sum must stay an exact fp32 integer
+	const bool exact = !qs->inexact && amax <= 256.f && 2.0 * (double)d * amax * amax < lim;
 	if (!exact) atomicAdd(flags, 1u);
 }
 __global__ void tc_stats_init_kernel(TcStats* s) {

@@ -13,9 +13,15 @@ struct TcStats { uint32_t vmin, vmax, inexact, nmax; };
 //   mode 1 (exact): dst[kd] = bf16(x), zero padded
 //   mode 2 (split): seg = kd/3; base rows [xh | xl | xh], query rows [qh | qh | ql] with x = xh + xl (+ residual)
 // also: norm2[row] = sum x^2 (fp32), value statistics for the exactness decision.
+// scale (queries of the second form: -2 for L2, -1 for the inner product; exact, a power of two) multiplies every
+// written operand value. xx (base rows of the second form, may be null): bf16[rows][16] holding ||x||^2 as three bf16
+// terms hi+mid+lo (24 bits: exact for integer norms < 2^24), each HALVED and written to BOTH 16-byte halves of the
+// 32-byte row ([h/2 m/2 l/2 0 0 0 0 0 | h/2 m/2 l/2 0 0 0 0 0]) so that the extra MMA K-step against a row of
+// [1 1 1 0 0 0 0 0 | 1 1 1 0 0 0 0 0] adds ||x||^2 whatever the 32B-swizzle does to the two halves; zeros for IP.
 __global__ void tc_convert_kernel(const float* __restrict__ src, size_t src_stride, uint32_t d, size_t rows,
                                   __nv_bfloat16* __restrict__ dst, uint32_t kd, int mode, int is_query,
-                                  float* __restrict__ norm2, TcStats* __restrict__ stats) {
+                                  float* __restrict__ norm2, TcStats* __restrict__ stats, float scale = 1.f,
+                                  __nv_bfloat16* __restrict__ xx = nullptr, int xx_norm = 0) {
 	const size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const int lane = threadIdx.x & 31;
 	if (row >= rows) return;
@@ -30,11 +36,12 @@ __global__ void tc_convert_kernel(const float* __restrict__ src, size_t src_stri
 		const float hf = __bfloat162float(h);
 		if (mode == 2) {
 			const __nv_bfloat16 l = __float2bfloat16_rn(v - hf);
-			o[i] = h;
-			o[seg + i] = is_query ? h : l;
-			o[2 * seg + i] = is_query ? l : h;
+			const __nv_bfloat16 hs = __float2bfloat16_rn(scale * hf), ls = __float2bfloat16_rn(scale * __bfloat162float(l));
+			o[i] = hs;
+			o[seg + i] = is_query ? hs : ls;
+			o[2 * seg + i] = is_query ? ls : hs;
 		} else
-			o[i] = h;
+			o[i] = __float2bfloat16_rn(scale * hf);
 		if (i < d) {
 			s = fmaf(v, v, s);
 			mn = fminf(mn, v);
@@ -48,6 +55,17 @@ __global__ void tc_convert_kernel(const float* __restrict__ src, size_t src_stri
 		mn = fminf(mn, __shfl_xor_sync(FULL, mn, of));
 		mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, of));
 		bad |= __shfl_xor_sync(FULL, bad, of);
+	}
+	if (xx && lane < 16) {
+		float t = 0.f;
+		if (xx_norm) {
+			const float h = __bfloat162float(__float2bfloat16_rn(s));
+			const float mres = s - h, mm = __bfloat162float(__float2bfloat16_rn(mres));
+			const float lres = mres - mm, ll = __bfloat162float(__float2bfloat16_rn(lres));
+			const int j = lane & 7;
+			t = 0.5f * (j == 0 ? h : j == 1 ? mm : j == 2 ? ll : 0.f);
+		}
+		xx[row * 16 + lane] = __float2bfloat16_rn(t);
 	}
 	if (lane == 0) {
 		if (norm2) norm2[row] = s;
