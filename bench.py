@@ -39,6 +39,21 @@ WORKLOADS = {
 }
 
 
+def ncu_traffic(key):
+    """DRAM bytes (read + write) per launch of a kernel from the committed ncu --set full capture of the same kernel on
+    the C2 shape (profiles/r1_ncu_summary.json); None when there is no capture"""
+    try:
+        j = json.load(open(os.path.join(ROOT, "profiles", "r1_ncu_summary.json")))
+        for name, d in j.items():
+            if name.startswith(key):
+                unit = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
+                r, w = d["dram__bytes_read.sum"], d["dram__bytes_write.sum"]
+                return int(float(r[0]) * unit[r[1]] + float(w[0]) * unit[w[1]])
+    except Exception:  # noqa: BLE001
+        pass
+    return None
+
+
 def tensor_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -167,7 +182,9 @@ def scan_hbm_leg(eng, torch, dq, k, n_rows, d, stream, peak, peak_src, steps):
                         "base is 4x L2, passes back to back, no flush" % (n_rows, d),
             "passes": passes,
             "roofline": {"bound": "hbm", "kernel": "scan_topk_f32_kernel (1 query per pass)", "achieved": p1["achieved_GBs"],
-                         "peak": peak, "unit": "GB/s", "frac": p1["frac"], "traffic": None, "peak_source": peak_src,
+                         "peak": peak, "unit": "GB/s", "frac": p1["frac"],
+                         "traffic": ncu_traffic("scan_topk_f32_kernel<1") if (n_rows == 1_000_000 and d == 128) else None,
+                         "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": int(alg), "kernel_ms_per_launch": p1["kernel_ms"]}}
 
 
@@ -354,7 +371,9 @@ def main():
             tpeak, tpeak_sus, tsrc = tensor_peaks()
             roof = {"bound": "tensor", "kernel": "tc_filter2_kernel (tcgen05.mma bf16, fp32 accumulate in TMEM)", "achieved": achieved,
                     "peak": tpeak, "unit": "TFLOP/s", "frac": achieved / tpeak, "frac_of_sustained_peak": achieved / tpeak_sus,
-                    "traffic": None, "peak_source": tsrc, "algorithmic_flops_per_launch": flops, "kernel_ms_per_launch": hot_ms,
+                    "traffic": ncu_traffic("tc_filter2_kernel") if (args.workload == "c2" and world == 1 and m == 10000) else None,
+                    "traffic_unit": "DRAM bytes per launch (ncu --set full, profiles/r1_ncu_summary.json)",
+                    "peak_source": tsrc, "algorithmic_flops_per_launch": flops, "kernel_ms_per_launch": hot_ms,
                     "tc_mode": "bf16-exact" if st1["tc_mode"] == 1 else "two-term bf16 split", "kd": kd,
                     "note": "flops = 2*m*n*kd of the candidate filter; survivors (about k per query) are re-ranked in fp32 by K4. "
                             "peak = cuBLAS bf16 burst figure; frac_of_sustained_peak uses the seconds-long figure"}
