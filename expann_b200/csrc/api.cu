@@ -362,6 +362,8 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 	} else if (nm == "kprime") {
 		if (value < 0 || value > 128) return fail(h, EXPANN_ERR_ARG, "kprime must be in 0..128");
 		h->opt_kprime = (int)value;
+	} else if (nm == "tc_pair") {
+		h->opt_tc_pair = value != 0;
 	} else if (nm == "tc_v1") {
 		h->opt_tc_v1 = value != 0;
 	} else if (nm == "tc") {

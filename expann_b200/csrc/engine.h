@@ -63,6 +63,7 @@ struct expann_gpu {
 	expann::DevBuf tc_xb, tc_xn, tc_stats, tc_qstats, tc_qb, tc_qn, tc_thr, tc_cnt, tc_cand, tc_gthr, tc_sel, tc_xx;
 	CUtensorMap tmap_xb{}, tmap_xb128{}, tmap_xx{};
 	int opt_tc_v1 = 0; // force the chunked first form of K3 (tests)
+	int opt_tc_pair = 1; // pair form of K3 (clusters of two CTAs, tcgen05.mma.cta_group::2)
 	// quantised scan engine (K6 + K4)
 	int quantizer = 0;       // 0 = quantizer_simple<uint8_t>, 1 = quantizer_ranged_q8
 	int opt_kprime = 0;      // 0 = auto

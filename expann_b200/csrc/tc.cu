@@ -12,6 +12,7 @@
 #include "rerank.cuh"
 #include "tc_filter.cuh"
 #include "tc_filter2.cuh"
+#include "tc_filter3.cuh"
 #include "tc_prep.cuh"
 #include <algorithm>
 #include <cmath>
@@ -226,6 +227,20 @@ static int launch_filter2(expann_gpu* h, const CUtensorMap& tq, const Tc2Params&
 	return EXPANN_OK;
 }
 
+template <int NSTAGE>
+static int launch_filter_pair(expann_gpu* h, const CUtensorMap& tq, const Tc2Params& p, dim3 grid, cudaStream_t st) {
+	const size_t smem = Tc3Cfg::smem_bytes(p.kd, NSTAGE);
+	static thread_local int f_dev = -1, f_smem = 0;
+	if (f_dev != h->device || f_smem < (int)smem) {
+		EXPANN_CUDA(h, cudaFuncSetAttribute(tc_filter_pair_kernel<NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		f_dev = h->device;
+		f_smem = (int)smem;
+	}
+	tc_filter_pair_kernel<NSTAGE><<<grid, Tc3Cfg::THREADS, smem, st>>>(tq, h->tmap_xb128, h->tmap_xx, p); // __cluster_dims__(2,1,1)
+	EXPANN_CUDA(h, cudaGetLastError());
+	return EXPANN_OK;
+}
+
 // row splits of the second form: whole waves of CTAs (>= 97 % of the SM slots of the last wave used), as few
 // splits as that allows (every split warms its own bound up), at least 8 tiles per CTA
 static uint32_t tc2_pick_rsplit(uint32_t qblocks, uint32_t ntiles, int sms) {
@@ -252,11 +267,15 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	const int nqb = Tc2Cfg<2>::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024 && m > TC_BM ? 2 : 1;
 	int sms = 148;
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
-	const uint32_t qblocks = (uint32_t)((m + TC_BM * nqb - 1) / (TC_BM * nqb));
-	const uint32_t ntiles = (uint32_t)((h->n + TC2_TN - 1) / TC2_TN);
-	uint32_t rsplit = tc2_pick_rsplit(qblocks, ntiles, sms);
-	const uint32_t tiles_per_cta = (ntiles + rsplit - 1) / rsplit;
-	rsplit = (ntiles + tiles_per_cta - 1) / tiles_per_cta;
+	// pair form (tc_filter3.cuh): clusters of two CTAs, 256 queries x 256-row tiles per MMA; each CTA contributes two
+	// candidate buffers per row split (one per half tile)
+	const bool pair = h->opt_tc_pair && m > TC_BM && Tc3Cfg::smem_bytes(kd, 4) <= 227 * 1024;
+	const uint32_t qblocks = pair ? 2 * (uint32_t)((m + 255) / 256) : (uint32_t)((m + TC_BM * nqb - 1) / (TC_BM * nqb));
+	const uint32_t ntiles = (uint32_t)((h->n + (pair ? TC3_TN : TC2_TN) - 1) / (pair ? TC3_TN : TC2_TN));
+	uint32_t rows_split = tc2_pick_rsplit(qblocks, ntiles, sms);
+	const uint32_t tiles_per_cta = (ntiles + rows_split - 1) / rows_split;
+	rows_split = (ntiles + tiles_per_cta - 1) / tiles_per_cta;
+	const uint32_t rsplit = pair ? 2 * rows_split : rows_split; // candidate buffers per query
 	EXPANN_CUDA(h, h->tc_qb.ensure(m * (size_t)kd * 2));
 	EXPANN_CUDA(h, h->tc_qn.ensure(m * 4));
 	EXPANN_CUDA(h, h->tc_gthr.ensure(m * 4));
@@ -302,18 +321,20 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	p.eps_rel = eps_rel;
 	p.eps_abs = eps_abs;
 	p.xnorm_max = h->tc_xnorm_max;
-	dim3 grid(qblocks, rsplit);
+	dim3 grid(qblocks, rows_split);
 	cudaEvent_t t0 = timing_begin(h, st);
 	// ring depth: 6 slots of 20 KB when they fit beside the resident query tile(s), else 4 (split mode, d up to 128)
 	const bool deep = Tc2Cfg<1>::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024;
-	int rc = nqb == 2 ? launch_filter2<2, TC2_NSTAGE>(h, tq, p, grid, st)
-	         : deep   ? launch_filter2<1, TC2_NSTAGE>(h, tq, p, grid, st)
-	                  : launch_filter2<1, 4>(h, tq, p, grid, st);
+	int rc = pair     ? (Tc3Cfg::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024 ? launch_filter_pair<TC2_NSTAGE>(h, tq, p, grid, st)
+	                                                                     : launch_filter_pair<4>(h, tq, p, grid, st))
+	         : nqb == 2 ? launch_filter2<2, TC2_NSTAGE>(h, tq, p, grid, st)
+	         : deep     ? launch_filter2<1, TC2_NSTAGE>(h, tq, p, grid, st)
+	                    : launch_filter2<1, 4>(h, tq, p, grid, st);
 	timing_end(h, t0, st);
 	if (rc) return rc;
 	h->stats.tc_launches++;
-	h->stats.last_qtile = TC_BM * nqb;
-	h->stats.last_nsplit = rsplit;
+	h->stats.last_qtile = pair ? 256 : TC_BM * nqb;
+	h->stats.last_nsplit = rows_split;
 	if (rsplit > 32) // many cold splits per query: one block per query
 		tc_select2_block_kernel<1><<<(unsigned)m, 256, 0, st>>>(p.cand, p.cnt, TC2_CAP, rsplit, p.m, p.k, p.qn, eps_rel, eps_abs,
 		                                                        h->tc_xnorm_max, h->tc_sel.as<uint64_t>(), TC_PAD, flags);

@@ -14,9 +14,10 @@ def ex():
     return expann_b200
 
 
-def run(ex, base, q, k, metric=0, tc=1, id_offset=0, v1=0):
+def run(ex, base, q, k, metric=0, tc=1, id_offset=0, v1=0, pair=1):
     e = ex.BruteForceEngine(metric=metric, id_offset=id_offset)
     e.set_option("tc", tc)
+    e.set_option("tc_pair", pair)  # 1 (default): clusters of two CTAs, tcgen05.mma.cta_group::2; 0: single-CTA form
     e.set_option("tc_v1", v1)   # 1: force the chunked first form of K3 (otherwise used for k > 16 only)
     e.store_many_vectors(base)
     e.build()
@@ -130,3 +131,21 @@ def test_second_form_real_valued_splits(ex):
         assert st["tc_mode"] == 2 and st["tc_launches"] == 1 and st["tc_fallbacks"] == 0
         ids2, dists2, _, _ = run(ex, base, q, 10, metric=metric, tc=0)
         assert np.array_equal(ids, ids2) and np.array_equal(dists, dists2)
+
+
+@pytest.mark.parametrize("real", [False, True])
+def test_single_cta_form_still_exact(ex, real):
+    """the single-CTA second form (tc_pair = 0; also what batches of <= 128 queries use) against the pair form"""
+    rng = np.random.default_rng(11)
+    if real:
+        base = rng.standard_normal((90_000, 96)).astype(np.float32)
+        q = rng.standard_normal((600, 96)).astype(np.float32)
+    else:
+        base = rng.integers(0, 256, (90_000, 128)).astype(np.float32)
+        q = rng.integers(0, 256, (600, 128)).astype(np.float32)
+    a = run(ex, base, q, 10, pair=0)
+    b = run(ex, base, q, 10, pair=1)
+    assert a[3]["tc_launches"] == 1 and b[3]["tc_launches"] == 1 and a[3]["tc_fallbacks"] == 0 and b[3]["tc_fallbacks"] == 0
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    c = run(ex, base, q[:100], 10)   # <= 128 queries: single-CTA form, many cold splits
+    assert np.array_equal(c[0], a[0][:100]) and np.array_equal(c[1], a[1][:100])
