@@ -182,7 +182,7 @@ void expann_gpu_destroy(expann_gpu_t* h) {
 	timing_collect(h);
 	for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
 	if (h->base) cudaFree(h->base);
-	for (DevBuf* b : { &h->tc_xb, &h->tc_xn, &h->tc_stats, &h->tc_qstats, &h->tc_qb, &h->tc_qn, &h->tc_thr, &h->tc_cnt, &h->tc_cand, &h->tc_gthr, &h->tc_sel, &h->tc_xx, &h->scan_cnt })
+	for (DevBuf* b : { &h->tc_xb, &h->tc_xn, &h->tc_stats, &h->tc_qstats, &h->tc_qb, &h->tc_qn, &h->tc_thr, &h->tc_cnt, &h->tc_cand, &h->tc_gthr, &h->tc_sel, &h->tc_xx, &h->tc_seed, &h->scan_cnt })
 		b->release();
 	for (DevBuf* b : { &h->q_codes, &h->q_cnorm, &h->q_mm, &h->qq_codes, &h->qq_norm, &h->q_cand }) b->release();
 	for (DevBuf* b : { &h->g_bottom, &h->g_upper, &h->g_upper_idx, &h->g_upper_nl, &h->g_visited, &h->g_epoch, &h->g_codes })
@@ -364,6 +364,8 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 		h->opt_kprime = (int)value;
 	} else if (nm == "tc_pair") {
 		h->opt_tc_pair = value != 0;
+	} else if (nm == "tc_boot") {
+		h->opt_tc_boot = value != 0;
 	} else if (nm == "tc_v1") {
 		h->opt_tc_v1 = value != 0;
 	} else if (nm == "tc") {

@@ -272,13 +272,18 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	const bool pair = h->opt_tc_pair && m > TC_BM && Tc3Cfg::smem_bytes(kd, 4) <= 227 * 1024;
 	const uint32_t qblocks = pair ? 2 * (uint32_t)((m + 255) / 256) : (uint32_t)((m + TC_BM * nqb - 1) / (TC_BM * nqb));
 	const uint32_t ntiles = (uint32_t)((h->n + (pair ? TC3_TN : TC2_TN) - 1) / (pair ? TC3_TN : TC2_TN));
-	uint32_t rows_split = tc2_pick_rsplit(qblocks, ntiles, sms);
-	const uint32_t tiles_per_cta = (ntiles + rows_split - 1) / rows_split;
-	rows_split = (ntiles + tiles_per_cta - 1) / tiles_per_cta;
-	const uint32_t rsplit = pair ? 2 * rows_split : rows_split; // candidate buffers per query
+	// pair form, large bases: a short first launch over the leading boot_tiles tiles seeds every stream of the main launch
+	// with the k smallest a' found there (Tc2Params::seed_in) -- far fewer bound-tightening events in the main launch
+	const uint32_t boot_tiles = pair && h->opt_tc_boot && ntiles >= 512 ? std::min(64u, ntiles / 32u) : 0u;
+	const uint32_t main_tiles = ntiles - boot_tiles;
+	uint32_t rows_split = tc2_pick_rsplit(qblocks, main_tiles, sms);
+	const uint32_t tiles_per_cta = (main_tiles + rows_split - 1) / rows_split;
+	rows_split = (main_tiles + tiles_per_cta - 1) / tiles_per_cta;
+	const uint32_t rsplit = (pair ? 2 * rows_split : rows_split) + (boot_tiles ? 2u : 0u); // candidate buffers per query
 	EXPANN_CUDA(h, h->tc_qb.ensure(m * (size_t)kd * 2));
 	EXPANN_CUDA(h, h->tc_qn.ensure(m * 4));
 	EXPANN_CUDA(h, h->tc_gthr.ensure(m * 4));
+	if (boot_tiles) EXPANN_CUDA(h, h->tc_seed.ensure(m * 32 * 4));
 	EXPANN_CUDA(h, h->tc_cnt.ensure(m * (size_t)rsplit * 4 + 16));
 	EXPANN_CUDA(h, h->tc_cand.ensure(m * (size_t)rsplit * TC2_CAP * 8));
 	EXPANN_CUDA(h, h->tc_sel.ensure(m * (size_t)TC_PAD * 8 + 16));
@@ -314,9 +319,13 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	p.n = (uint32_t)h->n;
 	p.kd = kd;
 	p.k = (uint32_t)k;
-	p.ntiles = ntiles;
+	p.ntiles = main_tiles;
 	p.tiles_per_cta = tiles_per_cta;
 	p.rsplit = rsplit;
+	p.tile_first = boot_tiles;
+	p.buf_first = boot_tiles ? 2u : 0u;
+	p.seed_in = boot_tiles ? h->tc_seed.as<float>() : nullptr;
+	p.seed_out = nullptr;
 	p.scale = ip ? -1.f : -2.f;
 	p.eps_rel = eps_rel;
 	p.eps_abs = eps_abs;
@@ -325,6 +334,20 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	cudaEvent_t t0 = timing_begin(h, st);
 	// ring depth: 6 slots of 20 KB when they fit beside the resident query tile(s), else 4 (split mode, d up to 128)
 	const bool deep = Tc2Cfg<1>::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024;
+	if (boot_tiles) {
+		Tc2Params b = p;
+		b.ntiles = boot_tiles;
+		b.tiles_per_cta = boot_tiles;
+		b.tile_first = 0;
+		b.buf_first = 0;
+		b.seed_in = nullptr;
+		b.seed_out = h->tc_seed.as<float>();
+		const dim3 bgrid(qblocks, 1);
+		int brc = Tc3Cfg::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024 ? launch_filter_pair<TC2_NSTAGE>(h, tq, b, bgrid, st)
+		                                                            : launch_filter_pair<4>(h, tq, b, bgrid, st);
+		if (brc) return brc;
+		h->stats.tc_launches++;
+	}
 	int rc = pair     ? (Tc3Cfg::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024 ? launch_filter_pair<TC2_NSTAGE>(h, tq, p, grid, st)
 	                                                                     : launch_filter_pair<4>(h, tq, p, grid, st))
 	         : nqb == 2 ? launch_filter2<2, TC2_NSTAGE>(h, tq, p, grid, st)

@@ -41,6 +41,11 @@ struct Tc2Params {
 	uint32_t cap, m, n, kd, k;
 	uint32_t ntiles, tiles_per_cta, rsplit;
 	float scale, eps_rel, eps_abs, xnorm_max;
+	// pair form only: a short first launch over the leading tiles leaves every query's k smallest a' in seed_out; the main
+	// launch starts its lists from them (seed_in), so its streams do not each warm a bound up from +inf
+	uint32_t tile_first, buf_first; // this launch covers tiles [tile_first, tile_first + ntiles), buffers from buf_first
+	const float* seed_in;           // [m][2][16] or null
+	float* seed_out;                // [m][2][16] or null
 };
 
 __device__ __forceinline__ uint32_t tc2_instr_desc() { // kind::f16, bf16 x bf16 -> fp32, K-major A and B, M = 128, N = 128

@@ -138,7 +138,7 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 			__syncwarp();
 			uint32_t it = 0;
 			for (uint32_t lt = 0; lt < my_tiles; ++lt) {
-				const uint32_t row = (t_begin + lt) * TC3_TN + rank * TC2_TN; // this CTA's half of the tile
+				const uint32_t row = (p.tile_first + t_begin + lt) * TC3_TN + rank * TC2_TN; // this CTA's half of the tile
 				for (uint32_t kb = 0; kb < nkb; ++kb, ++it) {
 					const uint32_t s = it % NSTAGE, use = it / NSTAGE;
 					if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
@@ -226,17 +226,31 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 #pragma unroll
 		for (int j = 0; j < TC2_KK; ++j) t.v[j] = j < TC2_KK - (int)p.k ? -INF : INF;
 		t.thr = qvalid ? INF : -INF;
+		if (p.seed_in && qvalid) {
+			// the k smallest a' of the first launch's rows (two sorted lists, one per half tile): all of them sit in that
+			// launch's candidate buffers, so the k-th of their union with this stream's values bounds the final k-th
+			const float* s0 = p.seed_in + (size_t)qg * 32;
+#pragma unroll
+			for (int j = 0; j < TC2_KK; ++j) t.v[j] = s0[j];
+			for (int j = TC2_KK - (int)p.k; j < TC2_KK; ++j) {
+				const float aj = s0[16 + j];
+#pragma unroll
+				for (int i = TC2_KK - 1; i >= 1; --i) t.v[i] = fminf(t.v[i], fmaxf(t.v[i - 1], aj));
+				t.v[0] = fminf(t.v[0], aj);
+			}
+			t.thr = __fadd_ru(t.v[TC2_KK - 1], t.slack);
+		}
 		float pub = t.thr;
 		t.cnt = 0;
 		t.cap = p.cap;
-		const uint32_t bsplit = split * 2 + half;
+		const uint32_t bsplit = p.buf_first + split * 2 + half;
 		t.cbuf = p.cand + ((size_t)(qvalid ? qg : 0) * p.rsplit + bsplit) * p.cap;
 		float* sc = sc_all + warp * 1024 + lane;
 		const uint32_t tm_empty_l0 = mapa_u32(&tm_empty[0], 0), tm_empty_l1 = mapa_u32(&tm_empty[1], 0);
 		uint32_t gnext = f32_orderable(INF);
 		for (uint32_t lt = 0; lt < my_tiles; ++lt) {
 			const uint32_t acc = lt & 1;
-			const uint32_t row0 = (t_begin + lt) * TC3_TN + half * TC2_TN;
+			const uint32_t row0 = (p.tile_first + t_begin + lt) * TC3_TN + half * TC2_TN;
 			if (qvalid) {
 				t.thr = fminf(t.thr, f32_from_orderable(gnext));
 				gnext = __ldcg(p.gthr + qg);
@@ -244,35 +258,35 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 			mbar_wait(&tm_full[acc], (lt >> 1) & 1);
 			tc_fence_after();
 			const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * TC3_TN + half * TC2_TN;
+			// two chunks of 32 rows in flight; a chunk with a hit is handled while its values are still in registers (no
+			// second TMEM read), the next chunk's load is issued as soon as the registers are free. Rolled over the two
+			// passes so that the hit code exists twice, not four times.
 			uint32_t dA[32], dB[32];
 			tc_ld32_nowait(tbase, dA);
 			tc_ld32_nowait(tbase + 32, dB);
-			tc_wait_ld(dA);
-			tc_wait_ld(dB);
-			const float mn0 = tc2_chunk_min(dA);
-			tc_ld32_nowait(tbase + 64, dA);
-			const float mn1 = tc2_chunk_min(dB);
-			tc_ld32_nowait(tbase + 96, dB);
-			tc_wait_ld(dA);
-			tc_wait_ld(dB);
-			const float mn2 = tc2_chunk_min(dA);
-			const float mn3 = tc2_chunk_min(dB);
-			const uint32_t hm = (mn0 <= t.thr ? 1u : 0u) | (mn1 <= t.thr ? 2u : 0u) | (mn2 <= t.thr ? 4u : 0u) | (mn3 <= t.thr ? 8u : 0u);
-			if (__any_sync(FULL, hm != 0)) {
 #pragma unroll 1
-				for (int c = 0; c < 4; ++c) {
-					if (!__any_sync(FULL, (hm >> c) & 1u)) continue;
-					tc_ld32_nowait(tbase + c * 32, dA);
-					tc_wait_ld(dA);
-					if ((hm >> c) & 1u) tc2_chunk_hits(t, dA, sc, row0 + c * 32, p.n);
-				}
+			for (uint32_t c = 0; c < 4; c += 2) {
+				tc_wait_ld(dA);
+				tc_wait_ld(dB);
+				const float mnA = tc2_chunk_min(dA);
+				if (__any_sync(FULL, mnA <= t.thr)) tc2_chunk_hits(t, dA, sc, row0 + c * 32, p.n);
+				if (c == 0) tc_ld32_nowait(tbase + 64, dA);
+				const float mnB = tc2_chunk_min(dB);
+				if (__any_sync(FULL, mnB <= t.thr)) tc2_chunk_hits(t, dB, sc, row0 + c * 32 + 32, p.n);
+				if (c == 0) tc_ld32_nowait(tbase + 96, dB);
 			}
 			tc_fence_before();
 			__syncwarp();
 			if (lane == 0) mbar_arrive_cluster(acc ? tm_empty_l1 : tm_empty_l0); // all 16 epilogue warps of the pair -> leader
 			if (t.thr < pub) { atomicMin(p.gthr + qg, f32_orderable(t.thr)); pub = t.thr; }
 		}
-		if (qvalid) p.cnt[(size_t)qg * p.rsplit + bsplit] = t.cnt;
+		if (qvalid) {
+			p.cnt[(size_t)qg * p.rsplit + bsplit] = t.cnt;
+			if (p.seed_out) {
+#pragma unroll
+				for (int j = 0; j < TC2_KK; ++j) p.seed_out[(size_t)qg * 32 + half * 16 + j] = t.v[j];
+			}
+		}
 	}
 	tc_fence_before();
 	cluster_sync_all(); // nobody leaves (or frees TMEM) while the peer may still read its shared memory / arrive on its barriers
