@@ -369,9 +369,11 @@ def main():
             flops = 2.0 * m * (hi - lo) * kd
             achieved = flops / (hot_ms * 1e-3) / 1e12
             tpeak, tpeak_sus, tsrc = tensor_peaks()
-            roof = {"bound": "tensor", "kernel": "tc_filter2_kernel (tcgen05.mma bf16, fp32 accumulate in TMEM)", "achieved": achieved,
+            kname = "tc_filter_pair_kernel" if qt == 256 else "tc_filter2_kernel"
+            roof = {"bound": "tensor", "kernel": kname + (" (tcgen05.mma.cta_group::2 bf16, fp32 accumulate in TMEM)" if qt == 256 else
+                                                          " (tcgen05.mma bf16, fp32 accumulate in TMEM)"), "achieved": achieved,
                     "peak": tpeak, "unit": "TFLOP/s", "frac": achieved / tpeak, "frac_of_sustained_peak": achieved / tpeak_sus,
-                    "traffic": ncu_traffic("tc_filter2_kernel") if (args.workload == "c2" and world == 1 and m == 10000) else None,
+                    "traffic": ncu_traffic(kname) if (args.workload == "c2" and world == 1 and m == 10000) else None,
                     "traffic_unit": "DRAM bytes per launch (ncu --set full, profiles/r1_ncu_summary.json)",
                     "peak_source": tsrc, "algorithmic_flops_per_launch": flops, "kernel_ms_per_launch": hot_ms,
                     "tc_mode": "bf16-exact" if st1["tc_mode"] == 1 else "two-term bf16 split", "kd": kd,

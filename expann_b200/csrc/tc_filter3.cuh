@@ -258,26 +258,29 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 			mbar_wait(&tm_full[acc], (lt >> 1) & 1);
 			tc_fence_after();
 			const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * TC3_TN + half * TC2_TN;
-			// two chunks of 32 rows in flight; a chunk with a hit is handled while its values are still in registers (no
-			// second TMEM read), the next chunk's load is issued as soon as the registers are free. Rolled over the two
-			// passes so that the hit code exists twice, not four times.
-			uint32_t dA[32], dB[32];
+			// the thread's 128 accumulator columns go to registers in one go and the accumulator is handed back to the MMA
+			// warp BEFORE they are looked at: a warp that has hits to work through no longer holds the other 15 warps of
+			// the pair (and the next MMA) up, it only has to be back in time for its next tile
+			uint32_t dA[32], dB[32], dC[32], dD[32];
 			tc_ld32_nowait(tbase, dA);
 			tc_ld32_nowait(tbase + 32, dB);
-#pragma unroll 1
-			for (uint32_t c = 0; c < 4; c += 2) {
-				tc_wait_ld(dA);
-				tc_wait_ld(dB);
-				const float mnA = tc2_chunk_min(dA);
-				if (__any_sync(FULL, mnA <= t.thr)) tc2_chunk_hits(t, dA, sc, row0 + c * 32, p.n);
-				if (c == 0) tc_ld32_nowait(tbase + 64, dA);
-				const float mnB = tc2_chunk_min(dB);
-				if (__any_sync(FULL, mnB <= t.thr)) tc2_chunk_hits(t, dB, sc, row0 + c * 32 + 32, p.n);
-				if (c == 0) tc_ld32_nowait(tbase + 96, dB);
-			}
+			tc_ld32_nowait(tbase + 64, dC);
+			tc_ld32_nowait(tbase + 96, dD);
+			tc_wait_ld(dA);
+			tc_wait_ld(dB);
+			tc_wait_ld(dC);
+			tc_wait_ld(dD);
 			tc_fence_before();
 			__syncwarp();
 			if (lane == 0) mbar_arrive_cluster(acc ? tm_empty_l1 : tm_empty_l0); // all 16 epilogue warps of the pair -> leader
+			const float mnA = tc2_chunk_min(dA);
+			if (__any_sync(FULL, mnA <= t.thr)) tc2_chunk_hits(t, dA, sc, row0, p.n);
+			const float mnB = tc2_chunk_min(dB);
+			if (__any_sync(FULL, mnB <= t.thr)) tc2_chunk_hits(t, dB, sc, row0 + 32, p.n);
+			const float mnC = tc2_chunk_min(dC);
+			if (__any_sync(FULL, mnC <= t.thr)) tc2_chunk_hits(t, dC, sc, row0 + 64, p.n);
+			const float mnD = tc2_chunk_min(dD);
+			if (__any_sync(FULL, mnD <= t.thr)) tc2_chunk_hits(t, dD, sc, row0 + 96, p.n);
 			if (t.thr < pub) { atomicMin(p.gthr + qg, f32_orderable(t.thr)); pub = t.thr; }
 		}
 		if (qvalid) {

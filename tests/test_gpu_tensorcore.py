@@ -93,7 +93,7 @@ def test_shard_offset_and_small_batches(ex, oracle):
     ids, dists, _, st = run(ex, base, q[:12], 10)       # below tc_min_batch (16): SIMT path
     assert st["tc_launches"] == 0 and np.array_equal(ids, oi[:12])
     ids, dists, _, st = run(ex, base, q[:100], 10)      # small batch on the tensor-core path: many cold row splits
-    assert st["tc_launches"] == 1 and np.array_equal(ids, oi[:100]) and np.array_equal(dists, od[:100])
+    assert st["tc_launches"] in (1, 2) and np.array_equal(ids, oi[:100]) and np.array_equal(dists, od[:100])
 
 
 def test_first_form_still_exact(ex, oracle):
@@ -115,7 +115,7 @@ def test_second_form_many_splits(ex, k):
     base = rng.integers(0, 256, (300_001, 128)).astype(np.float32)
     q = rng.integers(0, 256, (1300, 128)).astype(np.float32)
     ids, dists, counts, st = run(ex, base, q, k)
-    assert st["tc_launches"] == 1 and st["tc_fallbacks"] == 0 and st["last_nsplit"] > 1
+    assert st["tc_launches"] in (1, 2) and st["tc_fallbacks"] == 0 and st["last_nsplit"] > 1
     ids2, dists2, counts2, st2 = run(ex, base, q, k, tc=0)
     assert st2["tc_launches"] == 0
     assert np.array_equal(ids, ids2) and np.array_equal(dists, dists2) and np.array_equal(counts, counts2)
@@ -128,7 +128,7 @@ def test_second_form_real_valued_splits(ex):
     q = rng.standard_normal((700, 96)).astype(np.float32)
     for metric in (0, 1):
         ids, dists, _, st = run(ex, base, q, 10, metric=metric)
-        assert st["tc_mode"] == 2 and st["tc_launches"] == 1 and st["tc_fallbacks"] == 0
+        assert st["tc_mode"] == 2 and st["tc_launches"] in (1, 2) and st["tc_fallbacks"] == 0
         ids2, dists2, _, _ = run(ex, base, q, 10, metric=metric, tc=0)
         assert np.array_equal(ids, ids2) and np.array_equal(dists, dists2)
 
@@ -145,7 +145,7 @@ def test_single_cta_form_still_exact(ex, real):
         q = rng.integers(0, 256, (600, 128)).astype(np.float32)
     a = run(ex, base, q, 10, pair=0)
     b = run(ex, base, q, 10, pair=1)
-    assert a[3]["tc_launches"] == 1 and b[3]["tc_launches"] == 1 and a[3]["tc_fallbacks"] == 0 and b[3]["tc_fallbacks"] == 0
+    assert a[3]["tc_launches"] in (1, 2) and b[3]["tc_launches"] in (1, 2) and a[3]["tc_fallbacks"] == 0 and b[3]["tc_fallbacks"] == 0
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
     c = run(ex, base, q[:100], 10)   # <= 128 queries: single-CTA form, many cold splits
     assert np.array_equal(c[0], a[0][:100]) and np.array_equal(c[1], a[1][:100])
