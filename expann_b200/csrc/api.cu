@@ -365,7 +365,7 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 	} else if (nm == "tc_pair") {
 		h->opt_tc_pair = value != 0;
 	} else if (nm == "tc_boot") {
-		h->opt_tc_boot = value != 0;
+		h->opt_tc_boot = (int)value; // 0 off, 1 bf16-exact mode only (default), 2 both modes
 	} else if (nm == "tc_v1") {
 		h->opt_tc_v1 = value != 0;
 	} else if (nm == "tc") {
