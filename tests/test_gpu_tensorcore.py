@@ -149,3 +149,45 @@ def test_single_cta_form_still_exact(ex, real):
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
     c = run(ex, base, q[:100], 10)   # <= 128 queries: single-CTA form, many cold splits
     assert np.array_equal(c[0], a[0][:100]) and np.array_equal(c[1], a[1][:100])
+
+
+@pytest.mark.parametrize("n,m", [(100, 129), (256, 256), (257, 257), (32768, 130), (33000, 511), (70001, 1025)])
+def test_pair_form_edges(ex, n, m):
+    """pair form at its boundaries: a cluster whose second CTA holds 1 query, bases smaller than / equal to / one over a
+    256-row tile, the smallest base that gets a seeding launch (128 tiles); every case against the SIMT scan, both
+    metrics, integer-valued and real-valued rows"""
+    rng = np.random.default_rng(n + m)
+    for real in (False, True):
+        if real:
+            base = rng.standard_normal((n, 64)).astype(np.float32)
+            q = rng.standard_normal((m, 64)).astype(np.float32)
+        else:
+            base = rng.integers(0, 256, (n, 128)).astype(np.float32)
+            q = rng.integers(0, 256, (m, 128)).astype(np.float32)
+        for metric in (0, 1):
+            a = run(ex, base, q, 10, metric=metric)
+            b = run(ex, base, q, 10, metric=metric, tc=0)
+            assert a[3]["tc_launches"] >= 1 and a[3]["last_qtile"] == 256 and b[3]["tc_launches"] == 0
+            assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+
+
+def test_pair_form_seeded_ties_and_overflow(ex):
+    """seeding launch + main launch on a base of heavy duplicates (ties at the k-th value, broken by id) and on rows
+    ordered far-to-near (candidate buffers overflow, the batch falls back to the SIMT scan): both must equal the SIMT
+    result bit for bit"""
+    rng = np.random.default_rng(21)
+    pool = rng.integers(0, 256, (2000, 128)).astype(np.float32)
+    base = pool[rng.integers(0, 2000, 150_000)]
+    q = rng.integers(0, 256, (300, 128)).astype(np.float32)
+    a = run(ex, base, q, 10)
+    b = run(ex, base, q, 10, tc=0)
+    assert a[3]["tc_launches"] == 2
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    base2 = rng.integers(0, 256, (150_000, 32)).astype(np.float32)
+    c = np.rint(base2.mean(0))
+    base2 = np.ascontiguousarray(base2[np.argsort(-((base2 - c) ** 2).sum(1))])
+    q2 = np.ascontiguousarray(np.tile(c, (300, 1)) + rng.integers(-2, 3, (300, 32))).astype(np.float32)
+    a = run(ex, base2, q2, 10)
+    b = run(ex, base2, q2, 10, tc=0)
+    assert a[3]["tc_launches"] >= 1
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
