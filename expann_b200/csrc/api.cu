@@ -364,6 +364,9 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 		h->opt_kprime = (int)value;
 	} else if (nm == "tc_pair") {
 		h->opt_tc_pair = value != 0;
+	} else if (nm == "tc_astream") {
+		if (value < 0 || value > 2) return fail(h, EXPANN_ERR_ARG, "tc_astream must be 0, 1 or 2");
+		h->opt_tc_astream = (int)value;
 	} else if (nm == "tc_boot") {
 		h->opt_tc_boot = (int)value; // 0 off, 1 bf16-exact mode only (default), 2 both modes
 	} else if (nm == "tc_v1") {

@@ -64,6 +64,7 @@ struct expann_gpu {
 	CUtensorMap tmap_xb{}, tmap_xb128{}, tmap_xx{};
 	int opt_tc_v1 = 0; // force the chunked first form of K3 (tests)
 	int opt_tc_pair = 1; // pair form of K3 (clusters of two CTAs, tcgen05.mma.cta_group::2)
+	int opt_tc_astream = 1; // pair form with the query operand streamed through the ring: 0 off, 1 when nothing else fits, 2 always
 	int opt_tc_boot = 1; // pair form: seeding launch over the leading tiles of a large base
 	// quantised scan engine (K6 + K4)
 	int quantizer = 0;       // 0 = quantizer_simple<uint8_t>, 1 = quantizer_ranged_q8
@@ -106,6 +107,7 @@ int graph_read_distcomps(expann_gpu* h);
 // tc.cu
 int tc_finalize(expann_gpu* h);
 int launch_scan_tc(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);
+bool tc_first_form_fits(const expann_gpu* h); // the chunked first form of K3 keeps the query tile resident
 // quant.cu
 int quant_finalize(expann_gpu* h);
 int launch_quant_scan(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);

@@ -96,7 +96,9 @@ int launch_scan_f32(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 	if (h->tc_mode && h->opt_tc && k <= 128) {
 		// second form of K3 (k <= 16, single launch) pays from tc_min_batch queries on; the chunked first form (k <= 128)
 		// has ~10 launches and host round trips per batch and only pays for large batches
-		const bool second = k <= 16 && !h->opt_tc_v1;
+		const bool v1_fits = tc_first_form_fits(h); // resident query tile: d <= 128 real-valued
+		const bool second = k <= 16 && (!h->opt_tc_v1 || !v1_fits);
+		if (!second && !v1_fits) return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st);
 		const size_t need = second ? (size_t)h->opt_tc_min_batch : std::max<size_t>((size_t)h->opt_tc_min_batch, 512);
 		if (m >= need) return launch_scan_tc(h, d_q, m, k, d_keys_out, st);
 	}

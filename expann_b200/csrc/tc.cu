@@ -54,7 +54,8 @@ int tc_finalize(expann_gpu* h) {
 	if (!h->opt_tc || h->cfg.engine != EXPANN_ENGINE_BRUTE_FORCE) return EXPANN_OK;
 	cudaStream_t st = h->stream;
 	const uint32_t seg = (uint32_t)((h->d + 63) / 64 * 64);
-	if (tc_smem_bytes(3 * seg, TC_NSTAGE_SPLIT) > 227 * 1024) return EXPANN_OK; // d too large for the resident query tile
+	// d too large for a resident query tile: only the streamed-A pair form (tc_filter3.cuh, ASTREAM) can take it
+	if (tc_smem_bytes(3 * seg, TC_NSTAGE_SPLIT) > 227 * 1024 && !h->opt_tc_astream) return EXPANN_OK;
 	const size_t n_pad = (h->n + TC_BN - 1) / TC_BN * TC_BN;
 	EXPANN_CUDA(h, h->tc_xn.ensure(n_pad * 4));
 	for (int mode = 1; mode <= 2; ++mode) {
@@ -75,7 +76,9 @@ int tc_finalize(expann_gpu* h) {
 		h->tc_xnorm_max = std::sqrt(f32_from_orderable(s.nmax));
 		h->tc_kd = kd;
 		h->tc_mode = mode;
-		if (mode == 1 && !s.inexact) break; // integer, bf16-exact base: single GEMM, error bound 0
+		// integer, bf16-exact base whose dot products stay below 2^24: single GEMM, error bound 0
+		const float amax = std::max(std::fabs(h->tc_xmin), std::fabs(h->tc_xmax));
+		if (mode == 1 && !s.inexact && 2.0 * (double)h->d * amax * amax < 16777216.0) break;
 	}
 	if (n_pad > h->n) {
 		tc_fill_kernel<<<(unsigned)((n_pad - h->n + 255) / 256), 256, 0, st>>>(h->tc_xn.as<float>(), h->n, n_pad, nanf(""));
@@ -125,7 +128,8 @@ static int tc_batch(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 		const bool exact = !s.inexact && amax <= 256.f && dd * (hi - lo) * (hi - lo) < lim && dd * amax * amax < lim;
 		if (!exact) { *fell_back = true; return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st); }
 	} else {
-		eps_rel = 1.0f / 16384.0f;                                        // two-term bf16 split: < 2^-15 per product, doubled
+		// two-term split: 3 * 2^-18 for the dropped terms + fp32 accumulation over kd/16 MMA steps; 2^-14 covers kd <= 1024
+		eps_rel = (1.0f / 16384.0f) * std::max(1.0f, (float)kd / 1024.0f);                                        // two-term bf16 split: < 2^-15 per product, doubled
 		eps_abs = 1e-6f * (h->tc_xnorm_max * h->tc_xnorm_max + 1e-30f);   // fp32 rounding of ||x||^2 and of the final fma
 	}
 	CUtensorMap tq;
@@ -227,16 +231,16 @@ static int launch_filter2(expann_gpu* h, const CUtensorMap& tq, const Tc2Params&
 	return EXPANN_OK;
 }
 
-template <int NSTAGE>
+template <int NSTAGE, bool ASTREAM = false>
 static int launch_filter_pair(expann_gpu* h, const CUtensorMap& tq, const Tc2Params& p, dim3 grid, cudaStream_t st) {
-	const size_t smem = Tc3Cfg::smem_bytes(p.kd, NSTAGE);
+	const size_t smem = Tc3Cfg::smem_bytes(p.kd, NSTAGE, ASTREAM);
 	static thread_local int f_dev = -1, f_smem = 0;
 	if (f_dev != h->device || f_smem < (int)smem) {
-		EXPANN_CUDA(h, cudaFuncSetAttribute(tc_filter_pair_kernel<NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		EXPANN_CUDA(h, (cudaFuncSetAttribute(tc_filter_pair_kernel<NSTAGE, ASTREAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)));
 		f_dev = h->device;
 		f_smem = (int)smem;
 	}
-	tc_filter_pair_kernel<NSTAGE><<<grid, Tc3Cfg::THREADS, smem, st>>>(tq, h->tmap_xb128, h->tmap_xx, p); // __cluster_dims__(2,1,1)
+	tc_filter_pair_kernel<NSTAGE, ASTREAM><<<grid, Tc3Cfg::THREADS, smem, st>>>(tq, h->tmap_xb128, h->tmap_xx, p); // __cluster_dims__(2,1,1)
 	EXPANN_CUDA(h, cudaGetLastError());
 	return EXPANN_OK;
 }
@@ -269,7 +273,9 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
 	// pair form (tc_filter3.cuh): clusters of two CTAs, 256 queries x 256-row tiles per MMA; each CTA contributes two
 	// candidate buffers per row split (one per half tile)
-	const bool pair = h->opt_tc_pair && m > TC_BM && Tc3Cfg::smem_bytes(kd, 4) <= 227 * 1024;
+	// streamed-A pair form: the only one for operand rows too long for a resident query tile (any batch size then)
+	const bool astream = Tc2Cfg<1>::smem_bytes(kd, 4) > 227 * 1024 || h->opt_tc_astream == 2;
+	const bool pair = astream || (h->opt_tc_pair && m > TC_BM && Tc3Cfg::smem_bytes(kd, 4) <= 227 * 1024);
 	const uint32_t qblocks = pair ? 2 * (uint32_t)((m + 255) / 256) : (uint32_t)((m + TC_BM * nqb - 1) / (TC_BM * nqb));
 	const uint32_t ntiles = (uint32_t)((h->n + (pair ? TC3_TN : TC2_TN) - 1) / (pair ? TC3_TN : TC2_TN));
 	// pair form, large bases: a short first launch over the leading boot_tiles tiles seeds every stream of the main launch
@@ -302,7 +308,8 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 		tc_check_exact_kernel<<<1, 1, 0, st>>>(h->tc_qstats.as<TcStats>(), h->tc_xmin, h->tc_xmax, (float)h->d, flags);
 		h->stats.aux_launches++;
 	} else {
-		eps_rel = 1.0f / 16384.0f;
+		// two-term split: 3 * 2^-18 for the dropped terms + fp32 accumulation over kd/16 MMA steps; 2^-14 covers kd <= 1024
+		eps_rel = (1.0f / 16384.0f) * std::max(1.0f, (float)kd / 1024.0f);
 		eps_abs = 1e-6f * (h->tc_xnorm_max * h->tc_xnorm_max + 1e-30f);
 	}
 	CUtensorMap tq;
@@ -344,12 +351,14 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 		b.seed_in = nullptr;
 		b.seed_out = h->tc_seed.as<float>();
 		const dim3 bgrid(qblocks, 1);
-		int brc = Tc3Cfg::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024 ? launch_filter_pair<TC2_NSTAGE>(h, tq, b, bgrid, st)
-		                                                            : launch_filter_pair<4>(h, tq, b, bgrid, st);
+		int brc = astream                                              ? launch_filter_pair<5, true>(h, tq, b, bgrid, st)
+		          : Tc3Cfg::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024 ? launch_filter_pair<TC2_NSTAGE>(h, tq, b, bgrid, st)
+		                                                              : launch_filter_pair<4>(h, tq, b, bgrid, st);
 		if (brc) return brc;
 		h->stats.tc_launches++;
 	}
-	int rc = pair     ? (Tc3Cfg::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024 ? launch_filter_pair<TC2_NSTAGE>(h, tq, p, grid, st)
+	int rc = astream  ? launch_filter_pair<5, true>(h, tq, p, grid, st)
+	         : pair   ? (Tc3Cfg::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024 ? launch_filter_pair<TC2_NSTAGE>(h, tq, p, grid, st)
 	                                                                     : launch_filter_pair<4>(h, tq, p, grid, st))
 	         : nqb == 2 ? launch_filter2<2, TC2_NSTAGE>(h, tq, p, grid, st)
 	         : deep     ? launch_filter2<1, TC2_NSTAGE>(h, tq, p, grid, st)
@@ -402,11 +411,13 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 }
 
 // entry used by the brute-force engine for large batches
+bool tc_first_form_fits(const expann_gpu* h) { return tc_smem_bytes(h->tc_kd, h->tc_mode == 1 ? TC_NSTAGE_EXACT : TC_NSTAGE_SPLIT) <= 227 * 1024; }
+
 int launch_scan_tc(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st) {
 	for (size_t q0 = 0; q0 < m; q0 += TC_QBATCH) {
 		const size_t mb = std::min<size_t>(TC_QBATCH, m - q0);
 		bool fb = false;
-		const bool v2 = k <= TC2_KK && !h->opt_tc_v1;
+		const bool v2 = k <= TC2_KK && (!h->opt_tc_v1 || !tc_first_form_fits(h));
 		if (int rc = v2 ? tc_batch2(h, d_q + q0 * h->d_pad, mb, k, d_keys_out + q0 * k, st, &fb)
 		                : tc_batch(h, d_q + q0 * h->d_pad, mb, k, d_keys_out + q0 * k, st, &fb))
 			return rc;

@@ -69,24 +69,31 @@ __device__ __forceinline__ uint32_t tc3_instr_desc() { // kind::f16, bf16 x bf16
 struct Tc3Cfg {
 	static constexpr int EPI_WARPS = 8;
 	static constexpr int THREADS = 32 * (EPI_WARPS + 2);
-	static size_t smem_bytes(uint32_t kd, int nstage) {
-		return 1024 + (size_t)(kd / TC_BK) * TC_A_KB_BYTES + 4096 + (size_t)nstage * TC2_STAGE_BYTES + (size_t)EPI_WARPS * 4096 +
+	// astream: the query operand is not resident; its k-blocks travel through the ring beside the row tiles
+	static size_t smem_bytes(uint32_t kd, int nstage, bool astream = false) {
+		return 1024 + (astream ? 0 : (size_t)(kd / TC_BK) * TC_A_KB_BYTES) + 4096 +
+		       (size_t)nstage * (TC2_STAGE_BYTES + (astream ? TC_A_KB_BYTES : 0)) + (size_t)EPI_WARPS * 4096 +
 		       (size_t)(1 + 2 * nstage + 4) * 8 + 16;
 	}
 };
 
-// p.rsplit = buffers per query = 2 * gridDim.y; p.ntiles / p.tiles_per_cta count 256-row tiles
-template <int NSTAGE>
+// p.rsplit = buffers per query = 2 * gridDim.y; p.ntiles / p.tiles_per_cta count 256-row tiles.
+// ASTREAM = false: each CTA's 128 queries (all k-blocks) stay resident in shared memory (d <= 128 real-valued, <= 384
+// bf16-exact). ASTREAM = true: any d -- a ring slot carries [A k-block 16 KB | B k-block 16 KB | norm terms 4 KB], the
+// classic GEMM main loop (A comes from L2 again for every row tile: 64 B/clk per SM of L2 -> shared memory traffic).
+template <int NSTAGE, bool ASTREAM = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Tc3Cfg::THREADS, 1)
 tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
                       const __grid_constant__ CUtensorMap tmap_xx, const Tc2Params p) {
 	extern __shared__ uint8_t tc_smem_raw[];
 	uint8_t* smem = (uint8_t*)(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
 	const uint32_t nkb = p.kd / TC_BK;
-	uint8_t* smA = smem;                                   // [nkb][128 q][64 bf16]
-	uint8_t* smOnes = smA + (size_t)nkb * TC_A_KB_BYTES;   // [128 q][16 bf16]
-	uint8_t* smB = smOnes + 4096;                          // [NSTAGE]{[128 rows][64 bf16], [128 rows][16 bf16]}
-	float* sc_all = reinterpret_cast<float*>(smB + (size_t)NSTAGE * TC2_STAGE_BYTES);
+	constexpr uint32_t STG = TC2_STAGE_BYTES + (ASTREAM ? TC_A_KB_BYTES : 0); // ring slot
+	constexpr uint32_t BOFF = ASTREAM ? TC_A_KB_BYTES : 0;                    // B inside the slot; norm terms follow B
+	uint8_t* smA = smem;                                                    // [nkb][128 q][64 bf16] (resident form)
+	uint8_t* smOnes = smA + (ASTREAM ? 0 : (size_t)nkb * TC_A_KB_BYTES);    // [128 q][16 bf16]
+	uint8_t* smB = smOnes + 4096;                                           // [NSTAGE] slots
+	float* sc_all = reinterpret_cast<float*>(smB + (size_t)NSTAGE * STG);
 	uint64_t* bars = reinterpret_cast<uint64_t*>(sc_all + Tc3Cfg::EPI_WARPS * 1024);
 	uint64_t* a_full = bars;
 	uint64_t* full = bars + 1;
@@ -131,9 +138,11 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 				tma_prefetch_desc(&tmap_q);
 				tma_prefetch_desc(&tmap_x);
 				tma_prefetch_desc(&tmap_xx);
-				if (leader) mbar_expect_tx(a_full, 2 * nkb * TC_A_KB_BYTES);
-				for (uint32_t kb = 0; kb < nkb; ++kb)
-					tma_load_2d_2sm(smA + (size_t)kb * TC_A_KB_BYTES, &tmap_q, (int)(kb * TC_BK), (int)q0, a_full_l);
+				if (!ASTREAM) {
+					if (leader) mbar_expect_tx(a_full, 2 * nkb * TC_A_KB_BYTES);
+					for (uint32_t kb = 0; kb < nkb; ++kb)
+						tma_load_2d_2sm(smA + (size_t)kb * TC_A_KB_BYTES, &tmap_q, (int)(kb * TC_BK), (int)q0, a_full_l);
+				}
 			}
 			__syncwarp();
 			uint32_t it = 0;
@@ -145,9 +154,10 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 					if (elect_one()) {
 						const bool last = kb + 1 == nkb;
 						const uint32_t full_l = mapa_u32(&full[s], 0);
-						if (leader) mbar_expect_tx(&full[s], 2 * (TC2_B_STAGE_BYTES + (last ? TC2_X_BYTES : 0)));
-						tma_load_2d_2sm(smB + (size_t)s * TC2_STAGE_BYTES, &tmap_x, (int)(kb * TC_BK), (int)row, full_l);
-						if (last) tma_load_2d_2sm(smB + (size_t)s * TC2_STAGE_BYTES + TC2_B_STAGE_BYTES, &tmap_xx, 0, (int)row, full_l);
+						if (leader) mbar_expect_tx(&full[s], 2 * (BOFF + TC2_B_STAGE_BYTES + (last ? TC2_X_BYTES : 0)));
+						if (ASTREAM) tma_load_2d_2sm(smB + (size_t)s * STG, &tmap_q, (int)(kb * TC_BK), (int)q0, full_l);
+						tma_load_2d_2sm(smB + (size_t)s * STG + BOFF, &tmap_x, (int)(kb * TC_BK), (int)row, full_l);
+						if (last) tma_load_2d_2sm(smB + (size_t)s * STG + BOFF + TC2_B_STAGE_BYTES, &tmap_xx, 0, (int)row, full_l);
 					}
 					__syncwarp();
 				}
@@ -157,11 +167,14 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 		// ===================== MMA issuer (leader CTA only) =====================
 		if (my_tiles && leader) {
 			const uint32_t idesc = tc3_instr_desc();
-			const uint64_t a_desc0 = tc_smem_desc(smem_u32(smA)), b_desc0 = tc_smem_desc(smem_u32(smB));
-			const uint64_t ones_desc = tc_smem_desc_sw32(smem_u32(smOnes)), x_desc0 = tc_smem_desc_sw32(smem_u32(smB) + TC2_B_STAGE_BYTES);
-			mbar_wait(a_full, 0);
-			tc_fence_after();
-			if (nkb == 2 && NSTAGE == 6) {
+			const uint64_t a_desc0 = tc_smem_desc(smem_u32(smA)), b_desc0 = tc_smem_desc(smem_u32(smB) + BOFF);
+			const uint64_t as_desc0 = tc_smem_desc(smem_u32(smB)); // streamed A: first 16 KB of a slot
+			const uint64_t ones_desc = tc_smem_desc_sw32(smem_u32(smOnes)), x_desc0 = tc_smem_desc_sw32(smem_u32(smB) + BOFF + TC2_B_STAGE_BYTES);
+			if (!ASTREAM) {
+				mbar_wait(a_full, 0);
+				tc_fence_after();
+			}
+			if (!ASTREAM && nkb == 2 && NSTAGE == 6) {
 				// d <= 128, bf16-exact mode: a tile is 2 ring slots = 9 MMAs of 128 clk. One elected block per TILE with
 				// incrementally stepped slot numbers: the per-slot barrier / elect / descriptor overhead (~450 clk per slot
 				// in the generic loop) is otherwise not covered by so few queued MMAs.
@@ -200,12 +213,12 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 					mbar_wait(&full[s], (it / NSTAGE) & 1);
 					tc_fence_after();
 					if (elect_one()) {
-						const uint64_t bd0 = b_desc0 + (uint64_t)((s * TC2_STAGE_BYTES) >> 4);
-						const uint64_t ad0 = a_desc0 + (uint64_t)((kb * TC_A_KB_BYTES) >> 4);
+						const uint64_t bd0 = b_desc0 + (uint64_t)((s * STG) >> 4);
+						const uint64_t ad0 = ASTREAM ? as_desc0 + (uint64_t)((s * STG) >> 4) : a_desc0 + (uint64_t)((kb * TC_A_KB_BYTES) >> 4);
 #pragma unroll
 						for (int k = 0; k < TC_BK / TC_UMMA_K; ++k)
 							tc_mma_2sm(d_tmem, ad0 + 2 * k, bd0 + 2 * k, idesc, (kb | (uint32_t)k) != 0 ? 1u : 0u);
-						if (kb + 1 == nkb) tc_mma_2sm(d_tmem, ones_desc, x_desc0 + (uint64_t)((s * TC2_STAGE_BYTES) >> 4), idesc, 1u);
+						if (kb + 1 == nkb) tc_mma_2sm(d_tmem, ones_desc, x_desc0 + (uint64_t)((s * STG) >> 4), idesc, 1u);
 						tc_commit_2sm(&empty[s]);
 						if (kb + 1 == nkb) tc_commit_2sm(&tm_full[acc]);
 					}

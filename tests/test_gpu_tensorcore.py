@@ -191,3 +191,32 @@ def test_pair_form_seeded_ties_and_overflow(ex):
     b = run(ex, base2, q2, 10, tc=0)
     assert a[3]["tc_launches"] >= 1
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+@pytest.mark.parametrize("n,m,d,kind,astream", [(20011, 300, 128, "u8", 2), (50000, 300, 96, "real", 2), (50000, 300, 960, "unit", 1),
+                                               (40000, 100, 256, "real", 1), (30000, 600, 512, "u8", 1), (3000, 20, 960, "unit", 1)])
+def test_streamed_query_operand(ex, oracle, n, m, d, kind, astream):
+    """pair form with the query operand streamed through the ring (rows too long for a resident query tile: GIST d = 960,
+    d = 256 real-valued, d = 512 integers whose dot products pass 2^24 -> split mode), and forced (tc_astream = 2) on
+    shapes the resident form also takes. Against the SIMT scan bit for bit, and against the oracle."""
+    rng = np.random.default_rng(n + d)
+    if kind == "u8":
+        base = rng.integers(0, 256, (n, d)).astype(np.float32); q = rng.integers(0, 256, (m, d)).astype(np.float32)
+    elif kind == "real":
+        base = rng.standard_normal((n, d)).astype(np.float32); q = rng.standard_normal((m, d)).astype(np.float32)
+    else:
+        base = rng.random((n, d), dtype=np.float32); q = rng.random((m, d), dtype=np.float32)
+    for metric in (0, 1):
+        e = ex.BruteForceEngine(metric=metric)
+        e.set_option("tc_astream", astream)
+        e.store_many_vectors(base); e.build()
+        ids, dists, counts = e.query_k_batch(q, 10)
+        st = e.stats(); e.close()
+        assert st["tc_launches"] >= 1 and st["tc_fallbacks"] == 0 and st["last_qtile"] == 256
+        ids2, dists2, counts2, st2 = run(ex, base, q, 10, metric=metric, tc=0)
+        assert st2["tc_launches"] == 0
+        assert np.array_equal(ids, ids2) and np.array_equal(dists, dists2) and np.array_equal(counts, counts2)
+    if d == 960 and n == 50000:
+        oi, od, _ = oracle.bf_query(base, q, 10, metric=1, threads=16)
+        swaps = assert_topk_parity(ids, dists, oi, od, base, q, metric="ip", tag="streamed d960 ip")
+        assert swaps <= 4
