@@ -288,6 +288,10 @@ def main():
     ids_dev = torch.empty((m, k), dtype=torch.int64, device=dev)
     ids_host = torch.empty((m, k), dtype=torch.int64).pin_memory()
     dq_e2e = torch.empty_like(dq)
+    hq_np = hq.numpy()   # a view of the page-locked tensor
+    out_pinned = (torch.empty((m, k), dtype=torch.int64).pin_memory().numpy().view(np.uint64),
+                  torch.empty((m, k), dtype=torch.float32).pin_memory().numpy(),
+                  torch.empty((m,), dtype=torch.int64).pin_memory().numpy().view(np.uint64))
 
     def step_device(qptr):
         if world == 1:
@@ -299,7 +303,8 @@ def main():
 
     def step_e2e():
         if world == 1:
-            return eng.query_k_batch(q, k)[0]          # the C-ABI host call: H2D q, scan, merge, decode, D2H
+            # the C-ABI host call: H2D of the pinned queries, scan, decode, D2H into pinned result buffers
+            return eng.query_k_batch(hq_np, k, out=out_pinned)[0]
         dq_e2e.copy_(hq, non_blocking=True)
         step_device(dq_e2e.data_ptr())
         eng.decode_device(final_keys.data_ptr(), m, k, ids_dev.data_ptr(), 0, 0, stream)
@@ -399,7 +404,7 @@ def main():
                           "parallelism": "base rows sharded x%d, NCCL all-gather of [m][k] keys + K7 merge" % world if world > 1 else "single GPU"},
                "e2e": {"value": m * args.steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(m * d * 4),
                        "d2h_bytes_per_step": int(m * k * 8 + (m * k * 4 + m * 8 if world == 1 else 0)),
-                       "api": "expann_gpu_query (host buffers)" if world == 1 else "pinned H2D + query_device + all_gather + merge + decode + D2H"},
+                       "api": "expann_gpu_query (page-locked host buffers)" if world == 1 else "pinned H2D + query_device + all_gather + merge + decode + D2H"},
                "gpu_launches": int(launches),
                "roofline": roof,
                "clocks": clocks}

@@ -250,6 +250,15 @@ int expann_gpu_query_device(expann_gpu_t* h, const float* d_q, size_t m, size_t 
 	return query_device_impl(h, d_q, m, k, ef, d_keys_out, (cudaStream_t)stream);
 }
 
+static bool is_pinned_host(const void* p) {
+	cudaPointerAttributes a{};
+	if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+		cudaGetLastError(); // unregistered host memory reports an error on old drivers: not sticky, clear it
+		return false;
+	}
+	return a.type == cudaMemoryTypeHost;
+}
+
 int expann_gpu_query(expann_gpu_t* h, const float* q, size_t m, size_t k, size_t ef, uint64_t* ids_out, float* dist_out,
                      uint64_t* counts_out) {
 	if (!h || (m && (!q || !ids_out))) return fail(h, EXPANN_ERR_ARG, "null argument");
@@ -267,20 +276,24 @@ int expann_gpu_query(expann_gpu_t* h, const float* q, size_t m, size_t k, size_t
 	EXPANN_CUDA(h, h->ids.ensure(nk * 8));
 	EXPANN_CUDA(h, h->dists.ensure(nk * 4));
 	EXPANN_CUDA(h, h->counts.ensure(m * 8));
-	std::memcpy(h->h_q.p, q, qbytes);
+	// page-locked caller buffers (cudaHostAlloc / cudaHostRegister / torch pin_memory) are used by the copy engines
+	// directly; pageable ones go through the handle's pinned staging buffers
+	const bool q_pinned = is_pinned_host(q), ids_pinned = is_pinned_host(ids_out);
+	const bool dist_pinned = dist_out && is_pinned_host(dist_out), counts_pinned = counts_out && is_pinned_host(counts_out);
+	if (!q_pinned) std::memcpy(h->h_q.p, q, qbytes);
 	float* d_q = reinterpret_cast<float*>(h->keys.as<uint8_t>() + round_up(nk * 8, 256));
-	EXPANN_CUDA(h, cudaMemcpyAsync(d_q, h->h_q.p, qbytes, cudaMemcpyHostToDevice, st));
+	EXPANN_CUDA(h, cudaMemcpyAsync(d_q, q_pinned ? (const void*)q : h->h_q.p, qbytes, cudaMemcpyHostToDevice, st));
 	if (int rc = query_device_impl(h, d_q, m, k, ef, h->keys.as<uint64_t>(), st)) return rc;
 	if (int rc = launch_decode(h, h->keys.as<uint64_t>(), m, k, 0, h->ids.as<uint64_t>(), h->dists.as<float>(),
 	                           h->counts.as<uint64_t>(), st))
 		return rc;
-	EXPANN_CUDA(h, cudaMemcpyAsync(h->h_ids.p, h->ids.p, nk * 8, cudaMemcpyDeviceToHost, st));
-	if (dist_out) EXPANN_CUDA(h, cudaMemcpyAsync(h->h_dists.p, h->dists.p, nk * 4, cudaMemcpyDeviceToHost, st));
-	if (counts_out) EXPANN_CUDA(h, cudaMemcpyAsync(h->h_counts.p, h->counts.p, m * 8, cudaMemcpyDeviceToHost, st));
+	EXPANN_CUDA(h, cudaMemcpyAsync(ids_pinned ? (void*)ids_out : h->h_ids.p, h->ids.p, nk * 8, cudaMemcpyDeviceToHost, st));
+	if (dist_out) EXPANN_CUDA(h, cudaMemcpyAsync(dist_pinned ? (void*)dist_out : h->h_dists.p, h->dists.p, nk * 4, cudaMemcpyDeviceToHost, st));
+	if (counts_out) EXPANN_CUDA(h, cudaMemcpyAsync(counts_pinned ? (void*)counts_out : h->h_counts.p, h->counts.p, m * 8, cudaMemcpyDeviceToHost, st));
 	EXPANN_CUDA(h, cudaStreamSynchronize(st));
-	std::memcpy(ids_out, h->h_ids.p, nk * 8);
-	if (dist_out) std::memcpy(dist_out, h->h_dists.p, nk * 4);
-	if (counts_out) std::memcpy(counts_out, h->h_counts.p, m * 8);
+	if (!ids_pinned) std::memcpy(ids_out, h->h_ids.p, nk * 8);
+	if (dist_out && !dist_pinned) std::memcpy(dist_out, h->h_dists.p, nk * 4);
+	if (counts_out && !counts_pinned) std::memcpy(counts_out, h->h_counts.p, m * 8);
 	return EXPANN_OK;
 }
 

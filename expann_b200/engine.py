@@ -110,15 +110,24 @@ class GpuEngine:
 
     query_k_numpy = query_k  # src/pyrunner.cpp:85-90
 
-    def query_k_batch(self, q, k: int, ef: int | None = None):
-        """m queries -> (ids [m][k] uint64 padded with UINT64_MAX, keys [m][k] float32 padded with +inf, counts [m])"""
+    def query_k_batch(self, q, k: int, ef: int | None = None, out=None):
+        """m queries -> (ids [m][k] uint64 padded with UINT64_MAX, keys [m][k] float32 padded with +inf, counts [m]).
+        `out` = (ids, keys, counts) preallocated C-contiguous arrays to fill instead; page-locked buffers (for q too)
+        are copied by the GPU's copy engines directly, pageable ones through the handle's pinned staging."""
         q = _f32c(q)
         if q.ndim != 2:
             raise ValueError("q must be [m][d]")
         m = q.shape[0]
-        ids = np.empty((m, k), np.uint64)
-        dists = np.empty((m, k), np.float32)
-        counts = np.empty(m, np.uint64)
+        if out is not None:
+            ids, dists, counts = out
+            if (ids.shape != (m, k) or ids.dtype != np.uint64 or dists.shape != (m, k) or dists.dtype != np.float32 or
+                    counts.shape != (m,) or counts.dtype != np.uint64 or
+                    not (ids.flags.c_contiguous and dists.flags.c_contiguous and counts.flags.c_contiguous)):
+                raise ValueError("out must be (uint64 [m][k], float32 [m][k], uint64 [m]) C-contiguous arrays")
+        else:
+            ids = np.empty((m, k), np.uint64)
+            dists = np.empty((m, k), np.float32)
+            counts = np.empty(m, np.uint64)
         if self.d is not None and q.shape[1] != self.d:
             raise ValueError("query dimension mismatch")
         self._check(self._lib.expann_gpu_query(self._h, q.ctypes.data, m, k, self.ef_search if ef is None else ef,

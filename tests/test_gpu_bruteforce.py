@@ -175,3 +175,28 @@ def test_large_property_1m(ex, oracle):
     assert np.array_equal(ids[:8], oi) and np.array_equal(dists[:8], od)
     # a planted exact duplicate of a query must come back first with distance 0
     e.close()
+
+
+def test_host_call_with_page_locked_buffers(ex):
+    """expann_gpu_query with page-locked caller buffers (copied by the copy engines directly) and with pageable ones
+    (through the handle's staging buffers) must return the same thing"""
+    import torch
+    rng = np.random.default_rng(31)
+    base = rng.integers(0, 256, (30_000, 128)).astype(np.float32)
+    q = rng.integers(0, 256, (333, 128)).astype(np.float32)
+    e = ex.BruteForceEngine()
+    e.store_many_vectors(base); e.build()
+    ids, dists, counts = e.query_k_batch(q, 10)
+    hq = torch.from_numpy(q).pin_memory().numpy()
+    out = (torch.zeros((333, 10), dtype=torch.int64).pin_memory().numpy().view(np.uint64),
+           torch.zeros((333, 10), dtype=torch.float32).pin_memory().numpy(),
+           torch.zeros((333,), dtype=torch.int64).pin_memory().numpy().view(np.uint64))
+    r = e.query_k_batch(hq, 10, out=out)
+    assert r[0] is out[0]
+    assert np.array_equal(out[0], ids) and np.array_equal(out[1], dists) and np.array_equal(out[2], counts)
+    # mixed: pinned queries, pageable outputs
+    ids2, dists2, counts2 = e.query_k_batch(hq, 10)
+    assert np.array_equal(ids2, ids) and np.array_equal(dists2, dists)
+    with pytest.raises(ValueError):
+        e.query_k_batch(q, 10, out=(out[0][:, :5], out[1], out[2]))
+    e.close()
