@@ -218,7 +218,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
-    ap.add_argument("--engine", default="auto", choices=["auto", "bf", "quant"],
+    ap.add_argument("--ef", type=int, default=40, help="beam width of --engine graph")
+    ap.add_argument("--engine", default="auto", choices=["auto", "bf", "quant", "graph"],
                     help="bf: exact brute force (K1/K3+K4); quant: quantizer compressed scan + fp32 rerank (K6+K4); auto: quant for c5")
     ap.add_argument("--qtile", type=int, default=0)
     ap.add_argument("--m", type=int, default=0, help="override the query count")
@@ -230,6 +231,11 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     gen, variant, n, m, d, k, metric, desc = WORKLOADS[args.workload]
+    if args.engine == "graph":
+        # graph engines need data with neighbourhood structure: the low-rank SIFT-shape variant of SURVEY 8(d) (C3), not iid
+        if gen == "sift":
+            variant = "lowrank"
+        desc = desc.replace("(u8-valued iid)", "(u8-valued, low-rank)").replace("brute-force", "graph engine (sharded),").replace("exact ", "")
     if args.m:
         m = args.m
     from expann_b200 import datasets
@@ -272,12 +278,42 @@ def main():
     from expann_b200 import sharding
     lo, hi = sharding.shard_range(n, world, rank)
     use_quant = args.engine == "quant" or (args.engine == "auto" and args.workload == "c5")
-    if use_quant:   # BASELINE config 5: quantizer_ranged_q8 codes (src/quantizer.h:186-238) scanned with K6, k' = 100 survivors re-ranked in fp32
+    use_graph = args.engine == "graph"
+    truth_ids = None
+    if use_graph:
+        # BASELINE config 4's graph leg: every rank builds a graph over ITS rows (GPU build, reference prune rule) and
+        # searches it for all queries; per-GPU top-k lists meet through the same NCCL gather + K7 merge as the scans.
+        # Ground truth for recall@k: the sharded exact scan of the same rows (not timed).
+        bf = expann_b200.BruteForceEngine(metric=1 if metric == "ip" else 0, device=local_rank, id_offset=lo)
+        bf.store_many_vectors(base[lo:hi]); bf.build()
+        tq = torch.from_numpy(q).to(dev)
+        tk_local = torch.empty((m, k), dtype=torch.int64, device=dev)
+        bf.query_device(tq.data_ptr(), m, k, tk_local.data_ptr(), torch.cuda.current_stream().cuda_stream)
+        if world > 1:
+            g = sharding.gather_keys(tk_local, world)
+            tk_final = torch.empty_like(tk_local)
+            bf.merge_device(g.data_ptr(), m, world, k, k, m * k, k, tk_final.data_ptr(), torch.cuda.current_stream().cuda_stream)
+        else:
+            tk_final = tk_local
+        tids = torch.empty((m, k), dtype=torch.int64, device=dev)
+        bf.decode_device(tk_final.data_ptr(), m, k, tids.data_ptr(), 0, 0, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        truth_ids = tids.cpu().numpy()
+        bf.close()
+        del bf, tq, tk_local, tk_final, tids
+        eng = expann_b200.GraphEngine(metric=1 if metric == "ip" else 0, device=local_rank, id_offset=lo)
+        eng.store_many_vectors(base[lo:hi])
+        t_b = time.perf_counter()
+        eng.build_graph(M=16, M0=32, K=64)
+        graph_build_s = time.perf_counter() - t_b
+        eng.set_ef_search(args.ef)
+    elif use_quant:   # BASELINE config 5: quantizer_ranged_q8 codes (src/quantizer.h:186-238) scanned with K6, k' = 100 survivors re-ranked in fp32
         eng = expann_b200.QuantScanEngine(quantizer=1, kprime=100, metric=1 if metric == "ip" else 0, device=local_rank,
                                           qtile=args.qtile, id_offset=lo)
     else:
         eng = expann_b200.BruteForceEngine(metric=1 if metric == "ip" else 0, device=local_rank, qtile=args.qtile, id_offset=lo)
-    eng.store_many_vectors(base[lo:hi])
+    if not use_graph:
+        eng.store_many_vectors(base[lo:hi])
     eng.build()
 
     stream = torch.cuda.current_stream().cuda_stream
@@ -366,7 +402,15 @@ def main():
         hot_ms = (st1["hot_time_ns"] - st0["hot_time_ns"]) / 1e6 / max(1, st1["hot_timed_launches"] - st0["hot_timed_launches"])
         qt = st1["last_qtile"]
         used_tc = st1["tc_launches"] > st0["tc_launches"] and st1["tc_fallbacks"] == st0["tc_fallbacks"]
-        if used_tc:
+        if use_graph:
+            dcq = (st1["distcomps"] - st0["distcomps"]) / float(args.steps * m)   # this rank's shard
+            alg_bytes = dcq * d * 4 * m
+            achieved = alg_bytes / (hot_ms * 1e-3) / 1e9
+            roof = {"bound": "hbm", "kernel": "graph_search_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": int(alg_bytes), "kernel_ms_per_launch": hot_ms,
+                    "distcomps_per_query_per_gpu": dcq,
+                    "note": "algorithmic bytes = distance evaluations x d x 4 on rank 0's shard (random row gathers); latency-bound"}
+        elif used_tc:
             # K3: bf16 tcgen05 GEMM of a'(q,x) over the whole shard; flops = 2 * m * n_shard * kd (kd = operand row length:
             # d rounded up to 64 in the bf16-exact mode, 3x that in the two-term split mode)
             seg = (d + 63) // 64 * 64
@@ -393,11 +437,12 @@ def main():
                     "algorithmic_bytes_per_launch": int(alg_bytes), "kernel_ms_per_launch": hot_ms,
                     "note": "algorithmic bytes = ceil(m/qtile) passes x shard bytes (SURVEY 8(d)); CTAs of one "
                             "wave share rows through L2, so DRAM traffic is lower than this figure"}
-        out = {"metric": "QPS (exact brute-force top-%d)" % k, "value": m * args.steps / (ms * 1e-3), "unit": "queries/s",
+        out = {"metric": ("QPS (graph engine, ef=%d, top-%d)" % (args.ef, k)) if use_graph else "QPS (exact brute-force top-%d)" % k, "value": m * args.steps / (ms * 1e-3), "unit": "queries/s",
                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                "config": {"workload": desc, "n": n, "m": m, "d": d, "k": k, "metric": metric, "qtile": int(qt),
-                          "path": "K6 8-bit code scan (dp4a) + K4 fp32 rerank of 100 survivors" if use_quant else
+                          "path": "K5 graph beam search (one GPU-built graph per shard, M0=32)" if use_graph else
+                                  "K6 8-bit code scan (dp4a) + K4 fp32 rerank of 100 survivors" if use_quant else
                                   ("K3 tcgen05 filter + K4 fp32 rerank" if used_tc else "K1 fp32 SIMT scan"),
                           "nsplit": int(st1["last_nsplit"]), "rows_per_gpu": hi - lo,
                           "l2": "base shard (%.0f MB) %s L2 (126 MB); no explicit flush" % ((hi - lo) * d * 4 / 1e6, "larger than" if (hi - lo) * d * 4 > 126e6 else "fits in"),
@@ -408,10 +453,16 @@ def main():
                "gpu_launches": int(launches),
                "roofline": roof,
                "clocks": clocks}
-        if not args.no_cpu and world == 1:
+        if not args.no_cpu and world == 1 and not use_graph:
             qps, cores, kind, sample = cpu_reference_qps(base, q, k, metric)
             out["cpu_baseline"] = {"value": qps, "unit": "queries/s", "cores": cores, "kind": kind, "sample": sample}
         out["check"] = {"first_ids": got[0].tolist()}
+        if use_graph:
+            allids = ids_dev.cpu().numpy()
+            hit = sum(len(set(a.tolist()) & set(b.tolist())) for a, b in zip(allids, truth_ids))
+            out["check"]["recall_at_k_vs_exact"] = hit / float(m * k)
+            out["config"]["ef"] = args.ef
+            out["config"]["graph_build_s_per_shard"] = graph_build_s
         if use_quant and world == 1:
             # quality of the compressed scan: recall@10 against the exact fp32 scan of the same library (not timed)
             try:
@@ -426,7 +477,7 @@ def main():
                 out["check"]["recall_at_k_vs_exact"] = hit / float(msub * k)
             except Exception as exn:  # noqa: BLE001
                 out["check"]["recall_error"] = repr(exn)[:200]
-        if world == 1 and not args.no_extras and not use_quant:
+        if world == 1 and not args.no_extras and not use_quant and not use_graph:
             try:
                 out["scan_hbm"] = scan_hbm_leg(eng, torch, dq, k, hi - lo, d, stream, peak, peak_src, args.steps)
             except Exception as ex:  # noqa: BLE001
@@ -434,7 +485,7 @@ def main():
     eng.close()
     del eng
     if rank == 0:
-        if world == 1 and args.workload == "c2" and not args.no_extras:
+        if world == 1 and args.workload == "c2" and not args.no_extras and not use_graph:
             # BASELINE config 3 (graph engine, QPS at recall@10 >= 0.95) measured in the same run
             try:
                 from tools import bench_extras
