@@ -280,8 +280,10 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	const uint32_t ntiles = (uint32_t)((h->n + (pair ? TC3_TN : TC2_TN) - 1) / (pair ? TC3_TN : TC2_TN));
 	// pair form, large bases: a short first launch over the leading boot_tiles tiles seeds every stream of the main launch
 	// with the k smallest a' found there (Tc2Params::seed_in): fewer bound-tightening events in the main launch. Worth it
-	// only in the bf16-exact mode, whose epilogue is the limiter (the split mode is MMA-bound: 9.70 ms without, 9.94 with)
-	const uint32_t boot_tiles = pair && (h->opt_tc_boot == 2 || (h->opt_tc_boot == 1 && h->tc_mode == 1)) && ntiles >= 128 ? std::max(8u, std::min(64u, ntiles / 32u)) : 0u;
+	// only in the bf16-exact mode, whose epilogue is the limiter (the split mode is MMA-bound: 9.70 ms without, 9.94 with),
+	// and only for batches that fill the GPU with the seeding launch's one cluster per 256 queries (it costs ~0.14 ms
+	// whatever the batch: measured break-even at ~8000 queries on 1M rows)
+	const uint32_t boot_tiles = pair && (h->opt_tc_boot == 2 || (h->opt_tc_boot == 1 && h->tc_mode == 1 && m >= 8192)) && ntiles >= 128 ? std::max(8u, std::min(64u, ntiles / 32u)) : 0u;
 	const uint32_t main_tiles = ntiles - boot_tiles;
 	uint32_t rows_split = tc2_pick_rsplit(qblocks, main_tiles, sms);
 	const uint32_t tiles_per_cta = (main_tiles + rows_split - 1) / rows_split;

@@ -87,7 +87,9 @@ int expann_gpu_build(expann_gpu_t* h);
  * q: host [m][d]. Outputs (host, caller-owned): ids_out [m][k] nearest first under (key asc, id asc), unused
  * slots UINT64_MAX; dist_out [m][k] (may be NULL) the fp32 ranking key (dist2, or -dot), unused slots +inf;
  * counts_out [m] (may be NULL) = min(k, n). ef: beam width for the graph engine (0 = k*ef_search_mult,
- * src/antitopo_engine.h:858-859), ignored by scans. Includes H2D of q and D2H of the results. */
+ * src/antitopo_engine.h:858-859), ignored by scans. Includes H2D of q and D2H of the results: page-locked caller
+ * buffers (cudaHostAlloc / cudaHostRegister) are used by the copy engines directly, pageable ones are staged through
+ * the handle's own page-locked buffers (one extra host memcpy each way). */
 int expann_gpu_query(expann_gpu_t* h, const float* q, size_t m, size_t k, size_t ef, uint64_t* ids_out,
                      float* dist_out, uint64_t* counts_out);
 /* HBM-resident form: d_q device [m][d] (row stride d), d_keys_out device [m][k] 64-bit keys

@@ -14,10 +14,12 @@ def ex():
     return expann_b200
 
 
-def run(ex, base, q, k, metric=0, tc=1, id_offset=0, v1=0, pair=1):
+def run(ex, base, q, k, metric=0, tc=1, id_offset=0, v1=0, pair=1, boot=None):
     e = ex.BruteForceEngine(metric=metric, id_offset=id_offset)
     e.set_option("tc", tc)
     e.set_option("tc_pair", pair)  # 1 (default): clusters of two CTAs, tcgen05.mma.cta_group::2; 0: single-CTA form
+    if boot is not None:
+        e.set_option("tc_boot", boot)  # 2: seeding launch whatever the batch size / mode (default: exact mode, >= 8192 queries)
     e.set_option("tc_v1", v1)   # 1: force the chunked first form of K3 (otherwise used for k > 16 only)
     e.store_many_vectors(base)
     e.build()
@@ -115,7 +117,10 @@ def test_second_form_many_splits(ex, k):
     base = rng.integers(0, 256, (300_001, 128)).astype(np.float32)
     q = rng.integers(0, 256, (1300, 128)).astype(np.float32)
     ids, dists, counts, st = run(ex, base, q, k)
-    assert st["tc_launches"] in (1, 2) and st["tc_fallbacks"] == 0 and st["last_nsplit"] > 1
+    assert st["tc_launches"] == 1 and st["tc_fallbacks"] == 0 and st["last_nsplit"] > 1
+    ids3, dists3, counts3, st3 = run(ex, base, q, k, boot=2)   # with the seeding launch
+    assert st3["tc_launches"] == 2 and st3["tc_fallbacks"] == 0
+    assert np.array_equal(ids, ids3) and np.array_equal(dists, dists3) and np.array_equal(counts, counts3)
     ids2, dists2, counts2, st2 = run(ex, base, q, k, tc=0)
     assert st2["tc_launches"] == 0
     assert np.array_equal(ids, ids2) and np.array_equal(dists, dists2) and np.array_equal(counts, counts2)
@@ -165,9 +170,9 @@ def test_pair_form_edges(ex, n, m):
             base = rng.integers(0, 256, (n, 128)).astype(np.float32)
             q = rng.integers(0, 256, (m, 128)).astype(np.float32)
         for metric in (0, 1):
-            a = run(ex, base, q, 10, metric=metric)
+            a = run(ex, base, q, 10, metric=metric, boot=2)
             b = run(ex, base, q, 10, metric=metric, tc=0)
-            assert a[3]["tc_launches"] >= 1 and a[3]["last_qtile"] == 256 and b[3]["tc_launches"] == 0
+            assert a[3]["tc_launches"] == (2 if n >= 32768 else 1) and a[3]["last_qtile"] == 256 and b[3]["tc_launches"] == 0
             assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
 
 
@@ -179,7 +184,7 @@ def test_pair_form_seeded_ties_and_overflow(ex):
     pool = rng.integers(0, 256, (2000, 128)).astype(np.float32)
     base = pool[rng.integers(0, 2000, 150_000)]
     q = rng.integers(0, 256, (300, 128)).astype(np.float32)
-    a = run(ex, base, q, 10)
+    a = run(ex, base, q, 10, boot=2)
     b = run(ex, base, q, 10, tc=0)
     assert a[3]["tc_launches"] == 2
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
@@ -187,7 +192,7 @@ def test_pair_form_seeded_ties_and_overflow(ex):
     c = np.rint(base2.mean(0))
     base2 = np.ascontiguousarray(base2[np.argsort(-((base2 - c) ** 2).sum(1))])
     q2 = np.ascontiguousarray(np.tile(c, (300, 1)) + rng.integers(-2, 3, (300, 32))).astype(np.float32)
-    a = run(ex, base2, q2, 10)
+    a = run(ex, base2, q2, 10, boot=2)
     b = run(ex, base2, q2, 10, tc=0)
     assert a[3]["tc_launches"] >= 1
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
