@@ -182,7 +182,7 @@ void expann_gpu_destroy(expann_gpu_t* h) {
 	timing_collect(h);
 	for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
 	if (h->base) cudaFree(h->base);
-	for (DevBuf* b : { &h->tc_xb, &h->tc_xn, &h->tc_stats, &h->tc_qstats, &h->tc_qb, &h->tc_qn, &h->tc_thr, &h->tc_cnt, &h->tc_cand, &h->tc_gthr, &h->tc_sel, &h->tc_xx, &h->tc_seed, &h->scan_cnt })
+	for (DevBuf* b : { &h->tc_xb, &h->tc_xn, &h->tc_stats, &h->tc_qstats, &h->tc_qb, &h->tc_qn, &h->tc_thr, &h->tc_cnt, &h->tc_cand, &h->tc_gthr, &h->tc_sel, &h->tc_xx, &h->tc_seed, &h->tc_fbcount, &h->scan_cnt })
 		b->release();
 	for (DevBuf* b : { &h->q_codes, &h->q_cnorm, &h->q_mm, &h->qq_codes, &h->qq_norm, &h->q_cand }) b->release();
 	for (DevBuf* b : { &h->g_bottom, &h->g_upper, &h->g_upper_idx, &h->g_upper_nl, &h->g_visited, &h->g_epoch, &h->g_codes })
@@ -402,6 +402,11 @@ int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out) {
 	DeviceGuard g(h->device);
 	timing_collect(h);
 	if (h->cfg.engine == EXPANN_ENGINE_GRAPH) graph_read_distcomps(h);
+	if (h->tc_fbcount.cap >= 4) { // redo launches of K3's second form are counted on the device
+		uint32_t c = 0;
+		if (cudaDeviceSynchronize() == cudaSuccess && cudaMemcpy(&c, h->tc_fbcount.p, 4, cudaMemcpyDeviceToHost) == cudaSuccess)
+			h->stats.tc_fallbacks = c;
+	}
 	*out = h->stats;
 	return EXPANN_OK;
 }

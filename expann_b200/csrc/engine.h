@@ -60,7 +60,7 @@ struct expann_gpu {
 	int tc_mode = 0; // 0 off, 1 bf16-exact single GEMM, 2 two-term bf16 split
 	uint32_t tc_kd = 0;
 	float tc_xmin = 0.f, tc_xmax = 0.f, tc_xnorm_max = 0.f;
-	expann::DevBuf tc_xb, tc_xn, tc_stats, tc_qstats, tc_qb, tc_qn, tc_thr, tc_cnt, tc_cand, tc_gthr, tc_sel, tc_xx, tc_seed;
+	expann::DevBuf tc_xb, tc_xn, tc_stats, tc_qstats, tc_qb, tc_qn, tc_thr, tc_cnt, tc_cand, tc_gthr, tc_sel, tc_xx, tc_seed, tc_fbcount;
 	CUtensorMap tmap_xb{}, tmap_xb128{}, tmap_xx{};
 	int opt_tc_v1 = 0; // force the chunked first form of K3 (tests)
 	int opt_tc_pair = 1; // pair form of K3 (clusters of two CTAs, tcgen05.mma.cta_group::2)

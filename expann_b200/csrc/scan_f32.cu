@@ -89,7 +89,8 @@ template <int QT> static int launch_m(expann_gpu* h, const ScanParams& p, dim3 g
 	                                          : launch_k<QT, METRIC_L2>(h, p, grid, st);
 }
 
-int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);
+int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st,
+                         const uint32_t* gate = nullptr, uint32_t* gate_count = nullptr);
 
 // path selection: the tensor-core filter (K3) for large batches when build() prepared its operands, else the SIMT scan
 int launch_scan_f32(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st) {
@@ -105,7 +106,8 @@ int launch_scan_f32(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 	return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st);
 }
 
-int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st) {
+int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st,
+                         const uint32_t* gate, uint32_t* gate_count) {
 	int qt = h->cfg.qtile;
 	if (qt == 0) qt = m >= 8 ? 8 : (m >= 3 ? 4 : 1);
 	if (qt != 1 && qt != 4 && qt != 8) return fail(h, EXPANN_ERR_ARG, "qtile must be 0, 1, 4 or 8");
@@ -157,7 +159,11 @@ int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, ui
 		p.id_add = (uint32_t)h->cfg.id_offset;
 	}
 	p.partial = scan_out;
+	p.gate = gate;
+	p.gate_count = gate_count;
 	dim3 grid(qtiles, nsplit);
+	if (gate) // K3's queued redo: runs only if the device flag is up; neither timed nor counted on the host
+		return qt == 8 ? launch_m<8>(h, p, grid, st) : qt == 4 ? launch_m<4>(h, p, grid, st) : launch_m<1>(h, p, grid, st);
 	cudaEvent_t t0 = timing_begin(h, st);
 	int rc = qt == 8 ? launch_m<8>(h, p, grid, st) : qt == 4 ? launch_m<4>(h, p, grid, st) : launch_m<1>(h, p, grid, st);
 	timing_end(h, t0, st);

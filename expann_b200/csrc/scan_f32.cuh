@@ -44,6 +44,10 @@ struct ScanParams {
 	uint64_t* final_out;
 	uint32_t* counters;
 	uint32_t id_add;
+	// device-side gate (K3's fallback): when set, the launch does nothing unless *gate != 0; a launch that does run
+	// counts itself in *gate_count. Lets the tensor-core path queue its SIMT redo without a host round trip.
+	const uint32_t* gate;
+	uint32_t* gate_count;
 };
 
 __device__ __forceinline__ uint64_t pack2(float lo, float hi) {
@@ -114,6 +118,10 @@ template <int QT, int TR, int NWARP, int STAGES, int METRIC, int LPL>
 __global__ void __launch_bounds__(32 * (NWARP + 1), 1)
 scan_topk_f32_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
 	using Cfg = ScanCfg<QT, TR, NWARP, STAGES, METRIC, LPL>;
+	if (p.gate != nullptr) { // uniform over the grid: nobody has touched a barrier yet
+		if (*reinterpret_cast<const volatile uint32_t*>(p.gate) == 0u) return;
+		if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) atomicAdd(p.gate_count, 1u);
+	}
 	extern __shared__ uint8_t smem_raw[];
 	uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
 	static_assert(QT <= NWARP, "one owner warp per query of the tile");

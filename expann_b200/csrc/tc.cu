@@ -22,7 +22,8 @@ namespace expann {
 
 int encode_tensor_map_bf16(expann_gpu* h, CUtensorMap* out, void* base, uint64_t inner, uint64_t rows, uint32_t box_rows,
                            uint32_t box_inner = 64);
-int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);
+int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st,
+                         const uint32_t* gate = nullptr, uint32_t* gate_count = nullptr);
 
 constexpr uint32_t TC_CAP = 4096, TC_FIRST_ROWS = 2048, TC_PAD = 256, TC_QBATCH = 16384;
 constexpr int TC_NSTAGE_EXACT = 4, TC_NSTAGE_SPLIT = 3;
@@ -205,15 +206,14 @@ static int tc_batch(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 	EXPANN_CUDA(h, cudaGetLastError());
 	h->stats.aux_launches++;
 	// overflow check (needs the flag on the host): redo the batch with the SIMT scan if any buffer overflowed
-	uint32_t unsafe = 0;
-	EXPANN_CUDA(h, cudaMemcpyAsync(&unsafe, flags, 4, cudaMemcpyDeviceToHost, st));
-	EXPANN_CUDA(h, cudaStreamSynchronize(st));
-	if (unsafe) {
-		*fell_back = true;
-		h->stats.tc_fallbacks++;
-		return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st);
+	// A raised flag (queries not bf16-exact in the exact mode, a candidate buffer overflow, too many survivors) means the
+	// batch must be redone by the SIMT scan. No host round trip: the redo is queued behind the flag (ScanParams::gate)
+	// and returns at once when the flag is down; the launches that did run are counted in tc_fbcount (stats()).
+	if (h->tc_fbcount.cap < 4) {
+		EXPANN_CUDA(h, h->tc_fbcount.ensure(4));
+		EXPANN_CUDA(h, cudaMemsetAsync(h->tc_fbcount.p, 0, 4, st));
 	}
-	return EXPANN_OK;
+	return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st, flags, h->tc_fbcount.as<uint32_t>());
 }
 
 
@@ -286,6 +286,7 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	const uint32_t boot_tiles = pair && (h->opt_tc_boot == 2 || (h->opt_tc_boot == 1 && h->tc_mode == 1 && m >= 8192)) && ntiles >= 128 ? std::max(8u, std::min(64u, ntiles / 32u)) : 0u;
 	const uint32_t main_tiles = ntiles - boot_tiles;
 	uint32_t rows_split = tc2_pick_rsplit(qblocks, main_tiles, sms);
+	if (h->opt_nsplit > 0) rows_split = std::max(1u, std::min({ (uint32_t)h->opt_nsplit, main_tiles, (uint32_t)TC2_MAX_SPLIT / 2u - 1u })); // experiments
 	const uint32_t tiles_per_cta = (main_tiles + rows_split - 1) / rows_split;
 	rows_split = (main_tiles + tiles_per_cta - 1) / tiles_per_cta;
 	const uint32_t rsplit = (pair ? 2 * rows_split : rows_split) + (boot_tiles ? 2u : 0u); // candidate buffers per query
@@ -401,15 +402,14 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	rerank_kernel<1><<<(unsigned)((m + 3) / 4), 128, smem, st>>>(r);
 	EXPANN_CUDA(h, cudaGetLastError());
 	h->stats.aux_launches++;
-	uint32_t unsafe = 0;
-	EXPANN_CUDA(h, cudaMemcpyAsync(&unsafe, flags, 4, cudaMemcpyDeviceToHost, st));
-	EXPANN_CUDA(h, cudaStreamSynchronize(st));
-	if (unsafe) {
-		*fell_back = true;
-		h->stats.tc_fallbacks++;
-		return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st);
+	// A raised flag (queries not bf16-exact in the exact mode, a candidate buffer overflow, too many survivors) means the
+	// batch must be redone by the SIMT scan. No host round trip: the redo is queued behind the flag (ScanParams::gate)
+	// and returns at once when the flag is down; the launches that did run are counted in tc_fbcount (stats()).
+	if (h->tc_fbcount.cap < 4) {
+		EXPANN_CUDA(h, h->tc_fbcount.ensure(4));
+		EXPANN_CUDA(h, cudaMemsetAsync(h->tc_fbcount.p, 0, 4, st));
 	}
-	return EXPANN_OK;
+	return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st, flags, h->tc_fbcount.as<uint32_t>());
 }
 
 // entry used by the brute-force engine for large batches

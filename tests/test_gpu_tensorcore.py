@@ -85,6 +85,29 @@ def test_adversarial_order_falls_back(ex, oracle):
     assert st["tc_launches"] > 0
 
 
+def test_redo_behind_device_flag(ex, oracle):
+    """bf16-exact integer base, queries that are NOT bf16-exact: the device-side check raises the batch's flag and the
+    SIMT redo queued behind it (ScanParams::gate) runs -- no host round trip; counted in tc_fallbacks. A clean batch on
+    the same handle afterwards must not redo."""
+    rng = np.random.default_rng(12)
+    base = rng.integers(0, 256, (30000, 128)).astype(np.float32)
+    q = rng.integers(0, 256, (300, 128)).astype(np.float32)
+    e = ex.BruteForceEngine()
+    e.store_many_vectors(base); e.build()
+    qf = q + np.float32(0.25)
+    ids, dists, counts = e.query_k_batch(qf, 10)
+    st = e.stats()
+    assert st["tc_mode"] == 1 and st["tc_launches"] == 1 and st["tc_fallbacks"] == 1
+    oi, od, _ = oracle.bf_query(base, qf, 10, threads=16)
+    assert_topk_parity(ids, dists, oi, od, base, qf, tag="redo")
+    ids2, dists2, _ = e.query_k_batch(q, 10)
+    st2 = e.stats()
+    assert st2["tc_launches"] == 2 and st2["tc_fallbacks"] == 1
+    oi2, od2, _ = oracle.bf_query(base, q, 10, threads=16)
+    assert np.array_equal(ids2, oi2) and np.array_equal(dists2, od2)
+    e.close()
+
+
 def test_shard_offset_and_small_batches(ex, oracle):
     rng = np.random.default_rng(7)
     base = rng.integers(0, 256, (5000, 128)).astype(np.float32)
