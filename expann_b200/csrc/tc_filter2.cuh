@@ -397,6 +397,42 @@ __global__ void __launch_bounds__(128) tc_select2_kernel(const uint64_t* __restr
 	}
 	over = __any_sync(FULL, over);
 	__syncwarp();
+	uint64_t* o = out + (size_t)q * pad;
+	if (total <= 512) {
+		// the usual case (a few hundred keys per query): all keys in registers, 16 independent loads per lane in flight;
+		// the k-th smallest a' by a bitwise search over the orderable encoding (32 rounds of 16 compares + one warp sum)
+		// instead of ~200 dependent list insertions; survivors are compacted from the same registers
+		uint64_t kk[16];
+#pragma unroll
+		for (int u = 0; u < 16; ++u) kk[u] = tc2_flat_key(qbuf, pre, rsplit, cap, u * 32 + lane, total);
+		float t = __int_as_float(0x7f800000);
+		if (total >= k) {
+			uint32_t v = 0;
+#pragma unroll 1
+			for (int bit = 31; bit >= 0; --bit) {
+				const uint32_t trial = v | (1u << bit);
+				uint32_t c = 0;
+#pragma unroll
+				for (int u = 0; u < 16; ++u) c += (uint32_t)(kk[u] >> 32) < trial ? 1u : 0u; // KEY_EMPTY has hi = 0xffffffff: never below
+				c = __reduce_add_sync(FULL, c);
+				if (c < k) v = trial;
+			}
+			const float eps = eps_rel * sqrtf(qnorm2[q]) * xnorm_max + eps_abs;
+			t = __fadd_ru(f32_from_orderable(v), 2.f * eps);
+		}
+		uint32_t w = 0;
+#pragma unroll
+		for (int u = 0; u < 16; ++u) {
+			const bool keep = kk[u] != KEY_EMPTY && key_dist(kk[u]) <= t;
+			const unsigned mk = __ballot_sync(FULL, keep);
+			const uint32_t pos = w + __popc(mk & ((1u << lane) - 1));
+			if (keep && pos < pad) o[pos] = kk[u];
+			w += __popc(mk);
+		}
+		for (uint32_t i = w + lane; i < pad; i += 32) o[i] = KEY_EMPTY;
+		if ((over || w > pad) && lane == 0) atomicAdd(flags, 1u);
+		return;
+	}
 	WarpList<LPL> best;
 	best.init();
 	uint64_t tk = KEY_EMPTY;
@@ -420,7 +456,6 @@ __global__ void __launch_bounds__(128) tc_select2_kernel(const uint64_t* __restr
 		const float eps = eps_rel * sqrtf(qnorm2[q]) * xnorm_max + eps_abs;
 		t = __fadd_ru(key_dist(tk), 2.f * eps);
 	}
-	uint64_t* o = out + (size_t)q * pad;
 	uint32_t w = 0;
 	for (uint32_t i0 = 0; i0 < total; i0 += 128) {
 		uint64_t kk[4];
