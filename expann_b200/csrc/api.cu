@@ -380,6 +380,10 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 	} else if (nm == "tc_astream") {
 		if (value < 0 || value > 2) return fail(h, EXPANN_ERR_ARG, "tc_astream must be 0, 1 or 2");
 		h->opt_tc_astream = (int)value;
+	} else if (nm == "graph_occ") {
+		if (value != 2 && value != 4 && value != 5 && value != 8) return fail(h, EXPANN_ERR_ARG, "graph_occ must be 2, 4, 5 or 8");
+		if (h->built) return fail(h, EXPANN_ERR_STATE, "graph_occ must be set before build()");
+		h->opt_graph_occ = (int)value;
 	} else if (nm == "tc_boot") {
 		h->opt_tc_boot = (int)value; // 0 off, 1 bf16-exact mode only (default), 2 both modes
 	} else if (nm == "tc_v1") {

@@ -128,7 +128,7 @@ int graph_finalize(expann_gpu* h) {
 	// resident warp slots: every SM holds GS_CTAS_PER_SM CTAs of GS_WARPS warps; one visited byte-array per slot
 	int sms = 148;
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
-	h->g_ctas = (uint32_t)sms * 4;
+	h->g_ctas = (uint32_t)sms * (uint32_t)h->opt_graph_occ; // resident CTAs (GS_LAUNCH picks the matching register cap)
 	const size_t slots = (size_t)h->g_ctas * GS_WARPS;
 	h->g_vis_stride = (g.n + 15) / 16 * 16;
 	EXPANN_CUDA(h, h->g_visited.ensure(slots * h->g_vis_stride));
@@ -150,6 +150,8 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 	if (ef == 0) ef = k * std::max<uint64_t>(1, h->cfg.ef_search_mult); // src/antitopo_engine.h:858-859
 	const size_t cap = std::max(k, ef);
 	if (cap > 256) return fail(h, EXPANN_ERR_UNSUPPORTED, "graph search: max(k, ef) above 256");
+	int sms = 148;
+	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
 	GraphParams p{};
 	p.base = h->base;
 	p.codes = h->cfg.use_compression ? h->g_codes.as<uint8_t>() : nullptr;
@@ -178,16 +180,25 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 	if (smem > 200 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "graph search: d too large");
 	const unsigned grid = (unsigned)std::min<size_t>(h->g_ctas, (m + GS_WARPS - 1) / GS_WARPS);
 	cudaEvent_t t0 = timing_begin(h, st);
+#define GS_LAUNCH_B(L, B)                                                                                         \
+	do {                                                                                                          \
+		EXPANN_CUDA(h, (cudaFuncSetAttribute(graph_search_kernel<L, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))); \
+		graph_search_kernel<L, B><<<grid, 32 * GS_WARPS, smem, st>>>(p);                                         \
+	} while (0)
 #define GS_LAUNCH(L)                                                                                              \
 	do {                                                                                                          \
-		EXPANN_CUDA(h, cudaFuncSetAttribute(graph_search_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-		graph_search_kernel<L><<<grid, 32 * GS_WARPS, smem, st>>>(p);                                            \
+		const uint32_t occ = h->g_ctas / (uint32_t)std::max(1, sms);                                             \
+		if (occ >= 8) GS_LAUNCH_B(L, 8);                                                                         \
+		else if (occ >= 5) GS_LAUNCH_B(L, 5);                                                                    \
+		else if (occ >= 4) GS_LAUNCH_B(L, 4);                                                                    \
+		else GS_LAUNCH_B(L, 2);                                                                                  \
 	} while (0)
 	if (cap <= 32) GS_LAUNCH(1);
 	else if (cap <= 64) GS_LAUNCH(2);
 	else if (cap <= 128) GS_LAUNCH(4);
 	else GS_LAUNCH(8);
 #undef GS_LAUNCH
+#undef GS_LAUNCH_B
 	timing_end(h, t0, st);
 	EXPANN_CUDA(h, cudaGetLastError());
 	h->stats.graph_launches++;

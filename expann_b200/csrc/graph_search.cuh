@@ -118,8 +118,10 @@ __device__ __forceinline__ void gather_score_u8(const uint8_t* __restrict__ code
 // beam entry: (orderable(dist) << 32) | (id << 1) | expanded
 __device__ __forceinline__ uint64_t beam_key(float d, uint32_t id) { return ((uint64_t)f32_orderable(d) << 32) | ((uint64_t)id << 1); }
 
-template <int LPL>
-__global__ void __launch_bounds__(32 * GS_WARPS) graph_search_kernel(const GraphParams p) {
+// MINB = resident CTAs per SM the register allocation is held to (65536 / (128 * MINB) registers per thread): the
+// search is a chain of dependent DRAM round trips per hop, so resident warps, not registers, buy throughput
+template <int LPL, int MINB>
+__global__ void __launch_bounds__(32 * GS_WARPS, MINB) graph_search_kernel(const GraphParams p) {
 	extern __shared__ uint8_t gs_smem[];
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
 	const uint32_t slot = blockIdx.x * GS_WARPS + wib, nslots = gridDim.x * GS_WARPS;
