@@ -44,6 +44,7 @@ struct GraphParams {
 };
 
 __device__ __forceinline__ float4 ldg128f(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // fp32 squared distance of the warp's query (in smem) to `cnt` vertices listed in ids[] -> out[] (smem).
 // Teams of 8 lanes: team t handles vertex i*4+t; lane j of the team loads float4 #(j + 8*s).
@@ -212,15 +213,22 @@ __global__ void __launch_bounds__(32 * GS_WARPS, MINB) graph_search_kernel(const
 		if (p.ef == 1) { full = true; thr = nbd[0]; }
 		for (;;) {
 			// closest unexpanded entry among the first ef
-			int pos = -1;
+			int pos = -1, pos2 = -1;
 #pragma unroll
 			for (int s = 0; s < LPL; ++s) {
 				const int i = s * 32 + lane;
-				const unsigned mk = __ballot_sync(FULL, i < (int)p.ef && beam.e[s] != KEY_EMPTY && !(beam.e[s] & 1ull));
-				if (pos < 0 && mk) pos = s * 32 + __ffs(mk) - 1;
+				unsigned mk = __ballot_sync(FULL, i < (int)p.ef && beam.e[s] != KEY_EMPTY && !(beam.e[s] & 1ull));
+				if (pos < 0 && mk) { pos = s * 32 + __ffs(mk) - 1; mk &= mk - 1; }
+				if (pos >= 0 && pos2 < 0 && mk) pos2 = s * 32 + __ffs(mk) - 1;
 			}
 			if (pos < 0) break;
 			const uint64_t ck = beam.at(pos);
+			if (pos2 >= 0) {
+				// the runner-up is the likely next vertex to expand: pull its adjacency row into L2 now, one DRAM round
+				// trip earlier than the hop that will need it
+				const uint32_t nxt = (uint32_t)(beam.at(pos2) >> 1) & 0x7FFFFFFFu;
+				if ((uint32_t)lane * 32u < p.m0s) prefetch_l2(p.bottom + (size_t)nxt * p.m0s + lane * 32);
+			}
 #pragma unroll
 			for (int s = 0; s < LPL; ++s)
 				if (s * 32 + lane == pos) beam.e[s] |= 1ull;
@@ -242,6 +250,16 @@ __global__ void __launch_bounds__(32 * GS_WARPS, MINB) graph_search_kernel(const
 			}
 			__syncwarp();
 			if (cnt == 0) continue;
+			if (cnt > 8) {
+				// the gather below works through 8 vertices per round: ask for the rows of the later rounds now, so that only
+				// the first round waits for DRAM
+				const uint32_t row_bytes = p.compressed ? p.d_pad : p.d_pad * 4;
+				const char* rows = p.compressed ? reinterpret_cast<const char*>(p.codes) : reinterpret_cast<const char*>(p.base);
+				for (int i = 8 + lane; i < cnt; i += 32) {
+					const char* r = rows + (size_t)nb[i] * row_bytes;
+					for (uint32_t o = 0; o < row_bytes; o += 128) prefetch_l2(r + o);
+				}
+			}
 			if (p.compressed) gather_score_u8(p.codes, p.d_pad, qc, nb, nbd, cnt, lane);
 			else gather_dist_f32(p.base, p.d_pad, qsm, nb, nbd, cnt, lane);
 			dc += cnt;
