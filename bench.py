@@ -155,6 +155,7 @@ def scan_hbm_leg(eng, torch, dq, k, n_rows, d, stream, peak, peak_src, steps):
     NOT flushed: the input of a pass (512 MB at C2) is 4x the L2 capacity, so back-to-back passes stream it from DRAM
     again. The headline roofline object is the one-query pass (the reference's own call shape); `passes` lists all three."""
     keys = torch.empty((8, k), dtype=torch.int64, device=dq.device)
+    eng.set_option("tc", 0)   # this leg measures K1 itself (by default batches >= 5 take the tensor-core path)
     alg = n_rows * d * 4
     reps = max(20, steps)
     passes = []
@@ -177,6 +178,7 @@ def scan_hbm_leg(eng, torch, dq, k, n_rows, d, stream, peak, peak_src, steps):
         passes.append({"queries": mq, "qtile": int(s1["last_qtile"]), "nsplit": int(s1["last_nsplit"]), "kernel_ms": hot_ms,
                        "call_ms": call_ms, "qps_call": mq / (call_ms * 1e-3), "achieved_GBs": alg / (hot_ms * 1e-3) / 1e9,
                        "frac": alg / (hot_ms * 1e-3) / 1e9 / peak, "frac_whole_call": alg / (call_ms * 1e-3) / 1e9 / peak})
+    eng.set_option("tc", 1)
     p1 = passes[0]
     return {"workload": "one pass of the fp32 scan (+ fused split merge) over the %dx%d base for 1 / 4 / 8 queries; "
                         "base is 4x L2, passes back to back, no flush" % (n_rows, d),

@@ -56,7 +56,7 @@ struct expann_gpu {
 	expann::DevBuf h_q, h_ids, h_dists, h_counts;            // pinned host staging for the host-pointer API
 	expann_gpu_stats_t stats{};
 	// tensor-core candidate filter (K3)
-	int opt_tc = 1, opt_tc_min_batch = 9; // from 9 queries on K3 beats two passes of K1 (0.15 vs 0.22 ms on 1M x 128)
+	int opt_tc = 1, opt_tc_min_batch = 5; // from 5 queries on K3 is level with or ahead of K1 (1M x 128: 0.12 vs 0.15 ms at 6, 0.13 vs 0.22 at 12)
 	int tc_mode = 0; // 0 off, 1 bf16-exact single GEMM, 2 two-term bf16 split
 	uint32_t tc_kd = 0;
 	float tc_xmin = 0.f, tc_xmax = 0.f, tc_xnorm_max = 0.f;

@@ -299,8 +299,7 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	EXPANN_CUDA(h, h->tc_sel.ensure(m * (size_t)TC_PAD * 8 + 16));
 	uint32_t* flags = reinterpret_cast<uint32_t*>(h->tc_sel.as<uint64_t>() + m * (size_t)TC_PAD);
 	EXPANN_CUDA(h, h->tc_qstats.ensure(sizeof(TcStats)));
-	EXPANN_CUDA(h, cudaMemsetAsync(flags, 0, 16, st));
-	tc_stats_init_kernel<<<1, 1, 0, st>>>(h->tc_qstats.as<TcStats>());
+	tc_batch_init_kernel<<<(unsigned)((std::max<size_t>(m, 4) + 255) / 256), 256, 0, st>>>(h->tc_qstats.as<TcStats>(), flags, h->tc_gthr.as<uint32_t>(), (uint32_t)m);
 	tc_convert_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(d_q, h->d_pad, (uint32_t)h->d, m, h->tc_qb.as<__nv_bfloat16>(), kd,
 	                                                          h->tc_mode, 1, h->tc_qn.as<float>(), h->tc_qstats.as<TcStats>(), ip ? -1.f : -2.f);
 	EXPANN_CUDA(h, cudaGetLastError());
@@ -317,8 +316,6 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	}
 	CUtensorMap tq;
 	if (int rc = encode_tensor_map_bf16(h, &tq, h->tc_qb.p, kd, m, TC_BM)) return rc;
-	tc_fill_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(h->tc_gthr.as<float>(), 0, m, __uint_as_float_host(f32_orderable(INFINITY)));
-	h->stats.aux_launches++;
 	Tc2Params p{};
 	p.xn = h->tc_xn.as<float>();
 	p.qn = h->tc_qn.as<float>();
@@ -373,7 +370,7 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	h->stats.last_nsplit = rows_split;
 	if (rsplit > 32) // many cold splits per query: one block per query
 		tc_select2_block_kernel<1><<<(unsigned)m, 256, 0, st>>>(p.cand, p.cnt, TC2_CAP, rsplit, p.m, p.k, p.qn, eps_rel, eps_abs,
-		                                                        h->tc_xnorm_max, h->tc_sel.as<uint64_t>(), TC_PAD, flags);
+		                                                        h->tc_xnorm_max, h->tc_sel.as<uint64_t>(), TC_PAD, flags, p.gthr);
 	else
 		tc_select2_kernel<1><<<(unsigned)((m + 3) / 4), 128, 0, st>>>(p.cand, p.cnt, TC2_CAP, rsplit, p.m, p.k, p.qn, eps_rel, eps_abs,
 		                                                             h->tc_xnorm_max, h->tc_sel.as<uint64_t>(), TC_PAD, flags);

@@ -483,9 +483,11 @@ template <int LPL>
 __global__ void __launch_bounds__(256) tc_select2_block_kernel(const uint64_t* __restrict__ cand, const uint32_t* __restrict__ cnt, uint32_t cap,
                                                                 uint32_t rsplit, uint32_t m, uint32_t k, const float* __restrict__ qnorm2,
                                                                 float eps_rel, float eps_abs, float xnorm_max, uint64_t* __restrict__ out,
-                                                                uint32_t pad, uint32_t* __restrict__ flags) {
+                                                                uint32_t pad, uint32_t* __restrict__ flags, const uint32_t* __restrict__ gthr) {
 	__shared__ uint32_t pre[TC2_MAX_SPLIT + 8];
 	__shared__ uint64_t lists[8][32 * LPL];
+	__shared__ uint64_t fk[2048];
+	__shared__ uint32_t fcnt, red[2][8];
 	__shared__ float t_s;
 	__shared__ uint32_t w_s, over_s;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -509,10 +511,83 @@ __global__ void __launch_bounds__(256) tc_select2_block_kernel(const uint64_t* _
 			total += __shfl_sync(FULL, incl, 31);
 		}
 		over = __any_sync(FULL, over);
-		if (lane == 0) { pre[rsplit] = total; w_s = 0; over_s = over ? 1u : 0u; }
+		if (lane == 0) { pre[rsplit] = total; w_s = 0; over_s = over ? 1u : 0u; fcnt = 0; }
 	}
 	__syncthreads();
 	const uint32_t total = pre[rsplit];
+	if (gthr != nullptr) {
+		// Fast path. The filter's final shared bound gthr[q] is >= A_k + 2e (it is the smallest local k-th + 2e), so only keys
+		// at or below it can matter: usually ~10^3 of the ~10^4 buffered keys of a 148-split launch. They are parked in
+		// shared memory (8 independent loads in flight per thread), then the exact k-th smallest a' comes from a bitwise
+		// search over the orderable encoding with the keys in registers -- no list insertions.
+		const uint32_t gb = gthr[q];
+		const uint32_t tid = threadIdx.x;
+		// warp w walks splits w, w + 8, ...: four splits (3 x 32 keys each) in flight per round, lanes read neighbouring
+		// keys; the counts come from the prefix in shared memory, so no load depends on another
+		auto park = [&](uint64_t key) {
+			if (key != KEY_EMPTY && (uint32_t)(key >> 32) <= gb) {
+				const uint32_t pos = atomicAdd(&fcnt, 1u);
+				if (pos < 2048) fk[pos] = key;
+			}
+		};
+		for (uint32_t s0 = warp; s0 < rsplit; s0 += 32) {
+			uint64_t kk[4][3];
+			uint32_t c[4];
+#pragma unroll
+			for (int u = 0; u < 4; ++u) {
+				const uint32_t sp = s0 + 8 * u;
+				c[u] = sp < rsplit ? pre[sp + 1] - pre[sp] : 0u;
+#pragma unroll
+				for (int j = 0; j < 3; ++j)
+					kk[u][j] = (uint32_t)(lane + 32 * j) < c[u] ? __ldg(qbuf + (size_t)sp * cap + lane + 32 * j) : KEY_EMPTY;
+			}
+#pragma unroll
+			for (int u = 0; u < 4; ++u) {
+#pragma unroll
+				for (int j = 0; j < 3; ++j) park(kk[u][j]);
+				for (uint32_t i = 96 + lane; i < c[u]; i += 32) park(__ldg(qbuf + (size_t)(s0 + 8 * u) * cap + i)); // long buffers: rare
+			}
+		}
+		__syncthreads();
+		const uint32_t nf = fcnt;
+		if (nf <= 2048) {
+			uint64_t r[8];
+#pragma unroll
+			for (int u = 0; u < 8; ++u) r[u] = tid + u * 256 < nf ? fk[tid + u * 256] : KEY_EMPTY;
+			float t = __int_as_float(0x7f800000);
+			if (nf >= k) {
+				uint32_t v = 0;
+#pragma unroll 1
+				for (int bit = 31; bit >= 0; --bit) {
+					const uint32_t trial = v | (1u << bit);
+					uint32_t c = 0;
+#pragma unroll
+					for (int u = 0; u < 8; ++u) c += (uint32_t)(r[u] >> 32) < trial ? 1u : 0u;
+					c = __reduce_add_sync(FULL, c);
+					if (lane == 0) red[bit & 1][warp] = c;
+					__syncthreads(); // one barrier per round: the two halves of red[] alternate
+					uint32_t tot = 0;
+#pragma unroll
+					for (int w = 0; w < 8; ++w) tot += red[bit & 1][w];
+					if (tot < k) v = trial;
+				}
+				const float eps = eps_rel * sqrtf(qnorm2[q]) * xnorm_max + eps_abs;
+				t = __fadd_ru(f32_from_orderable(v), 2.f * eps);
+			}
+			uint64_t* o = out + (size_t)q * pad;
+#pragma unroll
+			for (int u = 0; u < 8; ++u)
+				if (r[u] != KEY_EMPTY && key_dist(r[u]) <= t) {
+					const uint32_t pos = atomicAdd(&w_s, 1u);
+					if (pos < pad) o[pos] = r[u];
+				}
+			__syncthreads();
+			const uint32_t w = w_s;
+			for (uint32_t i = w + tid; i < pad; i += 256) o[i] = KEY_EMPTY;
+			if ((over_s || w > pad) && tid == 0) atomicAdd(flags, 1u);
+			return;
+		}
+	}
 	const uint32_t per = (total + 7) / 8, i_begin = min(total, warp * per), i_end = min(total, i_begin + per);
 	// lane-private cursor into the prefix: flat indices of a lane only grow
 	auto fetch = [&](uint32_t i, uint32_t& sp) -> uint64_t {
@@ -606,6 +681,19 @@ __global__ void tc_check_exact_kernel(const TcStats* __restrict__ qs, float xmin
 	const bool exact = !qs->inexact && amax <= 256.f && 2.0 * (double)d * amax * amax < lim;
 	if (!exact) atomicAdd(flags, 1u);
 }
+// start of a batch in one launch: query statistics reset, the batch's flags cleared, shared bounds set to +inf
+__global__ void tc_batch_init_kernel(TcStats* s, uint32_t* flags, uint32_t* gthr, uint32_t m) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < m) gthr[i] = f32_orderable(__int_as_float(0x7f800000));
+	if (i < 4) flags[i] = 0u;
+	if (i == 0) {
+		s->vmin = f32_orderable(3.4e38f);
+		s->vmax = f32_orderable(-3.4e38f);
+		s->inexact = 0u;
+		s->nmax = f32_orderable(0.f);
+	}
+}
+
 __global__ void tc_stats_init_kernel(TcStats* s) {
 	s->vmin = f32_orderable(3.4e38f);
 	s->vmax = f32_orderable(-3.4e38f);

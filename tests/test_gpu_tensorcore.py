@@ -115,8 +115,10 @@ def test_shard_offset_and_small_batches(ex, oracle):
     ids, dists, _, st = run(ex, base, q, 10, id_offset=1000)
     oi, od, _ = oracle.bf_query(base, q, 10, threads=16)
     assert np.array_equal(ids, oi + np.uint64(1000)) and np.array_equal(dists, od)
-    ids, dists, _, st = run(ex, base, q[:8], 10)        # below tc_min_batch (9): SIMT path
-    assert st["tc_launches"] == 0 and np.array_equal(ids, oi[:8])
+    ids, dists, _, st = run(ex, base, q[:4], 10)        # below tc_min_batch (5): SIMT path
+    assert st["tc_launches"] == 0 and np.array_equal(ids, oi[:4])
+    ids, dists, _, st = run(ex, base, q[:5], 10)        # smallest batch on the tensor-core path
+    assert st["tc_launches"] == 1 and np.array_equal(ids, oi[:5]) and np.array_equal(dists, od[:5])
     ids, dists, _, st = run(ex, base, q[:100], 10)      # small batch on the tensor-core path: many cold row splits
     assert st["tc_launches"] in (1, 2) and np.array_equal(ids, oi[:100]) and np.array_equal(dists, od[:100])
 
