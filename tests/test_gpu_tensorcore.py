@@ -250,3 +250,29 @@ def test_streamed_query_operand(ex, oracle, n, m, d, kind, astream):
         oi, od, _ = oracle.bf_query(base, q, 10, metric=1, threads=16)
         swaps = assert_topk_parity(ids, dists, oi, od, base, q, metric="ip", tag="streamed d960 ip")
         assert swaps <= 4
+
+
+def test_streamed_exact_mode_long_rows_and_seeding(ex):
+    """streamed query operand in the bf16-EXACT mode (d = 960 of small integers: dot products stay below 2^24, 15 k-blocks
+    per tile), with and without the seeding launch; against the SIMT scan"""
+    rng = np.random.default_rng(77)
+    base = rng.integers(0, 64, (40_000, 960)).astype(np.float32)
+    q = rng.integers(0, 64, (300, 960)).astype(np.float32)
+    ref = run(ex, base, q, 10, tc=0)
+    for boot in (0, 2):
+        a = run(ex, base, q, 10, boot=boot)
+        assert a[3]["tc_mode"] == 1 and a[3]["tc_launches"] == (2 if boot else 1) and a[3]["tc_fallbacks"] == 0 and a[3]["last_qtile"] == 256
+        assert np.array_equal(a[0], ref[0]) and np.array_equal(a[1], ref[1])
+
+
+def test_small_batch_select_many_candidates(ex):
+    """block select of small batches: k = 16 on clustered data, where far more keys than the fast path parks (2048) sit
+    under the shared bound, must take the general path and still be exact"""
+    rng = np.random.default_rng(78)
+    centers = rng.integers(0, 256, (8, 64)).astype(np.float32)
+    base = np.clip(centers[rng.integers(0, 8, 400_000)] + rng.integers(-1, 2, (400_000, 64)), 0, 255).astype(np.float32)
+    q = np.clip(centers[rng.integers(0, 8, 20)] + rng.integers(-1, 2, (20, 64)), 0, 255).astype(np.float32)
+    a = run(ex, base, q, 16)
+    b = run(ex, base, q, 16, tc=0)
+    assert a[3]["tc_launches"] == 1
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
