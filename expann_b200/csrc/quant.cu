@@ -84,7 +84,11 @@ int launch_quant_scan(expann_gpu* h, const float* d_q, size_t m, size_t k, uint6
 	const uint32_t groups = (uint32_t)((h->n + QS_ROWS - 1) / QS_ROWS);
 	int sms = 148;
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
-	uint32_t want = (uint32_t)((16u * sms + qtiles - 1) / qtiles);
+	// whole waves of CTAs (1 CTA per SM), as few row splits as fill them: with k' ~ 100 every split pays a long list
+	// warm-up (the per-warp lists stay unselective for thousands of rows), so 125 query tiles x 1 split (22.6 ms at C5)
+	// beat 125 x 19 (41.4 ms); a single query tile still gets one split per SM
+	const uint32_t waves = std::max(1u, (qtiles + (uint32_t)sms - 1) / (uint32_t)sms);
+	const uint32_t want = std::max(1u, (uint32_t)((uint64_t)sms * waves / qtiles));
 	uint32_t nsplit = std::max(1u, std::min(want, std::max(1u, groups / 8u)));
 	if (h->opt_nsplit > 0) nsplit = std::min((uint32_t)h->opt_nsplit, groups);
 	const uint32_t gps = (groups + nsplit - 1) / nsplit;
