@@ -48,7 +48,8 @@ typedef struct expann_gpu_stats {
 	uint64_t last_nsplit, last_qtile;
 	uint64_t distcomps; /* RECORD_STATS num_distcomps analogue (src/antitopo_engine.h:125-129), graph engine */
 	uint64_t hot_time_ns, hot_timed_launches; /* CUDA-event time of the dominant kernel, see expann_gpu_set_timing */
-	uint64_t tc_launches, tc_fallbacks;       /* tensor-core filter launches; batches redone by the SIMT scan */
+	uint64_t tc_launches, tc_fallbacks;       /* tensor-core filter launches; batches redone by the SIMT scan (counted on
+	                                             the device: expann_gpu_stats() synchronises the device to read it) */
 	uint64_t tc_mode;                         /* 0 off, 1 bf16-exact, 2 two-term bf16 split (decided by build()) */
 	uint64_t reserved[3];
 } expann_gpu_stats_t;
@@ -118,9 +119,14 @@ int expann_gpu_pair_distances(int device, int kind, const void* a, const void* b
 int expann_gpu_set_timing(expann_gpu_t* h, int on);
 int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
 /* tuning knobs by name (the reference exposes its knobs as Engine::config members, src/bench_runner.h:133-172):
- * "qtile" (0 auto | 1 | 4 | 8), "nsplit" (0 auto | forced row splits per scan), "tc" (0/1: tensor-core candidate filter for large
- * batches, must be set before build()), "tc_min_batch" (default 16: measured crossover with the SIMT scan on 1M x 128), "kprime" (QUANT_SCAN: survivors
- * re-ranked in fp32, 0 auto = min(128, 10k)). Unknown names: EXPANN_ERR_ARG. */
+ * "qtile" (0 auto | 1 | 4 | 8), "nsplit" (0 auto | forced row splits per scan), "kprime" (QUANT_SCAN: survivors
+ * re-ranked in fp32, 0 auto = min(128, 10k)), "graph_occ" (GRAPH: resident CTAs of 4 warps per SM, 2 | 4 | 5 | 8,
+ * default 5, before build()).
+ * Tensor-core candidate filter of the brute-force engine: "tc" (0/1; operands are prepared by build(), so enabling
+ * needs to precede it), "tc_min_batch" (default 5: measured crossover with the SIMT scan on 1M x 128), "tc_pair" (0/1:
+ * clusters of two CTAs for batches > 128, default 1), "tc_astream" (0 off | 1 when the query tile cannot stay resident
+ * | 2 always), "tc_boot" (seeding launch: 0 off | 1 exact mode and >= 8192 queries | 2 always), "tc_v1" (force the
+ * chunked first form). Unknown names: EXPANN_ERR_ARG. */
 int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value);
 /* library build info: "sm_100a;..." */
 const char* expann_gpu_version(void);
