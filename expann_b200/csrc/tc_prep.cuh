@@ -70,10 +70,14 @@ __global__ void tc_convert_kernel(const float* __restrict__ src, size_t src_stri
 	if (lane == 0) {
 		if (norm2) norm2[row] = s;
 		if (stats) {
-			atomicMin(&stats->vmin, f32_orderable(mn));
-			atomicMax(&stats->vmax, f32_orderable(mx));
-			if (bad) atomicOr(&stats->inexact, 1u);
-			atomicMax(&stats->nmax, f32_orderable(s));
+			// the statistics only move one way, so a (possibly stale) read that already covers this row's value makes the
+			// atomic unnecessary: 10^4 rows would otherwise queue ~4 x 10^4 atomics on four addresses (~20 us)
+			volatile TcStats* vs = stats;
+			const uint32_t omn = f32_orderable(mn), omx = f32_orderable(mx), os = f32_orderable(s);
+			if (omn < vs->vmin) atomicMin(&stats->vmin, omn);
+			if (omx > vs->vmax) atomicMax(&stats->vmax, omx);
+			if (bad && !vs->inexact) atomicOr(&stats->inexact, 1u);
+			if (os > vs->nmax) atomicMax(&stats->nmax, os);
 		}
 	}
 }
