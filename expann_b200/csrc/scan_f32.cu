@@ -162,8 +162,10 @@ int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, ui
 	p.gate = gate;
 	p.gate_count = gate_count;
 	dim3 grid(qtiles, nsplit);
-	if (gate) // K3's queued redo: runs only if the device flag is up; neither timed nor counted on the host
+	if (gate) { // K3's queued redo: does its work only if the device flag is up; not timed, counted as an auxiliary launch
+		h->stats.aux_launches++;
 		return qt == 8 ? launch_m<8>(h, p, grid, st) : qt == 4 ? launch_m<4>(h, p, grid, st) : launch_m<1>(h, p, grid, st);
+	}
 	cudaEvent_t t0 = timing_begin(h, st);
 	int rc = qt == 8 ? launch_m<8>(h, p, grid, st) : qt == 4 ? launch_m<4>(h, p, grid, st) : launch_m<1>(h, p, grid, st);
 	timing_end(h, t0, st);
