@@ -1,4 +1,16 @@
-// Host side of K3: operand preparation at build(), chunked filter launches with threshold refresh, fp32 re-rank.
+// Host side of K3: operand preparation at build(), filter launches, selection, fp32 re-rank.
+//
+// Forms (all share the operand formats, the bound argument below and the re-rank):
+//   * second form, k <= 16 (tc_batch2): ONE filter launch with in-kernel per-query bounds shared between row splits --
+//       pair form  (tc_filter3.cuh, clusters of two CTAs, cta_group::2): batches > 128 queries; query tile resident in
+//                  shared memory, or streamed through the ring beside the row tiles when the rows are too long for that
+//                  (d > 128 real-valued / d > 384 bf16-exact: GIST's 960); optional seeding launch for big batches;
+//       single-CTA form (tc_filter2.cuh): batches <= 128 queries;
+//     then tc_select2 (exact k-th smallest a' per query, survivors) and K4 (rerank.cuh). A batch whose flag is up
+//     (buffer overflow, queries not bf16-exact, too many survivors) is redone by the SIMT scan, queued behind the flag
+//     on the device (ScanParams::gate) -- no host round trip.
+//   * first form, 16 < k <= 128 (tc_batch, tc_filter.cuh): row chunks of doubling size with the bound refreshed between
+//     launches; needs a resident query tile and >= 512 queries. The graph build's bottom-layer kNN (k = K + 1) uses it.
 //
 // Why the result is exact. Let a'(x) be the tensor-core value and e >= |a'(x) - a'_true(x)| the error bound of the
 // operand format (0 for bf16-exact integer data; eps_rel*|q|*max|x| for the two-term split). After any prefix of

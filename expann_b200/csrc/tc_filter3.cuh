@@ -16,6 +16,13 @@
 //     8 epilogue warps per CTA = (lane quadrant) x (column half): a thread owns (query, half of the tile's rows) and
 //     is one "split" of that query as far as bounds, buffers and the select kernels are concerned
 //     (buffers per query = 2 x row splits); all 16 epilogue warps of the pair arrive on the leader's tm_empty[acc].
+//   * the epilogue thread reads its 128 accumulator columns into registers in one go and the warp hands the accumulator
+//     back BEFORE looking at them; chunks whose minimum passes the bound are handled from those registers;
+//   * ASTREAM: no resident query tile -- every ring slot carries [A k-block | B k-block | norm terms] (any row length);
+//   * seeding (Tc2Params::seed_in / seed_out): a first launch over the leading tiles leaves each stream's sorted list,
+//     the main launch starts from their union instead of +inf.
+// Measured (B200): bf16-exact 10 000 x 1M x 128 in 1.80 ms (84-86 % of the cuBLAS bf16 burst peak, tensor pipe 82 %
+// active with the clock at the power limit); two-term split format 92-103 % of that peak (MMA-bound).
 #pragma once
 #include "tc_filter2.cuh"
 
