@@ -493,6 +493,8 @@ def main():
                 from tools import bench_extras
                 torch.cuda.empty_cache()
                 out["graph_c3"] = bench_extras.graph_c3(local_rank, max(2, args.steps), args.warmup, cpu=not args.no_cpu, peak_gbs=peak)
+                if "roofline" in out["graph_c3"]:   # DRAM bytes per launch of the ef = 40 search from the committed ncu capture
+                    out["graph_c3"]["roofline"]["traffic"] = ncu_traffic("graph_search_kernel")
             except Exception as ex:  # noqa: BLE001
                 out["graph_c3"] = {"error": repr(ex)[:300]}
         emit(out)
