@@ -268,32 +268,41 @@ int expann_gpu_query(expann_gpu_t* h, const float* q, size_t m, size_t k, size_t
 	DeviceGuard g(h->device);
 	cudaStream_t st = h->stream;
 	const size_t qbytes = m * h->d * sizeof(float), nk = m * k;
+	// results leave the device as ONE block [ids nk x 8 | keys nk x 4 | counts m x 8] (8-byte aligned parts): a staged
+	// (pageable) caller gets one device-to-host copy instead of three
+	const size_t off_d = nk * 8, off_c = round_up(off_d + nk * 4, 8), res_bytes = off_c + m * 8;
 	EXPANN_CUDA(h, h->h_q.ensure(qbytes));
-	EXPANN_CUDA(h, h->h_ids.ensure(nk * 8));
-	EXPANN_CUDA(h, h->h_dists.ensure(nk * 4));
-	EXPANN_CUDA(h, h->h_counts.ensure(m * 8));
+	EXPANN_CUDA(h, h->h_ids.ensure(res_bytes));
 	EXPANN_CUDA(h, h->keys.ensure(nk * 8 + qbytes + 256)); // keys | raw queries
-	EXPANN_CUDA(h, h->ids.ensure(nk * 8));
-	EXPANN_CUDA(h, h->dists.ensure(nk * 4));
-	EXPANN_CUDA(h, h->counts.ensure(m * 8));
+	EXPANN_CUDA(h, h->ids.ensure(res_bytes));
+	uint8_t* d_res = h->ids.as<uint8_t>();
+	uint64_t* d_ids = reinterpret_cast<uint64_t*>(d_res);
+	float* d_dist = reinterpret_cast<float*>(d_res + off_d);
+	uint64_t* d_cnt = reinterpret_cast<uint64_t*>(d_res + off_c);
 	// page-locked caller buffers (cudaHostAlloc / cudaHostRegister / torch pin_memory) are used by the copy engines
 	// directly; pageable ones go through the handle's pinned staging buffers
 	const bool q_pinned = is_pinned_host(q), ids_pinned = is_pinned_host(ids_out);
 	const bool dist_pinned = dist_out && is_pinned_host(dist_out), counts_pinned = counts_out && is_pinned_host(counts_out);
+	const bool direct = ids_pinned && (!dist_out || dist_pinned) && (!counts_out || counts_pinned);
 	if (!q_pinned) std::memcpy(h->h_q.p, q, qbytes);
 	float* d_q = reinterpret_cast<float*>(h->keys.as<uint8_t>() + round_up(nk * 8, 256));
 	EXPANN_CUDA(h, cudaMemcpyAsync(d_q, q_pinned ? (const void*)q : h->h_q.p, qbytes, cudaMemcpyHostToDevice, st));
 	if (int rc = query_device_impl(h, d_q, m, k, ef, h->keys.as<uint64_t>(), st)) return rc;
-	if (int rc = launch_decode(h, h->keys.as<uint64_t>(), m, k, 0, h->ids.as<uint64_t>(), h->dists.as<float>(),
-	                           h->counts.as<uint64_t>(), st))
-		return rc;
-	EXPANN_CUDA(h, cudaMemcpyAsync(ids_pinned ? (void*)ids_out : h->h_ids.p, h->ids.p, nk * 8, cudaMemcpyDeviceToHost, st));
-	if (dist_out) EXPANN_CUDA(h, cudaMemcpyAsync(dist_pinned ? (void*)dist_out : h->h_dists.p, h->dists.p, nk * 4, cudaMemcpyDeviceToHost, st));
-	if (counts_out) EXPANN_CUDA(h, cudaMemcpyAsync(counts_pinned ? (void*)counts_out : h->h_counts.p, h->counts.p, m * 8, cudaMemcpyDeviceToHost, st));
-	EXPANN_CUDA(h, cudaStreamSynchronize(st));
-	if (!ids_pinned) std::memcpy(ids_out, h->h_ids.p, nk * 8);
-	if (dist_out && !dist_pinned) std::memcpy(dist_out, h->h_dists.p, nk * 4);
-	if (counts_out && !counts_pinned) std::memcpy(counts_out, h->h_counts.p, m * 8);
+	if (int rc = launch_decode(h, h->keys.as<uint64_t>(), m, k, 0, d_ids, d_dist, d_cnt, st)) return rc;
+	if (direct) {
+		EXPANN_CUDA(h, cudaMemcpyAsync(ids_out, d_ids, nk * 8, cudaMemcpyDeviceToHost, st));
+		if (dist_out) EXPANN_CUDA(h, cudaMemcpyAsync(dist_out, d_dist, nk * 4, cudaMemcpyDeviceToHost, st));
+		if (counts_out) EXPANN_CUDA(h, cudaMemcpyAsync(counts_out, d_cnt, m * 8, cudaMemcpyDeviceToHost, st));
+		EXPANN_CUDA(h, cudaStreamSynchronize(st));
+	} else {
+		const size_t need = counts_out ? res_bytes : (dist_out ? off_d + nk * 4 : nk * 8);
+		EXPANN_CUDA(h, cudaMemcpyAsync(h->h_ids.p, d_res, need, cudaMemcpyDeviceToHost, st));
+		EXPANN_CUDA(h, cudaStreamSynchronize(st));
+		const uint8_t* r = static_cast<const uint8_t*>(h->h_ids.p);
+		std::memcpy(ids_out, r, nk * 8);
+		if (dist_out) std::memcpy(dist_out, r + off_d, nk * 4);
+		if (counts_out) std::memcpy(counts_out, r + off_c, m * 8);
+	}
 	return EXPANN_OK;
 }
 
