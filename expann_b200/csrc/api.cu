@@ -110,7 +110,7 @@ static int padded_queries(expann_gpu* h, const float* d_q, size_t m, cudaStream_
 	EXPANN_CUDA(h, h->qpad.ensure(m * h->d_pad * sizeof(float)));
 	EXPANN_CUDA(h, cudaMemsetAsync(h->qpad.p, 0, m * h->d_pad * sizeof(float), st));
 	EXPANN_CUDA(h, cudaMemcpy2DAsync(h->qpad.p, h->d_pad * sizeof(float), d_q, h->d * sizeof(float), h->d * sizeof(float),
-	                                 m, cudaMemcpyDeviceToDevice, st));
+	                                 m, cudaMemcpyDefault, st)); // d_q may be mapped host memory (small calls)
 	h->stats.aux_launches += 2;
 	*out = h->qpad.as<float>();
 	return EXPANN_OK;
@@ -250,6 +250,8 @@ int expann_gpu_query_device(expann_gpu_t* h, const float* d_q, size_t m, size_t 
 	return query_device_impl(h, d_q, m, k, ef, d_keys_out, (cudaStream_t)stream);
 }
 
+constexpr size_t SMALL_CALL_BYTES = 16 << 10; // queries / results of a call up to this size skip the copy engines
+
 static bool is_pinned_host(const void* p) {
 	cudaPointerAttributes a{};
 	if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
@@ -284,6 +286,32 @@ int expann_gpu_query(expann_gpu_t* h, const float* q, size_t m, size_t k, size_t
 	const bool q_pinned = is_pinned_host(q), ids_pinned = is_pinned_host(ids_out);
 	const bool dist_pinned = dist_out && is_pinned_host(dist_out), counts_pinned = counts_out && is_pinned_host(counts_out);
 	const bool direct = ids_pinned && (!dist_out || dist_pinned) && (!counts_out || counts_pinned);
+	if (qbytes <= SMALL_CALL_BYTES && res_bytes <= SMALL_CALL_BYTES) {
+		// few queries per call (the reference harness's own loop is one per call, src/basic_bench.h:82-126): no copy
+		// engine behind the kernels — the decode kernel writes the results into the handle's page-locked staging buffer
+		// (mapped into the device's address space), and the graph search reads its queries from one; up to four copy
+		// operations and their latencies are replaced by small host memcpys
+		const bool q_pin = is_pinned_host(q);
+		if (!q_pin) std::memcpy(h->h_q.p, q, qbytes);
+		const float* qsrc = static_cast<const float*>(h->h_q.p);
+		if (h->cfg.engine != EXPANN_ENGINE_GRAPH) {
+			// the scans read a query once per CTA: those reads stay in HBM (the graph search reads it exactly once)
+			float* d_q = reinterpret_cast<float*>(h->keys.as<uint8_t>() + round_up(nk * 8, 256));
+			EXPANN_CUDA(h, cudaMemcpyAsync(d_q, q_pin ? (const void*)q : h->h_q.p, qbytes, cudaMemcpyHostToDevice, st));
+			qsrc = d_q;
+		} else if (q_pin)
+			std::memcpy(h->h_q.p, q, qbytes);
+		uint8_t* r = static_cast<uint8_t*>(h->h_ids.p);
+		if (int rc = query_device_impl(h, qsrc, m, k, ef, h->keys.as<uint64_t>(), st)) return rc;
+		if (int rc = launch_decode(h, h->keys.as<uint64_t>(), m, k, 0, reinterpret_cast<uint64_t*>(r), reinterpret_cast<float*>(r + off_d),
+		                           reinterpret_cast<uint64_t*>(r + off_c), st))
+			return rc;
+		EXPANN_CUDA(h, cudaStreamSynchronize(st));
+		std::memcpy(ids_out, r, nk * 8);
+		if (dist_out) std::memcpy(dist_out, r + off_d, nk * 4);
+		if (counts_out) std::memcpy(counts_out, r + off_c, m * 8);
+		return EXPANN_OK;
+	}
 	if (!q_pinned) std::memcpy(h->h_q.p, q, qbytes);
 	float* d_q = reinterpret_cast<float*>(h->keys.as<uint8_t>() + round_up(nk * 8, 256));
 	EXPANN_CUDA(h, cudaMemcpyAsync(d_q, q_pinned ? (const void*)q : h->h_q.p, qbytes, cudaMemcpyHostToDevice, st));
@@ -393,6 +421,9 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 		if (value != 2 && value != 4 && value != 5 && value != 8) return fail(h, EXPANN_ERR_ARG, "graph_occ must be 2, 4, 5 or 8");
 		if (h->built) return fail(h, EXPANN_ERR_STATE, "graph_occ must be set before build()");
 		h->opt_graph_occ = (int)value;
+	} else if (nm == "graph_cta_batch") {
+		if (value < -1) return fail(h, EXPANN_ERR_ARG, "graph_cta_batch must be >= -1 (-1 = automatic)");
+		h->opt_graph_cta_batch = (int)value;
 	} else if (nm == "tc_boot") {
 		h->opt_tc_boot = (int)value; // 0 off, 1 bf16-exact mode only (default), 2 both modes
 	} else if (nm == "tc_v1") {

@@ -176,6 +176,27 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 	p.max_layer = h->graph.max_layer;
 	p.id_add = (uint32_t)h->cfg.id_offset;
 	p.compressed = h->cfg.use_compression ? 1 : 0;
+	if (m <= (size_t)(h->opt_graph_cta_batch < 0 ? sms : h->opt_graph_cta_batch)) {
+		// latency form: one CTA per query (few queries per call; nothing to hide the hops' round trips behind)
+		const size_t smem1 = (size_t)h->d_pad * 5 + GS_MAXNB * 8 + 16 + 256 * 8; // query | u8 query | nb | nbd | ctl | beam copy
+		if (smem1 > 200 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "graph search: d too large");
+		const unsigned grid1 = (unsigned)std::min<size_t>(m, (size_t)h->g_ctas * GS_WARPS);
+		cudaEvent_t t0 = timing_begin(h, st);
+#define GC_LAUNCH(L)                                                                                              \
+	do {                                                                                                          \
+		EXPANN_CUDA(h, (cudaFuncSetAttribute(graph_search_cta_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1))); \
+		graph_search_cta_kernel<L><<<grid1, 32 * GC_WARPS, smem1, st>>>(p);                                      \
+	} while (0)
+		if (cap <= 32) GC_LAUNCH(1);
+		else if (cap <= 64) GC_LAUNCH(2);
+		else if (cap <= 128) GC_LAUNCH(4);
+		else GC_LAUNCH(8);
+#undef GC_LAUNCH
+		timing_end(h, t0, st);
+		EXPANN_CUDA(h, cudaGetLastError());
+		h->stats.graph_launches++;
+		return EXPANN_OK;
+	}
 	const size_t smem = ((size_t)h->d_pad * 5 + GS_MAXNB * 8) * GS_WARPS;
 	if (smem > 200 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "graph search: d too large");
 	const unsigned grid = (unsigned)std::min<size_t>(h->g_ctas, (m + GS_WARPS - 1) / GS_WARPS);

@@ -328,4 +328,380 @@ __global__ void __launch_bounds__(32 * GS_WARPS, MINB) graph_search_kernel(const
 	}
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// K5, latency form: ONE CTA (GC_WARPS warps) per query, for calls with few queries (the reference harness's own
+// loop is one query per call, src/basic_bench.h:82-126). Same search as graph_search_kernel — same visit order,
+// same admission order, same per-vertex summation order, hence the same ids and distances bit for bit — but a
+// hop costs two dependent memory round trips instead of three plus one per gather round:
+//   * the 32 teams of 8 lanes score 32 neighbours of the expanded vertex at once (a whole row of M0 <= 32 in
+//     one round; the warp form needs four);
+//   * a team asks for its neighbour's vector and its visited byte together: the distance of an already visited
+//     vertex is computed and thrown away (bandwidth is idle in this regime, latency is not);
+//   * the beam stays in warp 0's registers; the other warps only score.
+// Entries of a row keep their positions (no compaction): nb[pos] = NO_VERTEX marks "not a candidate".
+// ---------------------------------------------------------------------------------------------------------
+constexpr int GC_WARPS = 8;
+
+template <bool VIS>
+__device__ __forceinline__ void cta_score_row(const GraphParams& p, const uint32_t* __restrict__ row, uint32_t rowlen,
+                                              bool compressed, const float* qsm, const uint8_t* qc, uint32_t* nb,
+                                              float* nbd, uint8_t* vis, uint8_t ep8, const uint32_t* __restrict__ row2,
+                                              uint32_t layer) {
+	const int tid = threadIdx.x, team = tid >> 3, tl = tid & 7, lane = tid & 31;
+	constexpr int NTEAM = GC_WARPS * 4;
+	// speculation on the next hop: row2 is the adjacency row of the runner-up of the beam (in L2 since the hop that
+	// found it, see below); its neighbours' vectors and visited bytes are asked into L2 while this hop is scored
+	uint32_t v2 = NO_VERTEX;
+	if (VIS && row2 && (uint32_t)tid < rowlen) v2 = __ldg(row2 + tid);
+	for (uint32_t p0 = 0; p0 < rowlen; p0 += NTEAM) {
+		const uint32_t pos = p0 + team;
+		uint32_t v = NO_VERTEX;
+		if (tl == 0 && pos < rowlen) v = __ldg(row + pos);
+		v = __shfl_sync(FULL, v, lane & ~7);
+		const bool have = v != NO_VERTEX;
+		if (VIS) {
+			// every neighbour may be expanded later: its own adjacency row goes to L2 now
+			if (have && (uint32_t)tl * 32u < rowlen) prefetch_l2(p.bottom + (size_t)v * p.m0s + tl * 32);
+			if (p0 == 0 && v2 != NO_VERTEX) {
+				const uint32_t row_bytes = compressed ? p.d_pad : p.d_pad * 4;
+				const char* r = (compressed ? reinterpret_cast<const char*>(p.codes) : reinterpret_cast<const char*>(p.base)) + (size_t)v2 * row_bytes;
+				for (uint32_t o = 0; o < row_bytes; o += 128) prefetch_l2(r + o);
+				prefetch_l2(vis + v2);
+			}
+		}
+		uint8_t seen = ep8;
+		if (VIS && have && tl == 0) seen = vis[v]; // in flight together with the vector loads below
+		// upper layers: the walk moves to one of these neighbours or drops a layer at the same vertex; the index of
+		// each neighbour's upper rows is fetched with its vector so that the rows themselves can be asked into L2
+		uint32_t ui2 = NO_VERTEX;
+		if (!VIS && have) {
+			if (tl == 1) ui2 = __ldg(p.upper_idx + v);
+			if (tl == 2) prefetch_l2(p.upper_nl + v);
+			if (tl == 3 && layer == 1) prefetch_l2(p.bottom + (size_t)v * p.m0s);
+		}
+		float dist;
+		if (compressed) {
+			const uint8_t* pa = p.codes + (size_t)(have ? v : 0) * p.d_pad;
+			const int nchunk = p.d_pad >> 4;
+			uint32_t sa = 0;
+			if (have)
+				for (int c = tl; c < nchunk; c += 8) {
+					const uint4 xa = __ldg(reinterpret_cast<const uint4*>(pa + c * 16));
+					const uint4 q = *reinterpret_cast<const uint4*>(qc + c * 16);
+					uint32_t t;
+					t = __vabsdiffu4(q.x, xa.x); sa = __dp4a(t, t, sa); t = __vabsdiffu4(q.y, xa.y); sa = __dp4a(t, t, sa);
+					t = __vabsdiffu4(q.z, xa.z); sa = __dp4a(t, t, sa); t = __vabsdiffu4(q.w, xa.w); sa = __dp4a(t, t, sa);
+				}
+#pragma unroll
+			for (int o = 4; o >= 1; o >>= 1) sa += __shfl_xor_sync(FULL, sa, o);
+			dist = (float)(int32_t)sa;
+		} else {
+			const float* pa = p.base + (size_t)(have ? v : 0) * p.d_pad + tl * 4;
+			const int nstep = p.d_pad >> 5;
+			float sa = 0.f;
+			if (have)
+				for (int s0 = 0; s0 < nstep; s0 += 4) {
+					float4 xa[4];
+#pragma unroll
+					for (int s = 0; s < 4; ++s)
+						if (s0 + s < nstep) xa[s] = ldg128f(pa + (s0 + s) * 32);
+#pragma unroll
+					for (int s = 0; s < 4; ++s)
+						if (s0 + s < nstep) { // same order of operations as gather_dist_f32
+							const float4 q = *reinterpret_cast<const float4*>(qsm + (s0 + s) * 32 + tl * 4);
+							float t;
+							t = q.x - xa[s].x; sa = fmaf(t, t, sa); t = q.y - xa[s].y; sa = fmaf(t, t, sa);
+							t = q.z - xa[s].z; sa = fmaf(t, t, sa); t = q.w - xa[s].w; sa = fmaf(t, t, sa);
+						}
+				}
+#pragma unroll
+			for (int o = 4; o >= 1; o >>= 1) sa += __shfl_xor_sync(FULL, sa, o);
+			dist = sa;
+		}
+		if (!VIS && ui2 != NO_VERTEX) { // rows of this layer and the one below are adjacent
+			const uint32_t lo = layer >= 2 ? layer - 2 : 0, bytes = (layer >= 2 ? 2 : 1) * p.ms * 4;
+			const char* r = reinterpret_cast<const char*>(p.upper + ((size_t)ui2 + lo) * p.ms);
+			for (uint32_t o = 0; o < bytes; o += 128) prefetch_l2(r + o);
+		}
+		if (tl == 0 && pos < rowlen) {
+			if (VIS && have) {
+				if (seen != ep8) vis[v] = ep8;
+				else v = NO_VERTEX;
+			}
+			nb[pos] = v;
+			nbd[pos] = dist;
+		}
+	}
+	__syncthreads();
+}
+
+template <int LPL>
+__global__ void __launch_bounds__(32 * GC_WARPS) graph_search_cta_kernel(const GraphParams p) {
+	extern __shared__ uint8_t gs_smem[];
+	const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
+	const uint32_t slot = blockIdx.x;
+	float* qsm = reinterpret_cast<float*>(gs_smem);
+	uint8_t* qc = gs_smem + (size_t)p.d_pad * 4;
+	uint32_t* nb = reinterpret_cast<uint32_t*>(qc + p.d_pad);
+	float* nbd = reinterpret_cast<float*>(nb + GS_MAXNB);
+	uint32_t* ctl = reinterpret_cast<uint32_t*>(nbd + GS_MAXNB); // [0] vertex to expand (NO_VERTEX = search over), [1] runner-up, [2] its distance
+	uint64_t* bm = reinterpret_cast<uint64_t*>(ctl + 4);         // [32 * LPL] shared-memory copy of the beam
+	uint8_t* vis = p.visited + (size_t)slot * p.vis_stride;
+	uint32_t epoch = p.epoch[slot];
+	unsigned long long dc_total = 0;
+	const bool comp = p.compressed != 0;
+
+	for (uint32_t qi = slot; qi < p.m; qi += gridDim.x) {
+		epoch++;
+		if ((epoch & 0xFF) == 0) {
+			epoch++;
+			for (size_t i = (size_t)tid * 16; i < p.vis_stride; i += 32 * GC_WARPS * 16)
+				*reinterpret_cast<uint4*>(vis + i) = make_uint4(0, 0, 0, 0);
+		}
+		const uint8_t ep8 = (uint8_t)(epoch & 0xFF);
+		for (uint32_t i = tid; i < p.d_pad; i += 32 * GC_WARPS) {
+			const float v = p.queries[(size_t)qi * p.d_pad + i];
+			qsm[i] = v;
+			qc[i] = (uint8_t)(uint32_t)v;
+		}
+		__syncthreads();
+		uint32_t dc = 0;
+#ifdef GC_PROFILE
+		long long pf_t0 = clock64(), pf_sel = 0, pf_score = 0, pf_adm = 0, pf_up = 0, pf_t;
+		int pf_hops = 0, pf_ins = 0, pf_upsteps = 0;
+#endif
+
+		// ---- upper layers: greedy descent, every warp tracks (ep, ep_dist) redundantly
+		uint32_t ep = p.start;
+		if (wib == 0) {
+			if (lane == 0) nb[0] = ep;
+			__syncwarp();
+			gather_dist_f32(p.base, p.d_pad, qsm, nb, nbd, 1, lane);
+		}
+		__syncthreads();
+		float ep_dist = nbd[0];
+		dc++;
+		__syncthreads();
+		for (uint32_t layer = p.max_layer > 0 ? p.max_layer - 1 : 0; layer > 0; --layer) {
+			bool changed = true;
+			while (changed) {
+				changed = false;
+				const uint32_t ui = __ldg(p.upper_idx + ep), unl = __ldg(p.upper_nl + ep); // both in flight together
+				if (ui == NO_VERTEX || unl <= layer) break;
+				const uint32_t* row = p.upper + ((size_t)ui + (layer - 1)) * p.ms;
+				cta_score_row<false>(p, row, p.ms, false, qsm, qc, nb, nbd, vis, ep8, nullptr, layer);
+#ifdef GC_PROFILE
+				pf_upsteps++;
+#endif
+				float best = ep_dist;
+				int besti = -1, cnt = 0;
+				for (uint32_t i0 = 0; i0 < p.ms; i0 += 32) {
+					const uint32_t i = i0 + lane;
+					const bool ok = i < p.ms && nb[i] != NO_VERTEX;
+					cnt += __popc(__ballot_sync(FULL, ok));
+					if (ok && nbd[i] < best) { best = nbd[i]; besti = (int)i; }
+				}
+#pragma unroll
+				for (int o = 16; o >= 1; o >>= 1) {
+					const float ob = __shfl_xor_sync(FULL, best, o);
+					const int oi = __shfl_xor_sync(FULL, besti, o);
+					if (oi >= 0 && (ob < best || (ob == best && (besti < 0 || oi < besti)))) { best = ob; besti = oi; }
+				}
+				dc += cnt;
+				if (besti >= 0) { ep = nb[besti]; ep_dist = best; changed = true; }
+				__syncthreads();
+			}
+		}
+
+#ifdef GC_PROFILE
+		pf_up = clock64() - pf_t0;
+		pf_t = clock64();
+#endif
+		// ---- bottom layer: warp 0 owns the beam
+		WarpList<LPL> beam;
+		float thr = __int_as_float(0x7f800000);
+		bool full = false;
+		int bsz = 0; // entries in the beam
+		if (wib == 0) {
+			beam.init();
+			if (lane == 0) nb[0] = ep;
+			__syncwarp();
+			if (comp) gather_score_u8(p.codes, p.d_pad, qc, nb, nbd, 1, lane);
+			else gather_dist_f32(p.base, p.d_pad, qsm, nb, nbd, 1, lane);
+			dc++;
+			beam.insert(beam_key(nbd[0], ep), lane);
+			if (lane == 0) { vis[ep] = ep8; bm[0] = beam_key(nbd[0], ep); }
+			bsz = 1;
+			if (p.ef == 1) { full = true; thr = nbd[0]; }
+			__syncwarp();
+		}
+		for (;;) {
+			if (wib == 0) {
+				int pos = -1, pos2 = -1;
+#pragma unroll
+				for (int s = 0; s < LPL; ++s) {
+					const int i = s * 32 + lane;
+					unsigned mk = __ballot_sync(FULL, i < (int)p.ef && beam.e[s] != KEY_EMPTY && !(beam.e[s] & 1ull));
+					if (pos < 0 && mk) { pos = s * 32 + __ffs(mk) - 1; mk &= mk - 1; }
+					if (pos >= 0 && pos2 < 0 && mk) pos2 = s * 32 + __ffs(mk) - 1;
+				}
+				uint32_t cur = NO_VERTEX, nxt = NO_VERTEX;
+				float nxt_d = 0.f;
+				if (pos >= 0) { // bm = the beam as of the last merge (expanded bits apart)
+					cur = (uint32_t)(bm[pos] >> 1) & 0x7FFFFFFFu;
+					if (pos2 >= 0) {
+						const uint64_t k2 = bm[pos2];
+						nxt = (uint32_t)(k2 >> 1) & 0x7FFFFFFFu;
+						nxt_d = f32_from_orderable((uint32_t)(k2 >> 32));
+					}
+#pragma unroll
+					for (int s = 0; s < LPL; ++s)
+						if (s * 32 + lane == pos) beam.e[s] |= 1ull;
+				}
+				if (lane == 0) { ctl[0] = cur; ctl[1] = nxt; ctl[2] = __float_as_uint(nxt_d); }
+			}
+			__syncthreads();
+#ifdef GC_PROFILE
+			{ long long t = clock64(); pf_sel += t - pf_t; pf_t = t; pf_hops++; }
+#endif
+			const uint32_t cur = ctl[0], nxt = ctl[1];
+			const float nxt_d = __uint_as_float(ctl[2]);
+			if (cur == NO_VERTEX) break;
+			cta_score_row<true>(p, p.bottom + (size_t)cur * p.m0s, p.m0s, comp, qsm, qc, nb, nbd, vis, ep8,
+			                    nxt == NO_VERTEX ? nullptr : p.bottom + (size_t)nxt * p.m0s, 0);
+#ifdef GC_PROFILE
+			{ long long t = clock64(); pf_score += t - pf_t; pf_t = t; }
+#endif
+			if (wib == 0) {
+				// admission (:666-676) of a whole row at once: every fresh neighbour under the bound the hop started with
+				// is merged into the sorted beam by rank counting (candidate c lands at #beam keys below c + #candidates
+				// below c, a beam key moves up by #candidates below it) through the shared-memory copy of the beam.
+				// The one-at-a-time rule of the warp form differs only when a candidate's distance EQUALS the bound it
+				// would meet after earlier insertions of the same row (it is then turned away instead of ordered by id).
+				for (uint32_t i0 = 0; i0 < p.m0s; i0 += 32) {
+					const uint32_t i = i0 + lane;
+					const uint32_t vv = i < p.m0s ? nb[i] : NO_VERTEX;
+					const float dv = vv != NO_VERTEX ? nbd[i] : 0.f;
+					dc += __popc(__ballot_sync(FULL, vv != NO_VERTEX));
+					const bool cand = vv != NO_VERTEX && (!full || dv < thr);
+					const unsigned mk = __ballot_sync(FULL, cand);
+					if (!mk) continue;
+					const uint64_t mykey = cand ? beam_key(dv, vv) : KEY_EMPTY;
+					int myrank = 0, mybelow = 0, shift[LPL];
+#pragma unroll
+					for (int s = 0; s < LPL; ++s) shift[s] = 0;
+					for (unsigned m2 = mk; m2; m2 &= m2 - 1) {
+						const int src = __ffs(m2) - 1;
+						const uint64_t kk = shfl_u64(mykey, src);
+						myrank += kk < mykey;
+#pragma unroll
+						for (int s = 0; s < LPL; ++s) {
+							const unsigned bl = __ballot_sync(FULL, beam.e[s] < kk);
+							if (lane == src) mybelow += __popc(bl);
+							shift[s] += kk < beam.e[s];
+						}
+					}
+#pragma unroll
+					for (int s = 0; s < LPL; ++s) {
+						const int np = s * 32 + lane + shift[s];
+						if (beam.e[s] != KEY_EMPTY && np < 32 * LPL) bm[np] = beam.e[s];
+					}
+					if (cand && myrank + mybelow < 32 * LPL) bm[myrank + mybelow] = mykey;
+					bsz = min(bsz + __popc(mk), 32 * LPL);
+					__syncwarp();
+#pragma unroll
+					for (int s = 0; s < LPL; ++s) beam.e[s] = s * 32 + lane < bsz ? bm[s * 32 + lane] : KEY_EMPTY;
+					full = bsz >= (int)p.ef;
+					if (full) thr = f32_from_orderable((uint32_t)(bm[p.ef - 1] >> 32));
+					__syncwarp();
+#ifdef GC_PROFILE
+					pf_ins += __popc(mk);
+#endif
+				}
+			} else if (wib == 1) {
+				// the vertex the next hop expands is the closer of the runner-up (whose neighbourhood was asked into L2
+				// while this hop was scored) and the closest fresh neighbour just scored: in the second case ask for ITS
+				// neighbours' vectors and visited bytes now, while warp 0 is busy with the admission
+				float best = __int_as_float(0x7f800000);
+				uint32_t bv = NO_VERTEX;
+				for (uint32_t i0 = 0; i0 < p.m0s; i0 += 32) {
+					const uint32_t i = i0 + lane;
+					const uint32_t vv = i < p.m0s ? nb[i] : NO_VERTEX;
+					if (vv != NO_VERTEX && nbd[i] < best) { best = nbd[i]; bv = vv; }
+				}
+#pragma unroll
+				for (int o = 16; o >= 1; o >>= 1) {
+					const float ob = __shfl_xor_sync(FULL, best, o);
+					const uint32_t ov = __shfl_xor_sync(FULL, bv, o);
+					if (ob < best) { best = ob; bv = ov; }
+				}
+				if (bv != NO_VERTEX && (nxt == NO_VERTEX || best < nxt_d)) {
+					const uint32_t* r2 = p.bottom + (size_t)bv * p.m0s;
+					const uint32_t row_bytes = comp ? p.d_pad : p.d_pad * 4;
+					const char* rows = comp ? reinterpret_cast<const char*>(p.codes) : reinterpret_cast<const char*>(p.base);
+					for (uint32_t t = lane; t < p.m0s; t += 32) {
+						const uint32_t v2 = __ldg(r2 + t);
+						if (v2 != NO_VERTEX) {
+							const char* r = rows + (size_t)v2 * row_bytes;
+							for (uint32_t o = 0; o < row_bytes; o += 128) prefetch_l2(r + o);
+							prefetch_l2(vis + v2);
+						}
+					}
+				}
+			}
+#ifdef GC_PROFILE
+			{ long long t = clock64(); pf_adm += t - pf_t; pf_t = t; }
+#endif
+			// warps 0 and 1 reach the next rendezvous only after they have read nb/nbd; nobody writes them before it
+		}
+		// ---- output (warp 0), as in the warp form
+		if (wib == 0) {
+			uint64_t* dst = p.out_keys + (size_t)qi * p.k;
+			if (!comp) {
+#pragma unroll
+				for (int s = 0; s < LPL; ++s) {
+					const int i = s * 32 + lane;
+					if (i < (int)p.k) {
+						uint64_t e = beam.e[s];
+						if (i >= (int)p.ef) e = KEY_EMPTY;
+						dst[i] = e == KEY_EMPTY ? KEY_EMPTY : ((e >> 32) << 32) | (((uint32_t)(e >> 1) & 0x7FFFFFFFu) + p.id_add);
+					}
+				}
+			} else {
+				__syncwarp();
+				int cnt = 0;
+#pragma unroll
+				for (int s = 0; s < LPL; ++s) {
+					const int i = s * 32 + lane;
+					const bool ok = i < (int)p.ef && beam.e[s] != KEY_EMPTY;
+					const unsigned mk = __ballot_sync(FULL, ok);
+					if (ok) nb[cnt + __popc(mk & ((1u << lane) - 1))] = (uint32_t)(beam.e[s] >> 1) & 0x7FFFFFFFu;
+					cnt += __popc(mk);
+				}
+				__syncwarp();
+				gather_dist_f32(p.base, p.d_pad, qsm, nb, nbd, cnt, lane);
+				WarpList<LPL> fin;
+				fin.init();
+				for (int i = 0; i < cnt; ++i) fin.insert(make_key(nbd[i], nb[i]), lane);
+#pragma unroll
+				for (int s = 0; s < LPL; ++s) {
+					const int i = s * 32 + lane;
+					if (i < (int)p.k) dst[i] = fin.e[s] == KEY_EMPTY ? KEY_EMPTY : fin.e[s] + p.id_add;
+				}
+			}
+			dc_total += dc;
+#ifdef GC_PROFILE
+			if (lane == 0 && (epoch & 63) == 1)
+				printf("GCPROF q=%u total=%lld upper=%lld (steps %d) select+sync=%lld score=%lld admit=%lld hops=%d inserts=%d dc=%u\n", qi,
+				       clock64() - pf_t0, pf_up, pf_upsteps, pf_sel, pf_score, pf_adm, pf_hops, pf_ins, dc);
+#endif
+		}
+		__syncthreads();
+	}
+	if (tid == 0) {
+		p.epoch[slot] = epoch;
+		if (p.distcomps && dc_total) atomicAdd(p.distcomps, dc_total);
+	}
+}
+
 } // namespace expann

@@ -120,3 +120,61 @@ def test_gpu_built_graph_roundtrip(ex, oracle, reference_128):
         last = r_gpu
     assert last >= 0.95, last
     e.close()
+
+
+def test_latency_form_real_valued(ex):
+    """one-CTA-per-query form of K5 (calls with few queries) against the one-warp-per-query form on the same graph,
+    real-valued rows (d = 96, unit norm): same visit order and same per-vertex summation order; the forms differ only
+    where a neighbour's distance EQUALS the beam's bound (row-at-once admission), which real-valued data almost never
+    produces => identical ids / distances / distance-evaluation counts for (nearly) every query. Covers more queries
+    than CTA slots, the 8-bit visited-epoch wrap and one query per call (src/basic_bench.h:82-126)."""
+    from expann_b200 import datasets
+    base, q = datasets.make("deep", 20000, 700, 96, seed=5)
+    e = ex.GraphEngine()
+    e.store_many_vectors(base)
+    e.build_graph(M=12, M0=24, K=48)
+    e.build()
+    for ef in (1, 10, 40, 100, 200):
+        k = 10 if ef >= 10 else 1
+        e.set_ef_search(ef)
+        e.set_option("graph_cta_batch", 0)
+        dc0 = e.stats()["distcomps"]
+        ids_w, dists_w, counts_w = e.query_k_batch(q, k)
+        dc1 = e.stats()["distcomps"]
+        e.set_option("graph_cta_batch", 1 << 20)
+        ids_c, dists_c, counts_c = e.query_k_batch(q, k)
+        dc2 = e.stats()["distcomps"]
+        same = np.all(ids_w == ids_c, axis=1) & np.all(dists_w == dists_c, axis=1)
+        assert same.mean() >= 0.99, (ef, same.mean())
+        assert np.array_equal(counts_w, counts_c), ef
+        assert abs((dc2 - dc1) - (dc1 - dc0)) <= 0.01 * (dc1 - dc0), ef
+        for i in (0, 7):
+            i1, d1, _ = e.query_k_batch(q[i:i + 1], k)
+            assert np.array_equal(i1[0], ids_c[i]) and np.array_equal(d1[0], dists_c[i])
+    e.close()
+
+
+@pytest.mark.parametrize("compressed", [False, True])
+def test_latency_form_golden_index(ex, compressed):
+    """the latency form on the reference-built golden graph (u8-valued rows: distance ties are common, so the forms
+    may order tied vertices differently): recall@10 >= the reference's at every beam width, same bar as
+    test_golden_index; result sets equal to the warp form's for most queries."""
+    g = gold("graph_u8_2000")
+    q = g["q"].astype(np.float32)
+    e = ex.GraphEngine(use_compression=compressed)
+    e.load_index(os.path.join(GOLD, "graph_u8_2000.index"))
+    e.build()
+    for ef in (10, 20, 40, 80):
+        e.set_ef_search(ef)
+        e.set_option("graph_cta_batch", 0)
+        ids_w, _, _ = e.query_k_batch(q, 10)
+        e.set_option("graph_cta_batch", 1 << 20)
+        ids, dists, counts = e.query_k_batch(q, 10)
+        ref_ids = g[f"ids_comp_ef{ef}" if compressed else f"ids_ef{ef}"]
+        assert np.all(counts == 10)
+        assert recall(ids, g["truth"]) >= recall(ref_ids, g["truth"]) - 1e-9, ef
+        assert all(len(set(r.tolist())) == 10 for r in ids)
+        assert np.all(np.diff(dists, axis=1) >= 0)
+        same = np.mean([set(a.tolist()) == set(b.tolist()) for a, b in zip(ids, ids_w)])
+        assert same >= 0.9, (ef, same)
+    e.close()
