@@ -302,10 +302,19 @@ int expann_gpu_query(expann_gpu_t* h, const float* q, size_t m, size_t k, size_t
 		} else if (q_pin)
 			std::memcpy(h->h_q.p, q, qbytes);
 		uint8_t* r = static_cast<uint8_t*>(h->h_ids.p);
-		if (int rc = query_device_impl(h, qsrc, m, k, ef, h->keys.as<uint64_t>(), st)) return rc;
-		if (int rc = launch_decode(h, h->keys.as<uint64_t>(), m, k, 0, reinterpret_cast<uint64_t*>(r), reinterpret_cast<float*>(r + off_d),
-		                           reinterpret_cast<uint64_t*>(r + off_c), st))
-			return rc;
+		h->fused = false;
+		if (h->cfg.engine == EXPANN_ENGINE_GRAPH) {
+			h->fuse_ids = reinterpret_cast<uint64_t*>(r);
+			h->fuse_dists = reinterpret_cast<float*>(r + off_d);
+			h->fuse_counts = reinterpret_cast<uint64_t*>(r + off_c);
+		}
+		const int qrc = query_device_impl(h, qsrc, m, k, ef, h->keys.as<uint64_t>(), st);
+		h->fuse_ids = nullptr;
+		if (qrc) return qrc;
+		if (!h->fused)
+			if (int rc = launch_decode(h, h->keys.as<uint64_t>(), m, k, 0, reinterpret_cast<uint64_t*>(r), reinterpret_cast<float*>(r + off_d),
+			                           reinterpret_cast<uint64_t*>(r + off_c), st))
+				return rc;
 		EXPANN_CUDA(h, cudaStreamSynchronize(st));
 		std::memcpy(ids_out, r, nk * 8);
 		if (dist_out) std::memcpy(dist_out, r + off_d, nk * 4);

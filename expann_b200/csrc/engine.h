@@ -66,7 +66,7 @@ struct expann_gpu {
 	int opt_tc_pair = 1; // pair form of K3 (clusters of two CTAs, tcgen05.mma.cta_group::2)
 	int opt_tc_astream = 1; // pair form with the query operand streamed through the ring: 0 off, 1 when nothing else fits, 2 always
 	int opt_graph_occ = 5; // graph search: resident CTAs of 4 warps per SM (2, 4, 5 or 8); set before build()
-	int opt_graph_cta_batch = -1; // graph search: calls with at most this many queries take the one-CTA-per-query latency form (-1 = one wave: the SM count)
+	int opt_graph_cta_batch = -1; // graph search: calls with at most this many queries take the one-CTA-per-query latency form (-1 = two waves: twice the SM count)
 	int opt_tc_boot = 1; // pair form: seeding launch over the leading tiles of a large base
 	// quantised scan engine (K6 + K4)
 	int quantizer = 0;       // 0 = quantizer_simple<uint8_t>, 1 = quantizer_ranged_q8
@@ -81,6 +81,11 @@ struct expann_gpu {
 	float build_ortho_factor = 0.5f, build_ortho_bias = 0.f;
 	uint64_t build_prune_overflow = 0, build_K = 0;
 	uint32_t g_ctas = 0;
+	// small host calls: where the latency form of the search may decode its results itself (set around one call)
+	uint64_t* fuse_ids = nullptr;
+	float* fuse_dists = nullptr;
+	uint64_t* fuse_counts = nullptr;
+	bool fused = false;
 	size_t g_vis_stride = 0;
 	int opt_nsplit = 0; // 0 = auto
 	bool timing = false;

@@ -176,11 +176,19 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 	p.max_layer = h->graph.max_layer;
 	p.id_add = (uint32_t)h->cfg.id_offset;
 	p.compressed = h->cfg.use_compression ? 1 : 0;
-	if (m <= (size_t)(h->opt_graph_cta_batch < 0 ? sms : h->opt_graph_cta_batch)) {
+	// automatic: up to two waves of one CTA per SM (measured on 1M x 128, ef 40: 128 queries 188 vs 394 us, 256 queries
+	// 320 vs 410 us, 512 queries 573 vs 419 us per call)
+	if (m <= (size_t)(h->opt_graph_cta_batch < 0 ? 2 * sms : h->opt_graph_cta_batch)) {
 		// latency form: one CTA per query (few queries per call; nothing to hide the hops' round trips behind)
 		const size_t smem1 = (size_t)h->d_pad * 5 + GS_MAXNB * 8 + 16 + 256 * 8; // query | u8 query | nb | nbd | ctl | beam copy
 		if (smem1 > 200 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "graph search: d too large");
 		const unsigned grid1 = (unsigned)std::min<size_t>(m, (size_t)h->g_ctas * GS_WARPS);
+		if (h->fuse_ids) { // small host call: the search decodes its own results (api.cu)
+			p.dec_ids = h->fuse_ids;
+			p.dec_dists = h->fuse_dists;
+			p.dec_counts = h->fuse_counts;
+			h->fused = true;
+		}
 		cudaEvent_t t0 = timing_begin(h, st);
 #define GC_LAUNCH(L)                                                                                              \
 	do {                                                                                                          \

@@ -41,6 +41,11 @@ struct GraphParams {
 	uint32_t n, vis_stride, d_pad, m0s, ms, m, k, ef;
 	uint32_t start, max_layer, id_add;
 	int compressed;
+	// latency form only: results also decoded in place (ids / distances / counts of expann_gpu_query), saving the
+	// decode launch of a small host call; null otherwise
+	uint64_t* dec_ids;
+	float* dec_dists;
+	uint64_t* dec_counts;
 };
 
 __device__ __forceinline__ float4 ldg128f(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
@@ -435,6 +440,16 @@ __device__ __forceinline__ void cta_score_row(const GraphParams& p, const uint32
 	__syncthreads();
 }
 
+// decode_keys_kernel's work for result slot i of query qi (warp-wide call; key = KEY_EMPTY beyond k)
+__device__ __forceinline__ void emit_decoded(const GraphParams& p, uint32_t qi, int i, uint64_t key, uint32_t& nres) {
+	const bool ok = key != KEY_EMPTY;
+	nres += __popc(__ballot_sync(FULL, ok));
+	if (p.dec_ids && i < (int)p.k) {
+		p.dec_ids[(size_t)qi * p.k + i] = ok ? (uint64_t)key_id(key) : 0xFFFFFFFFFFFFFFFFull;
+		if (p.dec_dists) p.dec_dists[(size_t)qi * p.k + i] = ok ? key_dist(key) : __int_as_float(0x7f800000);
+	}
+}
+
 template <int LPL>
 __global__ void __launch_bounds__(32 * GC_WARPS) graph_search_cta_kernel(const GraphParams p) {
 	extern __shared__ uint8_t gs_smem[];
@@ -657,15 +672,19 @@ __global__ void __launch_bounds__(32 * GC_WARPS) graph_search_cta_kernel(const G
 		// ---- output (warp 0), as in the warp form
 		if (wib == 0) {
 			uint64_t* dst = p.out_keys + (size_t)qi * p.k;
+			uint32_t nres = 0;
 			if (!comp) {
 #pragma unroll
 				for (int s = 0; s < LPL; ++s) {
 					const int i = s * 32 + lane;
+					uint64_t key = KEY_EMPTY;
 					if (i < (int)p.k) {
 						uint64_t e = beam.e[s];
 						if (i >= (int)p.ef) e = KEY_EMPTY;
-						dst[i] = e == KEY_EMPTY ? KEY_EMPTY : ((e >> 32) << 32) | (((uint32_t)(e >> 1) & 0x7FFFFFFFu) + p.id_add);
+						key = e == KEY_EMPTY ? KEY_EMPTY : ((e >> 32) << 32) | (((uint32_t)(e >> 1) & 0x7FFFFFFFu) + p.id_add);
+						dst[i] = key;
 					}
+					emit_decoded(p, qi, i, key, nres);
 				}
 			} else {
 				__syncwarp();
@@ -686,9 +705,15 @@ __global__ void __launch_bounds__(32 * GC_WARPS) graph_search_cta_kernel(const G
 #pragma unroll
 				for (int s = 0; s < LPL; ++s) {
 					const int i = s * 32 + lane;
-					if (i < (int)p.k) dst[i] = fin.e[s] == KEY_EMPTY ? KEY_EMPTY : fin.e[s] + p.id_add;
+					uint64_t key = KEY_EMPTY;
+					if (i < (int)p.k) {
+						key = fin.e[s] == KEY_EMPTY ? KEY_EMPTY : fin.e[s] + p.id_add;
+						dst[i] = key;
+					}
+					emit_decoded(p, qi, i, key, nres);
 				}
 			}
+			if (p.dec_counts && lane == 0) p.dec_counts[qi] = nres;
 			dc_total += dc;
 #ifdef GC_PROFILE
 			if (lane == 0 && (epoch & 63) == 1)

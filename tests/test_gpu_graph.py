@@ -149,8 +149,14 @@ def test_latency_form_real_valued(ex):
         assert np.array_equal(counts_w, counts_c), ef
         assert abs((dc2 - dc1) - (dc1 - dc0)) <= 0.01 * (dc1 - dc0), ef
         for i in (0, 7):
-            i1, d1, _ = e.query_k_batch(q[i:i + 1], k)
-            assert np.array_equal(i1[0], ids_c[i]) and np.array_equal(d1[0], dists_c[i])
+            i1, d1, c1 = e.query_k_batch(q[i:i + 1], k)   # small host call: the search decodes its own results
+            assert np.array_equal(i1[0], ids_c[i]) and np.array_equal(d1[0], dists_c[i]) and c1[0] == counts_c[i]
+    # fewer vertices reachable than k: unused slots are id = 2^64-1, dist = +inf, count < k (include/expann_gpu.h)
+    e.set_ef_search(3)
+    i1, d1, c1 = e.query_k_batch(q[:1], 10)
+    i2, d2, c2 = e.query_k_batch(q[:400], 10)
+    assert c1[0] == 3 and np.all(i1[0, 3:] == np.uint64(2**64 - 1)) and np.all(np.isinf(d1[0, 3:]))
+    assert np.array_equal(i1[0], i2[0]) and np.array_equal(d1[0], d2[0]) and c2[0] == 3
     e.close()
 
 
