@@ -433,6 +433,9 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 	} else if (nm == "graph_cta_batch") {
 		if (value < -1) return fail(h, EXPANN_ERR_ARG, "graph_cta_batch must be >= -1 (-1 = automatic)");
 		h->opt_graph_cta_batch = (int)value;
+	} else if (nm == "graph_cta_width") {
+		if (value != 1 && value != 2) return fail(h, EXPANN_ERR_ARG, "graph_cta_width must be 1 or 2");
+		h->opt_graph_cta_width = (int)value;
 	} else if (nm == "tc_boot") {
 		h->opt_tc_boot = (int)value; // 0 off, 1 bf16-exact mode only (default), 2 both modes
 	} else if (nm == "tc_v1") {

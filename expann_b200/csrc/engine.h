@@ -67,6 +67,7 @@ struct expann_gpu {
 	int opt_tc_astream = 1; // pair form with the query operand streamed through the ring: 0 off, 1 when nothing else fits, 2 always
 	int opt_graph_occ = 5; // graph search: resident CTAs of 4 warps per SM (2, 4, 5 or 8); set before build()
 	int opt_graph_cta_batch = -1; // graph search: calls with at most this many queries take the one-CTA-per-query latency form (-1 = two waves: twice the SM count)
+	int opt_graph_cta_width = 1; // latency form: vertices expanded per hop (1 = the reference's order, the default; 2 = half the dependent hops, recall >= at every beam width measured, +2 % distance evaluations)
 	int opt_tc_boot = 1; // pair form: seeding launch over the leading tiles of a large base
 	// quantised scan engine (K6 + K4)
 	int quantizer = 0;       // 0 = quantizer_simple<uint8_t>, 1 = quantizer_ranged_q8

@@ -180,9 +180,10 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 	// 320 vs 410 us, 512 queries 573 vs 419 us per call)
 	if (m <= (size_t)(h->opt_graph_cta_batch < 0 ? 2 * sms : h->opt_graph_cta_batch)) {
 		// latency form: one CTA per query (few queries per call; nothing to hide the hops' round trips behind)
-		const size_t smem1 = (size_t)h->d_pad * 5 + GS_MAXNB * 8 + 16 + 256 * 8; // query | u8 query | nb | nbd | ctl | beam copy
+		const size_t smem1 = (size_t)h->d_pad * 5 + GS_MAXNB * 8 + 16 + 256 * 8 + GS_MAXNB * 4; // query | u8 query | nb | nbd | ctl | beam copy
 		if (smem1 > 200 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "graph search: d too large");
 		const unsigned grid1 = (unsigned)std::min<size_t>(m, (size_t)h->g_ctas * GS_WARPS);
+		p.width = h->opt_graph_cta_width == 2 && 2 * h->graph.m0s <= (size_t)GS_MAXNB && ef >= 2 ? 2 : 1;
 		if (h->fuse_ids) { // small host call: the search decodes its own results (api.cu)
 			p.dec_ids = h->fuse_ids;
 			p.dec_dists = h->fuse_dists;

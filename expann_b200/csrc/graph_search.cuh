@@ -41,6 +41,7 @@ struct GraphParams {
 	uint32_t n, vis_stride, d_pad, m0s, ms, m, k, ef;
 	uint32_t start, max_layer, id_add;
 	int compressed;
+	int width; // latency form: vertices expanded per hop (1 or 2)
 	// latency form only: results also decoded in place (ids / distances / counts of expann_gpu_query), saving the
 	// decode launch of a small host call; null otherwise
 	uint64_t* dec_ids;
@@ -440,6 +441,111 @@ __device__ __forceinline__ void cta_score_row(const GraphParams& p, const uint32
 	__syncthreads();
 }
 
+// Two vertices expanded per hop (GraphParams::width == 2): the closest two unexpanded beam entries are taken together,
+// their rows (2 x M0 neighbours) scored in one pass with two vectors in flight per team — half as many dependent
+// hops for a few more distance evaluations (the second vertex is expanded before the first one's results could
+// have pushed it out of the beam). A neighbour both parents share is scored once (ids staged in shared memory and
+// compared before the loads). Results: nb/nbd[j] for parent A's neighbour j, nb/nbd[M0s + j] for parent B's.
+__device__ __forceinline__ void cta_score_pair(const GraphParams& p, uint32_t curA, uint32_t curB, bool compressed,
+                                               const float* qsm, const uint8_t* qc, uint32_t* nb, float* nbd,
+                                               uint32_t* idsrc, uint8_t* vis, uint8_t ep8,
+                                               const uint32_t* __restrict__ row2) {
+	const int tid = threadIdx.x, team = tid >> 3, tl = tid & 7, lane = tid & 31;
+	const uint32_t m0s = p.m0s;
+	uint32_t v2 = NO_VERTEX;
+	if (row2 && (uint32_t)tid < m0s) v2 = __ldg(row2 + tid);
+	if ((uint32_t)tid < 2 * m0s) {
+		const bool second = (uint32_t)tid >= m0s;
+		const uint32_t par = second ? curB : curA;
+		idsrc[tid] = par == NO_VERTEX ? NO_VERTEX : __ldg(p.bottom + (size_t)par * m0s + (tid - (second ? m0s : 0)));
+	}
+	__syncthreads();
+	const uint32_t row_bytes = compressed ? p.d_pad : p.d_pad * 4;
+	const char* rows = compressed ? reinterpret_cast<const char*>(p.codes) : reinterpret_cast<const char*>(p.base);
+	for (uint32_t j0 = 0; j0 < m0s; j0 += GC_WARPS * 4) {
+		const uint32_t j = j0 + team;
+		uint32_t va = j < m0s ? idsrc[j] : NO_VERTEX, vb = j < m0s ? idsrc[m0s + j] : NO_VERTEX;
+		bool dupl = false;
+		if (vb != NO_VERTEX)
+			for (uint32_t i = tl; i < m0s; i += 8) dupl |= idsrc[i] == vb;
+		if ((__ballot_sync(FULL, dupl) >> (lane & ~7)) & 0xFFu) vb = NO_VERTEX;
+		const bool ha = va != NO_VERTEX, hb = vb != NO_VERTEX;
+		if (ha && (uint32_t)tl * 32u < m0s) prefetch_l2(p.bottom + (size_t)va * m0s + tl * 32);
+		if (hb && (uint32_t)tl * 32u < m0s) prefetch_l2(p.bottom + (size_t)vb * m0s + tl * 32);
+		if (j0 == 0 && v2 != NO_VERTEX) {
+			const char* r = rows + (size_t)v2 * row_bytes;
+			for (uint32_t o = 0; o < row_bytes; o += 128) prefetch_l2(r + o);
+			prefetch_l2(vis + v2);
+		}
+		uint8_t seenA = ep8, seenB = ep8;
+		if (tl == 0) {
+			if (ha) seenA = vis[va];
+			if (hb) seenB = vis[vb];
+		}
+		float da, db;
+		if (compressed) {
+			const uint8_t* pa = p.codes + (size_t)(ha ? va : 0) * p.d_pad;
+			const uint8_t* pb = p.codes + (size_t)(hb ? vb : 0) * p.d_pad;
+			const int nchunk = p.d_pad >> 4;
+			uint32_t sa = 0, sb = 0;
+			for (int c = tl; c < nchunk; c += 8) {
+				uint4 xa = make_uint4(0, 0, 0, 0), xb = make_uint4(0, 0, 0, 0);
+				if (ha) xa = __ldg(reinterpret_cast<const uint4*>(pa + c * 16));
+				if (hb) xb = __ldg(reinterpret_cast<const uint4*>(pb + c * 16));
+				const uint4 q = *reinterpret_cast<const uint4*>(qc + c * 16);
+				uint32_t t;
+				t = __vabsdiffu4(q.x, xa.x); sa = __dp4a(t, t, sa); t = __vabsdiffu4(q.y, xa.y); sa = __dp4a(t, t, sa);
+				t = __vabsdiffu4(q.z, xa.z); sa = __dp4a(t, t, sa); t = __vabsdiffu4(q.w, xa.w); sa = __dp4a(t, t, sa);
+				t = __vabsdiffu4(q.x, xb.x); sb = __dp4a(t, t, sb); t = __vabsdiffu4(q.y, xb.y); sb = __dp4a(t, t, sb);
+				t = __vabsdiffu4(q.z, xb.z); sb = __dp4a(t, t, sb); t = __vabsdiffu4(q.w, xb.w); sb = __dp4a(t, t, sb);
+			}
+#pragma unroll
+			for (int o = 4; o >= 1; o >>= 1) { sa += __shfl_xor_sync(FULL, sa, o); sb += __shfl_xor_sync(FULL, sb, o); }
+			da = (float)(int32_t)sa;
+			db = (float)(int32_t)sb;
+		} else {
+			const float* pa = p.base + (size_t)(ha ? va : 0) * p.d_pad + tl * 4;
+			const float* pb = p.base + (size_t)(hb ? vb : 0) * p.d_pad + tl * 4;
+			const int nstep = p.d_pad >> 5;
+			float sa = 0.f, sb = 0.f;
+			for (int s0 = 0; s0 < nstep; s0 += 4) {
+				float4 xa[4], xb[4];
+#pragma unroll
+				for (int s = 0; s < 4; ++s) {
+					xa[s] = xb[s] = make_float4(0.f, 0.f, 0.f, 0.f);
+					if (s0 + s < nstep) {
+						if (ha) xa[s] = ldg128f(pa + (s0 + s) * 32);
+						if (hb) xb[s] = ldg128f(pb + (s0 + s) * 32);
+					}
+				}
+#pragma unroll
+				for (int s = 0; s < 4; ++s)
+					if (s0 + s < nstep) { // same order of operations as gather_dist_f32
+						const float4 q = *reinterpret_cast<const float4*>(qsm + (s0 + s) * 32 + tl * 4);
+						float t;
+						t = q.x - xa[s].x; sa = fmaf(t, t, sa); t = q.y - xa[s].y; sa = fmaf(t, t, sa);
+						t = q.z - xa[s].z; sa = fmaf(t, t, sa); t = q.w - xa[s].w; sa = fmaf(t, t, sa);
+						t = q.x - xb[s].x; sb = fmaf(t, t, sb); t = q.y - xb[s].y; sb = fmaf(t, t, sb);
+						t = q.z - xb[s].z; sb = fmaf(t, t, sb); t = q.w - xb[s].w; sb = fmaf(t, t, sb);
+					}
+			}
+#pragma unroll
+			for (int o = 4; o >= 1; o >>= 1) { sa += __shfl_xor_sync(FULL, sa, o); sb += __shfl_xor_sync(FULL, sb, o); }
+			da = sa;
+			db = sb;
+		}
+		if (tl == 0 && j < m0s) {
+			if (ha) { if (seenA != ep8) vis[va] = ep8; else va = NO_VERTEX; }
+			if (hb) { if (seenB != ep8) vis[vb] = ep8; else vb = NO_VERTEX; }
+			nb[j] = va;
+			nbd[j] = da;
+			nb[m0s + j] = vb;
+			nbd[m0s + j] = db;
+		}
+	}
+	__syncthreads();
+}
+
 // decode_keys_kernel's work for result slot i of query qi (warp-wide call; key = KEY_EMPTY beyond k)
 __device__ __forceinline__ void emit_decoded(const GraphParams& p, uint32_t qi, int i, uint64_t key, uint32_t& nres) {
 	const bool ok = key != KEY_EMPTY;
@@ -461,6 +567,8 @@ __global__ void __launch_bounds__(32 * GC_WARPS) graph_search_cta_kernel(const G
 	float* nbd = reinterpret_cast<float*>(nb + GS_MAXNB);
 	uint32_t* ctl = reinterpret_cast<uint32_t*>(nbd + GS_MAXNB); // [0] vertex to expand (NO_VERTEX = search over), [1] runner-up, [2] its distance
 	uint64_t* bm = reinterpret_cast<uint64_t*>(ctl + 4);         // [32 * LPL] shared-memory copy of the beam
+	uint32_t* idsrc = reinterpret_cast<uint32_t*>(bm + 256);     // [GS_MAXNB] neighbour ids of the hop's two parents
+	const uint32_t nrow = p.width == 2 ? 2 * p.m0s : p.m0s;      // result slots of a hop
 	uint8_t* vis = p.visited + (size_t)slot * p.vis_stride;
 	uint32_t epoch = p.epoch[slot];
 	unsigned long long dc_total = 0;
@@ -552,28 +660,35 @@ __global__ void __launch_bounds__(32 * GC_WARPS) graph_search_cta_kernel(const G
 		}
 		for (;;) {
 			if (wib == 0) {
-				int pos = -1, pos2 = -1;
+				int pos = -1, pos2 = -1, pos3 = -1;
 #pragma unroll
 				for (int s = 0; s < LPL; ++s) {
 					const int i = s * 32 + lane;
 					unsigned mk = __ballot_sync(FULL, i < (int)p.ef && beam.e[s] != KEY_EMPTY && !(beam.e[s] & 1ull));
 					if (pos < 0 && mk) { pos = s * 32 + __ffs(mk) - 1; mk &= mk - 1; }
-					if (pos >= 0 && pos2 < 0 && mk) pos2 = s * 32 + __ffs(mk) - 1;
+					if (pos >= 0 && pos2 < 0 && mk) { pos2 = s * 32 + __ffs(mk) - 1; mk &= mk - 1; }
+					if (pos2 >= 0 && pos3 < 0 && mk) pos3 = s * 32 + __ffs(mk) - 1;
 				}
-				uint32_t cur = NO_VERTEX, nxt = NO_VERTEX;
+				uint32_t cur = NO_VERTEX, curB = NO_VERTEX, nxt = NO_VERTEX;
 				float nxt_d = 0.f;
 				if (pos >= 0) { // bm = the beam as of the last merge (expanded bits apart)
 					cur = (uint32_t)(bm[pos] >> 1) & 0x7FFFFFFFu;
-					if (pos2 >= 0) {
-						const uint64_t k2 = bm[pos2];
+					int posn = pos2; // runner-up: the closest entry not expanded in this hop
+					if (p.width == 2 && pos2 >= 0) {
+						curB = (uint32_t)(bm[pos2] >> 1) & 0x7FFFFFFFu;
+						posn = pos3;
+					} else
+						pos2 = -1;
+					if (posn >= 0) {
+						const uint64_t k2 = bm[posn];
 						nxt = (uint32_t)(k2 >> 1) & 0x7FFFFFFFu;
 						nxt_d = f32_from_orderable((uint32_t)(k2 >> 32));
 					}
 #pragma unroll
 					for (int s = 0; s < LPL; ++s)
-						if (s * 32 + lane == pos) beam.e[s] |= 1ull;
+						if (s * 32 + lane == pos || s * 32 + lane == pos2) beam.e[s] |= 1ull;
 				}
-				if (lane == 0) { ctl[0] = cur; ctl[1] = nxt; ctl[2] = __float_as_uint(nxt_d); }
+				if (lane == 0) { ctl[0] = cur; ctl[1] = nxt; ctl[2] = __float_as_uint(nxt_d); ctl[3] = curB; }
 			}
 			__syncthreads();
 #ifdef GC_PROFILE
@@ -582,8 +697,12 @@ __global__ void __launch_bounds__(32 * GC_WARPS) graph_search_cta_kernel(const G
 			const uint32_t cur = ctl[0], nxt = ctl[1];
 			const float nxt_d = __uint_as_float(ctl[2]);
 			if (cur == NO_VERTEX) break;
-			cta_score_row<true>(p, p.bottom + (size_t)cur * p.m0s, p.m0s, comp, qsm, qc, nb, nbd, vis, ep8,
-			                    nxt == NO_VERTEX ? nullptr : p.bottom + (size_t)nxt * p.m0s, 0);
+			if (p.width == 2)
+				cta_score_pair(p, cur, ctl[3], comp, qsm, qc, nb, nbd, idsrc, vis, ep8,
+				               nxt == NO_VERTEX ? nullptr : p.bottom + (size_t)nxt * p.m0s);
+			else
+				cta_score_row<true>(p, p.bottom + (size_t)cur * p.m0s, p.m0s, comp, qsm, qc, nb, nbd, vis, ep8,
+				                    nxt == NO_VERTEX ? nullptr : p.bottom + (size_t)nxt * p.m0s, 0);
 #ifdef GC_PROFILE
 			{ long long t = clock64(); pf_score += t - pf_t; pf_t = t; }
 #endif
@@ -593,9 +712,9 @@ __global__ void __launch_bounds__(32 * GC_WARPS) graph_search_cta_kernel(const G
 				// below c, a beam key moves up by #candidates below it) through the shared-memory copy of the beam.
 				// The one-at-a-time rule of the warp form differs only when a candidate's distance EQUALS the bound it
 				// would meet after earlier insertions of the same row (it is then turned away instead of ordered by id).
-				for (uint32_t i0 = 0; i0 < p.m0s; i0 += 32) {
+				for (uint32_t i0 = 0; i0 < nrow; i0 += 32) {
 					const uint32_t i = i0 + lane;
-					const uint32_t vv = i < p.m0s ? nb[i] : NO_VERTEX;
+					const uint32_t vv = i < nrow ? nb[i] : NO_VERTEX;
 					const float dv = vv != NO_VERTEX ? nbd[i] : 0.f;
 					dc += __popc(__ballot_sync(FULL, vv != NO_VERTEX));
 					const bool cand = vv != NO_VERTEX && (!full || dv < thr);
@@ -639,9 +758,9 @@ __global__ void __launch_bounds__(32 * GC_WARPS) graph_search_cta_kernel(const G
 				// neighbours' vectors and visited bytes now, while warp 0 is busy with the admission
 				float best = __int_as_float(0x7f800000);
 				uint32_t bv = NO_VERTEX;
-				for (uint32_t i0 = 0; i0 < p.m0s; i0 += 32) {
+				for (uint32_t i0 = 0; i0 < nrow; i0 += 32) {
 					const uint32_t i = i0 + lane;
-					const uint32_t vv = i < p.m0s ? nb[i] : NO_VERTEX;
+					const uint32_t vv = i < nrow ? nb[i] : NO_VERTEX;
 					if (vv != NO_VERTEX && nbd[i] < best) { best = nbd[i]; bv = vv; }
 				}
 #pragma unroll

@@ -142,6 +142,7 @@ def test_latency_form_real_valued(ex):
         ids_w, dists_w, counts_w = e.query_k_batch(q, k)
         dc1 = e.stats()["distcomps"]
         e.set_option("graph_cta_batch", 1 << 20)
+        e.set_option("graph_cta_width", 1)
         ids_c, dists_c, counts_c = e.query_k_batch(q, k)
         dc2 = e.stats()["distcomps"]
         same = np.all(ids_w == ids_c, axis=1) & np.all(dists_w == dists_c, axis=1)
@@ -151,8 +152,23 @@ def test_latency_form_real_valued(ex):
         for i in (0, 7):
             i1, d1, c1 = e.query_k_batch(q[i:i + 1], k)   # small host call: the search decodes its own results
             assert np.array_equal(i1[0], ids_c[i]) and np.array_equal(d1[0], dists_c[i]) and c1[0] == counts_c[i]
+    # two vertices expanded per hop (option graph_cta_width = 2): a different visit order, so the bar is the
+    # engine's own — recall@10 >= the one-at-a-time search's at every beam width, no duplicates, ascending distances
+    truth = np.argsort(((base[None, :, :] - q[:64, None, :]) ** 2).sum(-1), axis=1, kind="stable")[:, :10]
+    for ef in (10, 20, 40, 100):
+        e.set_ef_search(ef)
+        e.set_option("graph_cta_width", 1)
+        ids_1, _, _ = e.query_k_batch(q[:64], 10)
+        e.set_option("graph_cta_width", 2)
+        ids_2, dists_2, counts_2 = e.query_k_batch(q[:64], 10)
+        assert recall(ids_2, truth) >= recall(ids_1, truth) - 0.005, (ef, recall(ids_2, truth), recall(ids_1, truth))
+        assert np.all(counts_2 == 10) and all(len(set(r.tolist())) == 10 for r in ids_2)
+        assert np.all(np.diff(dists_2, axis=1) >= 0)
+        ref = ((base[ids_2[5].astype(np.int64)] - q[5]) ** 2).sum(1, dtype=np.float64).astype(np.float32)
+        assert np.allclose(ref, dists_2[5], rtol=1e-5)
     # fewer vertices reachable than k: unused slots are id = 2^64-1, dist = +inf, count < k (include/expann_gpu.h)
     e.set_ef_search(3)
+    e.set_option("graph_cta_width", 1)
     i1, d1, c1 = e.query_k_batch(q[:1], 10)
     i2, d2, c2 = e.query_k_batch(q[:400], 10)
     assert c1[0] == 3 and np.all(i1[0, 3:] == np.uint64(2**64 - 1)) and np.all(np.isinf(d1[0, 3:]))
@@ -160,8 +176,9 @@ def test_latency_form_real_valued(ex):
     e.close()
 
 
+@pytest.mark.parametrize("width", [1, 2])
 @pytest.mark.parametrize("compressed", [False, True])
-def test_latency_form_golden_index(ex, compressed):
+def test_latency_form_golden_index(ex, compressed, width):
     """the latency form on the reference-built golden graph (u8-valued rows: distance ties are common, so the forms
     may order tied vertices differently): recall@10 >= the reference's at every beam width, same bar as
     test_golden_index; result sets equal to the warp form's for most queries."""
@@ -175,12 +192,14 @@ def test_latency_form_golden_index(ex, compressed):
         e.set_option("graph_cta_batch", 0)
         ids_w, _, _ = e.query_k_batch(q, 10)
         e.set_option("graph_cta_batch", 1 << 20)
+        e.set_option("graph_cta_width", width)
         ids, dists, counts = e.query_k_batch(q, 10)
         ref_ids = g[f"ids_comp_ef{ef}" if compressed else f"ids_ef{ef}"]
         assert np.all(counts == 10)
         assert recall(ids, g["truth"]) >= recall(ref_ids, g["truth"]) - 1e-9, ef
         assert all(len(set(r.tolist())) == 10 for r in ids)
         assert np.all(np.diff(dists, axis=1) >= 0)
-        same = np.mean([set(a.tolist()) == set(b.tolist()) for a, b in zip(ids, ids_w)])
-        assert same >= 0.9, (ef, same)
+        if width == 1:  # same visit order as the warp form
+            same = np.mean([set(a.tolist()) == set(b.tolist()) for a, b in zip(ids, ids_w)])
+            assert same >= 0.9, (ef, same)
     e.close()
