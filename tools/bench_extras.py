@@ -72,6 +72,22 @@ def graph_c3(device: int, steps: int, warmup: int, cpu: bool = True, n: int = 1_
             for _ in range(steps):
                 e.query_k_batch(hq, k, out=outp)
             chosen["e2e_qps"] = m * steps / (time.perf_counter() - t1)
+            # the reference harness's own pattern: one query per call (src/basic_bench.h:82-126) -> latency form of K5
+            one = (outp[0][:1], outp[1][:1], outp[2][:1])
+            lat = {}
+            for width in (1, 2):
+                e.set_option("graph_cta_width", width)
+                for i in range(30):
+                    e.query_k_batch(hq[i:i + 1], k, out=one)
+                nq = min(m, 500)
+                t1 = time.perf_counter()
+                for i in range(nq):
+                    e.query_k_batch(hq[i:i + 1], k, out=one)
+                lat["width%d_us_per_call" % width] = (time.perf_counter() - t1) / nq * 1e6
+            e.set_option("graph_cta_width", 1)
+            lat["note"] = ("expann_gpu_query with one query per call, graph_search_cta_kernel (one CTA per query); width1 = the "
+                           "reference's visit order (default), width2 = two vertices expanded per hop")
+            chosen["single_query_call"] = lat
     out = {"workload": "SIFT-shape synthetic (low-rank, u8-valued) %dx%d, %d queries, graph engine M0=%d (GPU-built, K=%d), "
                        "beam-width sweep" % (n, d, m, M0, K),
            "metric": "QPS @ smallest ef with recall@10 >= 0.95", "graph_build_s": build_s, "sweep": sweep, "at_recall_0.95": chosen}
