@@ -185,7 +185,8 @@ void expann_gpu_destroy(expann_gpu_t* h) {
 	for (DevBuf* b : { &h->tc_xb, &h->tc_xn, &h->tc_stats, &h->tc_qstats, &h->tc_qb, &h->tc_qn, &h->tc_thr, &h->tc_cnt, &h->tc_cand, &h->tc_gthr, &h->tc_sel, &h->tc_xx, &h->tc_seed, &h->tc_fbcount, &h->scan_cnt })
 		b->release();
 	for (DevBuf* b : { &h->q_codes, &h->q_cnorm, &h->q_mm, &h->qq_codes, &h->qq_norm, &h->q_cand }) b->release();
-	for (DevBuf* b : { &h->g_bottom, &h->g_upper, &h->g_upper_idx, &h->g_upper_nl, &h->g_visited, &h->g_epoch, &h->g_codes })
+	for (DevBuf* b : { &h->g_bottom, &h->g_upper, &h->g_upper_idx, &h->g_upper_nl, &h->g_visited, &h->g_epoch, &h->g_codes, &h->g_up_meta,
+	                   &h->g_upper_c, &h->g_up_vec })
 		b->release();
 	for (DevBuf* b : { &h->qpad, &h->partial, &h->keys, &h->ids, &h->dists, &h->counts, &h->h_q, &h->h_ids, &h->h_dists,
 	                   &h->h_counts })
@@ -436,6 +437,8 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 	} else if (nm == "graph_cta_width") {
 		if (value != 1 && value != 2) return fail(h, EXPANN_ERR_ARG, "graph_cta_width must be 1 or 2");
 		h->opt_graph_cta_width = (int)value;
+	} else if (nm == "graph_upper_compact") {
+		h->opt_graph_upper_compact = value != 0;
 	} else if (nm == "tc_boot") {
 		h->opt_tc_boot = (int)value; // 0 off, 1 bf16-exact mode only (default), 2 both modes
 	} else if (nm == "tc_v1") {

@@ -68,6 +68,7 @@ struct expann_gpu {
 	int opt_graph_occ = 5; // graph search: resident CTAs of 4 warps per SM (2, 4, 5 or 8); set before build()
 	int opt_graph_cta_batch = -1; // graph search: calls with at most this many queries take the one-CTA-per-query latency form (-1 = two waves: twice the SM count)
 	int opt_graph_cta_width = 1; // latency form: vertices expanded per hop (1 = the reference's order, the default; 2 = half the dependent hops, recall >= at every beam width measured, +2 % distance evaluations)
+	int opt_graph_upper_compact = 1; // latency form: upper layers in compact form (set before build())
 	int opt_tc_boot = 1; // pair form: seeding launch over the leading tiles of a large base
 	// quantised scan engine (K6 + K4)
 	int quantizer = 0;       // 0 = quantizer_simple<uint8_t>, 1 = quantizer_ranged_q8
@@ -78,7 +79,8 @@ struct expann_gpu {
 	CUtensorMap tmap_codes{};
 	// graph engine
 	expann::HostGraph graph;
-	expann::DevBuf g_bottom, g_upper, g_upper_idx, g_upper_nl, g_visited, g_epoch, g_codes;
+	expann::DevBuf g_bottom, g_upper, g_upper_idx, g_upper_nl, g_visited, g_epoch, g_codes, g_up_meta, g_upper_c, g_up_vec;
+	size_t g_nup = 0; // vertices with upper layers in the compact form (0 = not built)
 	float build_ortho_factor = 0.5f, build_ortho_bias = 0.f;
 	uint64_t build_prune_overflow = 0, build_K = 0;
 	uint32_t g_ctas = 0;

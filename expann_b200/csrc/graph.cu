@@ -14,6 +14,16 @@ __global__ void quantize_u8_kernel(const float* __restrict__ base, uint8_t* __re
 	for (; i < total; i += stride) codes[i] = (uint8_t)(uint32_t)base[i];
 }
 
+// up_vec[c] = base[meta[c].z]: one warp per row
+__global__ void gather_upper_rows_kernel(const float* __restrict__ base, const uint4* __restrict__ meta, float* __restrict__ out,
+                                         uint32_t nup, uint32_t d_pad) {
+	const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+	if (w >= nup) return;
+	const float4* src = reinterpret_cast<const float4*>(base + (size_t)meta[w].z * d_pad);
+	float4* dst = reinterpret_cast<float4*>(out + (size_t)w * d_pad);
+	for (uint32_t i = lane; i < d_pad / 4; i += 32) dst[i] = src[i];
+}
+
 // CSR over (vertex, layer) pairs in vertex-major order -> fixed-stride device layout
 int graph_set_csr(expann_gpu* h, size_t n, const uint32_t* nlayers, const uint64_t* offsets, const uint32_t* edges,
                   uint64_t start, uint64_t max_layer) {
@@ -135,6 +145,36 @@ int graph_finalize(expann_gpu* h) {
 	EXPANN_CUDA(h, cudaMemsetAsync(h->g_visited.p, 0, slots * h->g_vis_stride, st));
 	EXPANN_CUDA(h, h->g_epoch.ensure(slots * 4 + 8));
 	EXPANN_CUDA(h, cudaMemsetAsync(h->g_epoch.p, 0, slots * 4 + 8, st));
+	// compact form of the upper layers for the latency form of the search (GraphParams::up_meta)
+	h->g_nup = 0;
+	if (h->opt_graph_upper_compact && g.max_layer > 1) {
+		std::vector<uint32_t> cidx(g.n, NO_VERTEX);
+		std::vector<uint4> meta;
+		for (size_t v = 0; v < g.n; ++v)
+			if (g.upper_idx[v] != NO_VERTEX) {
+				cidx[v] = (uint32_t)meta.size();
+				meta.push_back(make_uint4(g.upper_idx[v], g.upper_nl[v], (uint32_t)v, 0));
+			}
+		std::vector<uint32_t> uc(g.upper.size());
+		bool ok = !meta.empty() && meta.size() * h->d_pad * 4 <= ((size_t)2 << 30);
+		for (size_t i = 0; ok && i < uc.size(); ++i) {
+			uc[i] = g.upper[i] == NO_VERTEX ? NO_VERTEX : cidx[g.upper[i]];
+			if (g.upper[i] != NO_VERTEX && uc[i] == NO_VERTEX) ok = false; // a neighbour without upper layers: keep the plain form
+		}
+		if (ok) {
+			EXPANN_CUDA(h, h->g_up_meta.ensure(meta.size() * 16));
+			EXPANN_CUDA(h, h->g_upper_c.ensure(uc.size() * 4));
+			EXPANN_CUDA(h, h->g_up_vec.ensure(meta.size() * h->d_pad * 4));
+			EXPANN_CUDA(h, cudaMemcpyAsync(h->g_up_meta.p, meta.data(), meta.size() * 16, cudaMemcpyHostToDevice, st));
+			EXPANN_CUDA(h, cudaMemcpyAsync(h->g_upper_c.p, uc.data(), uc.size() * 4, cudaMemcpyHostToDevice, st));
+			gather_upper_rows_kernel<<<(unsigned)((meta.size() * 32 + 255) / 256), 256, 0, st>>>(
+			    h->base, h->g_up_meta.as<uint4>(), h->g_up_vec.as<float>(), (uint32_t)meta.size(), (uint32_t)h->d_pad);
+			EXPANN_CUDA(h, cudaGetLastError());
+			EXPANN_CUDA(h, cudaStreamSynchronize(st)); // meta / uc are host temporaries
+			h->stats.aux_launches++;
+			h->g_nup = meta.size();
+		}
+	}
 	if (h->cfg.use_compression) {
 		const size_t total = h->n * h->d_pad;
 		EXPANN_CUDA(h, h->g_codes.ensure(total));
@@ -183,6 +223,13 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 		const size_t smem1 = (size_t)h->d_pad * 5 + GS_MAXNB * 8 + 16 + 256 * 8 + GS_MAXNB * 4; // query | u8 query | nb | nbd | ctl | beam copy
 		if (smem1 > 200 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "graph search: d too large");
 		const unsigned grid1 = (unsigned)std::min<size_t>(m, (size_t)h->g_ctas * GS_WARPS);
+		if (h->g_nup && h->opt_graph_upper_compact) {
+			p.up_meta = h->g_up_meta.as<uint4>();
+			p.upper_c = h->g_upper_c.as<uint32_t>();
+			p.up_vec = h->g_up_vec.as<float>();
+			p.up_start_ui = h->graph.upper_idx[h->graph.start];
+			p.up_start_nl = h->graph.upper_nl[h->graph.start];
+		}
 		p.width = h->opt_graph_cta_width == 2 && 2 * h->graph.m0s <= (size_t)GS_MAXNB && ef >= 2 ? 2 : 1;
 		if (h->fuse_ids) { // small host call: the search decodes its own results (api.cu)
 			p.dec_ids = h->fuse_ids;

@@ -42,6 +42,14 @@ struct GraphParams {
 	uint32_t start, max_layer, id_add;
 	int compressed;
 	int width; // latency form: vertices expanded per hop (1 or 2)
+	// latency form, upper layers in compact form (null = off): the vertices that have upper layers (~n/M of them) get a
+	// dense index c; up_meta[c] = {first upper row, number of layers, global id, 0}; upper_c = the upper rows with
+	// neighbours as dense indices; up_vec[c] = a copy of the vertex's vector. A step of the descent is then row ->
+	// {vectors, meta} (two dependent loads, not three), all in ~n/M * (d*4 + M*4) bytes that stay L2-resident.
+	const uint4* up_meta;
+	const uint32_t* upper_c;
+	const float* up_vec;
+	uint32_t up_start_ui, up_start_nl;
 	// latency form only: results also decoded in place (ids / distances / counts of expann_gpu_query), saving the
 	// decode launch of a small host call; null otherwise
 	uint64_t* dec_ids;
@@ -546,6 +554,49 @@ __device__ __forceinline__ void cta_score_pair(const GraphParams& p, uint32_t cu
 	__syncthreads();
 }
 
+// one step of the upper-layer descent on the compact form: scores the ms neighbours listed (as dense indices) in row,
+// leaving nb[pos] = dense index, nbd[pos] = distance, mt[pos] = first upper row | layers << 32, gid[pos] = global id
+__device__ __forceinline__ void cta_score_upper(const GraphParams& p, const uint32_t* __restrict__ row, uint32_t layer,
+                                                const float* qsm, uint32_t* nb, float* nbd, uint64_t* mt, uint32_t* gid) {
+	const int tid = threadIdx.x, team = tid >> 3, tl = tid & 7, lane = tid & 31;
+	for (uint32_t p0 = 0; p0 < p.ms; p0 += GC_WARPS * 4) {
+		const uint32_t pos = p0 + team;
+		uint32_t c = NO_VERTEX;
+		if (tl == 0 && pos < p.ms) c = __ldg(row + pos);
+		c = __shfl_sync(FULL, c, lane & ~7);
+		const bool have = c != NO_VERTEX;
+		uint4 m = make_uint4(0, 0, 0, 0);
+		if (have && tl == 1) m = __ldg(p.up_meta + c);
+		const float* pa = p.up_vec + (size_t)(have ? c : 0) * p.d_pad + tl * 4;
+		const int nstep = p.d_pad >> 5;
+		float sa = 0.f;
+		if (have)
+			for (int s0 = 0; s0 < nstep; s0 += 4) {
+				float4 xa[4];
+#pragma unroll
+				for (int s = 0; s < 4; ++s)
+					if (s0 + s < nstep) xa[s] = ldg128f(pa + (s0 + s) * 32);
+#pragma unroll
+				for (int s = 0; s < 4; ++s)
+					if (s0 + s < nstep) { // same order of operations as gather_dist_f32
+						const float4 q = *reinterpret_cast<const float4*>(qsm + (s0 + s) * 32 + tl * 4);
+						float t;
+						t = q.x - xa[s].x; sa = fmaf(t, t, sa); t = q.y - xa[s].y; sa = fmaf(t, t, sa);
+						t = q.z - xa[s].z; sa = fmaf(t, t, sa); t = q.w - xa[s].w; sa = fmaf(t, t, sa);
+					}
+			}
+#pragma unroll
+		for (int o = 4; o >= 1; o >>= 1) sa += __shfl_xor_sync(FULL, sa, o);
+		if (tl == 0 && pos < p.ms) { nb[pos] = c; nbd[pos] = sa; }
+		if (tl == 1 && have) {
+			mt[pos] = (uint64_t)m.x | ((uint64_t)m.y << 32);
+			gid[pos] = m.z;
+			if (layer == 1) prefetch_l2(p.bottom + (size_t)m.z * p.m0s);
+		}
+	}
+	__syncthreads();
+}
+
 // decode_keys_kernel's work for result slot i of query qi (warp-wide call; key = KEY_EMPTY beyond k)
 __device__ __forceinline__ void emit_decoded(const GraphParams& p, uint32_t qi, int i, uint64_t key, uint32_t& nres) {
 	const bool ok = key != KEY_EMPTY;
@@ -603,16 +654,22 @@ __global__ void __launch_bounds__(32 * GC_WARPS) graph_search_cta_kernel(const G
 		}
 		__syncthreads();
 		float ep_dist = nbd[0];
+		uint32_t cu_ui = p.up_start_ui, cu_nl = p.up_start_nl; // compact form: the current vertex's upper rows
 		dc++;
 		__syncthreads();
 		for (uint32_t layer = p.max_layer > 0 ? p.max_layer - 1 : 0; layer > 0; --layer) {
 			bool changed = true;
 			while (changed) {
 				changed = false;
-				const uint32_t ui = __ldg(p.upper_idx + ep), unl = __ldg(p.upper_nl + ep); // both in flight together
-				if (ui == NO_VERTEX || unl <= layer) break;
-				const uint32_t* row = p.upper + ((size_t)ui + (layer - 1)) * p.ms;
-				cta_score_row<false>(p, row, p.ms, false, qsm, qc, nb, nbd, vis, ep8, nullptr, layer);
+				if (p.up_meta) {
+					if (cu_nl <= layer) break;
+					cta_score_upper(p, p.upper_c + ((size_t)cu_ui + (layer - 1)) * p.ms, layer, qsm, nb, nbd, bm, idsrc);
+				} else {
+					const uint32_t ui = __ldg(p.upper_idx + ep), unl = __ldg(p.upper_nl + ep); // both in flight together
+					if (ui == NO_VERTEX || unl <= layer) break;
+					const uint32_t* row = p.upper + ((size_t)ui + (layer - 1)) * p.ms;
+					cta_score_row<false>(p, row, p.ms, false, qsm, qc, nb, nbd, vis, ep8, nullptr, layer);
+				}
 #ifdef GC_PROFILE
 				pf_upsteps++;
 #endif
@@ -631,7 +688,17 @@ __global__ void __launch_bounds__(32 * GC_WARPS) graph_search_cta_kernel(const G
 					if (oi >= 0 && (ob < best || (ob == best && (besti < 0 || oi < besti)))) { best = ob; besti = oi; }
 				}
 				dc += cnt;
-				if (besti >= 0) { ep = nb[besti]; ep_dist = best; changed = true; }
+				if (besti >= 0) {
+					if (p.up_meta) {
+						const uint64_t mt = bm[besti];
+						cu_ui = (uint32_t)mt;
+						cu_nl = (uint32_t)(mt >> 32);
+						ep = idsrc[besti];
+					} else
+						ep = nb[besti];
+					ep_dist = best;
+					changed = true;
+				}
 				__syncthreads();
 			}
 		}

@@ -124,7 +124,8 @@ int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
  * default 5, before build()), "graph_cta_batch" (GRAPH: calls with at most this many queries take the latency form
  * of the search, one CTA per query; -1 automatic = twice the SM count, 0 never), "graph_cta_width" (vertices the latency form expands per hop: 1 (default) =
  * exactly the reference's visit order, 2 = the two closest unexpanded beam entries together: half the dependent hops,
- * measured recall >= at every beam width for 2 % more distance evaluations).
+ * measured recall >= at every beam width for 2 % more distance evaluations), "graph_upper_compact" (0/1, before build():
+ * compact copy of the upper layers for the latency form, default 1).
  * Tensor-core candidate filter of the brute-force engine: "tc" (0/1; operands are prepared by build(), so enabling
  * needs to precede it), "tc_min_batch" (default 5: measured crossover with the SIMT scan on 1M x 128), "tc_pair" (0/1:
  * clusters of two CTAs for batches > 128, default 1), "tc_astream" (0 off | 1 when the query tile cannot stay resident
