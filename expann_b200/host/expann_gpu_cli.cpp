@@ -282,6 +282,7 @@ int main(int argc, char** argv) {
 					gpu_graph_engine_config c;
 					c.M = M0 / 2; c.M0 = M0; c.ef_search_mult = efm; c.ef_construction = 2 * M0; c.use_compression = comp;
 					c.index_filename = index; c.read_index = !first; c.write_index = first;
+					c.search_width = std::stoul(get("search_width", "1"));
 					gpu_graph_engine e(c);
 					report(get_benchmark_data(ds, e, per_query));
 					first = false;

@@ -91,6 +91,7 @@ struct gpu_graph_engine_config {
 	std::string index_filename;
 	bool read_index = false, write_index = false;
 	int device = 0;
+	size_t search_width = 1; // vertices expanded per hop by the one-query-per-call form of the search (1 = the reference's order, 2)
 };
 struct gpu_graph_engine : gpu_engine_base<gpu_graph_engine> {
 	using config = gpu_graph_engine_config;
@@ -103,6 +104,7 @@ struct gpu_graph_engine : gpu_engine_base<gpu_graph_engine> {
 		g.ef_search_mult = c.ef_search_mult;
 		g.use_compression = c.use_compression;
 		create(g);
+		if (c.search_width != 1) check(expann_gpu_set_option(h, "graph_cta_width", (int64_t)c.search_width));
 	}
 	void _store_vector(const fvec& v) {
 		if (conf.read_index) return; // src/antitopo_engine.h:312-313
@@ -127,6 +129,7 @@ struct gpu_graph_engine : gpu_engine_base<gpu_graph_engine> {
 		pl["ortho_bias"] = std::to_string(conf.ortho_bias);
 		pl["prune_overflow"] = std::to_string(conf.prune_overflow);
 		pl["use_compression"] = std::to_string(conf.use_compression);
+		pl["search_width"] = std::to_string(conf.search_width);
 		pl["num_distcomps"] = std::to_string(stats().distcomps);
 		return pl;
 	}

@@ -43,3 +43,22 @@ def test_cli_config_workflow(tmp_path):
     assert r.returncode == 0, r.stderr
     assert len(json.load(open(prefix + "data/latest.json"))) == 1
     assert len(json.load(open(prefix + "data/all.json"))) == 9
+
+
+@pytest.mark.gpu
+def test_cli_per_query_graph(tmp_path):
+    """the reference harness's own loop (one query per call, src/basic_bench.h:82-126) through the C++ shim: the graph
+    engine answers it with the one-CTA-per-query form of the search; search_width = 2 must not lower the recall"""
+    cfg = tmp_path / "config_synthetic.json"
+    cfg.write_text(json.dumps({"dataset": "Synthetic", "ds_name": "t_pq", "n": 4000, "m": 60, "d": 128, "k": 10}))
+    rec = {}
+    for width in ("1", "2"):
+        prefix = str(tmp_path / ("out" + width)) + "/"
+        r = subprocess.run([CLI, "--config", str(cfg), "--engines", "graph", "--per_query", "1", "--search_width", width,
+                            "--out_prefix", prefix], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+        latest = json.load(open(prefix + "data/latest.json"))
+        assert len(latest) == 6 and all(b["param_list"]["search_width"] == width for b in latest)
+        rec[width] = [b["recall"] for b in latest]
+        assert rec[width][-1] >= 0.9
+    assert all(b >= a - 0.01 for a, b in zip(rec["1"], rec["2"])), rec
