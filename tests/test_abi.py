@@ -57,3 +57,16 @@ def test_product_does_not_touch_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".hpp")) or f == "Makefile":
                 txt = open(os.path.join(dp, f), errors="ignore").read()
                 assert "oracle" not in txt.lower() or f.endswith(".md"), os.path.join(dp, f)
+
+
+def test_documented_options_exist():
+    """every tuning knob the header documents for expann_gpu_set_option is accepted by the implementation, and every
+    knob the implementation accepts is documented (string-level check; no GPU needed)"""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "expann_gpu.h")).read()
+    doc = hdr[hdr.index("tuning knobs by name"):hdr.index("int expann_gpu_set_option")]
+    documented = set(re.findall(r'"([a-z_0-9]+)"', doc))
+    src = open(os.path.join(root, "expann_b200", "csrc", "api.cu")).read()
+    accepted = set(re.findall(r'nm == "([a-z_0-9]+)"', src))
+    assert documented == accepted, (sorted(documented - accepted), sorted(accepted - documented))
