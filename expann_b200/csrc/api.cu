@@ -366,10 +366,17 @@ int expann_gpu_load_index(expann_gpu_t* h, const char* path) {
 	size_t n = 0, d = 0;
 	if (int rc = graph_load_index(h, path, vectors, n, d)) return rc;
 	// like read_index in the reference (src/antitopo_engine.h:312-313,476-481): the file's vectors replace any stored ones
+	// The base buffer is sized in rows of the OLD d_pad and its padding columns are only zero for the old d: drop it, so
+	// that reserve_rows() allocates and zero-fills for the file's dimension (a smaller d would overflow the buffer, the
+	// same d_pad with a smaller d would leave stale values in the padding the kernels rely on being zero).
 	h->staging.clear();
 	h->staged_rows = 0;
+	EXPANN_CUDA(h, cudaStreamSynchronize(h->stream));
+	if (h->base) { cudaFree(h->base); h->base = nullptr; }
+	h->cap_rows = 0;
 	h->n = 0;
 	h->d = 0;
+	h->built = false;
 	if (int rc = check_dim(h, d)) return rc;
 	return upload_rows(h, vectors.data(), n, cudaMemcpyHostToDevice, h->stream);
 }

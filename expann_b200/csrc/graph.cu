@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <stdexcept>
 
 namespace expann {
 
@@ -70,10 +71,22 @@ int graph_set_csr(expann_gpu* h, size_t n, const uint32_t* nlayers, const uint64
 }
 
 // reference index file, src/antitopo_engine.h:931-991 (writer) / :994-1074 (reader): raw little-endian dump.
-int graph_load_index(expann_gpu* h, const char* path, std::vector<float>& vectors, size_t& n_out, size_t& d_out) {
+// Nothing in the file is trusted: every count is checked against the bytes that are left before anything is allocated,
+// ids are range-checked in 64 bits, and no exception crosses the C ABI (a truncated or corrupt file is EXPANN_ERR_IO).
+static int graph_load_index_impl(expann_gpu* h, const char* path, std::vector<float>& vectors, size_t& n_out, size_t& d_out) {
 	FILE* f = std::fopen(path, "rb");
 	if (!f) return fail(h, EXPANN_ERR_IO, std::string("cannot open index file ") + path);
-	auto rd = [&](void* p, size_t sz) { return std::fread(p, 1, sz, f) == sz; };
+	struct Closer { FILE* f; ~Closer() { std::fclose(f); } } closer{ f };
+	const auto bad = [&](const char* why) { return fail(h, EXPANN_ERR_IO, std::string("malformed index file ") + path + ": " + why); };
+	uint64_t fsize = 0, pos = 0;
+	if (std::fseek(f, 0, SEEK_END) != 0) return bad("not seekable");
+	{ const long long e = (long long)ftello(f); if (e < 0) return bad("not seekable"); fsize = (uint64_t)e; }
+	std::rewind(f);
+	auto rd = [&](void* p, uint64_t sz) {
+		if (sz > fsize - pos || std::fread(p, 1, (size_t)sz, f) != sz) return false;
+		pos += sz;
+		return true;
+	};
 	uint64_t start, M, M0, u64, max_layer, n = 0;
 	uint8_t b;
 	float fl;
@@ -83,43 +96,66 @@ int graph_load_index(expann_gpu* h, const char* path, std::vector<float>& vector
 	     && rd(&fl, 4) && rd(&fl, 4) && rd(&u64, 8)      // ortho_factor, ortho_bias, prune_overflow
 	     && rd(&b, 1) && rd(&b, 1)                       // use_compression, use_largest_direction_filtering
 	     && rd(&max_layer, 8) && rd(&n, 8);
-	size_t d = 0;
-	for (uint64_t i = 0; ok && i < n; ++i) {
+	if (!ok) return bad("truncated header");
+	if (n == 0) return bad("no vectors");
+	if (n >= 0xFFFFFFFFull) return fail(h, EXPANN_ERR_UNSUPPORTED, "index file: vertex ids must fit 32 bits on device");
+	if (start >= n) return bad("starting vertex out of range");
+	if (max_layer > 64) return bad("implausible max_layer");
+	// every vector record is 8 + 4 d bytes, every vertex record at least 8: n is bounded by what is left in the file
+	if (n > (fsize - pos) / 8) return bad("vector count exceeds the file size");
+	uint64_t d = 0;
+	for (uint64_t i = 0; i < n; ++i) {
 		uint64_t sz;
-		ok = rd(&sz, 8);
-		if (ok && i == 0) { d = sz; vectors.resize((size_t)n * d); }
-		ok = ok && sz == d && rd(vectors.data() + i * d, 4 * d);
+		if (!rd(&sz, 8)) return bad("truncated vector section");
+		if (i == 0) {
+			d = sz;
+			if (d == 0 || d > (1u << 20)) return bad("implausible dimension");
+			if (n > (fsize - pos + 8) / (8 + 4 * d)) return bad("vector section exceeds the file size");
+			vectors.resize((size_t)(n * d)); // n * (8 + 4 d) <= file size: no overflow
+		}
+		if (sz != d) return bad("vectors of different dimensions");
+		if (!rd(vectors.data() + i * d, 4 * d)) return bad("truncated vector section");
 	}
 	uint64_t nv = 0;
-	ok = ok && rd(&nv, 8) && nv == n;
-	std::vector<uint32_t> nlayers(n), edges;
+	if (!rd(&nv, 8) || nv != n) return bad("vertex count differs from vector count");
+	if (n > (fsize - pos) / 8) return bad("vertex section exceeds the file size");
+	std::vector<uint32_t> nlayers((size_t)n), edges;
 	std::vector<uint64_t> offsets(1, 0);
 	std::vector<uint8_t> rec;
-	for (uint64_t v = 0; ok && v < n; ++v) {
+	edges.reserve((size_t)std::min<uint64_t>((fsize - pos) / 12, (uint64_t)1 << 32));
+	for (uint64_t v = 0; v < n; ++v) {
 		uint64_t nl;
-		ok = rd(&nl, 8);
+		if (!rd(&nl, 8)) return bad("truncated vertex section");
+		if (nl == 0 || nl > max_layer + 1 || nl > 64) return bad("vertex with an implausible layer count");
 		nlayers[v] = (uint32_t)nl;
-		for (uint64_t l = 0; ok && l < nl; ++l) {
+		for (uint64_t l = 0; l < nl; ++l) {
 			uint64_t deg;
-			ok = rd(&deg, 8) && deg < (1u << 20);
-			if (!ok) break;
-			rec.resize(deg * 12); // {float len; size_t id} packed as written field by field
-			ok = rd(rec.data(), deg * 12);
-			for (uint64_t e = 0; ok && e < deg; ++e) {
+			if (!rd(&deg, 8)) return bad("truncated adjacency list");
+			if (deg > (fsize - pos) / 12) return bad("adjacency list exceeds the file size");
+			rec.resize((size_t)deg * 12); // {float len; size_t id} packed as written field by field
+			if (!rd(rec.data(), deg * 12)) return bad("truncated adjacency list");
+			for (uint64_t e = 0; e < deg; ++e) {
 				uint64_t id;
 				std::memcpy(&id, rec.data() + e * 12 + 4, 8);
+				if (id >= n) return bad("edge to a vertex out of range");
 				edges.push_back((uint32_t)id);
 			}
 			offsets.push_back(edges.size());
 		}
 	}
-	std::fclose(f);
-	if (!ok || n == 0) return fail(h, EXPANN_ERR_IO, std::string("malformed index file ") + path);
-	n_out = n;
-	d_out = d;
+	n_out = (size_t)n;
+	d_out = (size_t)d;
 	h->cfg.M = M;
 	h->cfg.M0 = M0;
-	return graph_set_csr(h, n, nlayers.data(), offsets.data(), edges.data(), start, max_layer);
+	return graph_set_csr(h, (size_t)n, nlayers.data(), offsets.data(), edges.data(), start, max_layer);
+}
+
+int graph_load_index(expann_gpu* h, const char* path, std::vector<float>& vectors, size_t& n_out, size_t& d_out) {
+	try {
+		return graph_load_index_impl(h, path, vectors, n_out, d_out);
+	} catch (const std::exception& e) { // bad_alloc / length_error must not cross the extern "C" boundary
+		return fail(h, EXPANN_ERR_IO, std::string("index file ") + path + ": " + e.what());
+	}
 }
 
 int graph_finalize(expann_gpu* h) {

@@ -90,8 +90,12 @@ int tc_finalize(expann_gpu* h) {
 		h->tc_kd = kd;
 		h->tc_mode = mode;
 		// integer, bf16-exact base whose dot products stay below 2^24: single GEMM, error bound 0
+		// (same bound as tc_check_exact_kernel applies per batch once the queries are known: signed values let the
+		// accumulator reach 2 d amax^2 + ||x||^2_max)
 		const float amax = std::max(std::fabs(h->tc_xmin), std::fabs(h->tc_xmax));
-		if (mode == 1 && !s.inexact && 2.0 * (double)h->d * amax * amax < 16777216.0) break;
+		const double nmax = (double)h->tc_xnorm_max * h->tc_xnorm_max, dot2 = 2.0 * (double)h->d * amax * amax;
+		const double acc_max = h->tc_xmin >= 0.f ? std::max(dot2, nmax) : dot2 + nmax;
+		if (mode == 1 && !s.inexact && acc_max < 16777216.0) break;
 	}
 	if (n_pad > h->n) {
 		tc_fill_kernel<<<(unsigned)((n_pad - h->n + 255) / 256), 256, 0, st>>>(h->tc_xn.as<float>(), h->n, n_pad, nanf(""));
@@ -319,7 +323,8 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	float eps_rel = 0.f, eps_abs = 0.f;
 	if (h->tc_mode == 1) {
 		// exact only if the queries are bf16-exact integers too: checked on the device, a violation raises flags[0]
-		tc_check_exact_kernel<<<1, 1, 0, st>>>(h->tc_qstats.as<TcStats>(), h->tc_xmin, h->tc_xmax, (float)h->d, flags);
+		tc_check_exact_kernel<<<1, 1, 0, st>>>(h->tc_qstats.as<TcStats>(), h->tc_xmin, h->tc_xmax, (float)h->d,
+		                                      h->tc_xnorm_max * h->tc_xnorm_max, flags);
 		h->stats.aux_launches++;
 	} else {
 		// two-term split: 3 * 2^-18 for the dropped terms + fp32 accumulation over kd/16 MMA steps; 2^-14 covers kd <= 1024

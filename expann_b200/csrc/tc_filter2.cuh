@@ -671,14 +671,20 @@ __global__ void __launch_bounds__(256) tc_select2_block_kernel(const uint64_t* _
 }
 
 // exactness of the bf16 single-GEMM mode for THIS query batch, decided on the device (no host round trip): the queries
-// must be bf16-exact integers too and no partial sum may leave the 2^24 integer range; otherwise flags[0] is raised and
-// the caller redoes the batch with the SIMT scan.
-__global__ void tc_check_exact_kernel(const TcStats* __restrict__ qs, float xmin, float xmax, float d, uint32_t* __restrict__ flags) {
+// must be bf16-exact integers too, no partial sum of the accumulator may leave the 2^24 integer range, and the fp32
+// diff-form key of the SIMT scan / K4 must be exact as well (d * (hi - lo)^2 < 2^24, the predicate of the first form,
+// tc.cu) so that both paths stay bit-identical; otherwise flags[0] is raised and the caller redoes the batch with the
+// SIMT scan. The accumulator runs through sum (-2 q_i) x_i and takes ||x||^2 LAST (the norm step is the tile's final
+// MMA): for non-negative data the partial sums lie in [-2 d hi^2, 0] and the total in [-2 d hi^2, ||x||^2_max]; with
+// signed values the dot product can have either sign, so the total reaches 2 d amax^2 + ||x||^2_max.
+__global__ void tc_check_exact_kernel(const TcStats* __restrict__ qs, float xmin, float xmax, float d, float xnorm2_max,
+                                      uint32_t* __restrict__ flags) {
 	const float lo = fminf(xmin, f32_from_orderable(qs->vmin)), hi = fmaxf(xmax, f32_from_orderable(qs->vmax));
 	const float amax = fmaxf(fabsf(lo), fabsf(hi));
-	const double lim = 16777216.0;
-	// the accumulator runs through sum (-2 q_i) x_i (+ ||x||^2): every partial sum must stay an exact fp32 integer
-	const bool exact = !qs->inexact && amax <= 256.f && 2.0 * (double)d * amax * amax < lim;
+	const double lim = 16777216.0, dd = (double)d;
+	const double acc_max = lo >= 0.f ? fmax(2.0 * dd * amax * amax, (double)xnorm2_max) : 2.0 * dd * amax * amax + (double)xnorm2_max;
+	const double span = (double)hi - (double)lo;
+	const bool exact = !qs->inexact && amax <= 256.f && acc_max < lim && dd * span * span < lim;
 	if (!exact) atomicAdd(flags, 1u);
 }
 // start of a batch in one launch: query statistics reset, the batch's flags cleared, shared bounds set to +inf

@@ -203,3 +203,61 @@ def test_latency_form_golden_index(ex, compressed, width):
             same = np.mean([set(a.tolist()) == set(b.tolist()) for a, b in zip(ids, ids_w)])
             assert same >= 0.9, (ef, same)
     e.close()
+
+
+def test_corrupt_index_files_are_rejected(ex, tmp_path):
+    """a truncated or corrupt index must come back as an error code through the C ABI (no exception, no abort, no
+    out-of-range id aliasing a valid vertex): graph_load_index validates every count against the file size"""
+    from expann_b200._lib import ExpannError, ERR_IO
+    good = open(os.path.join(GOLD, "graph_u8_2000.index"), "rb").read()
+    cases = {
+        "empty": b"",
+        "header_only": good[:40],
+        "truncated_vectors": good[:len(good) // 3],
+        "truncated_edges": good[:len(good) - 1000],
+    }
+    # header layout (src/antitopo_engine.h:931-991): 4 x u64, bool has_ef [u64], 2 x u64, 2 x f32, u64, 2 x bool, u64 max_layer, u64 n
+    has_ef = good[32]
+    off_n = 33 + (8 if has_ef else 0) + 16 + 8 + 8 + 2 + 8
+    huge_n = bytearray(good); huge_n[off_n:off_n + 8] = (2**62).to_bytes(8, "little"); cases["huge_n"] = bytes(huge_n)
+    n = int.from_bytes(good[off_n:off_n + 8], "little")
+    d = int.from_bytes(good[off_n + 8:off_n + 16], "little")
+    assert n == 2000 and d == 128
+    huge_d = bytearray(good); huge_d[off_n + 8:off_n + 16] = (2**40).to_bytes(8, "little"); cases["huge_d"] = bytes(huge_d)
+    # first adjacency record: after the vectors, u64 n, u64 layers, u64 deg, then {f32 len, u64 id}
+    off_v = off_n + 8 + n * (8 + 4 * d) + 8
+    deg_off = off_v + 8
+    bad_id = bytearray(good); bad_id[deg_off + 8 + 4:deg_off + 8 + 12] = (2**32 + 5).to_bytes(8, "little"); cases["id_aliases_mod_2_32"] = bytes(bad_id)
+    bad_deg = bytearray(good); bad_deg[deg_off:deg_off + 8] = (2**50).to_bytes(8, "little"); cases["huge_degree"] = bytes(bad_deg)
+    bad_nl = bytearray(good); bad_nl[off_v:off_v + 8] = (2**33).to_bytes(8, "little"); cases["huge_layer_count"] = bytes(bad_nl)
+    for name, blob in cases.items():
+        p = tmp_path / (name + ".index")
+        p.write_bytes(blob)
+        e = ex.GraphEngine()
+        with pytest.raises(ExpannError) as ei:
+            e.load_index(str(p))
+        assert ei.value.code == ERR_IO, (name, ei.value)
+        e.close()
+    e = ex.GraphEngine()          # and the intact file still loads
+    e.load_index(os.path.join(GOLD, "graph_u8_2000.index"))
+    e.build()
+    e.close()
+
+
+def test_load_index_after_vectors_of_another_dimension(ex):
+    """vectors stored before load_index are replaced by the file's (read_index, src/antitopo_engine.h:312-313); the HBM
+    buffer sized for the old dimension must not be reused: d = 32 rows first, then the d = 128 golden index"""
+    g = gold("graph_u8_2000")
+    q = g["q"].astype(np.float32)
+    ref = ex.GraphEngine()
+    ref.load_index(os.path.join(GOLD, "graph_u8_2000.index")); ref.build(); ref.set_ef_search(40)
+    want = ref.query_k_batch(q, 10)
+    ref.close()
+    for d0 in (32, 100):    # smaller d_pad (buffer overflow before the fix) / same d_pad, smaller d (stale padding columns)
+        e = ex.GraphEngine()
+        e.store_many_vectors(np.full((5000, d0), 7.0, np.float32))
+        e.load_index(os.path.join(GOLD, "graph_u8_2000.index"))
+        e.build(); e.set_ef_search(40)
+        got = e.query_k_batch(q, 10)
+        e.close()
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])

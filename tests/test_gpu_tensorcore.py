@@ -276,3 +276,27 @@ def test_small_batch_select_many_candidates(ex):
     b = run(ex, base, q, 16, tc=0)
     assert a[3]["tc_launches"] == 1
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+@pytest.mark.parametrize("amp", [100, 200, 230, 250])
+def test_signed_integer_rows(ex, oracle, amp):
+    """signed integer-valued rows (int8-style embeddings): the accumulator of the exact mode runs through
+    sum(-2 q_i x_i) + ||x||^2 and reaches 2 d amax^2 + ||x||^2_max with mixed signs -- the exact-mode gate
+    (tc_check_exact_kernel and the build-time decision) must count that, or fall back. Whatever path is taken the
+    answer must equal the SIMT scan bit for bit and the oracle."""
+    rng = np.random.default_rng(300 + amp)
+    base = rng.integers(-amp, amp + 1, (40_000, 128)).astype(np.float32)
+    q = rng.integers(-amp, amp + 1, (400, 128)).astype(np.float32)
+    # a few rows / queries at the extremes of the range: largest norms and dot products of either sign
+    base[:64] = np.where(rng.random((64, 128)) < 0.5, -amp, amp)
+    q[:16] = base[:16]
+    q[16:32] = -base[16:32]
+    for metric in (0, 1):
+        a = run(ex, base, q, 10, metric=metric)
+        b = run(ex, base, q, 10, metric=metric, tc=0)
+        assert a[3]["tc_launches"] >= 1 and b[3]["tc_launches"] == 0
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+        oi, od, _ = oracle.bf_query(base, q, 10, metric=metric, threads=16)
+        assert_topk_parity(a[0], a[1], oi, od, base, q, metric="ip" if metric else "l2", tag=f"signed amp{amp} metric{metric}")
+    if amp <= 100:   # 3 d amax^2 < 2^24: stays in the exact mode without a redo
+        assert a[3]["tc_mode"] == 1 and a[3]["tc_fallbacks"] == 0
