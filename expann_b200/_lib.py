@@ -7,7 +7,8 @@ import os
 import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libexpann_gpu.so")
+# EXPANN_GPU_LIB: another build of the same library (kernel A/B experiments under tools/)
+LIB_PATH = os.environ.get("EXPANN_GPU_LIB") or os.path.join(HERE, "libexpann_gpu.so")
 
 OK, ERR_ARG, ERR_CUDA, ERR_STATE, ERR_UNSUPPORTED, ERR_IO = 0, -1, -2, -3, -4, -5
 ENGINE_BRUTE_FORCE, ENGINE_GRAPH, ENGINE_QUANT_SCAN = 0, 1, 2

@@ -181,6 +181,8 @@ void expann_gpu_destroy(expann_gpu_t* h) {
 	if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
 	timing_collect(h);
 	for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
+	if (h->tc_flag_event) cudaEventDestroy(h->tc_flag_event);
+	h->tc_flag_host.release();
 	if (h->base) cudaFree(h->base);
 	for (DevBuf* b : { &h->tc_xb, &h->tc_xn, &h->tc_stats, &h->tc_qstats, &h->tc_qb, &h->tc_qn, &h->tc_thr, &h->tc_cnt, &h->tc_cand, &h->tc_gthr, &h->tc_sel, &h->tc_xx, &h->tc_seed, &h->tc_fbcount, &h->scan_cnt })
 		b->release();
@@ -448,6 +450,10 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 		h->opt_graph_upper_compact = value != 0;
 	} else if (nm == "tc_boot") {
 		h->opt_tc_boot = (int)value; // 0 off, 1 bf16-exact mode only (default), 2 both modes
+	} else if (nm == "tc_real") {
+		if (value != 0 && value != 1) return fail(h, EXPANN_ERR_ARG, "tc_real must be 0 or 1");
+		if (h->built) return fail(h, EXPANN_ERR_STATE, "tc_real must be set before build()");
+		h->opt_tc_real = (int)value;
 	} else if (nm == "tc_v1") {
 		h->opt_tc_v1 = value != 0;
 	} else if (nm == "tc") {

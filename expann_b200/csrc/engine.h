@@ -57,7 +57,11 @@ struct expann_gpu {
 	expann_gpu_stats_t stats{};
 	// tensor-core candidate filter (K3)
 	int opt_tc = 1, opt_tc_min_batch = 5; // from 5 queries on K3 is level with or ahead of K1 (1M x 128: 0.12 vs 0.15 ms at 6, 0.13 vs 0.22 at 12)
-	int tc_mode = 0; // 0 off, 1 bf16-exact single GEMM, 2 two-term bf16 split
+	int tc_mode = 0; // 0 off, 1 bf16-exact single GEMM, 2 two-term bf16 split, 3 one bf16 term per value (real-valued data, wider slack)
+	int opt_tc_real = 1; // real-valued data: 1 = start in the one-term format (mode 3) and move to the split when a batch is redone, 0 = split from the start
+	bool tc_flag_pending = false; // mode 3: a copy of the last batch's flag word is on its way to tc_flag_host
+	cudaEvent_t tc_flag_event = nullptr;
+	expann::DevBuf tc_flag_host;
 	uint32_t tc_kd = 0;
 	float tc_xmin = 0.f, tc_xmax = 0.f, tc_xnorm_max = 0.f;
 	expann::DevBuf tc_xb, tc_xn, tc_stats, tc_qstats, tc_qb, tc_qn, tc_thr, tc_cnt, tc_cand, tc_gthr, tc_sel, tc_xx, tc_seed, tc_fbcount;
@@ -94,7 +98,7 @@ struct expann_gpu {
 	bool timing = false;
 	std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timed; // pending (start, stop) pairs of the dominant kernel
 	std::vector<cudaEvent_t> event_pool;
-	expann_gpu() { h_q.host = h_ids.host = h_dists.host = h_counts.host = true; }
+	expann_gpu() { h_q.host = h_ids.host = h_dists.host = h_counts.host = tc_flag_host.host = true; }
 };
 
 namespace expann {

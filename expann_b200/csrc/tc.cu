@@ -61,42 +61,36 @@ static int reset_stats(expann_gpu* h, DevBuf& buf, cudaStream_t st) {
 	return EXPANN_OK;
 }
 
-// build(): decide the operand format from the base values and materialise the bf16 operand + ||x||^2
-int tc_finalize(expann_gpu* h) {
-	h->tc_mode = 0;
-	if (!h->opt_tc || h->cfg.engine != EXPANN_ENGINE_BRUTE_FORCE) return EXPANN_OK;
-	cudaStream_t st = h->stream;
+// operand row length (bf16 elements) of a format: one term per value in the exact (1) and one-term (3) formats,
+// [xh | xl | xh] in the two-term split (2)
+static uint32_t tc_kd_of(const expann_gpu* h, int mode) {
 	const uint32_t seg = (uint32_t)((h->d + 63) / 64 * 64);
-	// d too large for a resident query tile: only the streamed-A pair form (tc_filter3.cuh, ASTREAM) can take it
-	if (tc_smem_bytes(3 * seg, TC_NSTAGE_SPLIT) > 227 * 1024 && !h->opt_tc_astream) return EXPANN_OK;
+	return mode == 2 ? 3 * seg : seg;
+}
+
+// materialise the bf16 operand of `fmt` (1 = one bf16 term per value, 2 = two-term split), ||x||^2 and its three-term
+// form, the value statistics and the tensor maps
+static int tc_prepare(expann_gpu* h, int fmt, TcStats* s_out) {
+	cudaStream_t st = h->stream;
 	const size_t n_pad = (h->n + TC_BN - 1) / TC_BN * TC_BN;
+	const uint32_t kd = tc_kd_of(h, fmt);
 	EXPANN_CUDA(h, h->tc_xn.ensure(n_pad * 4));
-	for (int mode = 1; mode <= 2; ++mode) {
-		const uint32_t kd = mode == 1 ? seg : 3 * seg;
-		EXPANN_CUDA(h, h->tc_xb.ensure(h->n * (size_t)kd * 2));
-		if (int rc = reset_stats(h, h->tc_stats, st)) return rc;
-		EXPANN_CUDA(h, h->tc_xx.ensure(h->n * 32));
-		tc_convert_kernel<<<(unsigned)((h->n + 7) / 8), 256, 0, st>>>(h->base, h->d_pad, (uint32_t)h->d, h->n,
-		                                                             h->tc_xb.as<__nv_bfloat16>(), kd, mode, 0, h->tc_xn.as<float>(),
-		                                                             h->tc_stats.as<TcStats>(), 1.f, h->tc_xx.as<__nv_bfloat16>(),
-		                                                             h->cfg.metric == EXPANN_METRIC_IP ? 0 : 1);
-		EXPANN_CUDA(h, cudaGetLastError());
-		h->stats.aux_launches++;
-		TcStats s;
-		if (int rc = read_stats(h, h->tc_stats, &s, st)) return rc;
-		h->tc_xmin = f32_from_orderable(s.vmin);
-		h->tc_xmax = f32_from_orderable(s.vmax);
-		h->tc_xnorm_max = std::sqrt(f32_from_orderable(s.nmax));
-		h->tc_kd = kd;
-		h->tc_mode = mode;
-		// integer, bf16-exact base whose dot products stay below 2^24: single GEMM, error bound 0
-		// (same bound as tc_check_exact_kernel applies per batch once the queries are known: signed values let the
-		// accumulator reach 2 d amax^2 + ||x||^2_max)
-		const float amax = std::max(std::fabs(h->tc_xmin), std::fabs(h->tc_xmax));
-		const double nmax = (double)h->tc_xnorm_max * h->tc_xnorm_max, dot2 = 2.0 * (double)h->d * amax * amax;
-		const double acc_max = h->tc_xmin >= 0.f ? std::max(dot2, nmax) : dot2 + nmax;
-		if (mode == 1 && !s.inexact && acc_max < 16777216.0) break;
-	}
+	EXPANN_CUDA(h, h->tc_xb.ensure(h->n * (size_t)kd * 2));
+	if (int rc = reset_stats(h, h->tc_stats, st)) return rc;
+	EXPANN_CUDA(h, h->tc_xx.ensure(h->n * 32));
+	tc_convert_kernel<<<(unsigned)((h->n + 7) / 8), 256, 0, st>>>(h->base, h->d_pad, (uint32_t)h->d, h->n,
+	                                                             h->tc_xb.as<__nv_bfloat16>(), kd, fmt, 0, h->tc_xn.as<float>(),
+	                                                             h->tc_stats.as<TcStats>(), 1.f, h->tc_xx.as<__nv_bfloat16>(),
+	                                                             h->cfg.metric == EXPANN_METRIC_IP ? 0 : 1);
+	EXPANN_CUDA(h, cudaGetLastError());
+	h->stats.aux_launches++;
+	TcStats s;
+	if (int rc = read_stats(h, h->tc_stats, &s, st)) return rc;
+	h->tc_xmin = f32_from_orderable(s.vmin);
+	h->tc_xmax = f32_from_orderable(s.vmax);
+	h->tc_xnorm_max = std::sqrt(f32_from_orderable(s.nmax));
+	h->tc_kd = kd;
+	if (s_out) *s_out = s;
 	if (n_pad > h->n) {
 		tc_fill_kernel<<<(unsigned)((n_pad - h->n + 255) / 256), 256, 0, st>>>(h->tc_xn.as<float>(), h->n, n_pad, nanf(""));
 		h->stats.aux_launches++;
@@ -108,6 +102,76 @@ int tc_finalize(expann_gpu* h) {
 	if (int rc = encode_tensor_map_bf16(h, &h->tmap_xb128, h->tc_xb.p, h->tc_kd, h->n, TC2_TN)) return rc;
 	if (int rc = encode_tensor_map_bf16(h, &h->tmap_xx, h->tc_xx.p, 16, h->n, TC2_TN, 16)) return rc;
 	return encode_tensor_map_bf16(h, &h->tmap_xb, h->tc_xb.p, h->tc_kd, h->n, TC_BN);
+}
+
+// build(): decide the operand format from the base values and materialise the bf16 operand + ||x||^2.
+//   mode 1  bf16-exact integers whose accumulator stays below 2^24: one GEMM, error bound 0;
+//   mode 3  anything else, one bf16 term per value (the SAME operand as mode 1: kd = d, a third of the split's flops)
+//           with the slack its rounding error needs; a batch that ends with too many survivors / a full buffer is redone
+//           by the SIMT scan and moves the handle to
+//   mode 2  the two-term split [qh|qh|ql].[xh|xl|xh] (kd = 3 d, error 2^-14 |q| max|x|) for good (option tc_real = 0
+//           starts there).
+int tc_finalize(expann_gpu* h) {
+	h->tc_mode = 0;
+	h->tc_flag_pending = false;
+	if (!h->opt_tc || h->cfg.engine != EXPANN_ENGINE_BRUTE_FORCE) return EXPANN_OK;
+	const uint32_t seg = (uint32_t)((h->d + 63) / 64 * 64);
+	// d too large for a resident query tile: only the streamed-A pair form (tc_filter3.cuh, ASTREAM) can take it
+	if (tc_smem_bytes(3 * seg, TC_NSTAGE_SPLIT) > 227 * 1024 && !h->opt_tc_astream) return EXPANN_OK;
+	TcStats s;
+	if (int rc = tc_prepare(h, 1, &s)) return rc;
+	// integer, bf16-exact base whose accumulator stays below 2^24: single GEMM, error bound 0
+	// (same bound as tc_check_exact_kernel applies per batch once the queries are known: signed values let the
+	// accumulator reach 2 d amax^2 + ||x||^2_max)
+	const float amax = std::max(std::fabs(h->tc_xmin), std::fabs(h->tc_xmax));
+	const double nmax = (double)h->tc_xnorm_max * h->tc_xnorm_max, dot2 = 2.0 * (double)h->d * amax * amax;
+	const double acc_max = h->tc_xmin >= 0.f ? std::max(dot2, nmax) : dot2 + nmax;
+	if (!s.inexact && acc_max < 16777216.0) { h->tc_mode = 1; return EXPANN_OK; }
+	if (h->opt_tc_real == 1) { h->tc_mode = 3; return EXPANN_OK; }
+	if (int rc = tc_prepare(h, 2, nullptr)) return rc;
+	h->tc_mode = 2;
+	return EXPANN_OK;
+}
+
+// error bound of the operand format, as e = eps_rel * |q| * max|x| + eps_abs on the a' scale (see the header comment)
+static void tc_eps(const expann_gpu* h, float* eps_rel, float* eps_abs) {
+	*eps_rel = 0.f;
+	*eps_abs = 0.f;
+	if (h->tc_mode == 1) return;
+	const float acc = (float)h->tc_kd / 16.f * (1.0f / 8388608.0f); // fp32 accumulation over kd/16 MMA steps, 2^-23 each
+	if (h->tc_mode == 3)
+		// one bf16 term per operand: unit roundoff 2^-8 each, so a product is off by at most (2^-7 + 2^-16) |q_i x_i|; the
+		// query operand carries the factor -2 (L2; -1 for the inner product, where this is twice what is needed)
+		*eps_rel = 2.0f * (1.0f / 128.0f + 1.0f / 65536.0f) + acc;
+	else
+		// two-term split: 3 * 2^-18 for the dropped terms + fp32 accumulation over kd/16 MMA steps; 2^-14 covers kd <= 1024
+		*eps_rel = (1.0f / 16384.0f) * std::max(1.0f, (float)h->tc_kd / 1024.0f);
+	*eps_abs = 1e-6f * (h->tc_xnorm_max * h->tc_xnorm_max + 1e-30f); // fp32 rounding of ||x||^2 and of the final fma
+}
+
+// one-term format: has an earlier batch been redone? (its flag word was copied to page-locked memory behind the batch;
+// looked at here without waiting) -> the handle moves to the two-term split for good
+static int tc_adapt_format(expann_gpu* h) {
+	if (h->tc_mode != 3 || !h->tc_flag_pending) return EXPANN_OK;
+	if (cudaEventQuery(h->tc_flag_event) != cudaSuccess) { cudaGetLastError(); return EXPANN_OK; }
+	h->tc_flag_pending = false;
+	if (*h->tc_flag_host.as<uint32_t>() == 0) return EXPANN_OK;
+	EXPANN_CUDA(h, cudaDeviceSynchronize()); // operand buffers are about to be rewritten
+	if (int rc = tc_prepare(h, 2, nullptr)) return rc;
+	h->tc_mode = 2;
+	h->stats.tc_mode = 2;
+	return EXPANN_OK;
+}
+static int tc_watch_flag(expann_gpu* h, const uint32_t* flags, cudaStream_t st) {
+	if (h->tc_mode != 3 || h->tc_flag_pending) return EXPANN_OK;
+	if (!h->tc_flag_event) {
+		EXPANN_CUDA(h, h->tc_flag_host.ensure(4));
+		EXPANN_CUDA(h, cudaEventCreateWithFlags(&h->tc_flag_event, cudaEventDisableTiming));
+	}
+	EXPANN_CUDA(h, cudaMemcpyAsync(h->tc_flag_host.p, flags, 4, cudaMemcpyDeviceToHost, st));
+	EXPANN_CUDA(h, cudaEventRecord(h->tc_flag_event, st));
+	h->tc_flag_pending = true;
+	return EXPANN_OK;
 }
 
 template <int NSTAGE>
@@ -131,7 +195,7 @@ static int tc_batch(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 	uint32_t* flags = h->tc_cnt.as<uint32_t>() + m;
 	if (int rc = reset_stats(h, h->tc_qstats, st)) return rc;
 	tc_convert_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(d_q, h->d_pad, (uint32_t)h->d, m, h->tc_qb.as<__nv_bfloat16>(), kd,
-	                                                          h->tc_mode, 1, h->tc_qn.as<float>(), h->tc_qstats.as<TcStats>());
+	                                                          h->tc_mode == 2 ? 2 : 1, 1, h->tc_qn.as<float>(), h->tc_qstats.as<TcStats>());
 	EXPANN_CUDA(h, cudaGetLastError());
 	h->stats.aux_launches++;
 	float eps_rel = 0.f, eps_abs = 0.f;
@@ -144,11 +208,8 @@ static int tc_batch(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 		const double lim = 16777216.0, dd = (double)h->d;
 		const bool exact = !s.inexact && amax <= 256.f && dd * (hi - lo) * (hi - lo) < lim && dd * amax * amax < lim;
 		if (!exact) { *fell_back = true; return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st); }
-	} else {
-		// two-term split: 3 * 2^-18 for the dropped terms + fp32 accumulation over kd/16 MMA steps; 2^-14 covers kd <= 1024
-		eps_rel = (1.0f / 16384.0f) * std::max(1.0f, (float)kd / 1024.0f);                                        // two-term bf16 split: < 2^-15 per product, doubled
-		eps_abs = 1e-6f * (h->tc_xnorm_max * h->tc_xnorm_max + 1e-30f);   // fp32 rounding of ||x||^2 and of the final fma
-	}
+	} else
+		tc_eps(h, &eps_rel, &eps_abs);
 	CUtensorMap tq;
 	if (int rc = encode_tensor_map_bf16(h, &tq, h->tc_qb.p, kd, m, TC_BM)) return rc;
 	EXPANN_CUDA(h, cudaMemsetAsync(h->tc_cnt.p, 0, m * 4 + 16, st));
@@ -180,7 +241,7 @@ static int tc_batch(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 		rsplit = (nt + p.tiles_per_cta - 1) / p.tiles_per_cta;
 		dim3 grid(qblocks, rsplit);
 		cudaEvent_t t0 = timing_begin(h, st);
-		int rc = h->tc_mode == 1 ? launch_filter<TC_NSTAGE_EXACT>(h, tq, p, grid, st) : launch_filter<TC_NSTAGE_SPLIT>(h, tq, p, grid, st);
+		int rc = h->tc_mode != 2 ? launch_filter<TC_NSTAGE_EXACT>(h, tq, p, grid, st) : launch_filter<TC_NSTAGE_SPLIT>(h, tq, p, grid, st);
 		timing_end(h, t0, st);
 		if (rc) return rc;
 		h->stats.tc_launches++;
@@ -282,6 +343,7 @@ static uint32_t tc2_pick_rsplit(uint32_t qblocks, uint32_t ntiles, int sms) {
 // second form of K3 (k <= 16): ONE filter launch with in-kernel bounds, one select launch, one re-rank launch
 static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st, bool* fell_back) {
 	*fell_back = false;
+	if (int rc = tc_adapt_format(h)) return rc;
 	const uint32_t kd = h->tc_kd;
 	const bool ip = h->cfg.metric == EXPANN_METRIC_IP;
 	const int nqb = Tc2Cfg<2>::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024 && m > TC_BM ? 2 : 1;
@@ -299,7 +361,7 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	// only in the bf16-exact mode, whose epilogue is the limiter (the split mode is MMA-bound: 9.70 ms without, 9.94 with),
 	// and only for batches that fill the GPU with the seeding launch's one cluster per 256 queries (it costs ~0.14 ms
 	// whatever the batch: measured break-even at ~8000 queries on 1M rows)
-	const uint32_t boot_tiles = pair && (h->opt_tc_boot == 2 || (h->opt_tc_boot == 1 && h->tc_mode == 1 && m >= 8192)) && ntiles >= 128 ? std::max(8u, std::min(64u, ntiles / 32u)) : 0u;
+	const uint32_t boot_tiles = pair && (h->opt_tc_boot == 2 || (h->opt_tc_boot == 1 && h->tc_mode != 2 && m >= 8192)) && ntiles >= 128 ? std::max(8u, std::min(64u, ntiles / 32u)) : 0u;
 	const uint32_t main_tiles = ntiles - boot_tiles;
 	uint32_t rows_split = tc2_pick_rsplit(qblocks, main_tiles, sms);
 	if (h->opt_nsplit > 0) rows_split = std::max(1u, std::min({ (uint32_t)h->opt_nsplit, main_tiles, (uint32_t)TC2_MAX_SPLIT / 2u - 1u })); // experiments
@@ -317,7 +379,7 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	EXPANN_CUDA(h, h->tc_qstats.ensure(sizeof(TcStats)));
 	tc_batch_init_kernel<<<(unsigned)((std::max<size_t>(m, 4) + 255) / 256), 256, 0, st>>>(h->tc_qstats.as<TcStats>(), flags, h->tc_gthr.as<uint32_t>(), (uint32_t)m);
 	tc_convert_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(d_q, h->d_pad, (uint32_t)h->d, m, h->tc_qb.as<__nv_bfloat16>(), kd,
-	                                                          h->tc_mode, 1, h->tc_qn.as<float>(), h->tc_qstats.as<TcStats>(), ip ? -1.f : -2.f);
+	                                                          h->tc_mode == 2 ? 2 : 1, 1, h->tc_qn.as<float>(), h->tc_qstats.as<TcStats>(), ip ? -1.f : -2.f);
 	EXPANN_CUDA(h, cudaGetLastError());
 	h->stats.aux_launches += 2;
 	float eps_rel = 0.f, eps_abs = 0.f;
@@ -326,11 +388,8 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 		tc_check_exact_kernel<<<1, 1, 0, st>>>(h->tc_qstats.as<TcStats>(), h->tc_xmin, h->tc_xmax, (float)h->d,
 		                                      h->tc_xnorm_max * h->tc_xnorm_max, flags);
 		h->stats.aux_launches++;
-	} else {
-		// two-term split: 3 * 2^-18 for the dropped terms + fp32 accumulation over kd/16 MMA steps; 2^-14 covers kd <= 1024
-		eps_rel = (1.0f / 16384.0f) * std::max(1.0f, (float)kd / 1024.0f);
-		eps_abs = 1e-6f * (h->tc_xnorm_max * h->tc_xnorm_max + 1e-30f);
-	}
+	} else
+		tc_eps(h, &eps_rel, &eps_abs);
 	CUtensorMap tq;
 	if (int rc = encode_tensor_map_bf16(h, &tq, h->tc_qb.p, kd, m, TC_BM)) return rc;
 	Tc2Params p{};
@@ -423,11 +482,12 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 		EXPANN_CUDA(h, h->tc_fbcount.ensure(4));
 		EXPANN_CUDA(h, cudaMemsetAsync(h->tc_fbcount.p, 0, 4, st));
 	}
-	return launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st, flags, h->tc_fbcount.as<uint32_t>());
+	if (int rc = launch_scan_f32_simt(h, d_q, m, k, d_keys_out, st, flags, h->tc_fbcount.as<uint32_t>())) return rc;
+	return tc_watch_flag(h, flags, st);
 }
 
 // entry used by the brute-force engine for large batches
-bool tc_first_form_fits(const expann_gpu* h) { return tc_smem_bytes(h->tc_kd, h->tc_mode == 1 ? TC_NSTAGE_EXACT : TC_NSTAGE_SPLIT) <= 227 * 1024; }
+bool tc_first_form_fits(const expann_gpu* h) { return tc_smem_bytes(h->tc_kd, h->tc_mode != 2 ? TC_NSTAGE_EXACT : TC_NSTAGE_SPLIT) <= 227 * 1024; }
 
 int launch_scan_tc(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st) {
 	for (size_t q0 = 0; q0 < m; q0 += TC_QBATCH) {

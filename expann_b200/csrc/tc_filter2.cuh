@@ -105,26 +105,60 @@ __device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c
 	asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
 	return r;
 }
-// pass 1 of a chunk: only the minimum of its 32 accumulator columns (= a' values of one query)
-__device__ __forceinline__ float tc2_chunk_min(const uint32_t (&d)[32]) {
-	float mn[11];
+// pass 1 of a chunk: only the minimum of its 32 accumulator columns (= a' values of one query). The minima of the
+// eleven triples are left in mn[] for pass 2.
+__device__ __forceinline__ float tc2_chunk_min(const uint32_t (&d)[32], float (&mn)[11]) {
 #pragma unroll
 	for (int j = 0; j < 10; ++j) mn[j] = min3f(__uint_as_float(d[3 * j]), __uint_as_float(d[3 * j + 1]), __uint_as_float(d[3 * j + 2]));
 	mn[10] = fminf(__uint_as_float(d[30]), __uint_as_float(d[31]));
 	const float m0 = min3f(mn[0], mn[1], mn[2]), m1 = min3f(mn[3], mn[4], mn[5]), m2 = min3f(mn[6], mn[7], mn[8]);
 	return min3f(min3f(m0, m1, m2), mn[9], mn[10]);
 }
-// pass 2 (rare): a chunk known to hold some a' <= thr. The values are parked in this lane's scratch column and the hit
-// mask is built without branches; only the set bits (usually one) are visited. thr tightens while we go, hence the
-// second compare. Rows >= n (zero-filled by TMA: a' = 0) are masked here.
-__device__ __forceinline__ void tc2_chunk_hits(Tc2Thread& t, const uint32_t (&d)[32], float* sc, uint32_t row_c, uint32_t n) {
+__device__ __forceinline__ float tc2_chunk_min(const uint32_t (&d)[32]) {
+	float mn[11];
+	return tc2_chunk_min(d, mn);
+}
+#ifndef TC2_HITS_V2
+#define TC2_HITS_V2 1
+#endif
+// pass 2 (rare per lane, frequent per warp on short row ranges): a chunk known to hold some a' <= thr. Only the triples
+// whose minimum passes the bound are looked at (usually one triple of one lane): their values are parked in this lane's
+// scratch column, the hit mask is built from them and only the set bits are visited. thr tightens while we go, hence
+// the second compare. Rows >= n (zero-filled by TMA: a' = 0) are masked here. (The first version parked and compared
+// all 32 values of the chunk on every entry: ~100 instructions before the first event; on a 125k-row shard nearly
+// every chunk of every warp enters here -- see profiles/r2_notes.md.)
+__device__ __forceinline__ void tc2_chunk_hits(Tc2Thread& t, const uint32_t (&d)[32], const float (&mn)[11], float* sc, uint32_t row_c,
+                                               uint32_t n) {
 	const uint32_t sca = smem_u32(sc);
 	uint32_t mask = 0;
+#if TC2_HITS_V2
+#pragma unroll
+	for (int g = 0; g < 4; ++g) { // triples 0-2, 3-5, 6-8, 9-10: a real branch per group, then one per triple
+		const int j0 = 3 * g, j1 = g < 3 ? 3 * g + 3 : 11;
+		const float gm = g < 3 ? min3f(mn[j0], mn[j0 + 1], mn[j0 + 2]) : fminf(mn[9], mn[10]);
+		if (gm <= t.thr) {
+#pragma unroll
+			for (int j = j0; j < j1; ++j) {
+				if (mn[j] <= t.thr) {
+#pragma unroll
+					for (int c = 0; c < 3; ++c) {
+						const int jj = 3 * j + c;
+						if (jj < 32) {
+							asm volatile("st.shared.b32 [%0], %1;" ::"r"(sca + jj * 128), "r"(d[jj]) : "memory");
+							mask |= __uint_as_float(d[jj]) <= t.thr ? 1u << jj : 0u;
+						}
+					}
+				}
+			}
+		}
+	}
+#else
 #pragma unroll
 	for (int j = 0; j < 32; ++j) {
 		asm volatile("st.shared.b32 [%0], %1;" ::"r"(sca + j * 128), "r"(d[j]) : "memory");
 		mask |= __uint_as_float(d[j]) <= t.thr ? 1u << j : 0u;
 	}
+#endif
 	while (mask) {
 		const int j = __ffs(mask) - 1;
 		mask &= mask - 1;
@@ -132,6 +166,19 @@ __device__ __forceinline__ void tc2_chunk_hits(Tc2Thread& t, const uint32_t (&d)
 		asm volatile("ld.shared.f32 %0, [%1];" : "=f"(aj) : "r"(sca + j * 128) : "memory");
 		if (aj <= t.thr && row_c + j < n) tc2_event(t, aj, row_c + j);
 	}
+}
+// same, with the triple minima recomputed here. The values pass through an empty asm so that the compiler cannot merge this
+// with the caller's min tree and keep eleven more registers live across the vote (spills in the pair kernel).
+__device__ __forceinline__ void tc2_chunk_hits(Tc2Thread& t, const uint32_t (&d)[32], float* sc, uint32_t row_c, uint32_t n) {
+	uint32_t e[32];
+#pragma unroll
+	for (int j = 0; j < 32; ++j) {
+		e[j] = d[j];
+		asm volatile("" : "+r"(e[j]));
+	}
+	float mn[11];
+	tc2_chunk_min(e, mn);
+	tc2_chunk_hits(t, e, mn, sc, row_c, n);
 }
 __device__ __forceinline__ void tc_ld32_nowait(uint32_t taddr, uint32_t (&v)[32]) {
 	asm volatile(

@@ -293,6 +293,7 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 			tc_fence_before();
 			__syncwarp();
 			if (lane == 0) mbar_arrive_cluster(acc ? tm_empty_l1 : tm_empty_l0); // all 16 epilogue warps of the pair -> leader
+			// (the triple minima are recomputed inside the hit path: keeping them live across the vote costs spills)
 			const float mnA = tc2_chunk_min(dA);
 			if (__any_sync(FULL, mnA <= t.thr)) tc2_chunk_hits(t, dA, sc, row0, p.n);
 			const float mnB = tc2_chunk_min(dB);

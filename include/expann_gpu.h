@@ -50,7 +50,10 @@ typedef struct expann_gpu_stats {
 	uint64_t hot_time_ns, hot_timed_launches; /* CUDA-event time of the dominant kernel, see expann_gpu_set_timing */
 	uint64_t tc_launches, tc_fallbacks;       /* tensor-core filter launches; batches redone by the SIMT scan (counted on
 	                                             the device: expann_gpu_stats() synchronises the device to read it) */
-	uint64_t tc_mode;                         /* 0 off, 1 bf16-exact, 2 two-term bf16 split (decided by build()) */
+	uint64_t tc_mode;                         /* operand format of the tensor-core filter: 0 off, 1 bf16-exact integers (error 0),
+	                                             3 one bf16 term per value (real-valued data; slack 2^-6 |q| max|x|), 2 two-term bf16
+	                                             split (3x the flops, slack 2^-14 |q| max|x|). build() picks 1 or 3; a batch of
+	                                             format 3 that had to be redone moves the handle to 2 */
 	uint64_t reserved[3];
 } expann_gpu_stats_t;
 
@@ -129,8 +132,9 @@ int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
  * Tensor-core candidate filter of the brute-force engine: "tc" (0/1; operands are prepared by build(), so enabling
  * needs to precede it), "tc_min_batch" (default 5: measured crossover with the SIMT scan on 1M x 128), "tc_pair" (0/1:
  * clusters of two CTAs for batches > 128, default 1), "tc_astream" (0 off | 1 when the query tile cannot stay resident
- * | 2 always), "tc_boot" (seeding launch: 0 off | 1 exact mode and >= 8192 queries | 2 always), "tc_v1" (force the
- * chunked first form). Unknown names: EXPANN_ERR_ARG. */
+ * | 2 always), "tc_boot" (seeding launch: 0 off | 1 one-term formats and >= 8192 queries | 2 always), "tc_v1" (force the
+ * chunked first form), "tc_real" (real-valued rows, before build(): 1 (default) one bf16 term per value, falling back to the
+ * two-term split when a batch had to be redone | 0 the split from the start). Unknown names: EXPANN_ERR_ARG. */
 int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value);
 /* library build info: "sm_100a;..." */
 const char* expann_gpu_version(void);

@@ -14,9 +14,11 @@ def ex():
     return expann_b200
 
 
-def run(ex, base, q, k, metric=0, tc=1, id_offset=0, v1=0, pair=1, boot=None):
+def run(ex, base, q, k, metric=0, tc=1, id_offset=0, v1=0, pair=1, boot=None, real=None):
     e = ex.BruteForceEngine(metric=metric, id_offset=id_offset)
     e.set_option("tc", tc)
+    if real is not None:
+        e.set_option("tc_real", real)  # real-valued rows: 1 (default) one bf16 term per value (mode 3), 0 two-term split (mode 2)
     e.set_option("tc_pair", pair)  # 1 (default): clusters of two CTAs, tcgen05.mma.cta_group::2; 0: single-CTA form
     if boot is not None:
         e.set_option("tc_boot", boot)  # 2: seeding launch whatever the batch size / mode (default: exact mode, >= 8192 queries)
@@ -45,14 +47,17 @@ def test_exact_mode_u8_bit_identical(ex, oracle, metric):
     assert np.array_equal(ids, ids2) and np.array_equal(dists, dists2)
 
 
+@pytest.mark.parametrize("real", [0, 1])
 @pytest.mark.parametrize("d", [128, 96, 20])
-def test_split_mode_real_valued(ex, oracle, d):
+def test_split_mode_real_valued(ex, oracle, d, real):
+    """real-valued rows in both operand formats: the two-term split (mode 2) and one bf16 term per value (mode 3, the
+    default: a third of the flops, slack 2^-6 |q| max|x|)"""
     rng = np.random.default_rng(d)
     base = rng.standard_normal((30000, d)).astype(np.float32)
     q = rng.standard_normal((600, d)).astype(np.float32)
     for metric in (0, 1):
-        ids, dists, counts, st = run(ex, base, q, 10, metric=metric)
-        assert st["tc_mode"] == 2 and st["tc_launches"] > 0 and st["tc_fallbacks"] == 0
+        ids, dists, counts, st = run(ex, base, q, 10, metric=metric, real=real)
+        assert st["tc_mode"] == (3 if real else 2) and st["tc_launches"] > 0 and st["tc_fallbacks"] == 0
         oi, od, oc = oracle.bf_query(base, q, 10, metric=metric, threads=16)
         swaps = assert_topk_parity(ids, dists, oi, od, base, q, metric="ip" if metric else "l2", tag=f"tc split d{d}")
         assert swaps <= 4
@@ -157,10 +162,11 @@ def test_second_form_real_valued_splits(ex):
     base /= np.linalg.norm(base, axis=1, keepdims=True)
     q = rng.standard_normal((700, 96)).astype(np.float32)
     for metric in (0, 1):
-        ids, dists, _, st = run(ex, base, q, 10, metric=metric)
-        assert st["tc_mode"] == 2 and st["tc_launches"] in (1, 2) and st["tc_fallbacks"] == 0
         ids2, dists2, _, _ = run(ex, base, q, 10, metric=metric, tc=0)
-        assert np.array_equal(ids, ids2) and np.array_equal(dists, dists2)
+        for real in (0, 1):
+            ids, dists, _, st = run(ex, base, q, 10, metric=metric, real=real)
+            assert st["tc_mode"] == (3 if real else 2) and st["tc_launches"] in (1, 2) and st["tc_fallbacks"] == 0
+            assert np.array_equal(ids, ids2) and np.array_equal(dists, dists2)
 
 
 @pytest.mark.parametrize("real", [False, True])
@@ -300,3 +306,27 @@ def test_signed_integer_rows(ex, oracle, amp):
         assert_topk_parity(a[0], a[1], oi, od, base, q, metric="ip" if metric else "l2", tag=f"signed amp{amp} metric{metric}")
     if amp <= 100:   # 3 d amax^2 < 2^24: stays in the exact mode without a redo
         assert a[3]["tc_mode"] == 1 and a[3]["tc_fallbacks"] == 0
+
+
+def test_one_term_format_moves_to_split_after_a_redo(ex, oracle):
+    """mode 3 (one bf16 term per value) on data whose distances are too concentrated for its slack: nearly every row
+    survives, the batch is redone by the SIMT scan (exact answer), and the NEXT batch runs in the two-term split
+    (tc_mode 2) without a redo"""
+    rng = np.random.default_rng(31)
+    n, d = 60_000, 64
+    c = rng.standard_normal(d).astype(np.float32) * 40.0
+    base = (c + 1e-3 * rng.standard_normal((n, d))).astype(np.float32)   # a tight ball far from the origin
+    q = (c + 1e-3 * rng.standard_normal((300, d))).astype(np.float32)
+    e = ex.BruteForceEngine()
+    e.store_many_vectors(base); e.build()
+    assert e.stats()["tc_mode"] == 3
+    ref = run(ex, base, q, 10, tc=0)
+    a = e.query_k_batch(q, 10)
+    st = e.stats()
+    assert st["tc_fallbacks"] == 1
+    assert np.array_equal(a[0], ref[0]) and np.array_equal(a[1], ref[1])
+    b = e.query_k_batch(q, 10)          # the flag word of the first batch has arrived by now (the host call synchronised)
+    st = e.stats()
+    assert st["tc_mode"] == 2 and st["tc_launches"] >= 2
+    assert np.array_equal(b[0], ref[0]) and np.array_equal(b[1], ref[1])
+    e.close()
