@@ -18,7 +18,8 @@ METRIC_L2, METRIC_IP = 0, 1
 class Cfg(C.Structure):
     _fields_ = [("engine", C.c_int32), ("metric", C.c_int32), ("device", C.c_int32), ("qtile", C.c_int32),
                 ("id_offset", C.c_uint64), ("M", C.c_uint64), ("M0", C.c_uint64), ("ef_search_mult", C.c_uint64),
-                ("use_compression", C.c_int32), ("quantizer", C.c_int32), ("reserved", C.c_int32 * 6)]
+                ("use_compression", C.c_int32), ("quantizer", C.c_int32), ("n_devices", C.c_int32), ("row_groups", C.c_int32),
+                ("reserved", C.c_int32 * 4)]
 
 
 class Stats(C.Structure):
@@ -26,13 +27,15 @@ class Stats(C.Structure):
                 ("merge_launches", C.c_uint64), ("graph_launches", C.c_uint64), ("aux_launches", C.c_uint64),
                 ("last_nsplit", C.c_uint64), ("last_qtile", C.c_uint64), ("distcomps", C.c_uint64),
                 ("hot_time_ns", C.c_uint64), ("hot_timed_launches", C.c_uint64), ("tc_launches", C.c_uint64),
-                ("tc_fallbacks", C.c_uint64), ("tc_mode", C.c_uint64), ("reserved", C.c_uint64 * 3)]
+                ("tc_fallbacks", C.c_uint64), ("tc_mode", C.c_uint64), ("peer_bytes", C.c_uint64), ("query_groups", C.c_uint64),
+                ("row_groups", C.c_uint64)]
 
 
 # every symbol include/expann_gpu.h declares: name -> (restype, argtypes)
 _vp, _sz, _u64 = C.c_void_p, C.c_size_t, C.c_uint64
 SYMBOLS = {
     "expann_gpu_create": (C.c_int, [C.POINTER(Cfg), C.POINTER(_vp)]),
+    "expann_gpu_create_multi": (C.c_int, [C.POINTER(Cfg), C.POINTER(C.c_int32), _sz, C.POINTER(_vp)]),
     "expann_gpu_destroy": (None, [_vp]),
     "expann_gpu_last_error": (C.c_char_p, [_vp]),
     "expann_gpu_add": (C.c_int, [_vp, _vp, _sz, _sz]),

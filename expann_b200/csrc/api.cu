@@ -51,12 +51,6 @@ static void timing_collect(expann_gpu* h) {
 
 static size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-struct DeviceGuard {
-	int prev = -1;
-	explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); }
-	~DeviceGuard() { int cur; cudaGetDevice(&cur); if (prev >= 0 && cur != prev) cudaSetDevice(prev); }
-};
-
 // grow the HBM base buffer to hold `rows` rows (zero-filled so the d..d_pad padding columns stay 0)
 static int reserve_rows(expann_gpu* h, size_t rows) {
 	if (rows <= h->cap_rows) return EXPANN_OK;
@@ -116,8 +110,8 @@ static int padded_queries(expann_gpu* h, const float* d_q, size_t m, cudaStream_
 	return EXPANN_OK;
 }
 
-static int query_device_impl(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out,
-                             cudaStream_t st) {
+int query_device_impl(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out,
+                      cudaStream_t st) {
 	if (!h->built) return fail(h, EXPANN_ERR_STATE, "query before build()");
 	if (k == 0) return fail(h, EXPANN_ERR_ARG, "k must be > 0");
 	if (m == 0) return EXPANN_OK;
@@ -133,6 +127,15 @@ static int query_device_impl(expann_gpu* h, const float* d_q, size_t m, size_t k
 	default:
 		return fail(h, EXPANN_ERR_UNSUPPORTED, "engine kind not implemented");
 	}
+}
+
+bool is_pinned_host(const void* p) {
+	cudaPointerAttributes a{};
+	if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+		cudaGetLastError(); // unregistered host memory reports an error on old drivers: not sticky, clear it
+		return false;
+	}
+	return a.type == cudaMemoryTypeHost;
 }
 
 } // namespace expann
@@ -159,6 +162,12 @@ int expann_gpu_create(const expann_gpu_cfg* cfg, expann_gpu_t** out) {
 	int dev = cfg->device;
 	if (dev < 0) cudaGetDevice(&dev);
 	if (dev >= ndev) return fail(nullptr, EXPANN_ERR_ARG, "device ordinal out of range");
+	if (cfg->n_devices > 1) { // GPUs dev .. dev + n_devices - 1 behind one handle (multi.cu)
+		if (cfg->n_devices > 64) return fail(nullptr, EXPANN_ERR_ARG, "n_devices must be <= 64");
+		int32_t list[64];
+		for (int i = 0; i < cfg->n_devices; ++i) list[i] = dev + i;
+		return mg_create(cfg, list, (size_t)cfg->n_devices, out);
+	}
 	cudaDeviceProp prop;
 	e = cudaGetDeviceProperties(&prop, dev);
 	if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaGetDeviceProperties");
@@ -175,8 +184,19 @@ int expann_gpu_create(const expann_gpu_cfg* cfg, expann_gpu_t** out) {
 	return EXPANN_OK;
 }
 
+int expann_gpu_create_multi(const expann_gpu_cfg* cfg, const int32_t* devices, size_t n_devices, expann_gpu_t** out) {
+	if (!cfg || !out) return fail(nullptr, EXPANN_ERR_ARG, "null argument");
+	*out = nullptr;
+	if (cfg->engine != EXPANN_ENGINE_BRUTE_FORCE && cfg->engine != EXPANN_ENGINE_GRAPH && cfg->engine != EXPANN_ENGINE_QUANT_SCAN)
+		return fail(nullptr, EXPANN_ERR_UNSUPPORTED, "engine kind not implemented");
+	if (cfg->quantizer != 0 && cfg->quantizer != 1) return fail(nullptr, EXPANN_ERR_ARG, "bad quantizer");
+	if (cfg->metric != EXPANN_METRIC_L2 && cfg->metric != EXPANN_METRIC_IP) return fail(nullptr, EXPANN_ERR_ARG, "bad metric");
+	return mg_create(cfg, devices, n_devices, out);
+}
+
 void expann_gpu_destroy(expann_gpu_t* h) {
 	if (!h) return;
+	if (h->mg) mg_destroy(h);
 	DeviceGuard g(h->device);
 	if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
 	timing_collect(h);
@@ -200,6 +220,7 @@ const char* expann_gpu_last_error(const expann_gpu_t* h) { return h ? h->err.c_s
 
 int expann_gpu_add(expann_gpu_t* h, const float* rows, size_t n, size_t d) {
 	if (!h || (!rows && n)) return fail(h, EXPANN_ERR_ARG, "null argument");
+	if (h->mg) return mg_add(h, rows, n, d, false, nullptr);
 	if (int rc = check_dim(h, d)) return rc;
 	if (n == 0) return EXPANN_OK;
 	DeviceGuard g(h->device);
@@ -217,6 +238,7 @@ int expann_gpu_add(expann_gpu_t* h, const float* rows, size_t n, size_t d) {
 
 int expann_gpu_add_device(expann_gpu_t* h, const float* d_rows, size_t n, size_t d, void* stream) {
 	if (!h || (!d_rows && n)) return fail(h, EXPANN_ERR_ARG, "null argument");
+	if (h->mg) return mg_add(h, d_rows, n, d, true, (cudaStream_t)stream);
 	if (int rc = check_dim(h, d)) return rc;
 	if (n == 0) return EXPANN_OK;
 	DeviceGuard g(h->device);
@@ -228,6 +250,7 @@ int expann_gpu_add_device(expann_gpu_t* h, const float* d_rows, size_t n, size_t
 
 int expann_gpu_build(expann_gpu_t* h) {
 	if (!h) return EXPANN_ERR_ARG;
+	if (h->mg) return mg_build(h);
 	DeviceGuard g(h->device);
 	if (int rc = flush_staging(h)) return rc;
 	if (h->n == 0) return fail(h, EXPANN_ERR_STATE, "build() on an empty engine (the reference asserts n > 0)");
@@ -249,24 +272,17 @@ int expann_gpu_build(expann_gpu_t* h) {
 int expann_gpu_query_device(expann_gpu_t* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out,
                             void* stream) {
 	if (!h || (m && (!d_q || !d_keys_out))) return fail(h, EXPANN_ERR_ARG, "null argument");
+	if (h->mg) return mg_query_device(h, d_q, m, k, ef, d_keys_out, (cudaStream_t)stream);
 	DeviceGuard g(h->device);
 	return query_device_impl(h, d_q, m, k, ef, d_keys_out, (cudaStream_t)stream);
 }
 
 constexpr size_t SMALL_CALL_BYTES = 16 << 10; // queries / results of a call up to this size skip the copy engines
 
-static bool is_pinned_host(const void* p) {
-	cudaPointerAttributes a{};
-	if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
-		cudaGetLastError(); // unregistered host memory reports an error on old drivers: not sticky, clear it
-		return false;
-	}
-	return a.type == cudaMemoryTypeHost;
-}
-
 int expann_gpu_query(expann_gpu_t* h, const float* q, size_t m, size_t k, size_t ef, uint64_t* ids_out, float* dist_out,
                      uint64_t* counts_out) {
 	if (!h || (m && (!q || !ids_out))) return fail(h, EXPANN_ERR_ARG, "null argument");
+	if (h->mg) return mg_query(h, q, m, k, ef, ids_out, dist_out, counts_out);
 	if (!h->built) return fail(h, EXPANN_ERR_STATE, "query before build()");
 	if (k == 0) return fail(h, EXPANN_ERR_ARG, "k must be > 0");
 	if (m == 0) return EXPANN_OK;
@@ -363,6 +379,7 @@ int expann_gpu_decode_device(expann_gpu_t* h, const uint64_t* d_keys, size_t m, 
 int expann_gpu_load_index(expann_gpu_t* h, const char* path) {
 	if (!h || !path) return fail(h, EXPANN_ERR_ARG, "null argument");
 	if (h->cfg.engine != EXPANN_ENGINE_GRAPH) return fail(h, EXPANN_ERR_STATE, "load_index: not a graph engine");
+	if (h->mg) return mg_load_index(h, path);
 	DeviceGuard g(h->device);
 	std::vector<float> vectors;
 	size_t n = 0, d = 0;
@@ -387,6 +404,7 @@ int expann_gpu_build_graph(expann_gpu_t* h, uint64_t M, uint64_t M0, uint64_t K,
                            uint64_t prune_overflow, uint64_t seed) {
 	if (!h) return EXPANN_ERR_ARG;
 	if (h->cfg.engine != EXPANN_ENGINE_GRAPH) return fail(h, EXPANN_ERR_STATE, "build_graph: not a graph engine");
+	if (h->mg) return mg_build_graph(h, M, M0, K, ortho_factor, ortho_bias, prune_overflow, seed);
 	DeviceGuard g(h->device);
 	if (int rc = flush_staging(h)) return rc;
 	return graph_build_gpu(h, M, M0, K, ortho_factor, ortho_bias, prune_overflow, seed);
@@ -395,6 +413,7 @@ int expann_gpu_build_graph(expann_gpu_t* h, uint64_t M, uint64_t M0, uint64_t K,
 int expann_gpu_save_index(expann_gpu_t* h, const char* path) {
 	if (!h || !path) return EXPANN_ERR_ARG;
 	if (h->cfg.engine != EXPANN_ENGINE_GRAPH) return fail(h, EXPANN_ERR_STATE, "save_index: not a graph engine");
+	if (h->mg) return fail(h, EXPANN_ERR_UNSUPPORTED, "save_index: a multi-device handle holds one sub-graph per GPU (save from single-device handles)");
 	DeviceGuard g(h->device);
 	if (int rc = flush_staging(h)) return rc;
 	return graph_save_index(h, path);
@@ -404,6 +423,7 @@ int expann_gpu_set_graph(expann_gpu_t* h, size_t n, const uint32_t* nlayers, con
                          uint64_t starting_vertex, uint64_t max_layer) {
 	if (!h || !nlayers || !offsets || !edges) return fail(h, EXPANN_ERR_ARG, "null argument");
 	if (h->cfg.engine != EXPANN_ENGINE_GRAPH) return fail(h, EXPANN_ERR_STATE, "set_graph: not a graph engine");
+	if (h->mg) return fail(h, EXPANN_ERR_UNSUPPORTED, "set_graph: multi-device handles take the graph from load_index (replicas) or build_graph (one sub-graph per shard)");
 	return graph_set_csr(h, n, nlayers, offsets, edges, starting_vertex, max_layer);
 }
 
@@ -416,6 +436,7 @@ int expann_gpu_get_quantizer(const expann_gpu_t* h, float* scale, float* offset)
 
 int expann_gpu_set_timing(expann_gpu_t* h, int on) {
 	if (!h) return EXPANN_ERR_ARG;
+	if (h->mg) return mg_set_timing(h, on);
 	DeviceGuard g(h->device);
 	timing_collect(h);
 	h->timing = on != 0;
@@ -425,6 +446,7 @@ int expann_gpu_set_timing(expann_gpu_t* h, int on) {
 int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 	if (!h || !name) return EXPANN_ERR_ARG;
 	const std::string nm(name);
+	if (h->mg && nm == "mgpu_row_groups") return mg_set_option(h, name, value);
 	if (nm == "qtile") {
 		if (value != 0 && value != 1 && value != 4 && value != 8) return fail(h, EXPANN_ERR_ARG, "qtile must be 0, 1, 4 or 8");
 		h->cfg.qtile = (int32_t)value;
@@ -466,11 +488,13 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 		h->opt_nsplit = (int)value;
 	} else
 		return fail(h, EXPANN_ERR_ARG, "unknown option: " + nm);
+	if (h->mg) return mg_set_option(h, name, value); // validated above on the parent's own fields; now every GPU's handle
 	return EXPANN_OK;
 }
 
 int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out) {
 	if (!h || !out) return EXPANN_ERR_ARG;
+	if (h->mg) return mg_stats(h, out);
 	DeviceGuard g(h->device);
 	timing_collect(h);
 	if (h->cfg.engine == EXPANN_ENGINE_GRAPH) graph_read_distcomps(h);

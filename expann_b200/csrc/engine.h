@@ -38,11 +38,20 @@ struct HostGraph {
 	std::vector<float> bottom_len, upper_len; // edge lengths when known (GPU build), for the index writer
 };
 
+struct Multi; // multi.cu: state of a multi-device handle
+
+struct DeviceGuard {
+	int prev = -1;
+	explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); }
+	~DeviceGuard() { int cur; cudaGetDevice(&cur); if (prev >= 0 && cur != prev) cudaSetDevice(prev); }
+};
+
 } // namespace expann
 
 struct expann_gpu {
 	expann_gpu_cfg cfg{};
 	int device = 0;
+	expann::Multi* mg = nullptr; // non-null: this handle fans out to one child handle per GPU (multi.cu)
 	std::string err;
 	// base set: row-major float[n][d_pad] in HBM, d_pad = d rounded up to 32 floats (128 B rows-chunks for TMA)
 	size_t n = 0, d = 0, d_pad = 0, cap_rows = 0;
@@ -79,6 +88,7 @@ struct expann_gpu {
 	int opt_kprime = 0;      // 0 = auto
 	size_t dc_pad = 0;       // code row stride (d rounded up to 128)
 	float q_scale = 1.f, q_offset = 0.f;
+	bool q_range_fixed = false; // ranged q8: scale / offset were set from outside (multi-device handle: one range for all shards)
 	expann::DevBuf q_codes, q_cnorm, q_mm, qq_codes, qq_norm, q_cand;
 	CUtensorMap tmap_codes{};
 	// graph engine
@@ -107,6 +117,21 @@ int fail(expann_gpu* h, int code, const std::string& msg);
 cudaEvent_t timing_begin(expann_gpu* h, cudaStream_t st);
 void timing_end(expann_gpu* h, cudaEvent_t start, cudaStream_t st);
 int cuda_fail(expann_gpu* h, cudaError_t e, const char* what);
+// api.cu
+int query_device_impl(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out, cudaStream_t st);
+bool is_pinned_host(const void* p);
+// multi.cu — every entry of the C ABI on a multi-device handle
+int mg_create(const expann_gpu_cfg* cfg, const int32_t* devices, size_t ndev, expann_gpu** out);
+void mg_destroy(expann_gpu* h);
+int mg_add(expann_gpu* h, const float* rows, size_t n, size_t d, bool device_rows, cudaStream_t st);
+int mg_build(expann_gpu* h);
+int mg_build_graph(expann_gpu* h, uint64_t M, uint64_t M0, uint64_t K, float ortho_factor, float ortho_bias, uint64_t prune_overflow, uint64_t seed);
+int mg_load_index(expann_gpu* h, const char* path);
+int mg_query(expann_gpu* h, const float* q, size_t m, size_t k, size_t ef, uint64_t* ids_out, float* dist_out, uint64_t* counts_out);
+int mg_query_device(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out, cudaStream_t st);
+int mg_set_option(expann_gpu* h, const char* name, int64_t value);
+int mg_set_timing(expann_gpu* h, int on);
+int mg_stats(expann_gpu* h, expann_gpu_stats_t* out);
 // scan_f32.cu
 int launch_scan_f32(expann_gpu* h, const float* d_q_padded, size_t m, size_t k, uint64_t* d_keys_out,
                     cudaStream_t st);
@@ -124,6 +149,8 @@ int launch_scan_tc(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t
 bool tc_first_form_fits(const expann_gpu* h); // the chunked first form of K3 keeps the query tile resident
 // quant.cu
 int quant_finalize(expann_gpu* h);
+int quant_minmax(expann_gpu* h, float* mn_out, float* mx_out);
+void quant_set_range(expann_gpu* h, float mn, float mx);
 int launch_quant_scan(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);
 // graph_build.cu
 int graph_build_gpu(expann_gpu* h, uint64_t M, uint64_t M0, uint64_t K, float ortho_factor, float ortho_bias,

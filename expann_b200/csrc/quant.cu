@@ -26,25 +26,41 @@ static int quantize_rows(expann_gpu* h, const float* src, size_t src_stride, siz
 	return EXPANN_OK;
 }
 
+// global min / max over all components of the stored rows (quantizer_ranged_q8::build, src/quantizer.h:206-216)
+int quant_minmax(expann_gpu* h, float* mn_out, float* mx_out) {
+	cudaStream_t st = h->stream;
+	EXPANN_CUDA(h, h->q_mm.ensure(8));
+	const uint32_t init[2] = { f32_orderable(1.17549435e-38f), f32_orderable(3.402823466e+38f) };
+	EXPANN_CUDA(h, cudaMemcpyAsync(h->q_mm.p, init, 8, cudaMemcpyHostToDevice, st));
+	minmax_kernel<<<1184, 256, 0, st>>>(h->base, h->d_pad, (uint32_t)h->d, h->n, h->q_mm.as<float>());
+	EXPANN_CUDA(h, cudaGetLastError());
+	h->stats.aux_launches++;
+	uint32_t mm[2];
+	EXPANN_CUDA(h, cudaMemcpyAsync(mm, h->q_mm.p, 8, cudaMemcpyDeviceToHost, st));
+	EXPANN_CUDA(h, cudaStreamSynchronize(st));
+	*mx_out = f32_from_orderable(mm[0]);
+	*mn_out = f32_from_orderable(mm[1]);
+	return EXPANN_OK;
+}
+// scale_factor / offset from the value range (src/quantizer.h:217-227). A multi-device handle fits ONE range over all
+// shards and hands it to every shard (q_range_fixed), so the codes do not depend on the partitioning.
+void quant_set_range(expann_gpu* h, float mn, float mx) {
+	h->q_scale = 128.0f / (mx - mn);          // :219, q_range() = 128
+	h->q_offset = -h->q_scale * mn - 0.0f;    // :220, q_min = 0
+	h->q_range_fixed = true;
+}
+
 int quant_finalize(expann_gpu* h) {
 	cudaStream_t st = h->stream;
 	h->dc_pad = (h->d + 127) / 128 * 128;
 	EXPANN_CUDA(h, h->q_codes.ensure(h->n * h->dc_pad));
 	EXPANN_CUDA(h, h->q_cnorm.ensure(h->n * 4));
-	if (h->quantizer == 1) {
+	if (h->quantizer == 1 && !h->q_range_fixed) {
 		// quantizer_ranged_q8::build (src/quantizer.h:206-227)
-		EXPANN_CUDA(h, h->q_mm.ensure(8));
-		const uint32_t init[2] = { f32_orderable(1.17549435e-38f), f32_orderable(3.402823466e+38f) };
-		EXPANN_CUDA(h, cudaMemcpyAsync(h->q_mm.p, init, 8, cudaMemcpyHostToDevice, st));
-		minmax_kernel<<<1184, 256, 0, st>>>(h->base, h->d_pad, (uint32_t)h->d, h->n, h->q_mm.as<float>());
-		EXPANN_CUDA(h, cudaGetLastError());
-		h->stats.aux_launches++;
-		uint32_t mm[2];
-		EXPANN_CUDA(h, cudaMemcpyAsync(mm, h->q_mm.p, 8, cudaMemcpyDeviceToHost, st));
-		EXPANN_CUDA(h, cudaStreamSynchronize(st));
-		const float mx = f32_from_orderable(mm[0]), mn = f32_from_orderable(mm[1]);
-		h->q_scale = 128.0f / (mx - mn);          // :219, q_range() = 128
-		h->q_offset = -h->q_scale * mn - 0.0f;    // :220, q_min = 0
+		float mn, mx;
+		if (int rc = quant_minmax(h, &mn, &mx)) return rc;
+		quant_set_range(h, mn, mx);
+		h->q_range_fixed = false; // fitted from this handle's own rows: refit on the next build()
 	}
 	if (int rc = quantize_rows(h, h->base, h->d_pad, h->n, h->q_codes.as<uint8_t>(), h->q_cnorm.as<int32_t>(), st)) return rc;
 	EXPANN_CUDA(h, cudaStreamSynchronize(st));

@@ -27,7 +27,11 @@ class GpuEngine:
     _engine_kind = _lib.ENGINE_BRUTE_FORCE
     _name = "GPU Engine"
 
-    def __init__(self, metric: int = METRIC_L2, device: int = -1, qtile: int = 0, id_offset: int = 0, **kw):
+    def __init__(self, metric: int = METRIC_L2, device: int = -1, qtile: int = 0, id_offset: int = 0, devices=None,
+                 row_groups: int = 0, **kw):
+        """devices: list of CUDA ordinals -> ONE engine over several GPUs of this process (rows sharded by contiguous
+        ranges, per-GPU top-k merged on devices[0]; an ordinal may repeat); row_groups: 0 = one row shard per GPU, R = R
+        row shards each held by len(devices) / R GPUs that split the queries. Results do not depend on either."""
         self._lib = _lib.load()
         cfg = _lib.Cfg()
         cfg.engine = self._engine_kind
@@ -40,11 +44,17 @@ class GpuEngine:
         cfg.ef_search_mult = kw.get("ef_search_mult", 1)
         cfg.use_compression = int(kw.get("use_compression", False))
         cfg.quantizer = int(kw.get("quantizer", 0))
+        cfg.row_groups = int(row_groups)
         h = C.c_void_p()
-        rc = self._lib.expann_gpu_create(C.byref(cfg), C.byref(h))
+        if devices is not None:
+            devs = (C.c_int32 * len(devices))(*[int(x) for x in devices])
+            rc = self._lib.expann_gpu_create_multi(C.byref(cfg), devs, len(devices), C.byref(h))
+        else:
+            rc = self._lib.expann_gpu_create(C.byref(cfg), C.byref(h))
         if rc != 0:
             raise ExpannError(rc, self._lib.expann_gpu_last_error(None).decode())
         self._h = h
+        self.devices = list(devices) if devices is not None else None
         self.metric = metric
         self.qtile = qtile
         self.id_offset = id_offset
@@ -158,7 +168,7 @@ class GpuEngine:
     def stats(self) -> dict:
         st = _lib.Stats()
         self._check(self._lib.expann_gpu_stats(self._h, C.byref(st)))
-        return {f: getattr(st, f) for f, _ in st._fields_ if f != "reserved"}
+        return {f: getattr(st, f) for f, _ in st._fields_}
 
 
 class BruteForceEngine(GpuEngine):

@@ -7,7 +7,7 @@
  * binds; the *_device entry points take HBM-resident buffers and a CUDA stream for
  * callers that already own device memory (bench.py / the multi-GPU merge).
  *
- * One handle = one engine instance on one GPU = one host thread at a time (the reference engines are not
+ * One handle = one engine instance on one GPU (or, with a device list, on several GPUs of this process) = one host thread at a time (the reference engines are not
  * re-entrant either: src/antitopo_engine.h:208-209). Distinct handles are independent.
  */
 #ifndef EXPANN_GPU_H
@@ -39,7 +39,13 @@ typedef struct expann_gpu_cfg {
 	int32_t use_compression; /* src/antitopo_engine.h:197-199: quantizer_simple<uint8_t> codes */
 	int32_t quantizer;       /* QUANT_SCAN: 0 = quantizer_simple<uint8_t> (src/quantizer.h:125-150),
 	                            1 = quantizer_ranged_q8 (src/quantizer.h:186-238) */
-	int32_t reserved[6];
+	/* device list: n_devices > 1 puts GPUs device .. device + n_devices - 1 behind this ONE handle; the
+	   base set is sharded by contiguous row ranges, every call fans out and the per-GPU top-k lists are merged on the
+	   first GPU. expann_gpu_create_multi takes an explicit list instead. row_groups: 0 = one row shard per GPU; R > 0 = R
+	   row shards, each held by n_devices / R GPUs that split the queries of a call between them (option
+	   "mgpu_row_groups"). The result does not depend on either. */
+	int32_t n_devices, row_groups;
+	int32_t reserved[4];
 } expann_gpu_cfg;
 
 typedef struct expann_gpu_stats {
@@ -54,11 +60,22 @@ typedef struct expann_gpu_stats {
 	                                             3 one bf16 term per value (real-valued data; slack 2^-6 |q| max|x|), 2 two-term bf16
 	                                             split (3x the flops, slack 2^-14 |q| max|x|). build() picks 1 or 3; a batch of
 	                                             format 3 that had to be redone moves the handle to 2 */
-	uint64_t reserved[3];
+	uint64_t peer_bytes;                      /* multi-device handle: bytes moved between GPUs so far (query blocks out over
+	                                             NVLink, [m][k] key lists stored into the first GPU's gather buffer) */
+	uint64_t query_groups, row_groups;        /* multi-device handle: decomposition n_devices = query_groups x row_groups (else 0) */
 } expann_gpu_stats_t;
 
 /* ann_engine() / Engine(config) constructor — src/ann_engine.h:17, src/bench_runner.h:33 */
 int expann_gpu_create(const expann_gpu_cfg* cfg, expann_gpu_t** out);
+/* the same engine over an explicit list of CUDA ordinals (cfg->device / n_devices are ignored). Every other entry point
+ * works on the handle unchanged: add / build shard the rows, query / query_device fan out over the GPUs (device pointers
+ * and the stream of query_device belong to devices[0]) and return the merged result, stats() sums the launches and
+ * reports the slowest GPU's kernel time. An ordinal may repeat (several shards on one GPU). Multi-device handles are
+ * immutable after build(): add() then fails with EXPANN_ERR_STATE; save_index / set_graph are single-device only;
+ * load_index replicates the graph on every GPU and splits the queries. stats() of a multi-device handle: hot_time_ns is
+ * the slowest GPU's. No host thread per GPU, no NCCL: cross-GPU ordering is by CUDA events, the [m][k] key lists are
+ * stored by each GPU's last kernel straight into the first GPU's memory over NVLink. */
+int expann_gpu_create_multi(const expann_gpu_cfg* cfg, const int32_t* devices, size_t n_devices, expann_gpu_t** out);
 void expann_gpu_destroy(expann_gpu_t* h);
 /* last error text of this handle (or of the failed create when h == NULL); never NULL */
 const char* expann_gpu_last_error(const expann_gpu_t* h);
@@ -134,7 +151,10 @@ int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
  * clusters of two CTAs for batches > 128, default 1), "tc_astream" (0 off | 1 when the query tile cannot stay resident
  * | 2 always), "tc_boot" (seeding launch: 0 off | 1 one-term formats and >= 8192 queries | 2 always), "tc_v1" (force the
  * chunked first form), "tc_real" (real-valued rows, before build(): 1 (default) one bf16 term per value, falling back to the
- * two-term split when a batch had to be redone | 0 the split from the start). Unknown names: EXPANN_ERR_ARG. */
+ * two-term split when a batch had to be redone | 0 the split from the start).
+ * Multi-device handles: "mgpu_row_groups" (0 (default) one row shard per GPU | R row shards, each on n_devices / R GPUs that
+ * split the queries of a call; before build()); every other knob is applied to each GPU's engine.
+ * Unknown names: EXPANN_ERR_ARG. */
 int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value);
 /* library build info: "sm_100a;..." */
 const char* expann_gpu_version(void);
