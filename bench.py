@@ -4,16 +4,19 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c4|c5]
 
 A "step" is one pass of the hot path over one batch of m synthetic queries against the HBM-resident base set.
-  value : QPS, device-resident queries in, merged 64-bit (dist,id) keys out (CUDA events, max over ranks)
-  e2e   : QPS through the reference-facing host-buffer call (expann_gpu_query at N=1), H2D of the queries and
-          D2H of ids inside the timed region
-  roofline : algorithmic bytes of the dominant kernel / its CUDA-event time (events recorded inside the library
-          around every scan launch on the launching stream)
+  value : QPS, device-resident queries in, merged 64-bit (dist,id) keys out (CUDA events on the launching stream)
+  e2e   : QPS through the reference-facing host-buffer call (expann_gpu_query), H2D of the queries and D2H of the
+          results inside the timed region; page-locked caller buffers (headline) and pageable ones (`pageable_value`)
+  roofline : the dominant kernel of the step (algorithmic flops or bytes / CUDA-event time recorded inside the library on
+          the launching stream) plus, as sub-objects the driver keeps whole: `hbm_scan` (the HBM-bound one-query-tile
+          passes of the fp32 scan), `graph` (BASELINE config 3), `c4` / `c5` (the other named configs, bounded legs)
   cpu_baseline : the UNMODIFIED reference brute_force_engine (oracle/_ref) — or the C restatement when that
           build is not usable on this host — timed on a bounded query sample with all host threads
-N > 1 (torchrun): the base set is sharded by contiguous row ranges (strong scaling: the same 1M-row base over
-N GPUs), every rank scans its shard for all queries, the per-rank [m][k] key lists are all-gathered over NCCL
-and merged by K7 on every rank.
+N > 1: ONE process drives all N GPUs through ONE multi-device handle (expann_gpu_create_multi, csrc/multi.cu): the base
+set is sharded by contiguous row ranges inside the library, the queries fan out over NVLink, every GPU's last kernel
+stores its [m][k] keys into GPU 0's gather buffer and K7 merges there — the path a reference-side caller gets. Under the
+driver's torchrun launch rank 0 owns the handle; the other ranks only join the NCCL barriers that bracket the timed
+region (they hold no data and launch nothing), so `value` is the whole job's throughput.
 """
 from __future__ import annotations
 
@@ -37,21 +40,23 @@ WORKLOADS = {
     "c4": ("deep", None, 10_000_000, 10_000, 96, 10, "l2", "Deep-shape synthetic 10Mx96 fp32, 10k queries, sharded brute-force L2 top-10"),
     "c5": ("gist", None, 1_000_000, 1_000, 960, 10, "ip", "GIST-shape synthetic 1Mx960 fp32, 1k queries, brute-force inner-product top-10"),
 }
+T_START = time.perf_counter()
 
 
 def ncu_traffic(key):
     """DRAM bytes (read + write) per launch of a kernel from the committed ncu --set full capture of the same kernel on
-    the C2 shape (profiles/r1_ncu_summary.json); None when there is no capture"""
-    try:
-        j = json.load(open(os.path.join(ROOT, "profiles", "r1_ncu_summary.json")))
-        for name, d in j.items():
-            if name.startswith(key):
-                unit = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
-                r, w = d["dram__bytes_read.sum"], d["dram__bytes_write.sum"]
-                return int(float(r[0]) * unit[r[1]] + float(w[0]) * unit[w[1]])
-    except Exception:  # noqa: BLE001
-        pass
-    return None
+    the C2 shape (profiles/*_ncu_summary.json, newest round first); (None, None) when there is no capture"""
+    for name in ("r2_ncu_summary.json", "r1_ncu_summary.json"):
+        try:
+            j = json.load(open(os.path.join(ROOT, "profiles", name)))
+            for kname, d in j.items():
+                if kname.startswith(key):
+                    unit = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
+                    r, w = d["dram__bytes_read.sum"], d["dram__bytes_write.sum"]
+                    return int(float(r[0]) * unit[r[1]] + float(w[0]) * unit[w[1]]), "committed ncu --set full capture, profiles/" + name
+        except Exception:  # noqa: BLE001
+            pass
+    return None, None
 
 
 def tensor_peaks():
@@ -86,18 +91,22 @@ class ClockSampler:
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
              "clocks_event_reasons.sw_power_cap")
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100",
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "50",
                                           "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
+            time.sleep(0.3)   # let the first samples arrive before the timed region starts
         except Exception:  # noqa: BLE001
             self.proc = None
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
 
-    def stop(self):
+    def window(self, t0, t1):
+        return [r for t, r in self.rows if t0 <= t <= t1 + 0.06]
+
+    def stop(self, t0=None, t1=None):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -106,12 +115,14 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except Exception:  # noqa: BLE001
             self.proc.kill()
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        rows = self.window(t0, t1) if t0 is not None else [r for _, r in self.rows]
+        sm = [float(r[0]) for r in rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        pw = [float(r[2]) for r in rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        reasons = sorted({names[i] for r in rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "power_w_max": max(pw) if pw else None}
 
 
 def cpu_reference_qps(base, q, k, metric, budget_s=15.0):
@@ -124,7 +135,6 @@ def cpu_reference_qps(base, q, k, metric, budget_s=15.0):
     if metric == "l2":
         try:
             ref = pyoracle.Reference(128 if d == 128 else None)
-            t0 = time.perf_counter()
             eng = ref.bf(base)  # store_vector x n + build (not timed as query time)
             kind = "reference"
         except Exception:  # noqa: BLE001
@@ -153,11 +163,11 @@ def scan_hbm_leg(eng, torch, dq, k, n_rows, d, stream, peak, peak_src, steps):
     """HBM-bound regime of the path: ONE pass of the streaming fp32 scan (K1) over the base for a tile of 1, 4 and 8
     queries (brute_force_engine::_query_k, src/brute_force_engine.h:29-46, is one such pass per query). L2 is
     NOT flushed: the input of a pass (512 MB at C2) is 4x the L2 capacity, so back-to-back passes stream it from DRAM
-    again. The headline roofline object is the one-query pass (the reference's own call shape); `passes` lists all three."""
+    again. The headline numbers of this object are the one-query pass (the reference's own call shape)."""
     keys = torch.empty((8, k), dtype=torch.int64, device=dq.device)
     eng.set_option("tc", 0)   # this leg measures K1 itself (by default batches >= 5 take the tensor-core path)
     alg = n_rows * d * 4
-    reps = max(20, steps)
+    reps = max(20, min(steps, 200))
     passes = []
     for mq in (1, 4, 8):
         for _ in range(3):
@@ -180,14 +190,12 @@ def scan_hbm_leg(eng, torch, dq, k, n_rows, d, stream, peak, peak_src, steps):
                        "frac": alg / (hot_ms * 1e-3) / 1e9 / peak, "frac_whole_call": alg / (call_ms * 1e-3) / 1e9 / peak})
     eng.set_option("tc", 1)
     p1 = passes[0]
-    return {"workload": "one pass of the fp32 scan (+ fused split merge) over the %dx%d base for 1 / 4 / 8 queries; "
-                        "base is 4x L2, passes back to back, no flush" % (n_rows, d),
-            "passes": passes,
-            "roofline": {"bound": "hbm", "kernel": "scan_topk_f32_kernel (1 query per pass)", "achieved": p1["achieved_GBs"],
-                         "peak": peak, "unit": "GB/s", "frac": p1["frac"],
-                         "traffic": ncu_traffic("scan_topk_f32_kernel<1") if (n_rows == 1_000_000 and d == 128) else None,
-                         "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": int(alg), "kernel_ms_per_launch": p1["kernel_ms"]}}
+    traffic, tsrc = ncu_traffic("scan_topk_f32_kernel<1") if (n_rows == 1_000_000 and d == 128) else (None, None)
+    return {"bound": "hbm", "kernel": "scan_topk_f32_kernel (one pass of the fp32 scan + fused split merge, 1 query per pass)",
+            "workload": "one pass over the %dx%d base for 1 / 4 / 8 queries; base is 4x L2, passes back to back, no flush" % (n_rows, d),
+            "achieved": p1["achieved_GBs"], "peak": peak, "unit": "GB/s", "frac": p1["frac"], "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": int(alg), "kernel_ms_per_launch": p1["kernel_ms"],
+            "traffic": traffic, "traffic_source": tsrc, "passes": passes}
 
 
 _REAL_STDOUT = None
@@ -212,12 +220,131 @@ def emit(obj):
         os.write(_REAL_STDOUT, line)
 
 
+def tensor_roofline(st0, st1, m, n_rows_per_gpu, d, G, gq, workload, hot_ms):
+    """roofline object of the K3 filter: issued flops 2*m*n*kd per GPU against the bf16 tensor peak; `useful` counts
+    2*m*n*d only (the two-term split issues 3x that)"""
+    seg = (d + 63) // 64 * 64
+    mode = int(st1["tc_mode"])
+    kd = 3 * seg if mode == 2 else seg
+    m_gpu = (m + gq - 1) // gq
+    flops = 2.0 * m_gpu * n_rows_per_gpu * kd
+    useful = 2.0 * m_gpu * n_rows_per_gpu * d
+    achieved = flops / (hot_ms * 1e-3) / 1e12
+    tpeak, tpeak_sus, tsrc = tensor_peaks()
+    qt = int(st1["last_qtile"])
+    kname = "tc_filter_pair_kernel" if qt == 256 else "tc_filter2_kernel"
+    traffic, trsrc = ncu_traffic(kname) if (workload == "c2" and G == 1 and m == 10000) else (None, None)
+    return {"bound": "tensor", "kernel": kname + (" (tcgen05.mma.cta_group::2 bf16, fp32 accumulate in TMEM)" if qt == 256 else
+                                                  " (tcgen05.mma bf16, fp32 accumulate in TMEM)"),
+            "achieved": achieved, "peak": tpeak, "unit": "TFLOP/s", "frac": achieved / tpeak, "frac_of_sustained_peak": achieved / tpeak_sus,
+            "useful_flops_per_launch": useful, "achieved_useful": useful / (hot_ms * 1e-3) / 1e12, "frac_useful": useful / (hot_ms * 1e-3) / 1e12 / tpeak,
+            "traffic": traffic, "traffic_source": trsrc, "traffic_unit": "DRAM bytes per launch (read + write)",
+            "peak_source": tsrc, "algorithmic_flops_per_launch": flops, "kernel_ms_per_launch": hot_ms,
+            "tc_mode": {1: "bf16-exact (integer rows)", 2: "two-term bf16 split (3x the flops)", 3: "one bf16 term per value (real-valued rows)"}.get(mode, str(mode)),
+            "kd": kd, "per_gpu": G > 1,
+            "note": "flops = 2*m*n*kd of the candidate filter on ONE GPU's shard (the slowest GPU's kernel time when several run side by "
+                    "side); useful = 2*m*n*d; survivors (about k per query) are re-ranked in fp32 by K4. peak = cuBLAS bf16 burst figure; "
+                    "frac_of_sustained_peak uses the seconds-long figure"}
+
+
+def timed_steps(torch, dist, world, dev, fn, steps):
+    """K steps bracketed by barrier + synchronize on both sides, CUDA events on the launching stream, max over ranks"""
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    barrier()
+    t1 = time.perf_counter()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item()), t0, t1
+
+
+def extra_leg(expann_b200, torch, name, G, budget_left, steps=5):
+    """bounded, non-headline legs of the other named configurations through the same handle type (one handle over G GPUs):
+    c4 = Deep-shape 10M x 96 exact brute force; c5 = GIST-shape 1M x 960 inner product, ranged-q8 code scan + fp32
+    rerank of 100 and the exact scan beside it. Returns a roofline-style dict with QPS."""
+    from expann_b200 import datasets
+    gen, variant, n, m, d, k, metric, desc = WORKLOADS[name]
+    t0 = time.perf_counter()
+    base, q = datasets.make(gen, n, m, d, variant=variant or "lowrank")
+    gen_s = time.perf_counter() - t0
+    devs = list(range(G)) if G > 1 else None
+    out = {"workload": desc, "n": n, "m": m, "d": d, "k": k, "metric": metric, "gpus": G, "datagen_s": gen_s}
+    dev0 = torch.device("cuda", 0)
+    dq = torch.from_numpy(q).to(dev0)
+    keys = torch.empty((m, k), dtype=torch.int64, device=dev0)
+    stream = torch.cuda.current_stream(dev0).cuda_stream
+
+    def run(eng, label):
+        for _ in range(3):
+            eng.query_device(dq.data_ptr(), m, k, keys.data_ptr(), stream)
+        torch.cuda.synchronize()
+        s0 = eng.stats()
+        eng.set_timing(True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            eng.query_device(dq.data_ptr(), m, k, keys.data_ptr(), stream)
+        e1.record()
+        torch.cuda.synchronize()
+        s1 = eng.stats()
+        eng.set_timing(False)
+        ms = e0.elapsed_time(e1) / steps
+        hot = (s1["hot_time_ns"] - s0["hot_time_ns"]) / 1e6 / max(1, s1["hot_timed_launches"] - s0["hot_timed_launches"])
+        t1 = time.perf_counter()
+        ids = eng.query_k_batch(q, k)[0]
+        e2e_ms = (time.perf_counter() - t1) * 1e3
+        row = {"qps": m / ms * 1e3, "ms_per_step": ms, "kernel_ms": hot, "e2e_qps_pageable": m / e2e_ms * 1e3,
+               "tc_fallbacks": int(s1["tc_fallbacks"]), "row_groups": int(s1["row_groups"]) or 1, "query_groups": int(s1["query_groups"]) or 1}
+        out[label] = row
+        return ids, s0, s1, hot
+
+    mt = 1 if metric == "ip" else 0
+    if name == "c4":
+        eng = expann_b200.BruteForceEngine(metric=mt, devices=devs)
+        tb = time.perf_counter()
+        eng.store_many_vectors(base)
+        eng.build()
+        out["build_s"] = time.perf_counter() - tb
+        ids, s0, s1, hot = run(eng, "exact_scan")
+        gr = out["exact_scan"]["row_groups"]
+        out["exact_scan"]["roofline"] = tensor_roofline(s0, s1, m, (n + gr - 1) // gr, d, G, out["exact_scan"]["query_groups"], name, hot)
+        eng.close()
+    else:
+        ex = expann_b200.BruteForceEngine(metric=mt, devices=devs)
+        ex.store_many_vectors(base)
+        ex.build()
+        eids, s0, s1, hot = run(ex, "exact_scan")
+        gr = out["exact_scan"]["row_groups"]
+        out["exact_scan"]["roofline"] = tensor_roofline(s0, s1, m, (n + gr - 1) // gr, d, G, out["exact_scan"]["query_groups"], name, hot)
+        ex.close()
+        if time.perf_counter() - T_START < budget_left:
+            qe = expann_b200.QuantScanEngine(quantizer=1, kprime=100, metric=mt, devices=devs)
+            qe.store_many_vectors(base)
+            qe.build()
+            qids, s0, s1, hot = run(qe, "code_scan")
+            hit = sum(len(set(a.tolist()) & set(b.tolist())) for a, b in zip(qids, eids))
+            out["code_scan"]["recall_at_k_vs_exact"] = hit / float(m * k)
+            out["code_scan"]["path"] = "quantizer_ranged_q8 codes (src/quantizer.h:186-238), k' = 100 survivors re-ranked in fp32"
+            qe.close()
+    return out
+
+
 def main():
     protect_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--ef", type=int, default=40, help="beam width of --engine graph")
@@ -225,19 +352,22 @@ def main():
                     help="bf: exact brute force (K1/K3+K4); quant: quantizer compressed scan + fp32 rerank (K6+K4); auto: quant for c5")
     ap.add_argument("--qtile", type=int, default=0)
     ap.add_argument("--m", type=int, default=0, help="override the query count")
+    ap.add_argument("--row-groups", type=int, default=0, help="N > 1: row shards (0 = one per GPU); N / row_groups GPUs split the queries")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--no-extras", action="store_true", help="skip the extra legs (graph engine sweep, BASELINE config 3)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the extra legs (hbm scan, graph engine sweep, c4 / c5)")
+    ap.add_argument("--extras-budget-s", type=float, default=300.0, help="extra legs start only while the run is younger than this")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    G = max(args.gpus, world)
     gen, variant, n, m, d, k, metric, desc = WORKLOADS[args.workload]
     if args.engine == "graph":
         # graph engines need data with neighbourhood structure: the low-rank SIFT-shape variant of SURVEY 8(d) (C3), not iid
         if gen == "sift":
             variant = "lowrank"
-        desc = desc.replace("(u8-valued iid)", "(u8-valued, low-rank)").replace("brute-force", "graph engine (sharded),").replace("exact ", "")
+        desc = desc.replace("(u8-valued iid)", "(u8-valued, low-rank)").replace("brute-force", "graph engine (one sub-graph per row shard),").replace("exact ", "")
     if args.m:
         m = args.m
     from expann_b200 import datasets
@@ -247,7 +377,7 @@ def main():
             return 0
         base, q = datasets.make(gen, n, m, d, variant=variant or "lowrank")
         # each step = a bounded sample of the workload's queries on the full base
-        budget = max(4.0, 120.0 / max(1, args.steps + args.warmup))
+        budget = max(2.0, 120.0 / max(1, args.steps + args.warmup))
         vals = []
         info = None
         for i in range(args.warmup + args.steps):
@@ -255,11 +385,13 @@ def main():
             if i >= args.warmup:
                 vals.append(qps)
             info = (cores, kind, sample)
+            if time.perf_counter() - T_START > 240 and len(vals) >= 3:   # bounded: the arm must end within minutes whatever K
+                break
         v = float(np.mean(vals))
         out = {"impl": "reference", "metric": "QPS (exact brute-force top-%d)" % k, "value": v, "unit": "queries/s",
                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * m / v,
                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-               "config": {"workload": desc, "n": n, "m": m, "d": d, "k": k, "metric": metric},
+               "config": {"workload": desc, "n": n, "m": m, "d": d, "k": k, "metric": metric, "steps_measured": len(vals)},
                "cpu_baseline": {"value": v, "unit": "queries/s", "cores": info[0], "kind": info[1], "sample": info[2]},
                "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         emit(out)
@@ -276,229 +408,249 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
 
+    if rank != 0:
+        # ONE process (rank 0) drives all N GPUs through one multi-device handle; this rank only joins the barriers and the
+        # max-over-ranks reductions that bracket rank 0's timed regions, in the same order (headline, then e2e)
+        for _ in range(2):
+            dist.barrier(); torch.cuda.synchronize()
+            dist.barrier(); torch.cuda.synchronize()
+            z = torch.zeros(1, device=dev)
+            dist.all_reduce(z, op=dist.ReduceOp.MAX)
+        dist.barrier()
+        dist.destroy_process_group()
+        return 0
+
+    if G > torch.cuda.device_count():
+        raise SystemExit(f"--gpus {G} but only {torch.cuda.device_count()} visible")
+    devs = list(range(G)) if G > 1 else None
     base, q = datasets.make(gen, n, m, d, variant=variant or "lowrank")
-    from expann_b200 import sharding
-    lo, hi = sharding.shard_range(n, world, rank)
     use_quant = args.engine == "quant" or (args.engine == "auto" and args.workload == "c5")
     use_graph = args.engine == "graph"
+    mt = 1 if metric == "ip" else 0
     truth_ids = None
+    graph_build_s = None
     if use_graph:
-        # BASELINE config 4's graph leg: every rank builds a graph over ITS rows (GPU build, reference prune rule) and
-        # searches it for all queries; per-GPU top-k lists meet through the same NCCL gather + K7 merge as the scans.
-        # Ground truth for recall@k: the sharded exact scan of the same rows (not timed).
-        bf = expann_b200.BruteForceEngine(metric=1 if metric == "ip" else 0, device=local_rank, id_offset=lo)
-        bf.store_many_vectors(base[lo:hi]); bf.build()
-        tq = torch.from_numpy(q).to(dev)
-        tk_local = torch.empty((m, k), dtype=torch.int64, device=dev)
-        bf.query_device(tq.data_ptr(), m, k, tk_local.data_ptr(), torch.cuda.current_stream().cuda_stream)
-        if world > 1:
-            g = sharding.gather_keys(tk_local, world)
-            tk_final = torch.empty_like(tk_local)
-            bf.merge_device(g.data_ptr(), m, world, k, k, m * k, k, tk_final.data_ptr(), torch.cuda.current_stream().cuda_stream)
-        else:
-            tk_final = tk_local
-        tids = torch.empty((m, k), dtype=torch.int64, device=dev)
-        bf.decode_device(tk_final.data_ptr(), m, k, tids.data_ptr(), 0, 0, torch.cuda.current_stream().cuda_stream)
-        torch.cuda.synchronize()
-        truth_ids = tids.cpu().numpy()
+        # the graph engines shard like the scans: one GPU-built sub-graph per row shard, every query searches every shard
+        # with the same beam width, K7 merges. Ground truth for recall@k: the exact scan of the same handle type (not timed).
+        bf = expann_b200.BruteForceEngine(metric=mt, devices=devs)
+        bf.store_many_vectors(base); bf.build()
+        truth_ids = bf.query_k_batch(q, k)[0]
         bf.close()
-        del bf, tq, tk_local, tk_final, tids
-        eng = expann_b200.GraphEngine(metric=1 if metric == "ip" else 0, device=local_rank, id_offset=lo)
-        eng.store_many_vectors(base[lo:hi])
+        eng = expann_b200.GraphEngine(metric=mt, devices=devs)
+        eng.store_many_vectors(base)
         t_b = time.perf_counter()
         eng.build_graph(M=16, M0=32, K=64)
         graph_build_s = time.perf_counter() - t_b
         eng.set_ef_search(args.ef)
-    elif use_quant:   # BASELINE config 5: quantizer_ranged_q8 codes (src/quantizer.h:186-238) scanned with K6, k' = 100 survivors re-ranked in fp32
-        eng = expann_b200.QuantScanEngine(quantizer=1, kprime=100, metric=1 if metric == "ip" else 0, device=local_rank,
-                                          qtile=args.qtile, id_offset=lo)
+    elif use_quant:   # BASELINE config 5: quantizer_ranged_q8 codes (src/quantizer.h:186-238) scanned, k' = 100 survivors re-ranked in fp32
+        eng = expann_b200.QuantScanEngine(quantizer=1, kprime=100, metric=mt, qtile=args.qtile, devices=devs)
     else:
-        eng = expann_b200.BruteForceEngine(metric=1 if metric == "ip" else 0, device=local_rank, qtile=args.qtile, id_offset=lo)
+        eng = expann_b200.BruteForceEngine(metric=mt, qtile=args.qtile, devices=devs, row_groups=args.row_groups)
     if not use_graph:
-        eng.store_many_vectors(base[lo:hi])
+        eng.store_many_vectors(base)
     eng.build()
 
     stream = torch.cuda.current_stream().cuda_stream
     dq = torch.from_numpy(q).to(dev)
     hq = torch.from_numpy(q).pin_memory()
-    local_keys = torch.empty((m, k), dtype=torch.int64, device=dev)
     final_keys = torch.empty((m, k), dtype=torch.int64, device=dev)
     ids_dev = torch.empty((m, k), dtype=torch.int64, device=dev)
-    ids_host = torch.empty((m, k), dtype=torch.int64).pin_memory()
-    dq_e2e = torch.empty_like(dq)
     hq_np = hq.numpy()   # a view of the page-locked tensor
     out_pinned = (torch.empty((m, k), dtype=torch.int64).pin_memory().numpy().view(np.uint64),
                   torch.empty((m, k), dtype=torch.float32).pin_memory().numpy(),
                   torch.empty((m,), dtype=torch.int64).pin_memory().numpy().view(np.uint64))
+    out_pageable = (np.empty((m, k), np.uint64), np.empty((m, k), np.float32), np.empty((m,), np.uint64))
+    q_pageable = np.array(q, copy=True)
 
-    def step_device(qptr):
-        if world == 1:
-            eng.query_device(qptr, m, k, final_keys.data_ptr(), stream)
-        else:
-            eng.query_device(qptr, m, k, local_keys.data_ptr(), stream)
-            gathered = sharding.gather_keys(local_keys, world)   # NCCL all-gather -> [world][m][k]
-            eng.merge_device(gathered.data_ptr(), m, world, k, k, m * k, k, final_keys.data_ptr(), stream)
+    def step_device():
+        eng.query_device(dq.data_ptr(), m, k, final_keys.data_ptr(), stream)
 
     def step_e2e():
-        if world == 1:
-            # the C-ABI host call: H2D of the pinned queries, scan, decode, D2H into pinned result buffers
-            return eng.query_k_batch(hq_np, k, out=out_pinned)[0]
-        dq_e2e.copy_(hq, non_blocking=True)
-        step_device(dq_e2e.data_ptr())
-        eng.decode_device(final_keys.data_ptr(), m, k, ids_dev.data_ptr(), 0, 0, stream)
-        ids_host.copy_(ids_dev, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return ids_host
+        # the C-ABI host call: H2D of the pinned queries, scan (all GPUs), merge, decode, D2H into pinned result buffers
+        return eng.query_k_batch(hq_np, k, out=out_pinned)[0]
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, steps):
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
-            fn()
-        e1.record()
-        barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item())
+    def step_e2e_pageable():
+        return eng.query_k_batch(q_pageable, k, out=out_pageable)[0]
 
     for _ in range(args.warmup):
-        step_device(dq.data_ptr())
-    barrier()
+        step_device()
+    torch.cuda.synchronize()
     st0 = eng.stats()
     eng.set_timing(True)
     sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
-    ms = timed(lambda: step_device(dq.data_ptr()), args.steps)
-    clocks = sampler.stop() if rank == 0 else None
+    sampler.start()
+    ms, tw0, tw1 = timed_steps(torch, dist, world, dev, step_device, args.steps)
     st1 = eng.stats()
     eng.set_timing(False)
+    # sustained region: the same step for >= 0.5 s, so that the clock sampler sees the loaded clock and the seconds-long tensor
+    # peak is the right denominator; the headline value stays the K-step region above
+    sus = None
+    if ms < 400.0 and not args.no_extras:
+        reps = int(min(2000, max(args.steps, 500.0 / max(ms / args.steps, 1e-3))))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            step_device()
+        e1.record()
+        torch.cuda.synchronize()
+        tw1 = time.perf_counter()
+        sus = {"steps": reps, "ms_per_step": e0.elapsed_time(e1) / reps, "qps": m * reps / (e0.elapsed_time(e1) * 1e-3)}
+    clocks = sampler.stop(tw0, tw1)
     # e2e leg (host buffers): its own warm-up, then K timed steps by wall clock bracketed by barriers
     for _ in range(max(1, min(args.warmup, 2))):
         step_e2e()
-    barrier()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    p0 = eng.stats()["peer_bytes"]
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step_e2e()
-    barrier()
-    e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    peer_per_step = (eng.stats()["peer_bytes"] - p0) / max(1, args.steps)
     if world > 1:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_s = float(e2e_s.item())
+        dist.barrier()
+        t = torch.tensor([e2e_s], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    step_e2e_pageable()
+    nrep = max(3, min(args.steps, 20))
+    t0 = time.perf_counter()
+    for _ in range(nrep):
+        step_e2e_pageable()
+    e2e_pageable_s = (time.perf_counter() - t0) / nrep
 
-    # correctness spot check on rank 0 (not timed): the keys decode to sorted unique ids
+    # correctness (not timed): keys decode to the ids of the host call; N > 1: ids of 256 queries equal a ONE-GPU scan of the whole base
     eng.decode_device(final_keys.data_ptr(), m, k, ids_dev.data_ptr(), 0, 0, stream)
     torch.cuda.synchronize()
-    got = ids_dev[:4].cpu().numpy()
+    got = ids_dev.cpu().numpy().view(np.uint64)
+    check = {"first_ids": [int(x) for x in got[0]], "device_path_equals_host_call": bool(np.array_equal(got, step_e2e()))}
+    if G > 1 and not use_graph:
+        msub = min(m, 256)
+        one = (expann_b200.QuantScanEngine(quantizer=1, kprime=100, metric=mt, device=0) if use_quant
+               else expann_b200.BruteForceEngine(metric=mt, device=0))
+        one.store_many_vectors(base); one.build()
+        w = one.query_k_batch(q[:msub], k)
+        one.close()
+        g = eng.query_k_batch(q[:msub], k)
+        same = bool(np.array_equal(w[0], g[0]) and np.array_equal(w[1], g[1]))
+        check["ids_equal_one_gpu_scan"] = {"queries": msub, "equal": same}
+        assert same, "multi-GPU result differs from the one-GPU scan of the same rows"
 
-    if rank == 0:
-        peak, peak_src = peaks()
-        launches = sum(st1[x] - st0[x] for x in ("scan_launches", "merge_launches", "graph_launches", "aux_launches", "tc_launches"))
-        hot_ms = (st1["hot_time_ns"] - st0["hot_time_ns"]) / 1e6 / max(1, st1["hot_timed_launches"] - st0["hot_timed_launches"])
-        qt = st1["last_qtile"]
-        used_tc = st1["tc_launches"] > st0["tc_launches"] and st1["tc_fallbacks"] == st0["tc_fallbacks"]
-        if use_graph:
-            dcq = (st1["distcomps"] - st0["distcomps"]) / float(args.steps * m)   # this rank's shard
-            alg_bytes = dcq * d * 4 * m
-            achieved = alg_bytes / (hot_ms * 1e-3) / 1e9
-            roof = {"bound": "hbm", "kernel": "graph_search_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": int(alg_bytes), "kernel_ms_per_launch": hot_ms,
-                    "distcomps_per_query_per_gpu": dcq,
-                    "note": "algorithmic bytes = distance evaluations x d x 4 on rank 0's shard (random row gathers); latency-bound"}
-        elif used_tc:
-            # K3: bf16 tcgen05 GEMM of a'(q,x) over the whole shard; flops = 2 * m * n_shard * kd (kd = operand row length:
-            # d rounded up to 64 in the bf16-exact mode, 3x that in the two-term split mode)
-            seg = (d + 63) // 64 * 64
-            kd = seg if st1["tc_mode"] == 1 else 3 * seg
-            flops = 2.0 * m * (hi - lo) * kd
-            achieved = flops / (hot_ms * 1e-3) / 1e12
-            tpeak, tpeak_sus, tsrc = tensor_peaks()
-            kname = "tc_filter_pair_kernel" if qt == 256 else "tc_filter2_kernel"
-            roof = {"bound": "tensor", "kernel": kname + (" (tcgen05.mma.cta_group::2 bf16, fp32 accumulate in TMEM)" if qt == 256 else
-                                                          " (tcgen05.mma bf16, fp32 accumulate in TMEM)"), "achieved": achieved,
-                    "peak": tpeak, "unit": "TFLOP/s", "frac": achieved / tpeak, "frac_of_sustained_peak": achieved / tpeak_sus,
-                    "traffic": ncu_traffic(kname) if (args.workload == "c2" and world == 1 and m == 10000) else None,
-                    "traffic_unit": "DRAM bytes per launch (ncu --set full, profiles/r1_ncu_summary.json)",
-                    "peak_source": tsrc, "algorithmic_flops_per_launch": flops, "kernel_ms_per_launch": hot_ms,
-                    "tc_mode": "bf16-exact" if st1["tc_mode"] == 1 else "two-term bf16 split", "kd": kd,
-                    "note": "flops = 2*m*n*kd of the candidate filter; survivors (about k per query) are re-ranked in fp32 by K4. "
-                            "peak = cuBLAS bf16 burst figure; frac_of_sustained_peak uses the seconds-long figure"}
-        else:
-            passes = (m + qt - 1) // qt
-            alg_bytes = passes * (hi - lo) * d * (1 if use_quant else 4)
-            achieved = alg_bytes / (hot_ms * 1e-3) / 1e9
-            roof = {"bound": "hbm", "kernel": "scan_topk_u8_kernel" if use_quant else "scan_topk_f32_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": int(alg_bytes), "kernel_ms_per_launch": hot_ms,
-                    "note": "algorithmic bytes = ceil(m/qtile) passes x shard bytes (SURVEY 8(d)); CTAs of one "
-                            "wave share rows through L2, so DRAM traffic is lower than this figure"}
-        out = {"metric": ("QPS (graph engine, ef=%d, top-%d)" % (args.ef, k)) if use_graph else "QPS (exact brute-force top-%d)" % k, "value": m * args.steps / (ms * 1e-3), "unit": "queries/s",
-               "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-               "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-               "config": {"workload": desc, "n": n, "m": m, "d": d, "k": k, "metric": metric, "qtile": int(qt),
-                          "path": "K5 graph beam search (one GPU-built graph per shard, M0=32)" if use_graph else
-                                  "K6 8-bit code scan (dp4a) + K4 fp32 rerank of 100 survivors" if use_quant else
-                                  ("K3 tcgen05 filter + K4 fp32 rerank" if used_tc else "K1 fp32 SIMT scan"),
-                          "nsplit": int(st1["last_nsplit"]), "rows_per_gpu": hi - lo,
-                          "l2": "base shard (%.0f MB) %s L2 (126 MB); no explicit flush" % ((hi - lo) * d * 4 / 1e6, "larger than" if (hi - lo) * d * 4 > 126e6 else "fits in"),
-                          "parallelism": "base rows sharded x%d, NCCL all-gather of [m][k] keys + K7 merge" % world if world > 1 else "single GPU"},
-               "e2e": {"value": m * args.steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(m * d * 4),
-                       "d2h_bytes_per_step": int(m * k * 8 + (m * k * 4 + m * 8 if world == 1 else 0)),
-                       "api": "expann_gpu_query (page-locked host buffers)" if world == 1 else "pinned H2D + query_device + all_gather + merge + decode + D2H"},
-               "gpu_launches": int(launches),
-               "roofline": roof,
-               "clocks": clocks}
-        if not args.no_cpu and world == 1 and not use_graph:
-            qps, cores, kind, sample = cpu_reference_qps(base, q, k, metric)
-            out["cpu_baseline"] = {"value": qps, "unit": "queries/s", "cores": cores, "kind": kind, "sample": sample}
-        out["check"] = {"first_ids": got[0].tolist()}
-        if use_graph:
-            allids = ids_dev.cpu().numpy()
-            hit = sum(len(set(a.tolist()) & set(b.tolist())) for a, b in zip(allids, truth_ids))
-            out["check"]["recall_at_k_vs_exact"] = hit / float(m * k)
-            out["config"]["ef"] = args.ef
-            out["config"]["graph_build_s_per_shard"] = graph_build_s
-        if use_quant and world == 1:
-            # quality of the compressed scan: recall@10 against the exact fp32 scan of the same library (not timed)
-            try:
-                ex = expann_b200.BruteForceEngine(metric=1 if metric == "ip" else 0, device=local_rank)
-                ex.store_many_vectors(base)
-                ex.build()
-                msub = min(m, 1000)
-                eids = ex.query_k_batch(q[:msub], k)[0]
-                ex.close()
-                qids = eng.query_k_batch(q[:msub], k)[0]
-                hit = sum(len(set(a.tolist()) & set(b.tolist())) for a, b in zip(qids, eids))
-                out["check"]["recall_at_k_vs_exact"] = hit / float(msub * k)
-            except Exception as exn:  # noqa: BLE001
-                out["check"]["recall_error"] = repr(exn)[:200]
-        if world == 1 and not args.no_extras and not use_quant and not use_graph:
-            try:
-                out["scan_hbm"] = scan_hbm_leg(eng, torch, dq, k, hi - lo, d, stream, peak, peak_src, args.steps)
-            except Exception as ex:  # noqa: BLE001
-                out["scan_hbm"] = {"error": repr(ex)[:300]}
+    peak, peak_src = peaks()
+    launches = sum(st1[x] - st0[x] for x in ("scan_launches", "merge_launches", "graph_launches", "aux_launches", "tc_launches"))
+    hot_ms = (st1["hot_time_ns"] - st0["hot_time_ns"]) / 1e6 / max(1, st1["hot_timed_launches"] - st0["hot_timed_launches"])
+    qt = st1["last_qtile"]
+    gr, gq = int(st1["row_groups"]) or 1, int(st1["query_groups"]) or 1
+    rows_gpu = (n + gr - 1) // gr
+    used_tc = st1["tc_launches"] > st0["tc_launches"] and st1["tc_fallbacks"] == st0["tc_fallbacks"]
+    if use_graph:
+        dcq = (st1["distcomps"] - st0["distcomps"]) / float(args.steps * m)   # all shards together
+        alg_bytes = dcq * d * 4 * m / max(1, gr * gq)
+        achieved = alg_bytes / (hot_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": "graph_search_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "traffic_source": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": int(alg_bytes), "kernel_ms_per_launch": hot_ms,
+                "distcomps_per_query_all_gpus": dcq,
+                "note": "algorithmic bytes = distance evaluations x d x 4 per GPU (random row gathers); latency-bound"}
+    elif used_tc:
+        roof = tensor_roofline(st0, st1, m, rows_gpu, d, G, gq, args.workload, hot_ms)
+    else:
+        passes = (m + qt - 1) // max(1, qt)
+        alg_bytes = passes * rows_gpu * d * (1 if use_quant else 4)
+        achieved = alg_bytes / (hot_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": "scan_topk_u8_kernel" if use_quant else "scan_topk_f32_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "traffic_source": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": int(alg_bytes), "kernel_ms_per_launch": hot_ms,
+                "note": "algorithmic bytes = ceil(m/qtile) passes x shard bytes (SURVEY 8(d)); CTAs of one "
+                        "wave share rows through L2, so DRAM traffic is lower than this figure"}
+    if sus:
+        roof["sustained"] = sus
+    ms_step = ms / args.steps
+    out = {"metric": ("QPS (graph engine, ef=%d, top-%d)" % (args.ef, k)) if use_graph else "QPS (exact brute-force top-%d)" % k,
+           "value": m * args.steps / (ms * 1e-3), "unit": "queries/s",
+           "n_gpus": G, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+           "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": desc, "n": n, "m": m, "d": d, "k": k, "metric": metric, "qtile": int(qt),
+                      "path": "K5 graph beam search (one GPU-built graph per shard, M0=32)" if use_graph else
+                              "K6 8-bit code scan + K4 fp32 rerank of 100 survivors" if use_quant else
+                              ("K3 tcgen05 filter + K4 fp32 rerank" if used_tc else "K1 fp32 SIMT scan"),
+                      "nsplit": int(st1["last_nsplit"]), "rows_per_gpu": rows_gpu, "row_groups": gr, "query_groups": gq,
+                      "l2": "base shard (%.0f MB) %s L2 (126 MB); no explicit flush" % (rows_gpu * d * 4 / 1e6, "larger than" if rows_gpu * d * 4 > 126e6 else "fits in"),
+                      "step_minus_kernel_ms": ms_step - hot_ms,
+                      "parallelism": ("one process, one multi-device handle over %d GPUs: %d row shards x %d query groups, queries fanned out over "
+                                      "NVLink, per-GPU [m][k] keys stored by each GPU's last kernel into GPU 0's gather buffer, K7 merge "
+                                      "(no NCCL on the data path; torchrun ranks > 0 only join the barriers)" % (G, gr, gq)) if G > 1 else "single GPU"},
+           "e2e": {"value": m * args.steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(m * d * 4),
+                   "d2h_bytes_per_step": int(m * k * 8 + m * k * 4 + m * 8),
+                   "api": "expann_gpu_query (page-locked caller buffers)", "pageable_value": m / e2e_pageable_s,
+                   "pageable_api": "expann_gpu_query (pageable numpy arrays, staged through the handle's page-locked buffers)",
+                   "peer_bytes_per_step": int(peer_per_step)},
+           "gpu_launches": int(launches),
+           "roofline": roof,
+           "clocks": clocks}
+    if not args.no_cpu and G == 1 and not use_graph:
+        qps, cores, kind, sample = cpu_reference_qps(base, q, k, metric)
+        out["cpu_baseline"] = {"value": qps, "unit": "queries/s", "cores": cores, "kind": kind, "sample": sample}
+    out["check"] = check
+    if use_graph:
+        hit = sum(len(set(a.tolist()) & set(b.tolist())) for a, b in zip(got, truth_ids))
+        out["check"]["recall_at_k_vs_exact"] = hit / float(m * k)
+        out["config"]["ef"] = args.ef
+        out["config"]["graph_build_s"] = graph_build_s
+    if use_quant and G == 1:
+        # quality of the compressed scan: recall@10 against the exact fp32 scan of the same library (not timed)
+        try:
+            ex = expann_b200.BruteForceEngine(metric=mt, device=local_rank)
+            ex.store_many_vectors(base)
+            ex.build()
+            msub = min(m, 1000)
+            eids = ex.query_k_batch(q[:msub], k)[0]
+            ex.close()
+            qids = eng.query_k_batch(q[:msub], k)[0]
+            hit = sum(len(set(a.tolist()) & set(b.tolist())) for a, b in zip(qids, eids))
+            out["check"]["recall_at_k_vs_exact"] = hit / float(msub * k)
+        except Exception as exn:  # noqa: BLE001
+            out["check"]["recall_error"] = repr(exn)[:200]
+    extras = not args.no_extras and not use_quant and not use_graph and args.workload == "c2"
+
+    def young():
+        return time.perf_counter() - T_START < args.extras_budget_s
+
+    if extras and G == 1:
+        try:
+            roof["hbm_scan"] = scan_hbm_leg(eng, torch, dq, k, n, d, stream, peak, peak_src, args.steps)
+        except Exception as ex:  # noqa: BLE001
+            roof["hbm_scan"] = {"error": repr(ex)[:300]}
     eng.close()
     del eng
-    if rank == 0:
-        if world == 1 and args.workload == "c2" and not args.no_extras and not use_graph:
-            # BASELINE config 3 (graph engine, QPS at recall@10 >= 0.95) measured in the same run
+    if extras and G == 1 and young():
+        # BASELINE config 3 (graph engine, QPS at recall@10 >= 0.95) measured in the same run
+        try:
+            from tools import bench_extras
+            torch.cuda.empty_cache()
+            g3 = bench_extras.graph_c3(local_rank, max(2, min(args.steps, 20)), args.warmup, cpu=not args.no_cpu, peak_gbs=peak)
+            if "roofline" in g3:   # DRAM bytes per launch of the ef = 40 search from the committed ncu capture
+                g3["roofline"]["traffic"], g3["roofline"]["traffic_source"] = ncu_traffic("graph_search_kernel")
+            roof["graph"] = g3
+            if g3.get("at_recall_0.95"):
+                out["graph_qps_at_recall_0_95"] = g3["at_recall_0.95"]["qps"]
+        except Exception as ex:  # noqa: BLE001
+            roof["graph"] = {"error": repr(ex)[:300]}
+    # the other named configurations, bounded and not timed as the headline: C4 wherever it is sharded (N > 1), C5 at 1 and 8 GPUs
+    del base, q
+    for leg, want in (("c4", G > 1), ("c5", G in (1, 8))):
+        if extras and want and young():
             try:
-                from tools import bench_extras
                 torch.cuda.empty_cache()
-                out["graph_c3"] = bench_extras.graph_c3(local_rank, max(2, args.steps), args.warmup, cpu=not args.no_cpu, peak_gbs=peak)
-                if "roofline" in out["graph_c3"]:   # DRAM bytes per launch of the ef = 40 search from the committed ncu capture
-                    out["graph_c3"]["roofline"]["traffic"] = ncu_traffic("graph_search_kernel")
+                roof[leg] = extra_leg(expann_b200, torch, leg, G, args.extras_budget_s)
             except Exception as ex:  # noqa: BLE001
-                out["graph_c3"] = {"error": repr(ex)[:300]}
-        emit(out)
+                roof[leg] = {"error": repr(ex)[:300]}
+    out["run_s"] = time.perf_counter() - T_START
+    emit(out)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
     return 0
 

@@ -98,11 +98,11 @@ static int graph_load_index_impl(expann_gpu* h, const char* path, std::vector<fl
 	     && rd(&max_layer, 8) && rd(&n, 8);
 	if (!ok) return bad("truncated header");
 	if (n == 0) return bad("no vectors");
+	// every vector record is 8 + 4 d bytes, every vertex record at least 8: n is bounded by what is left in the file
+	if (n > (fsize - pos) / 8) return bad("vector count exceeds the file size");
 	if (n >= 0xFFFFFFFFull) return fail(h, EXPANN_ERR_UNSUPPORTED, "index file: vertex ids must fit 32 bits on device");
 	if (start >= n) return bad("starting vertex out of range");
 	if (max_layer > 64) return bad("implausible max_layer");
-	// every vector record is 8 + 4 d bytes, every vertex record at least 8: n is bounded by what is left in the file
-	if (n > (fsize - pos) / 8) return bad("vector count exceeds the file size");
 	uint64_t d = 0;
 	for (uint64_t i = 0; i < n; ++i) {
 		uint64_t sz;

@@ -25,6 +25,7 @@
 #include <algorithm>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <utility>
 
 namespace expann {
@@ -214,6 +215,20 @@ static int mg_materialize(expann_gpu* h) {
 	return EXPANN_OK;
 }
 
+// run f on every kid, one host thread per kid (the builds are seconds of per-GPU work with host synchronisations inside:
+// side by side they cost one GPU's time, not G times that); first failure wins
+template <class F> static int mg_each_kid(expann_gpu* h, F f) {
+	Multi& g = *h->mg;
+	std::vector<int> rcs(g.kids.size(), 0);
+	std::vector<std::thread> th;
+	for (size_t c = 1; c < g.kids.size(); ++c) th.emplace_back([&rcs, &g, &f, c] { rcs[c] = f(g.kids[c]); });
+	if (!g.kids.empty()) rcs[0] = f(g.kids[0]);
+	for (auto& t : th) t.join();
+	for (size_t c = 0; c < g.kids.size(); ++c)
+		if (rcs[c]) return kid_fail(h, g.kids[c], rcs[c], c);
+	return EXPANN_OK;
+}
+
 int mg_load_index(expann_gpu* h, const char* path) {
 	Multi& g = *h->mg;
 	if (g.materialized) return fail(h, EXPANN_ERR_STATE, "multi-device handle: load_index after the shards were created");
@@ -232,9 +247,7 @@ int mg_build_graph(expann_gpu* h, uint64_t M, uint64_t M0, uint64_t K, float ort
 	if (!g.index_path.empty()) return fail(h, EXPANN_ERR_STATE, "build_graph: an index file was loaded");
 	if (int rc = mg_materialize(h)) return rc;
 	// one sub-graph per row shard (mode (B) of SURVEY 8(e)): every query searches every shard with the same ef
-	for (size_t c = 0; c < g.kids.size(); ++c)
-		if (int rc = expann_gpu_build_graph(g.kids[c], M, M0, K, ortho_factor, ortho_bias, prune_overflow, seed)) return kid_fail(h, g.kids[c], rc, c);
-	return EXPANN_OK;
+	return mg_each_kid(h, [=](expann_gpu* kid) { return expann_gpu_build_graph(kid, M, M0, K, ortho_factor, ortho_bias, prune_overflow, seed); });
 }
 
 int mg_build(expann_gpu* h) {
@@ -249,8 +262,7 @@ int mg_build(expann_gpu* h) {
 		for (expann_gpu* kid : g.kids) quant_set_range(kid, mn, mx);
 		quant_set_range(h, mn, mx);
 	}
-	for (size_t c = 0; c < g.kids.size(); ++c)
-		if (int rc = expann_gpu_build(g.kids[c])) return kid_fail(h, g.kids[c], rc, c);
+	if (int rc = mg_each_kid(h, [](expann_gpu* kid) { return expann_gpu_build(kid); })) return rc;
 	g.rows.clear();
 	g.rows.shrink_to_fit();
 	h->stats.n = h->n;

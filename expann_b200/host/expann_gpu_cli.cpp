@@ -121,8 +121,12 @@ static dataset make_synthetic(size_t n, size_t m, size_t k, size_t d, const std:
 	return ds;
 }
 
+static int g_gpus = 1; // --gpus: GPUs 0 .. gpus-1 behind every engine of the run
+
 static void ground_truth(dataset& ds) { // src/dataset_loader.h:27-38: exhaustive search fills all_query_ans
-	gpu_brute_force_engine eng;
+	gpu_brute_force_engine_config gc;
+	gc.gpus = g_gpus;
+	gpu_brute_force_engine eng(gc);
 	std::vector<uint64_t> ids, counts;
 	for (size_t i = 0; i < ds.n; ++i) eng.store_vector(fvec(ds.vecs.begin() + i * ds.dim, ds.vecs.begin() + (i + 1) * ds.dim));
 	eng.build();
@@ -223,7 +227,7 @@ int main(int argc, char** argv) {
 	}
 	if (argc == 2 && (std::string(argv[1]) == "--help" || std::string(argv[1]) == "-h")) {
 		std::cout << "usage: expann_gpu --config f.json [--dataset Synthetic|Sift1M] [--ds_name s] [--n N] [--m M] [--d D] [--k K]\n"
-		             "                  [--engines bf,graph,quant] [--M0 32] [--per_query 0|1] [--out_prefix dir/]\n";
+		             "                  [--engines bf,graph,quant] [--M0 32] [--per_query 0|1] [--out_prefix dir/] [--gpus G]\n";
 		return 0;
 	}
 	if (!config_file.empty()) {
@@ -240,6 +244,7 @@ int main(int argc, char** argv) {
 	const std::string engines = get("engines", "bf,graph");
 	const bool per_query = get("per_query", "0") == "1";
 	const size_t M0 = std::stoul(get("M0", "32"));
+	g_gpus = std::max(1, std::stoi(get("gpus", "1")));
 	try {
 		dataset ds;
 		if (dataset_kind == "Sift1M") { // load_sift1m, src/dataset_loader.h:127-168 (paths of src/main.cpp:77-79)
@@ -268,7 +273,9 @@ int main(int argc, char** argv) {
 			latest.push_back(b);
 		};
 		if (engines.find("bf") != std::string::npos) {
-			gpu_brute_force_engine e;
+			gpu_brute_force_engine_config c;
+			c.gpus = g_gpus;
+			gpu_brute_force_engine e(c);
 			report(get_benchmark_data(ds, e, per_query));
 		}
 		if (engines.find("graph") != std::string::npos) {
@@ -277,12 +284,23 @@ int main(int argc, char** argv) {
 			const std::string index = get("out_prefix", "./data/" + ds_name + "/") + "index_M0_" + std::to_string(M0) + ".index";
 			mkdirs(index.substr(0, index.rfind('/')));
 			bool first = true;
+			if (g_gpus > 1) {
+				// several GPUs: the graph is built once on one GPU and written to the index file; every job of the grid then
+				// reads it on all GPUs (replicas: the queries of a call are split between the GPUs, mode (A) of SURVEY 8(e))
+				gpu_graph_engine_config c;
+				c.M = M0 / 2; c.M0 = M0; c.ef_construction = 2 * M0; c.index_filename = index; c.write_index = true;
+				gpu_graph_engine b(c);
+				for (size_t i = 0; i < ds.n; ++i) b.store_vector(fvec(ds.vecs.begin() + i * ds.dim, ds.vecs.begin() + (i + 1) * ds.dim));
+				b.build();
+				first = false;
+			}
 			for (int comp = 0; comp <= (get("compression", "0") == "1" ? 1 : 0); ++comp)
 				for (size_t efm = 1; efm <= 6; ++efm) {
 					gpu_graph_engine_config c;
 					c.M = M0 / 2; c.M0 = M0; c.ef_search_mult = efm; c.ef_construction = 2 * M0; c.use_compression = comp;
 					c.index_filename = index; c.read_index = !first; c.write_index = first;
 					c.search_width = std::stoul(get("search_width", "1"));
+					c.gpus = g_gpus;
 					gpu_graph_engine e(c);
 					report(get_benchmark_data(ds, e, per_query));
 					first = false;
@@ -290,7 +308,7 @@ int main(int argc, char** argv) {
 		}
 		if (engines.find("quant") != std::string::npos) {
 			gpu_quant_scan_engine_config c;
-			c.quantizer = 1; c.kprime = 100;
+			c.quantizer = 1; c.kprime = 100; c.gpus = g_gpus;
 			gpu_quant_scan_engine e(c);
 			report(get_benchmark_data(ds, e, per_query));
 		}

@@ -61,6 +61,8 @@ protected:
 // ---- brute_force_engine<T> (src/brute_force_engine.h:10-46) ---------------------------------------------
 struct gpu_brute_force_engine_config {
 	int device = 0;
+	int gpus = 1;       // > 1: GPUs device .. device + gpus - 1 behind this one engine (rows sharded, per-GPU top-k merged)
+	int row_groups = 0; // 0 = one row shard per GPU; R = R shards, each on gpus / R GPUs that split the queries
 	int metric = EXPANN_METRIC_L2;
 };
 struct gpu_brute_force_engine : gpu_engine_base<gpu_brute_force_engine> {
@@ -70,12 +72,15 @@ struct gpu_brute_force_engine : gpu_engine_base<gpu_brute_force_engine> {
 		g.engine = EXPANN_ENGINE_BRUTE_FORCE;
 		g.metric = c.metric;
 		g.device = c.device;
+		g.n_devices = c.gpus;
+		g.row_groups = c.row_groups;
 		create(g);
 	}
 	const std::string _name() { return "Brute-Force Engine (B200)"; }
 	const param_list_t _param_list() {
 		param_list_t pl;
 		pl["metric"] = conf.metric == EXPANN_METRIC_IP ? "ip" : "l2";
+		pl["gpus"] = std::to_string(conf.gpus);
 		return pl;
 	}
 	config conf;
@@ -91,14 +96,20 @@ struct gpu_graph_engine_config {
 	std::string index_filename;
 	bool read_index = false, write_index = false;
 	int device = 0;
+	int gpus = 1; // > 1: read_index replicates the graph on every GPU and splits the queries; otherwise one sub-graph per row shard
 	size_t search_width = 1; // vertices expanded per hop by the one-query-per-call form of the search (1 = the reference's order, 2)
 };
 struct gpu_graph_engine : gpu_engine_base<gpu_graph_engine> {
 	using config = gpu_graph_engine_config;
 	explicit gpu_graph_engine(config c) : conf(c) {
+		// the reference runs ortho_count independent candidate searches per layer during construction
+		// (src/antitopo_engine.h:382-425); the GPU build takes exact nearest neighbours as candidates instead, which has no
+		// such repetition: a value other than the shipped grid's 1 (src/bench_runner.h:138) is refused, not ignored
+		if (c.ortho_count != 1) throw std::invalid_argument("gpu_graph_engine: ortho_count must be 1 (the GPU graph build has no repeated candidate searches)");
 		expann_gpu_cfg g{};
 		g.engine = EXPANN_ENGINE_GRAPH;
 		g.device = c.device;
+		g.n_devices = c.gpus;
 		g.M = c.M;
 		g.M0 = c.M0;
 		g.ef_search_mult = c.ef_search_mult;
@@ -130,6 +141,7 @@ struct gpu_graph_engine : gpu_engine_base<gpu_graph_engine> {
 		pl["prune_overflow"] = std::to_string(conf.prune_overflow);
 		pl["use_compression"] = std::to_string(conf.use_compression);
 		pl["search_width"] = std::to_string(conf.search_width);
+		pl["gpus"] = std::to_string(conf.gpus);
 		pl["num_distcomps"] = std::to_string(stats().distcomps);
 		return pl;
 	}
@@ -139,6 +151,7 @@ struct gpu_graph_engine : gpu_engine_base<gpu_graph_engine> {
 // ---- quantizer.h compressed scan + fp32 rerank (src/quantizer.h:20-238) ---------------------------------
 struct gpu_quant_scan_engine_config {
 	int device = 0;
+	int gpus = 1;
 	int metric = EXPANN_METRIC_L2;
 	int quantizer = 0; // 0 quantizer_simple<uint8_t>, 1 quantizer_ranged_q8
 	size_t kprime = 0;
@@ -151,6 +164,7 @@ struct gpu_quant_scan_engine : gpu_engine_base<gpu_quant_scan_engine> {
 		g.metric = c.metric;
 		g.device = c.device;
 		g.quantizer = c.quantizer;
+		g.n_devices = c.gpus;
 		create(g);
 		if (c.kprime) check(expann_gpu_set_option(h, "kprime", (int64_t)c.kprime));
 	}
@@ -159,6 +173,7 @@ struct gpu_quant_scan_engine : gpu_engine_base<gpu_quant_scan_engine> {
 		param_list_t pl;
 		pl["quantizer"] = conf.quantizer ? "ranged_q8" : "simple_u8";
 		pl["kprime"] = std::to_string(conf.kprime);
+		pl["gpus"] = std::to_string(conf.gpus);
 		return pl;
 	}
 	config conf;
