@@ -3,6 +3,8 @@
 #include "engine.h"
 #include <algorithm>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <new>
 
 namespace expann {
@@ -15,6 +17,21 @@ int fail(expann_gpu* h, int code, const std::string& msg) {
 }
 int cuda_fail(expann_gpu* h, cudaError_t e, const char* what) {
 	return fail(h, EXPANN_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize belongs to the (kernel, device) pair, not to a handle or a thread: every
+// launch site goes through here, the value only ever grows, and the check + set is one critical section (a per-thread or
+// per-call-site cache lets a later, smaller request lower the limit under a launch that still needs the larger one).
+int ensure_dyn_smem(expann_gpu* h, const void* kernel, size_t bytes) {
+	static std::mutex mu;
+	static std::map<std::pair<const void*, int>, size_t> granted;
+	std::lock_guard<std::mutex> lk(mu);
+	size_t& cur = granted[{ kernel, h->device }];
+	if (bytes > cur) {
+		EXPANN_CUDA(h, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+		cur = bytes;
+	}
+	return EXPANN_OK;
 }
 
 static cudaEvent_t get_event(expann_gpu* h) {
@@ -206,7 +223,7 @@ void expann_gpu_destroy(expann_gpu_t* h) {
 	if (h->base) cudaFree(h->base);
 	for (DevBuf* b : { &h->tc_xb, &h->tc_xn, &h->tc_stats, &h->tc_qstats, &h->tc_qb, &h->tc_qn, &h->tc_thr, &h->tc_cnt, &h->tc_cand, &h->tc_gthr, &h->tc_sel, &h->tc_xx, &h->tc_seed, &h->tc_fbcount, &h->scan_cnt })
 		b->release();
-	for (DevBuf* b : { &h->q_codes, &h->q_cnorm, &h->q_mm, &h->qq_codes, &h->qq_norm, &h->q_cand }) b->release();
+	for (DevBuf* b : { &h->q_codes, &h->q_cnorm, &h->q_mm, &h->qq_codes, &h->qq_norm, &h->q_cand, &h->q_cnb, &h->q_thrfin, &h->q_zero }) b->release();
 	for (DevBuf* b : { &h->g_bottom, &h->g_upper, &h->g_upper_idx, &h->g_upper_nl, &h->g_visited, &h->g_epoch, &h->g_codes, &h->g_up_meta,
 	                   &h->g_upper_c, &h->g_up_vec })
 		b->release();
@@ -476,6 +493,11 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 		if (value != 0 && value != 1) return fail(h, EXPANN_ERR_ARG, "tc_real must be 0 or 1");
 		if (h->built) return fail(h, EXPANN_ERR_STATE, "tc_real must be set before build()");
 		h->opt_tc_real = (int)value;
+	} else if (nm == "quant_tc") {
+		h->opt_quant_tc = value != 0;
+	} else if (nm == "quant_tc_min_batch") {
+		if (value < 1) return fail(h, EXPANN_ERR_ARG, "quant_tc_min_batch must be >= 1");
+		h->opt_quant_tc_min_batch = (int)value;
 	} else if (nm == "tc_v1") {
 		h->opt_tc_v1 = value != 0;
 	} else if (nm == "tc") {

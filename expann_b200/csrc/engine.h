@@ -89,8 +89,11 @@ struct expann_gpu {
 	size_t dc_pad = 0;       // code row stride (d rounded up to 128)
 	float q_scale = 1.f, q_offset = 0.f;
 	bool q_range_fixed = false; // ranged q8: scale / offset were set from outside (multi-device handle: one range for all shards)
-	expann::DevBuf q_codes, q_cnorm, q_mm, qq_codes, qq_norm, q_cand;
-	CUtensorMap tmap_codes{};
+	expann::DevBuf q_codes, q_cnorm, q_mm, qq_codes, qq_norm, q_cand, q_cnb, q_thrfin, q_zero;
+	CUtensorMap tmap_codes{}, tmap_codes128{};
+	int opt_quant_tc = 1, opt_quant_tc_min_batch = 32; // code scan through the tensor-core filter (kind::i8) from this many queries on
+	bool q_tc_ready = false;
+	uint64_t q_tc_launches = 0;
 	// graph engine
 	expann::HostGraph graph;
 	expann::DevBuf g_bottom, g_upper, g_upper_idx, g_upper_nl, g_visited, g_epoch, g_codes, g_up_meta, g_upper_c, g_up_vec;
@@ -118,6 +121,9 @@ cudaEvent_t timing_begin(expann_gpu* h, cudaStream_t st);
 void timing_end(expann_gpu* h, cudaEvent_t start, cudaStream_t st);
 int cuda_fail(expann_gpu* h, cudaError_t e, const char* what);
 // api.cu
+// opt-in dynamic shared memory of a kernel: raised when a launch needs more than any launch before it on that device,
+// never lowered (several engines, row lengths and host threads share the kernels of this library)
+int ensure_dyn_smem(expann_gpu* h, const void* kernel, size_t bytes);
 int query_device_impl(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out, cudaStream_t st);
 bool is_pinned_host(const void* p);
 // multi.cu — every entry of the C ABI on a multi-device handle
@@ -147,6 +153,12 @@ int graph_read_distcomps(expann_gpu* h);
 int tc_finalize(expann_gpu* h);
 int launch_scan_tc(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);
 bool tc_first_form_fits(const expann_gpu* h); // the chunked first form of K3 keeps the query tile resident
+uint32_t tc2_pick_rsplit(uint32_t qblocks, uint32_t ntiles, int sms);
+// tc_i8.cu: the quantised engine's code scan on the tensor cores (tcgen05.mma.kind::i8)
+int tc_code_prepare(expann_gpu* h);
+bool tc_code_ready(const expann_gpu* h);
+bool tc_code_fits(const expann_gpu* h, size_t kp);
+int launch_code_filter(expann_gpu* h, size_t m, size_t kp, uint64_t* d_cand_out, cudaStream_t st, const uint32_t** flags_out);
 // quant.cu
 int quant_finalize(expann_gpu* h);
 int quant_minmax(expann_gpu* h, float* mn_out, float* mx_out);
@@ -158,7 +170,7 @@ int graph_build_gpu(expann_gpu* h, uint64_t M, uint64_t M0, uint64_t K, float or
 int graph_save_index(expann_gpu* h, const char* path);
 // merge_topk.cu
 int launch_merge(expann_gpu* h, const uint64_t* in, size_t m, size_t nlists, size_t klist, size_t stride_q,
-                 size_t stride_s, size_t k, uint32_t id_add, uint64_t* out, cudaStream_t st);
+                 size_t stride_s, size_t k, uint32_t id_add, uint64_t* out, cudaStream_t st, const uint32_t* gate = nullptr);
 int launch_decode(expann_gpu* h, const uint64_t* keys, size_t m, size_t k, int kind, uint64_t* ids, float* dists,
                   uint64_t* counts, cudaStream_t st);
 } // namespace expann

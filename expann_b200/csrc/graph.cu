@@ -276,7 +276,7 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 		cudaEvent_t t0 = timing_begin(h, st);
 #define GC_LAUNCH(L)                                                                                              \
 	do {                                                                                                          \
-		EXPANN_CUDA(h, (cudaFuncSetAttribute(graph_search_cta_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1))); \
+		if (int rc_ = ensure_dyn_smem(h, (const void*)graph_search_cta_kernel<L>, smem1)) return rc_;                    \
 		graph_search_cta_kernel<L><<<grid1, 32 * GC_WARPS, smem1, st>>>(p);                                      \
 	} while (0)
 		if (cap <= 32) GC_LAUNCH(1);
@@ -295,7 +295,7 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 	cudaEvent_t t0 = timing_begin(h, st);
 #define GS_LAUNCH_B(L, B)                                                                                         \
 	do {                                                                                                          \
-		EXPANN_CUDA(h, (cudaFuncSetAttribute(graph_search_kernel<L, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))); \
+		if (int rc_ = ensure_dyn_smem(h, (const void*)graph_search_kernel<L, B>, smem)) return rc_;                      \
 		graph_search_kernel<L, B><<<grid, 32 * GS_WARPS, smem, st>>>(p);                                         \
 	} while (0)
 #define GS_LAUNCH(L)                                                                                              \

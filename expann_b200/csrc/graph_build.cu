@@ -81,7 +81,7 @@ int build_layer(expann_gpu* h, Scratch& s, const uint32_t* d_rowmap_for_prune, c
 	p.lazy = 0;
 	const size_t smem = (size_t)GB_MAXC * 8 + (size_t)GB_MAXC * (h->d_pad + 1) * 4;
 	if (smem > 220 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "graph build: d too large for the prune kernel");
-	EXPANN_CUDA(h, cudaFuncSetAttribute(prune_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	if (int rc = ensure_dyn_smem(h, (const void*)prune_select_kernel, smem)) return rc;
 	prune_select_kernel<<<ns, GB_THREADS, smem, st>>>(p);
 	EXPANN_CUDA(h, cudaGetLastError());
 	h->stats.aux_launches++;

@@ -5,7 +5,7 @@
 namespace expann {
 
 int launch_merge(expann_gpu* h, const uint64_t* in, size_t m, size_t nlists, size_t klist, size_t stride_q,
-                 size_t stride_s, size_t k, uint32_t id_add, uint64_t* out, cudaStream_t st) {
+                 size_t stride_s, size_t k, uint32_t id_add, uint64_t* out, cudaStream_t st, const uint32_t* gate) {
 	if (m == 0) return EXPANN_OK;
 	if (k == 0 || k > 128) return fail(h, EXPANN_ERR_UNSUPPORTED, "merge: k must be in 1..128");
 	MergeParams p{};
@@ -18,6 +18,7 @@ int launch_merge(expann_gpu* h, const uint64_t* in, size_t m, size_t nlists, siz
 	p.k = (uint32_t)k;
 	p.id_add = id_add;
 	p.out_keys = out;
+	p.gate = gate;
 	const int wpb = 4;
 	dim3 grid((unsigned)((m + wpb - 1) / wpb));
 	if (nlists * klist >= 512 && m <= 4096) { // few queries, many lists: one block per query

@@ -14,12 +14,14 @@ struct MergeParams {
 	uint32_t m, k;
 	uint32_t id_add;     // added to the 32-bit id of every non-empty key written to out_keys (shard offset)
 	uint64_t* out_keys;  // [m][k] or null
+	const uint32_t* gate; // device-side gate (a redo queued behind a flag): when set, the launch does nothing unless *gate != 0
 };
 
 template <int LPL> __global__ void __launch_bounds__(128) merge_topk_kernel(const MergeParams p) {
 	const int lane = threadIdx.x & 31;
 	const uint32_t q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	if (q >= p.m) return;
+	if (p.gate != nullptr && *reinterpret_cast<const volatile uint32_t*>(p.gate) == 0u) return;
 	WarpList<LPL> out;
 	out.init();
 	uint64_t tk = KEY_EMPTY;
@@ -62,6 +64,7 @@ template <int LPL> __global__ void __launch_bounds__(256) merge_topk_block_kerne
 	__shared__ uint64_t sm[8][32 * LPL];
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const uint32_t q = blockIdx.x;
+	if (p.gate != nullptr && *reinterpret_cast<const volatile uint32_t*>(p.gate) == 0u) return; // uniform over the block
 	WarpList<LPL> out;
 	out.init();
 	uint64_t tk = KEY_EMPTY;

@@ -221,7 +221,14 @@ template <class F> static int mg_each_kid(expann_gpu* h, F f) {
 	Multi& g = *h->mg;
 	std::vector<int> rcs(g.kids.size(), 0);
 	std::vector<std::thread> th;
-	for (size_t c = 1; c < g.kids.size(); ++c) th.emplace_back([&rcs, &g, &f, c] { rcs[c] = f(g.kids[c]); });
+	for (size_t c = 1; c < g.kids.size(); ++c)
+		th.emplace_back([&rcs, &g, &f, c] {
+			// a new host thread has no CUDA context bound: driver entry points (cuTensorMapEncodeTiled) fail with
+			// CUDA_ERROR_INVALID_CONTEXT until a runtime call has made the device's primary context current
+			cudaSetDevice(g.kids[c]->device);
+			cudaFree(nullptr);
+			rcs[c] = f(g.kids[c]);
+		});
 	if (!g.kids.empty()) rcs[0] = f(g.kids[0]);
 	for (auto& t : th) t.join();
 	for (size_t c = 0; c < g.kids.size(); ++c)

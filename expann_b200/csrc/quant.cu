@@ -64,7 +64,8 @@ int quant_finalize(expann_gpu* h) {
 	}
 	if (int rc = quantize_rows(h, h->base, h->d_pad, h->n, h->q_codes.as<uint8_t>(), h->q_cnorm.as<int32_t>(), st)) return rc;
 	EXPANN_CUDA(h, cudaStreamSynchronize(st));
-	return encode_tensor_map_2d(h, &h->tmap_codes, 1, h->q_codes.p, h->dc_pad, h->n, h->dc_pad, 128, 256);
+	if (int rc = encode_tensor_map_2d(h, &h->tmap_codes, 1, h->q_codes.p, h->dc_pad, h->n, h->dc_pad, 128, 256)) return rc;
+	return tc_code_prepare(h); // operands of the tensor-core form of the scan (tc_i8.cu)
 }
 
 template <int QT, int METRIC, int LPL>
@@ -74,7 +75,7 @@ static int launch_u8_inst(expann_gpu* h, const QScanParams& p, dim3 grid, cudaSt
 	size_t merge = (size_t)QS_NWARP * QT * Cfg::KMAX * 8, stg = (size_t)QS_STAGES * Cfg::STAGE_BYTES;
 	const size_t smem = 1024 + std::max(merge, stg) + (((size_t)QT * p.dc_pad + 15) & ~(size_t)15) + 2 * QS_STAGES * 8 + 64;
 	if (smem > 227 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "quant scan: d too large");
-	EXPANN_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	if (int rc = ensure_dyn_smem(h, (const void*)kern, smem)) return rc;
 	kern<<<grid, Cfg::THREADS, smem, st>>>(h->tmap_codes, p);
 	EXPANN_CUDA(h, cudaGetLastError());
 	return EXPANN_OK;
@@ -93,6 +94,19 @@ int launch_quant_scan(expann_gpu* h, const float* d_q, size_t m, size_t k, uint6
 	EXPANN_CUDA(h, h->qq_norm.ensure(m * 4));
 	EXPANN_CUDA(h, h->q_cand.ensure(m * kp * 8));
 	if (int rc = quantize_rows(h, d_q, h->d_pad, m, h->qq_codes.as<uint8_t>(), h->qq_norm.as<int32_t>(), st)) return rc;
+
+	// Large batches: the code scan runs as a tensor-core candidate filter (tc_i8.cu, tcgen05.mma.kind::i8) that leaves the
+	// same k' best codes in q_cand; the SIMT scan below is then only its redo, queued behind the filter's device flag.
+	const uint32_t* gate = nullptr;
+	uint32_t* gate_count = nullptr;
+	if (tc_code_ready(h) && h->opt_quant_tc && m >= (size_t)h->opt_quant_tc_min_batch && tc_code_fits(h, kp)) {
+		if (int rc = launch_code_filter(h, m, kp, h->q_cand.as<uint64_t>(), st, &gate)) return rc;
+		if (h->tc_fbcount.cap < 4) {
+			EXPANN_CUDA(h, h->tc_fbcount.ensure(4));
+			EXPANN_CUDA(h, cudaMemsetAsync(h->tc_fbcount.p, 0, 4, st));
+		}
+		gate_count = h->tc_fbcount.as<uint32_t>();
+	}
 
 	int qt = h->cfg.qtile;
 	if (qt == 0) qt = m >= 8 ? 8 : (m >= 3 ? 4 : 1);
@@ -119,6 +133,8 @@ int launch_quant_scan(expann_gpu* h, const float* d_q, size_t m, size_t k, uint6
 	p.n = (uint32_t)h->n;
 	p.rows_per_split = gps * QS_ROWS;
 	p.nsplit = nsplit;
+	p.gate = gate;
+	p.gate_count = gate_count;
 	uint64_t* scan_out = h->q_cand.as<uint64_t>();
 	if (nsplit > 1) {
 		EXPANN_CUDA(h, h->partial.ensure(m * nsplit * kp * 8));
@@ -127,18 +143,22 @@ int launch_quant_scan(expann_gpu* h, const float* d_q, size_t m, size_t k, uint6
 	p.partial = scan_out;
 	dim3 grid(qtiles, nsplit);
 	const bool ip = h->cfg.metric == EXPANN_METRIC_IP;
-	cudaEvent_t t0 = timing_begin(h, st);
+	cudaEvent_t t0 = gate ? nullptr : timing_begin(h, st);
 	int rc;
 	if (qt == 8) rc = ip ? launch_u8_k<8, METRIC_IP>(h, p, grid, st) : launch_u8_k<8, METRIC_L2>(h, p, grid, st);
 	else if (qt == 4) rc = ip ? launch_u8_k<4, METRIC_IP>(h, p, grid, st) : launch_u8_k<4, METRIC_L2>(h, p, grid, st);
 	else rc = ip ? launch_u8_k<1, METRIC_IP>(h, p, grid, st) : launch_u8_k<1, METRIC_L2>(h, p, grid, st);
 	timing_end(h, t0, st);
 	if (rc) return rc;
-	h->stats.scan_launches++;
-	h->stats.last_nsplit = nsplit;
-	h->stats.last_qtile = qt;
+	if (gate)
+		h->stats.aux_launches++; // the queued redo: returns at once while the flag is down
+	else {
+		h->stats.scan_launches++;
+		h->stats.last_nsplit = nsplit;
+		h->stats.last_qtile = qt;
+	}
 	if (nsplit > 1)
-		if (int r2 = launch_merge(h, scan_out, m, nsplit, kp, (size_t)nsplit * kp, kp, kp, 0, h->q_cand.as<uint64_t>(), st)) return r2;
+		if (int r2 = launch_merge(h, scan_out, m, nsplit, kp, (size_t)nsplit * kp, kp, kp, 0, h->q_cand.as<uint64_t>(), st, gate)) return r2;
 	// K4: exact fp32 keys of the k' survivors, final (key, id) order, truncation to k
 	RerankParams r{};
 	r.base = h->base;
@@ -155,10 +175,10 @@ int launch_quant_scan(expann_gpu* h, const float* d_q, size_t m, size_t k, uint6
 	const size_t smem = ((size_t)h->d_pad * 4 + GS_MAXNB * 8) * 4;
 	const unsigned blocks = (unsigned)((m + 3) / 4);
 	if (kp <= 32) {
-		EXPANN_CUDA(h, cudaFuncSetAttribute(rerank_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		if (int rc = ensure_dyn_smem(h, (const void*)rerank_kernel<1>, smem)) return rc;
 		rerank_kernel<1><<<blocks, 128, smem, st>>>(r);
 	} else {
-		EXPANN_CUDA(h, cudaFuncSetAttribute(rerank_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		if (int rc = ensure_dyn_smem(h, (const void*)rerank_kernel<4>, smem)) return rc;
 		rerank_kernel<4><<<blocks, 128, smem, st>>>(r);
 	}
 	EXPANN_CUDA(h, cudaGetLastError());

@@ -21,6 +21,10 @@ struct QScanParams {
 	const int32_t* cnorm;    // [n] sum c^2
 	uint64_t* partial;       // [m][nsplit][k] keys (biased int32 score << 32 | local id)
 	uint32_t m, k, dc_pad, n, rows_per_split, nsplit;
+	// device-side gate (the tensor-core code filter's redo): when set, the launch does nothing unless *gate != 0; a launch
+	// that does run counts itself in *gate_count
+	const uint32_t* gate;
+	uint32_t* gate_count;
 };
 
 template <int QT, int TR, int NWARP, int STAGES, int METRIC, int LPL>
@@ -28,6 +32,10 @@ __global__ void __launch_bounds__(32 * (NWARP + 1), 1)
 scan_topk_u8_kernel(const __grid_constant__ CUtensorMap tmap, const QScanParams p) {
 	using Cfg = ScanCfg<QT, TR, NWARP, STAGES, METRIC, LPL>;
 	extern __shared__ uint8_t smem_raw[];
+	if (p.gate != nullptr) { // uniform over the grid: nobody has touched a barrier yet
+		if (*reinterpret_cast<const volatile uint32_t*>(p.gate) == 0u) return;
+		if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) atomicAdd(p.gate_count, 1u);
+	}
 	uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
 	size_t stage_area = (size_t)STAGES * Cfg::STAGE_BYTES;
 	{

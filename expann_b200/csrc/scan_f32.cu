@@ -68,12 +68,7 @@ static int launch_inst(expann_gpu* h, const ScanParams& p, dim3 grid, cudaStream
 	auto kern = scan_topk_f32_kernel<QT, SCAN_TR, SCAN_NWARP, SCAN_STAGES, METRIC, LPL>;
 	const size_t smem = Cfg::smem_bytes(p.d_pad);
 	if (smem > 227 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "scan: d too large for the shared-memory query tile");
-	static thread_local int attr_dev = -1, attr_smem = 0; // per instantiation: set once per device / size, not per launch
-	if (attr_dev != h->device || attr_smem < (int)smem) {
-		EXPANN_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		attr_dev = h->device;
-		attr_smem = (int)smem;
-	}
+	if (int rc = ensure_dyn_smem(h, (const void*)kern, smem)) return rc;
 	kern<<<grid, Cfg::THREADS, smem, st>>>(h->tmap_base, p);
 	EXPANN_CUDA(h, cudaGetLastError());
 	return EXPANN_OK;

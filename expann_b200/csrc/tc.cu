@@ -177,7 +177,7 @@ static int tc_watch_flag(expann_gpu* h, const uint32_t* flags, cudaStream_t st) 
 template <int NSTAGE>
 static int launch_filter(expann_gpu* h, const CUtensorMap& tq, const TcParams& p, dim3 grid, cudaStream_t st) {
 	const size_t smem = tc_smem_bytes(p.kd, NSTAGE);
-	EXPANN_CUDA(h, cudaFuncSetAttribute(tc_filter_kernel<NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	if (int rc = ensure_dyn_smem(h, (const void*)tc_filter_kernel<NSTAGE>, smem)) return rc;
 	tc_filter_kernel<NSTAGE><<<grid, TC_THREADS, smem, st>>>(tq, h->tmap_xb, p);
 	EXPANN_CUDA(h, cudaGetLastError());
 	return EXPANN_OK;
@@ -274,10 +274,10 @@ static int tc_batch(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 	const size_t smem = ((size_t)h->d_pad * 4 + GS_MAXNB * 8) * 4;
 	const unsigned blocks = (unsigned)((m + 3) / 4);
 	if (k <= 32) {
-		EXPANN_CUDA(h, cudaFuncSetAttribute(rerank_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		if (int rc = ensure_dyn_smem(h, (const void*)rerank_kernel<1>, smem)) return rc;
 		rerank_kernel<1><<<blocks, 128, smem, st>>>(r);
 	} else {
-		EXPANN_CUDA(h, cudaFuncSetAttribute(rerank_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		if (int rc = ensure_dyn_smem(h, (const void*)rerank_kernel<4>, smem)) return rc;
 		rerank_kernel<4><<<blocks, 128, smem, st>>>(r);
 	}
 	EXPANN_CUDA(h, cudaGetLastError());
@@ -297,12 +297,7 @@ static int tc_batch(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_
 template <int NQB, int NSTAGE>
 static int launch_filter2(expann_gpu* h, const CUtensorMap& tq, const Tc2Params& p, dim3 grid, cudaStream_t st) {
 	const size_t smem = Tc2Cfg<NQB>::smem_bytes(p.kd, NSTAGE);
-	static thread_local int f_dev = -1, f_smem = 0;
-	if (f_dev != h->device || f_smem < (int)smem) {
-		EXPANN_CUDA(h, cudaFuncSetAttribute(tc_filter2_kernel<NQB, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		f_dev = h->device;
-		f_smem = (int)smem;
-	}
+	if (int rc = ensure_dyn_smem(h, (const void*)tc_filter2_kernel<NQB, NSTAGE>, smem)) return rc;
 	tc_filter2_kernel<NQB, NSTAGE><<<grid, Tc2Cfg<NQB>::THREADS, smem, st>>>(tq, h->tmap_xb128, h->tmap_xx, p);
 	EXPANN_CUDA(h, cudaGetLastError());
 	return EXPANN_OK;
@@ -311,12 +306,7 @@ static int launch_filter2(expann_gpu* h, const CUtensorMap& tq, const Tc2Params&
 template <int NSTAGE, bool ASTREAM = false>
 static int launch_filter_pair(expann_gpu* h, const CUtensorMap& tq, const Tc2Params& p, dim3 grid, cudaStream_t st) {
 	const size_t smem = Tc3Cfg::smem_bytes(p.kd, NSTAGE, ASTREAM);
-	static thread_local int f_dev = -1, f_smem = 0;
-	if (f_dev != h->device || f_smem < (int)smem) {
-		EXPANN_CUDA(h, (cudaFuncSetAttribute(tc_filter_pair_kernel<NSTAGE, ASTREAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)));
-		f_dev = h->device;
-		f_smem = (int)smem;
-	}
+	if (int rc = ensure_dyn_smem(h, (const void*)tc_filter_pair_kernel<NSTAGE, ASTREAM>, smem)) return rc;
 	tc_filter_pair_kernel<NSTAGE, ASTREAM><<<grid, Tc3Cfg::THREADS, smem, st>>>(tq, h->tmap_xb128, h->tmap_xx, p); // __cluster_dims__(2,1,1)
 	EXPANN_CUDA(h, cudaGetLastError());
 	return EXPANN_OK;
@@ -324,7 +314,7 @@ static int launch_filter_pair(expann_gpu* h, const CUtensorMap& tq, const Tc2Par
 
 // row splits of the second form: whole waves of CTAs (>= 97 % of the SM slots of the last wave used), as few
 // splits as that allows (every split warms its own bound up), at least 8 tiles per CTA
-static uint32_t tc2_pick_rsplit(uint32_t qblocks, uint32_t ntiles, int sms) {
+uint32_t tc2_pick_rsplit(uint32_t qblocks, uint32_t ntiles, int sms) {
 	const uint32_t max_split = std::max(1u, std::min((uint32_t)TC2_MAX_SPLIT, ntiles / 8u));
 	uint32_t best = 1;
 	double best_eff = 0.0;
@@ -466,12 +456,7 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	r.metric = ip ? 1 : 0;
 	r.scan_order = 1;
 	const size_t smem = ((size_t)h->d_pad * 4 + GS_MAXNB * 8) * 4;
-	static thread_local int rr_dev = -1, rr_smem = 0;
-	if (rr_dev != h->device || rr_smem < (int)smem) {
-		EXPANN_CUDA(h, cudaFuncSetAttribute(rerank_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		rr_dev = h->device;
-		rr_smem = (int)smem;
-	}
+	if (int rc = ensure_dyn_smem(h, (const void*)rerank_kernel<1>, smem)) return rc;
 	rerank_kernel<1><<<(unsigned)((m + 3) / 4), 128, smem, st>>>(r);
 	EXPANN_CUDA(h, cudaGetLastError());
 	h->stats.aux_launches++;

@@ -46,6 +46,14 @@ struct Tc2Params {
 	uint32_t tile_first, buf_first; // this launch covers tiles [tile_first, tile_first + ntiles), buffers from buf_first
 	const float* seed_in;           // [m][2][16] or null
 	float* seed_out;                // [m][2][16] or null
+	// more than 16 results per query (the code scan's k' survivors): every stream still keeps ITS 16 smallest (k = 16) and
+	// reports the bound it ended with; the select kernel takes the k'-th smallest key T over all buffers and verifies
+	// T <= every stream's final bound -- then no stream has dropped a row at or below T and the buffers hold the exact top
+	// k'; otherwise (row order that piles more than 16 of the top k' into one stream) the batch is flagged and redone
+	uint32_t* thr_out;              // [m][rsplit] orderable final bound per stream, or null
+	// pair form, KIND 1 (8-bit codes, tcgen05.mma.kind::i8): biased code norms and the bias (see tc_filter3.cuh)
+	const int32_t* cnb;             // [ceil(n/256)*256 + 256] sum c^2 + ibias, rows >= n: 0x7F000000
+	int32_t ibias;
 };
 
 __device__ __forceinline__ uint32_t tc2_instr_desc() { // kind::f16, bf16 x bf16 -> fp32, K-major A and B, M = 128, N = 128
@@ -118,47 +126,17 @@ __device__ __forceinline__ float tc2_chunk_min(const uint32_t (&d)[32]) {
 	float mn[11];
 	return tc2_chunk_min(d, mn);
 }
-#ifndef TC2_HITS_V2
-#define TC2_HITS_V2 1
-#endif
-// pass 2 (rare per lane, frequent per warp on short row ranges): a chunk known to hold some a' <= thr. Only the triples
-// whose minimum passes the bound are looked at (usually one triple of one lane): their values are parked in this lane's
-// scratch column, the hit mask is built from them and only the set bits are visited. thr tightens while we go, hence
-// the second compare. Rows >= n (zero-filled by TMA: a' = 0) are masked here. (The first version parked and compared
-// all 32 values of the chunk on every entry: ~100 instructions before the first event; on a 125k-row shard nearly
-// every chunk of every warp enters here -- see profiles/r2_notes.md.)
-__device__ __forceinline__ void tc2_chunk_hits(Tc2Thread& t, const uint32_t (&d)[32], const float (&mn)[11], float* sc, uint32_t row_c,
-                                               uint32_t n) {
+// pass 2 (rare per lane, frequent per warp on short row ranges): a chunk known to hold some a' <= thr. The values are
+// parked in this lane's scratch column and the hit mask is built without branches; only the set bits (usually one) are
+// visited. thr tightens while we go, hence the second compare. Rows >= n (zero-filled by TMA: a' = 0) are masked here.
+__device__ __forceinline__ void tc2_chunk_hits(Tc2Thread& t, const uint32_t (&d)[32], float* sc, uint32_t row_c, uint32_t n) {
 	const uint32_t sca = smem_u32(sc);
 	uint32_t mask = 0;
-#if TC2_HITS_V2
-#pragma unroll
-	for (int g = 0; g < 4; ++g) { // triples 0-2, 3-5, 6-8, 9-10: a real branch per group, then one per triple
-		const int j0 = 3 * g, j1 = g < 3 ? 3 * g + 3 : 11;
-		const float gm = g < 3 ? min3f(mn[j0], mn[j0 + 1], mn[j0 + 2]) : fminf(mn[9], mn[10]);
-		if (gm <= t.thr) {
-#pragma unroll
-			for (int j = j0; j < j1; ++j) {
-				if (mn[j] <= t.thr) {
-#pragma unroll
-					for (int c = 0; c < 3; ++c) {
-						const int jj = 3 * j + c;
-						if (jj < 32) {
-							asm volatile("st.shared.b32 [%0], %1;" ::"r"(sca + jj * 128), "r"(d[jj]) : "memory");
-							mask |= __uint_as_float(d[jj]) <= t.thr ? 1u << jj : 0u;
-						}
-					}
-				}
-			}
-		}
-	}
-#else
 #pragma unroll
 	for (int j = 0; j < 32; ++j) {
 		asm volatile("st.shared.b32 [%0], %1;" ::"r"(sca + j * 128), "r"(d[j]) : "memory");
 		mask |= __uint_as_float(d[j]) <= t.thr ? 1u << j : 0u;
 	}
-#endif
 	while (mask) {
 		const int j = __ffs(mask) - 1;
 		mask &= mask - 1;
@@ -167,19 +145,14 @@ __device__ __forceinline__ void tc2_chunk_hits(Tc2Thread& t, const uint32_t (&d)
 		if (aj <= t.thr && row_c + j < n) tc2_event(t, aj, row_c + j);
 	}
 }
-// same, with the triple minima recomputed here. The values pass through an empty asm so that the compiler cannot merge this
-// with the caller's min tree and keep eleven more registers live across the vote (spills in the pair kernel).
-__device__ __forceinline__ void tc2_chunk_hits(Tc2Thread& t, const uint32_t (&d)[32], float* sc, uint32_t row_c, uint32_t n) {
-	uint32_t e[32];
-#pragma unroll
-	for (int j = 0; j < 32; ++j) {
-		e[j] = d[j];
-		asm volatile("" : "+r"(e[j]));
-	}
-	float mn[11];
-	tc2_chunk_min(e, mn);
-	tc2_chunk_hits(t, e, mn, sc, row_c, n);
-}
+// Four other forms of this pass were built and measured on B200 (filter kernel, 10 000 queries x 125k / 1M rows of C2;
+// this form: 0.418-0.434 / 1.78-1.84 ms; profiles/r2_notes.md):
+//   * branching down the min tree to the hit triple and parking only that triple: 0.555 / 2.27 ms;
+//   * the whole warp working on one hit lane at a time (16-byte parking, one vote per hit lane for its mask, values
+//     handed over by shuffles): 0.856 / 2.20 ms -- all lanes that have hits run the loop below SIDE BY SIDE, serialising
+//     over hit lanes multiplies the event cost by their number;
+//   * 16-byte parking into a lane-private row + set/lop3 mask: the compiler turns each pair into FSETP + SEL + LOP3
+//     (no gain); + an 11-bit mask of the hit triples instead of the 32-bit one: 0.475 / 1.96 ms.
 __device__ __forceinline__ void tc_ld32_nowait(uint32_t taddr, uint32_t (&v)[32]) {
 	asm volatile(
 	    "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
@@ -415,11 +388,21 @@ __device__ __forceinline__ uint64_t tc2_flat_key(const uint64_t* __restrict__ qb
 	return __ldg(qbuf + (size_t)lo * cap + (i - pre[lo]));
 }
 
+// k > 16 (Tc2Params::thr_out): the selection bound t must not exceed the bound any stream of the query ended with
+__device__ __forceinline__ bool tc2_bound_verified(const uint32_t* __restrict__ thr_fin, uint32_t q, uint32_t rsplit, float t, int lane) {
+	if (thr_fin == nullptr) return true;
+	const uint32_t to = f32_orderable(t);
+	bool ok = true;
+	for (uint32_t s = lane; s < rsplit; s += 32) ok = ok && to <= thr_fin[(size_t)q * rsplit + s];
+	return __all_sync(FULL, ok);
+}
+
 template <int LPL>
 __global__ void __launch_bounds__(128) tc_select2_kernel(const uint64_t* __restrict__ cand, const uint32_t* __restrict__ cnt, uint32_t cap,
                                                           uint32_t rsplit, uint32_t m, uint32_t k, const float* __restrict__ qnorm2,
                                                           float eps_rel, float eps_abs, float xnorm_max, uint64_t* __restrict__ out,
-                                                          uint32_t pad, uint32_t* __restrict__ flags) {
+                                                          uint32_t pad, uint32_t* __restrict__ flags,
+                                                          const uint32_t* __restrict__ thr_fin = nullptr) {
 	__shared__ uint32_t pre_s[4][TC2_MAX_SPLIT + 8];
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
 	const uint32_t q = blockIdx.x * (blockDim.x >> 5) + wib;
@@ -477,7 +460,8 @@ __global__ void __launch_bounds__(128) tc_select2_kernel(const uint64_t* __restr
 			w += __popc(mk);
 		}
 		for (uint32_t i = w + lane; i < pad; i += 32) o[i] = KEY_EMPTY;
-		if ((over || w > pad) && lane == 0) atomicAdd(flags, 1u);
+		const bool ver = tc2_bound_verified(thr_fin, q, rsplit, t, lane);
+		if ((over || w > pad || !ver) && lane == 0) atomicAdd(flags, 1u);
 		return;
 	}
 	WarpList<LPL> best;
@@ -518,7 +502,8 @@ __global__ void __launch_bounds__(128) tc_select2_kernel(const uint64_t* __restr
 		}
 	}
 	for (uint32_t i = w + lane; i < pad; i += 32) o[i] = KEY_EMPTY;
-	if ((over || w > pad) && lane == 0) atomicAdd(flags, 1u);
+	const bool ver = tc2_bound_verified(thr_fin, q, rsplit, t, lane);
+	if ((over || w > pad || !ver) && lane == 0) atomicAdd(flags, 1u);
 }
 
 
@@ -530,7 +515,8 @@ template <int LPL>
 __global__ void __launch_bounds__(256) tc_select2_block_kernel(const uint64_t* __restrict__ cand, const uint32_t* __restrict__ cnt, uint32_t cap,
                                                                 uint32_t rsplit, uint32_t m, uint32_t k, const float* __restrict__ qnorm2,
                                                                 float eps_rel, float eps_abs, float xnorm_max, uint64_t* __restrict__ out,
-                                                                uint32_t pad, uint32_t* __restrict__ flags, const uint32_t* __restrict__ gthr) {
+                                                                uint32_t pad, uint32_t* __restrict__ flags, const uint32_t* __restrict__ gthr,
+                                                                const uint32_t* __restrict__ thr_fin = nullptr) {
 	__shared__ uint32_t pre[TC2_MAX_SPLIT + 8];
 	__shared__ uint64_t lists[8][32 * LPL];
 	__shared__ uint64_t fk[2048];
@@ -714,7 +700,9 @@ __global__ void __launch_bounds__(256) tc_select2_block_kernel(const uint64_t* _
 	__syncthreads();
 	const uint32_t w = w_s;
 	for (uint32_t i = w + threadIdx.x; i < pad; i += 256) o[i] = KEY_EMPTY;
-	if ((over_s || w > pad) && threadIdx.x == 0) atomicAdd(flags, 1u);
+	bool ver = true;
+	if (warp == 0) ver = tc2_bound_verified(thr_fin, q, rsplit, t, lane);
+	if ((over_s || w > pad || !ver) && threadIdx.x == 0) atomicAdd(flags, 1u);
 }
 
 // exactness of the bf16 single-GEMM mode for THIS query batch, decided on the device (no host round trip): the queries
@@ -724,7 +712,7 @@ __global__ void __launch_bounds__(256) tc_select2_block_kernel(const uint64_t* _
 // SIMT scan. The accumulator runs through sum (-2 q_i) x_i and takes ||x||^2 LAST (the norm step is the tile's final
 // MMA): for non-negative data the partial sums lie in [-2 d hi^2, 0] and the total in [-2 d hi^2, ||x||^2_max]; with
 // signed values the dot product can have either sign, so the total reaches 2 d amax^2 + ||x||^2_max.
-__global__ void tc_check_exact_kernel(const TcStats* __restrict__ qs, float xmin, float xmax, float d, float xnorm2_max,
+static __global__ void tc_check_exact_kernel(const TcStats* __restrict__ qs, float xmin, float xmax, float d, float xnorm2_max,
                                       uint32_t* __restrict__ flags) {
 	const float lo = fminf(xmin, f32_from_orderable(qs->vmin)), hi = fmaxf(xmax, f32_from_orderable(qs->vmax));
 	const float amax = fmaxf(fabsf(lo), fabsf(hi));
@@ -735,7 +723,7 @@ __global__ void tc_check_exact_kernel(const TcStats* __restrict__ qs, float xmin
 	if (!exact) atomicAdd(flags, 1u);
 }
 // start of a batch in one launch: query statistics reset, the batch's flags cleared, shared bounds set to +inf
-__global__ void tc_batch_init_kernel(TcStats* s, uint32_t* flags, uint32_t* gthr, uint32_t m) {
+static __global__ void tc_batch_init_kernel(TcStats* s, uint32_t* flags, uint32_t* gthr, uint32_t m) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i < m) gthr[i] = f32_orderable(__int_as_float(0x7f800000));
 	if (i < 4) flags[i] = 0u;
@@ -747,7 +735,7 @@ __global__ void tc_batch_init_kernel(TcStats* s, uint32_t* flags, uint32_t* gthr
 	}
 }
 
-__global__ void tc_stats_init_kernel(TcStats* s) {
+static __global__ void tc_stats_init_kernel(TcStats* s) {
 	s->vmin = f32_orderable(3.4e38f);
 	s->vmax = f32_orderable(-3.4e38f);
 	s->inexact = 0u;

@@ -56,12 +56,22 @@ __device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const void* tmap
 	    "l"(tmap), "r"(mbar_cluster_addr), "r"(c0), "r"(c1)
 	    : "memory");
 }
+// KIND 0: kind::f16 (bf16 x bf16 -> fp32). KIND 1: kind::i8 (u8 x u8 -> s32, K = 32 per instruction: the same 32 bytes
+// of every operand row as a bf16 step, so descriptors and k-block layout are unchanged).
+template <int KIND>
 __device__ __forceinline__ void tc_mma_2sm(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-	asm volatile(
-	    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-	    "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
-	    "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-	    : "memory");
+	if (KIND == 0)
+		asm volatile(
+		    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+		    "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+		    "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+		    : "memory");
+	else
+		asm volatile(
+		    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+		    "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+		    "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+		    : "memory");
 }
 // commit of the leader's MMAs: one arrival on the barrier at this shared-memory offset in BOTH CTAs of the pair
 __device__ __forceinline__ void tc_commit_2sm(uint64_t* bar) {
@@ -69,8 +79,11 @@ __device__ __forceinline__ void tc_commit_2sm(uint64_t* bar) {
 	             "h"((uint16_t)3)
 	             : "memory");
 }
-__device__ __forceinline__ uint32_t tc3_instr_desc() { // kind::f16, bf16 x bf16 -> fp32, K-major, M = 256 (pair), N = 256
-	return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC3_TN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+template <int KIND>
+__device__ __forceinline__ uint32_t tc3_instr_desc() { // K-major operands, M = 256 (pair), N = 256
+	// KIND 0: D = fp32 (bits 4-5 = 1), A = B = bf16 (format 1 at bits 7-9 / 10-12); KIND 1: D = s32 (2), A = B = unsigned 8 bit (0)
+	const uint32_t fmt = KIND == 0 ? (1u << 4) | (1u << 7) | (1u << 10) : (2u << 4);
+	return fmt | ((uint32_t)(TC3_TN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
 }
 
 struct Tc3Cfg {
@@ -88,7 +101,26 @@ struct Tc3Cfg {
 // ASTREAM = false: each CTA's 128 queries (all k-blocks) stay resident in shared memory (d <= 128 real-valued, <= 384
 // bf16-exact). ASTREAM = true: any d -- a ring slot carries [A k-block 16 KB | B k-block 16 KB | norm terms 4 KB], the
 // classic GEMM main loop (A comes from L2 again for every row tile: 64 B/clk per SM of L2 -> shared memory traffic).
-template <int NSTAGE, bool ASTREAM = false>
+// KIND 1 epilogue: int32 dot products of one 32-column chunk -> a'' = cnb[row] - 2 dot (inner product: bias - dot), kept as
+// the integer's bit pattern. The biased code norms are the same for every lane: broadcast 16-byte loads through L1.
+__device__ __forceinline__ void tc3_code_chunk(uint32_t (&d)[32], const int4* __restrict__ c4, bool ipm, int32_t ibias) {
+#pragma unroll
+	for (int i = 0; i < 8; ++i) {
+		const int4 c = ipm ? make_int4(ibias, ibias, ibias, ibias) : __ldg(c4 + i);
+		const int mul = ipm ? 1 : 2;
+		d[4 * i] = (uint32_t)(c.x - mul * (int)d[4 * i]);
+		d[4 * i + 1] = (uint32_t)(c.y - mul * (int)d[4 * i + 1]);
+		d[4 * i + 2] = (uint32_t)(c.z - mul * (int)d[4 * i + 2]);
+		d[4 * i + 3] = (uint32_t)(c.w - mul * (int)d[4 * i + 3]);
+	}
+}
+
+// KIND = 1 (the compressed scan of the quantised engine on the tensor cores): operands are 8-bit codes (query codes x base
+// codes, tcgen05.mma.kind::i8, exact int32 dot products in TMEM; p.kd counts 2-byte units, i.e. code bytes / 2), there is
+// no norm step, and the epilogue forms  a'' = cnb[row] - 2 dot  (p.cnb = sum c^2 + bias; inner product: bias - dot) as an
+// integer in (0, 2^31 - 2^23): such integers order like the positive floats with the same bits, so bound, lists, keys and
+// the select kernels of the float path are used unchanged (slack 0).
+template <int NSTAGE, bool ASTREAM = false, int KIND = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Tc3Cfg::THREADS, 1)
 tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
                       const __grid_constant__ CUtensorMap tmap_xx, const Tc2Params p) {
@@ -96,6 +128,7 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 	uint8_t* smem = (uint8_t*)(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
 	const uint32_t nkb = p.kd / TC_BK;
 	constexpr uint32_t STG = TC2_STAGE_BYTES + (ASTREAM ? TC_A_KB_BYTES : 0); // ring slot
+	constexpr int KMUL = KIND == 1 ? 2 : 1; // tensor-map elements per 2-byte unit of the operand rows (u8 codes: 2)
 	constexpr uint32_t BOFF = ASTREAM ? TC_A_KB_BYTES : 0;                    // B inside the slot; norm terms follow B
 	uint8_t* smA = smem;                                                    // [nkb][128 q][64 bf16] (resident form)
 	uint8_t* smOnes = smA + (ASTREAM ? 0 : (size_t)nkb * TC_A_KB_BYTES);    // [128 q][16 bf16]
@@ -148,7 +181,7 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 				if (!ASTREAM) {
 					if (leader) mbar_expect_tx(a_full, 2 * nkb * TC_A_KB_BYTES);
 					for (uint32_t kb = 0; kb < nkb; ++kb)
-						tma_load_2d_2sm(smA + (size_t)kb * TC_A_KB_BYTES, &tmap_q, (int)(kb * TC_BK), (int)q0, a_full_l);
+						tma_load_2d_2sm(smA + (size_t)kb * TC_A_KB_BYTES, &tmap_q, (int)(kb * TC_BK * KMUL), (int)q0, a_full_l);
 				}
 			}
 			__syncwarp();
@@ -159,11 +192,11 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 					const uint32_t s = it % NSTAGE, use = it / NSTAGE;
 					if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
 					if (elect_one()) {
-						const bool last = kb + 1 == nkb;
+						const bool last = KIND == 0 && kb + 1 == nkb; // the norm terms of the tile travel with its last k-block
 						const uint32_t full_l = mapa_u32(&full[s], 0);
 						if (leader) mbar_expect_tx(&full[s], 2 * (BOFF + TC2_B_STAGE_BYTES + (last ? TC2_X_BYTES : 0)));
-						if (ASTREAM) tma_load_2d_2sm(smB + (size_t)s * STG, &tmap_q, (int)(kb * TC_BK), (int)q0, full_l);
-						tma_load_2d_2sm(smB + (size_t)s * STG + BOFF, &tmap_x, (int)(kb * TC_BK), (int)row, full_l);
+						if (ASTREAM) tma_load_2d_2sm(smB + (size_t)s * STG, &tmap_q, (int)(kb * TC_BK * KMUL), (int)q0, full_l);
+						tma_load_2d_2sm(smB + (size_t)s * STG + BOFF, &tmap_x, (int)(kb * TC_BK * KMUL), (int)row, full_l);
 						if (last) tma_load_2d_2sm(smB + (size_t)s * STG + BOFF + TC2_B_STAGE_BYTES, &tmap_xx, 0, (int)row, full_l);
 					}
 					__syncwarp();
@@ -173,7 +206,7 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 	} else if (warp == Tc3Cfg::EPI_WARPS + 1) {
 		// ===================== MMA issuer (leader CTA only) =====================
 		if (my_tiles && leader) {
-			const uint32_t idesc = tc3_instr_desc();
+			const uint32_t idesc = tc3_instr_desc<KIND>();
 			const uint64_t a_desc0 = tc_smem_desc(smem_u32(smA)), b_desc0 = tc_smem_desc(smem_u32(smB) + BOFF);
 			const uint64_t as_desc0 = tc_smem_desc(smem_u32(smB)); // streamed A: first 16 KB of a slot
 			const uint64_t ones_desc = tc_smem_desc_sw32(smem_u32(smOnes)), x_desc0 = tc_smem_desc_sw32(smem_u32(smB) + BOFF + TC2_B_STAGE_BYTES);
@@ -181,7 +214,7 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 				mbar_wait(a_full, 0);
 				tc_fence_after();
 			}
-			if (!ASTREAM && nkb == 2 && NSTAGE == 6) {
+			if (KIND == 0 && !ASTREAM && nkb == 2 && NSTAGE == 6) {
 				// d <= 128, bf16-exact mode: a tile is 2 ring slots = 9 MMAs of 128 clk. One elected block per TILE with
 				// incrementally stepped slot numbers: the per-slot barrier / elect / descriptor overhead (~450 clk per slot
 				// in the generic loop) is otherwise not covered by so few queued MMAs.
@@ -197,11 +230,11 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 						const uint64_t bd0 = b_desc0 + (uint64_t)((s0 * TC2_STAGE_BYTES) >> 4), bd1 = bd0 + (uint64_t)(TC2_STAGE_BYTES >> 4);
 						const uint64_t ad1 = a_desc0 + (uint64_t)(TC_A_KB_BYTES >> 4);
 #pragma unroll
-						for (int k = 0; k < 4; ++k) tc_mma_2sm(d_tmem, a_desc0 + 2 * k, bd0 + 2 * k, idesc, k != 0 ? 1u : 0u);
+						for (int k = 0; k < 4; ++k) tc_mma_2sm<0>(d_tmem, a_desc0 + 2 * k, bd0 + 2 * k, idesc, k != 0 ? 1u : 0u);
 						tc_commit_2sm(&empty[s0]);
 #pragma unroll
-						for (int k = 0; k < 4; ++k) tc_mma_2sm(d_tmem, ad1 + 2 * k, bd1 + 2 * k, idesc, 1u);
-						tc_mma_2sm(d_tmem, ones_desc, x_desc0 + (uint64_t)(((s0 + 1) * TC2_STAGE_BYTES) >> 4), idesc, 1u);
+						for (int k = 0; k < 4; ++k) tc_mma_2sm<0>(d_tmem, ad1 + 2 * k, bd1 + 2 * k, idesc, 1u);
+						tc_mma_2sm<0>(d_tmem, ones_desc, x_desc0 + (uint64_t)(((s0 + 1) * TC2_STAGE_BYTES) >> 4), idesc, 1u);
 						tc_commit_2sm(&empty[s0 + 1]);
 						tc_commit_2sm(&tm_full[acc]);
 					}
@@ -224,8 +257,8 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 						const uint64_t ad0 = ASTREAM ? as_desc0 + (uint64_t)((s * STG) >> 4) : a_desc0 + (uint64_t)((kb * TC_A_KB_BYTES) >> 4);
 #pragma unroll
 						for (int k = 0; k < TC_BK / TC_UMMA_K; ++k)
-							tc_mma_2sm(d_tmem, ad0 + 2 * k, bd0 + 2 * k, idesc, (kb | (uint32_t)k) != 0 ? 1u : 0u);
-						if (kb + 1 == nkb) tc_mma_2sm(d_tmem, ones_desc, x_desc0 + (uint64_t)((s * STG) >> 4), idesc, 1u);
+							tc_mma_2sm<KIND>(d_tmem, ad0 + 2 * k, bd0 + 2 * k, idesc, (kb | (uint32_t)k) != 0 ? 1u : 0u);
+						if (KIND == 0 && kb + 1 == nkb) tc_mma_2sm<0>(d_tmem, ones_desc, x_desc0 + (uint64_t)((s * STG) >> 4), idesc, 1u);
 						tc_commit_2sm(&empty[s]);
 						if (kb + 1 == nkb) tc_commit_2sm(&tm_full[acc]);
 					}
@@ -265,47 +298,81 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 		t.cap = p.cap;
 		const uint32_t bsplit = p.buf_first + split * 2 + half;
 		t.cbuf = p.cand + ((size_t)(qvalid ? qg : 0) * p.rsplit + bsplit) * p.cap;
-		float* sc = sc_all + warp * 1024 + lane;
+		float* sc = sc_all + warp * 1024 + lane; // hit-path scratch: value j of this lane at sc[j * 32]
 		const uint32_t tm_empty_l0 = mapa_u32(&tm_empty[0], 0), tm_empty_l1 = mapa_u32(&tm_empty[1], 0);
 		uint32_t gnext = f32_orderable(INF);
+		// more than 16 results per query (thr_out): a stream's bound is ITS 16th smallest; adopting the smallest such bound of
+		// all streams would cut into the k'-th smallest overall, so the streams keep to themselves
+		const bool share = p.thr_out == nullptr;
 		for (uint32_t lt = 0; lt < my_tiles; ++lt) {
 			const uint32_t acc = lt & 1;
 			const uint32_t row0 = (p.tile_first + t_begin + lt) * TC3_TN + half * TC2_TN;
-			if (qvalid) {
+			if (qvalid && share) {
 				t.thr = fminf(t.thr, f32_from_orderable(gnext));
 				gnext = __ldcg(p.gthr + qg);
 			}
 			mbar_wait(&tm_full[acc], (lt >> 1) & 1);
 			tc_fence_after();
 			const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * TC3_TN + half * TC2_TN;
-			// the thread's 128 accumulator columns go to registers in one go and the accumulator is handed back to the MMA
-			// warp BEFORE they are looked at: a warp that has hits to work through no longer holds the other 15 warps of
-			// the pair (and the next MMA) up, it only has to be back in time for its next tile
-			uint32_t dA[32], dB[32], dC[32], dD[32];
-			tc_ld32_nowait(tbase, dA);
-			tc_ld32_nowait(tbase + 32, dB);
-			tc_ld32_nowait(tbase + 64, dC);
-			tc_ld32_nowait(tbase + 96, dD);
-			tc_wait_ld(dA);
-			tc_wait_ld(dB);
-			tc_wait_ld(dC);
-			tc_wait_ld(dD);
-			tc_fence_before();
-			__syncwarp();
-			if (lane == 0) mbar_arrive_cluster(acc ? tm_empty_l1 : tm_empty_l0); // all 16 epilogue warps of the pair -> leader
-			// (the triple minima are recomputed inside the hit path: keeping them live across the vote costs spills)
-			const float mnA = tc2_chunk_min(dA);
-			if (__any_sync(FULL, mnA <= t.thr)) tc2_chunk_hits(t, dA, sc, row0, p.n);
-			const float mnB = tc2_chunk_min(dB);
-			if (__any_sync(FULL, mnB <= t.thr)) tc2_chunk_hits(t, dB, sc, row0 + 32, p.n);
-			const float mnC = tc2_chunk_min(dC);
-			if (__any_sync(FULL, mnC <= t.thr)) tc2_chunk_hits(t, dC, sc, row0 + 64, p.n);
-			const float mnD = tc2_chunk_min(dD);
-			if (__any_sync(FULL, mnD <= t.thr)) tc2_chunk_hits(t, dD, sc, row0 + 96, p.n);
-			if (t.thr < pub) { atomicMin(p.gthr + qg, f32_orderable(t.thr)); pub = t.thr; }
+			if (KIND == 0) {
+				// the thread's 128 accumulator columns go to registers in one go and the accumulator is handed back to the MMA
+				// warp BEFORE they are looked at: a warp that has hits to work through no longer holds the other 15 warps of
+				// the pair (and the next MMA) up, it only has to be back in time for its next tile
+				uint32_t dA[32], dB[32], dC[32], dD[32];
+				tc_ld32_nowait(tbase, dA);
+				tc_ld32_nowait(tbase + 32, dB);
+				tc_ld32_nowait(tbase + 64, dC);
+				tc_ld32_nowait(tbase + 96, dD);
+				tc_wait_ld(dA);
+				tc_wait_ld(dB);
+				tc_wait_ld(dC);
+				tc_wait_ld(dD);
+				tc_fence_before();
+				__syncwarp();
+				if (lane == 0) mbar_arrive_cluster(acc ? tm_empty_l1 : tm_empty_l0); // all 16 epilogue warps of the pair -> leader
+					const float mnA = tc2_chunk_min(dA);
+				if (__any_sync(FULL, mnA <= t.thr)) tc2_chunk_hits(t, dA, sc, row0, p.n);
+				const float mnB = tc2_chunk_min(dB);
+				if (__any_sync(FULL, mnB <= t.thr)) tc2_chunk_hits(t, dB, sc, row0 + 32, p.n);
+				const float mnC = tc2_chunk_min(dC);
+				if (__any_sync(FULL, mnC <= t.thr)) tc2_chunk_hits(t, dC, sc, row0 + 64, p.n);
+				const float mnD = tc2_chunk_min(dD);
+				if (__any_sync(FULL, mnD <= t.thr)) tc2_chunk_hits(t, dD, sc, row0 + 96, p.n);
+			} else {
+				// 8-bit codes: two chunks of 32 columns at a time (the code norms need registers too), the accumulator is handed
+				// back after the last TMEM read — a tile is 32 MMA steps at d = 960, there is time
+				const int4* c4 = reinterpret_cast<const int4*>(p.cnb + row0);
+				const bool ipm = p.scale > -1.5f;
+				uint32_t dA[32], dB[32];
+				tc_ld32_nowait(tbase, dA);
+				tc_ld32_nowait(tbase + 32, dB);
+				tc_wait_ld(dA);
+				tc_wait_ld(dB);
+				tc3_code_chunk(dA, c4, ipm, p.ibias);
+				const float mnA = tc2_chunk_min(dA);
+				if (__any_sync(FULL, mnA <= t.thr)) tc2_chunk_hits(t, dA, sc, row0, p.n);
+				tc_ld32_nowait(tbase + 64, dA);
+				tc3_code_chunk(dB, c4 + 8, ipm, p.ibias);
+				const float mnB = tc2_chunk_min(dB);
+				if (__any_sync(FULL, mnB <= t.thr)) tc2_chunk_hits(t, dB, sc, row0 + 32, p.n);
+				tc_wait_ld(dA);
+				tc_ld32_nowait(tbase + 96, dB);
+				tc3_code_chunk(dA, c4 + 16, ipm, p.ibias);
+				const float mnC = tc2_chunk_min(dA);
+				if (__any_sync(FULL, mnC <= t.thr)) tc2_chunk_hits(t, dA, sc, row0 + 64, p.n);
+				tc_wait_ld(dB);
+				tc_fence_before();
+				__syncwarp();
+				if (lane == 0) mbar_arrive_cluster(acc ? tm_empty_l1 : tm_empty_l0);
+				tc3_code_chunk(dB, c4 + 24, ipm, p.ibias);
+				const float mnD = tc2_chunk_min(dB);
+				if (__any_sync(FULL, mnD <= t.thr)) tc2_chunk_hits(t, dB, sc, row0 + 96, p.n);
+			}
+			if (share && t.thr < pub) { atomicMin(p.gthr + qg, f32_orderable(t.thr)); pub = t.thr; }
 		}
 		if (qvalid) {
 			p.cnt[(size_t)qg * p.rsplit + bsplit] = t.cnt;
+			if (p.thr_out) p.thr_out[(size_t)qg * p.rsplit + bsplit] = f32_orderable(t.thr); // the bound this stream ended with
 			if (p.seed_out) {
 #pragma unroll
 				for (int j = 0; j < TC2_KK; ++j) p.seed_out[(size_t)qg * 32 + half * 16 + j] = t.v[j];

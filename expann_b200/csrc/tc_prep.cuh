@@ -18,7 +18,7 @@ struct TcStats { uint32_t vmin, vmax, inexact, nmax; };
 // terms hi+mid+lo (24 bits: exact for integer norms < 2^24), each HALVED and written to BOTH 16-byte halves of the
 // 32-byte row ([h/2 m/2 l/2 0 0 0 0 0 | h/2 m/2 l/2 0 0 0 0 0]) so that the extra MMA K-step against a row of
 // [1 1 1 0 0 0 0 0 | 1 1 1 0 0 0 0 0] adds ||x||^2 whatever the 32B-swizzle does to the two halves; zeros for IP.
-__global__ void tc_convert_kernel(const float* __restrict__ src, size_t src_stride, uint32_t d, size_t rows,
+static __global__ void tc_convert_kernel(const float* __restrict__ src, size_t src_stride, uint32_t d, size_t rows,
                                   __nv_bfloat16* __restrict__ dst, uint32_t kd, int mode, int is_query,
                                   float* __restrict__ norm2, TcStats* __restrict__ stats, float scale = 1.f,
                                   __nv_bfloat16* __restrict__ xx = nullptr, int xx_norm = 0) {
@@ -82,7 +82,7 @@ __global__ void tc_convert_kernel(const float* __restrict__ src, size_t src_stri
 	}
 }
 
-__global__ void tc_fill_kernel(float* p, size_t from, size_t to, float v) {
+static __global__ void tc_fill_kernel(float* p, size_t from, size_t to, float v) {
 	const size_t i = from + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i < to) p[i] = v;
 }

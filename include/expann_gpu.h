@@ -152,6 +152,9 @@ int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
  * | 2 always), "tc_boot" (seeding launch: 0 off | 1 one-term formats and >= 8192 queries | 2 always), "tc_v1" (force the
  * chunked first form), "tc_real" (real-valued rows, before build(): 1 (default) one bf16 term per value, falling back to the
  * two-term split when a batch had to be redone | 0 the split from the start).
+ * Quantised scan engine: "quant_tc" (0/1, default 1: batches of at least "quant_tc_min_batch" queries (default 32) run the
+ * code scan as a tensor-core candidate filter, tcgen05.mma.kind::i8 on the 8-bit codes, with the SIMT scan as its queued
+ * redo; same result).
  * Multi-device handles: "mgpu_row_groups" (0 (default) one row shard per GPU | R row shards, each on n_devices / R GPUs that
  * split the queries of a call; before build()); every other knob is applied to each GPU's engine.
  * Unknown names: EXPANN_ERR_ARG. */

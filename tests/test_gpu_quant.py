@@ -95,3 +95,76 @@ def test_ranged_q8(ex, oracle):
     rec = np.mean([len(set(a.tolist()) & set(b.tolist())) / 10 for a, b in zip(ids, bi)])
     assert rec >= 0.9, rec
     e.close()
+
+
+def _quant_run(ex, base, q, k, kprime, quantizer, metric, tc, min_batch=None, nsplit=None):
+    e = ex.QuantScanEngine(quantizer=quantizer, metric=metric, kprime=kprime)
+    e.set_option("quant_tc", tc)
+    if min_batch is not None:
+        e.set_option("quant_tc_min_batch", min_batch)
+    if nsplit is not None:
+        e.set_option("nsplit", nsplit)
+    e.store_many_vectors(base)
+    e.build()
+    out = e.query_k_batch(q, k)
+    st = e.stats()
+    e.close()
+    return out + (st,)
+
+
+@pytest.mark.parametrize("metric", [0, 1])
+@pytest.mark.parametrize("n,m,d,kprime", [(20011, 300, 128, 100), (20011, 300, 128, 10), (9000, 130, 960, 100), (5000, 64, 96, 16),
+                                          (70000, 700, 512, 128), (300, 40, 128, 100)])
+def test_code_scan_on_tensor_cores_equals_simt(ex, oracle, metric, n, m, d, kprime):
+    """K6 as a tensor-core candidate filter (tcgen05.mma.kind::i8, csrc/tc_i8.cu) must leave exactly the SIMT scan's k'
+    best codes: results of the two forms bit-identical (ids, fp32 keys, counts) for quantizer_simple<u8> codes, whose
+    scores are the reference's dist2_compressed integers (src/antitopo_engine.h:38-61), on resident (d <= 512) and
+    streamed (d = 960) query tiles, k' <= 16 (exact per-stream lists) and k' > 16 (verified union of per-stream lists);
+    and against the oracle's compressed scan"""
+    rng = np.random.default_rng(n + d + kprime + metric)
+    base = rng.integers(0, 256, (n, d)).astype(np.float32)
+    q = rng.integers(0, 256, (m, d)).astype(np.float32)
+    a = _quant_run(ex, base, q, 10, kprime, 0, metric, tc=1)
+    b = _quant_run(ex, base, q, 10, kprime, 0, metric, tc=0)
+    # (a base too small for enough row streams per query at k' > 16 stays on the SIMT scan: the 300-row case)
+    assert a[3]["tc_launches"] == (0 if n == 300 else 1) and a[3]["tc_fallbacks"] == 0 and b[3]["tc_launches"] == 0
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+    if n <= 20011:
+        codes = oracle.quant_simple_u8(base)
+        oi, od = oracle.scan_u8_query(base, codes, q, 10, kprime, metric=metric, threads=16)
+        exact = d * 255 * 255 < 2 ** 24
+        assert_topk_parity(a[0], a[1], oi, od, base, q, metric="ip" if metric else "l2", exact=exact, tag=f"code tc d{d} m{metric}")
+
+
+def test_code_scan_tensor_cores_ranged_q8_ties_and_redo(ex):
+    """ranged q8 codes (7-bit, many score ties: the k'-th place is decided by id) through both forms; and rows ordered so
+    that one row range owns far more than 16 of a query's best 100 codes: the select kernel's verification must raise the
+    flag and the queued SIMT redo must deliver the same answer (counted in tc_fallbacks)"""
+    from expann_b200 import datasets
+    base, q = datasets.make("gist", 30000, 200, 960)
+    for metric in (0, 1):
+        a = _quant_run(ex, base, q, 10, 100, 1, metric, tc=1)
+        b = _quant_run(ex, base, q, 10, 100, 1, metric, tc=0)
+        assert a[3]["tc_launches"] == 1 and a[3]["tc_fallbacks"] == 0
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    rng = np.random.default_rng(9)
+    n, d = 60000, 128
+    base = rng.integers(0, 256, (n, d)).astype(np.float32)
+    c = rng.integers(100, 156, d).astype(np.float32)
+    base[1000:1400] = np.clip(c + rng.integers(-3, 4, (400, d)), 0, 255)     # 400 near-duplicates of one point, contiguous rows
+    q = np.clip(c + rng.integers(-2, 3, (64, d)), 0, 255).astype(np.float32)
+    a = _quant_run(ex, base, q, 10, 100, 0, 0, tc=1, nsplit=4)
+    b = _quant_run(ex, base, q, 10, 100, 0, 0, tc=0)
+    assert a[3]["tc_launches"] == 1 and a[3]["tc_fallbacks"] == 1
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+def test_code_scan_small_batches_stay_on_the_simt_scan(ex):
+    rng = np.random.default_rng(10)
+    base = rng.integers(0, 256, (8000, 128)).astype(np.float32)
+    q = rng.integers(0, 256, (31, 128)).astype(np.float32)
+    a = _quant_run(ex, base, q, 10, 40, 0, 0, tc=1)
+    assert a[3]["tc_launches"] == 0 and a[3]["scan_launches"] == 1
+    b = _quant_run(ex, base, q, 10, 40, 0, 0, tc=1, min_batch=8)
+    assert b[3]["tc_launches"] == 1 and b[3]["tc_fallbacks"] == 0
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
