@@ -104,6 +104,8 @@ static int tc_prepare(expann_gpu* h, int fmt, TcStats* s_out) {
 	return encode_tensor_map_bf16(h, &h->tmap_xb, h->tc_xb.p, h->tc_kd, h->n, TC_BN);
 }
 
+static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st, bool* fell_back);
+
 // build(): decide the operand format from the base values and materialise the bf16 operand + ||x||^2.
 //   mode 1  bf16-exact integers whose accumulator stays below 2^24: one GEMM, error bound 0;
 //   mode 3  anything else, one bf16 term per value (the SAME operand as mode 1: kd = d, a third of the split's flops)
@@ -127,7 +129,28 @@ int tc_finalize(expann_gpu* h) {
 	const double nmax = (double)h->tc_xnorm_max * h->tc_xnorm_max, dot2 = 2.0 * (double)h->d * amax * amax;
 	const double acc_max = h->tc_xmin >= 0.f ? std::max(dot2, nmax) : dot2 + nmax;
 	if (!s.inexact && acc_max < 16777216.0) { h->tc_mode = 1; return EXPANN_OK; }
-	if (h->opt_tc_real == 1) { h->tc_mode = 3; return EXPANN_OK; }
+	if (h->opt_tc_real == 1) {
+		// Probe: the first rows of the base as a query batch through the one-term filter. Data whose distances are too
+		// concentrated for its slack (GIST-like d = 960, u8 values at d = 512: hundreds of survivors per query) is found out
+		// here instead of by the first user batch, whose redo by the SIMT scan costs tens of milliseconds.
+		h->tc_mode = 3;
+		const size_t pm = std::min<size_t>(h->n, 256), pk = std::min<size_t>(h->n, 10);
+		DevBuf probe_keys;
+		EXPANN_CUDA(h, probe_keys.ensure(pm * pk * 8));
+		bool fb = false;
+		int rc = tc_batch2(h, h->base, pm, pk, probe_keys.as<uint64_t>(), h->stream, &fb);
+		uint32_t redone = 0;
+		if (!rc) {
+			EXPANN_CUDA(h, cudaStreamSynchronize(h->stream));
+			EXPANN_CUDA(h, cudaMemcpy(&redone, h->tc_fbcount.p, 4, cudaMemcpyDeviceToHost));
+			EXPANN_CUDA(h, cudaMemset(h->tc_fbcount.p, 0, 4)); // the probe is not a user batch: not counted in tc_fallbacks
+		}
+		probe_keys.release();
+		h->tc_flag_pending = false;
+		h->stats.tc_launches = 0;
+		if (rc) return rc;
+		if (!redone) return EXPANN_OK;
+	}
 	if (int rc = tc_prepare(h, 2, nullptr)) return rc;
 	h->tc_mode = 2;
 	return EXPANN_OK;

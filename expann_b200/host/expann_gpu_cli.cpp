@@ -99,6 +99,57 @@ template <class T> static bool tvecs_read(const std::string& path, std::vector<T
 	return rows > 0;
 }
 
+// Binary dataset cache: the reference keeps a dataset (vectors, queries, ground truth) as one text-JSON file
+// ./data/<name>.dataset (save_imtd / load_imtd / exists_imtd, src/dataset_loader.h:42-95) so that the brute-force ground
+// truth is computed once; the same idea as raw little-endian arrays ("EXPANNDS", version, n, m, k, dim, vectors, queries,
+// n_answers x {count, ids}): 1M x 128 loads in a fraction of a second instead of minutes of JSON parsing.
+static const char DS_MAGIC[8] = { 'E', 'X', 'P', 'A', 'N', 'N', 'D', 'S' };
+static bool save_dataset_cache(const std::string& path, const dataset& ds) {
+	std::ofstream f(path, std::ios::binary);
+	if (!f) return false;
+	const uint64_t hdr[5] = { 1, ds.n, ds.m, ds.k, ds.dim };
+	f.write(DS_MAGIC, 8);
+	f.write(reinterpret_cast<const char*>(hdr), sizeof(hdr));
+	f.write(reinterpret_cast<const char*>(ds.vecs.data()), (std::streamsize)(ds.vecs.size() * 4));
+	f.write(reinterpret_cast<const char*>(ds.queries.data()), (std::streamsize)(ds.queries.size() * 4));
+	for (const auto& a : ds.answers) {
+		const uint64_t c = a.size();
+		f.write(reinterpret_cast<const char*>(&c), 8);
+		for (size_t id : a) { const uint64_t v = id; f.write(reinterpret_cast<const char*>(&v), 8); }
+	}
+	return (bool)f;
+}
+static bool load_dataset_cache(const std::string& path, dataset& ds) {
+	std::ifstream f(path, std::ios::binary);
+	if (!f) return false;
+	char magic[8];
+	uint64_t hdr[5];
+	if (!f.read(magic, 8) || std::memcmp(magic, DS_MAGIC, 8) != 0 || !f.read(reinterpret_cast<char*>(hdr), sizeof(hdr)) || hdr[0] != 1) return false;
+	f.seekg(0, std::ios::end);
+	const uint64_t fsize = (uint64_t)f.tellg();
+	f.seekg(8 + sizeof(hdr), std::ios::beg);
+	const uint64_t n = hdr[1], m = hdr[2], k = hdr[3], dim = hdr[4];
+	if (dim == 0 || dim > (1u << 20) || n > fsize / (4 * dim) || m > fsize / (4 * dim) || (n + m) * dim * 4 + m * 8 > fsize) return false; // sizes vs file size
+	ds.n = n; ds.m = m; ds.k = k; ds.dim = dim;
+	ds.vecs.resize(n * dim);
+	ds.queries.resize(m * dim);
+	if (!f.read(reinterpret_cast<char*>(ds.vecs.data()), (std::streamsize)(n * dim * 4)) ||
+	    !f.read(reinterpret_cast<char*>(ds.queries.data()), (std::streamsize)(m * dim * 4)))
+		return false;
+	ds.answers.assign(m, {});
+	for (uint64_t q = 0; q < m; ++q) {
+		uint64_t c;
+		if (!f.read(reinterpret_cast<char*>(&c), 8) || c > n) return false;
+		ds.answers[q].resize(c);
+		for (uint64_t j = 0; j < c; ++j) {
+			uint64_t v;
+			if (!f.read(reinterpret_cast<char*>(&v), 8) || v >= n) return false;
+			ds.answers[q][j] = (size_t)v;
+		}
+	}
+	return true;
+}
+
 static dataset make_synthetic(size_t n, size_t m, size_t k, size_t d, const std::string& name) {
 	// load_synethetic_uniform_sphere_points_no_cache (src/dataset_loader.h:10-41): iid N(0,1) components, base first
 	// then queries; the reference seeds from random_device (src/randomgeometry.h:80-82) — fixed seed here.
@@ -227,7 +278,8 @@ int main(int argc, char** argv) {
 	}
 	if (argc == 2 && (std::string(argv[1]) == "--help" || std::string(argv[1]) == "-h")) {
 		std::cout << "usage: expann_gpu --config f.json [--dataset Synthetic|Sift1M] [--ds_name s] [--n N] [--m M] [--d D] [--k K]\n"
-		             "                  [--engines bf,graph,quant] [--M0 32] [--per_query 0|1] [--out_prefix dir/] [--gpus G]\n";
+		             "                  [--engines bf,graph,quant] [--M0 32] [--per_query 0|1] [--out_prefix dir/] [--gpus G]\n"
+		             "                  [--sift_dir datasets/sift/] [--cache 0|1] [--cache_file path]\n";
 		return 0;
 	}
 	if (!config_file.empty()) {
@@ -263,8 +315,24 @@ int main(int argc, char** argv) {
 			} else
 				ground_truth(ds);
 		} else {
-			ds = make_synthetic(n, m, k, d, ds_name);
-			ground_truth(ds);
+			// load_synethetic_uniform_sphere_points (src/dataset_loader.h:76-95): the cached dataset if there is one, else make
+			// it (vectors, queries, exhaustive ground truth) and cache it; --cache 0 is the _no_cache form (:10-41)
+			const std::string cache = "./data/synthetic_uniform_sphere_n" + std::to_string(n) + "_dim" + std::to_string(d) + "_m" +
+			                          std::to_string(m) + "_k" + std::to_string(k) + ".dataset.bin";
+			const std::string cache_path = get("cache_file", cache);
+			const bool use_cache = get("cache", "0") == "1";
+			if (use_cache && load_dataset_cache(cache_path, ds)) {
+				ds.name = ds_name;
+				std::printf("dataset cache: loaded %s (n=%zu m=%zu k=%zu dim=%zu)\n", cache_path.c_str(), ds.n, ds.m, ds.k, ds.dim);
+			} else {
+				ds = make_synthetic(n, m, k, d, ds_name);
+				ground_truth(ds);
+				if (use_cache) {
+					mkdirs(cache_path.substr(0, cache_path.rfind('/') == std::string::npos ? 0 : cache_path.rfind('/')));
+					if (save_dataset_cache(cache_path, ds)) std::printf("dataset cache: saved %s\n", cache_path.c_str());
+					else std::cerr << "dataset cache: cannot write " << cache_path << std::endl; // the reference fails silently here (src/dataset_loader.h:65-76)
+				}
+			}
 		}
 		std::vector<bench_data> latest;
 		auto report = [&](const bench_data& b) {

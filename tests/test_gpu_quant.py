@@ -168,3 +168,26 @@ def test_code_scan_small_batches_stay_on_the_simt_scan(ex):
     b = _quant_run(ex, base, q, 10, 40, 0, 0, tc=1, min_batch=8)
     assert b[3]["tc_launches"] == 1 and b[3]["tc_fallbacks"] == 0
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+def test_primitives_wide_goldens(ex, oracle):
+    """the GPU primitives against 256 reference-minted pairs per dimension (d = 64, 128, 832, 960) incl. rows of extreme
+    values: fp32 kernels within 1e-5 relative of the reference's AVX-512 and Eigen results (another summation order),
+    dist2_compressed bit-exact, int8 / int16 equal to the mathematically correct value"""
+    from tests.util import WIDE_DIMS, wide_primitive_inputs
+    g, inp = gold("primitives_wide"), wide_primitive_inputs()
+    for d in WIDE_DIMS:
+        a, b = inp[f"a{d}"], inp[f"b{d}"]
+        got = ex.pair_distances(0, a, b)
+        for ref in (g[f"avx_dist2_{d}"], g[f"eigen_dist2_{d}"]):
+            assert np.all(np.abs(got.astype(np.float64) - ref) <= 1e-5 * np.abs(ref.astype(np.float64)) + 1e-45)
+        assert np.all(got[248:252] == 0) and np.all(got[254:256] == 0)           # identical vectors / zero vectors
+        assert np.array_equal(got[232:248], g[f"avx_dist2_{d}"][232:248]) or d * 255 * 255 >= 2 ** 24   # u8-valued rows: exact
+        dot = ex.pair_distances(1, a, b)
+        scale = np.linalg.norm(a.astype(np.float64), axis=1) * np.linalg.norm(b.astype(np.float64), axis=1)
+        assert np.all(np.abs(dot.astype(np.float64) - g[f"avx_dot_{d}"]) <= 1e-5 * scale + 1e-45)
+        assert np.array_equal(ex.pair_distances(2, inp[f"cq{d}"], inp[f"cc{d}"]), g[f"compressed_{d}"])
+        a8, b8 = inp[f"i8a{d}"], inp[f"i8b{d}"]
+        assert np.array_equal(ex.pair_distances(3, a8, b8), ((a8.astype(np.int64) - b8.astype(np.int64)) ** 2).sum(1).astype(np.int32))
+        a16, b16 = inp[f"i16a{d}"], inp[f"i16b{d}"]
+        assert np.array_equal(ex.pair_distances(4, a16, b16), ((a16.astype(np.int64) - b16.astype(np.int64)) ** 2).sum(1).astype(np.int32))

@@ -245,6 +245,7 @@ def test_streamed_query_operand(ex, oracle, n, m, d, kind, astream):
     for metric in (0, 1):
         e = ex.BruteForceEngine(metric=metric)
         e.set_option("tc_astream", astream)
+        e.set_option("tc_real", 0)   # the two-term split: the format whose rows are too long for a resident query tile
         e.store_many_vectors(base); e.build()
         ids, dists, counts = e.query_k_batch(q, 10)
         st = e.stats(); e.close()
@@ -309,14 +310,16 @@ def test_signed_integer_rows(ex, oracle, amp):
 
 
 def test_one_term_format_moves_to_split_after_a_redo(ex, oracle):
-    """mode 3 (one bf16 term per value) on data whose distances are too concentrated for its slack: nearly every row
-    survives, the batch is redone by the SIMT scan (exact answer), and the NEXT batch runs in the two-term split
-    (tc_mode 2) without a redo"""
+    """mode 3 (one bf16 term per value) passes the build probe on this base, but the QUERIES carry a large component
+    orthogonal to the data: the slack (2^-6 |q| max|x|) then dwarfs the spread of the distances, every row survives, the
+    batch is redone by the SIMT scan (exact answer), and the NEXT batch runs in the two-term split (tc_mode 2)"""
     rng = np.random.default_rng(31)
     n, d = 60_000, 64
-    c = rng.standard_normal(d).astype(np.float32) * 40.0
-    base = (c + 1e-3 * rng.standard_normal((n, d))).astype(np.float32)   # a tight ball far from the origin
-    q = (c + 1e-3 * rng.standard_normal((300, d))).astype(np.float32)
+    base = np.zeros((n, d), np.float32)
+    base[:, :32] = rng.standard_normal((n, 32))
+    q = np.zeros((300, d), np.float32)
+    q[:, :32] = rng.standard_normal((300, 32))
+    q[:, 32:] = 200.0
     e = ex.BruteForceEngine()
     e.store_many_vectors(base); e.build()
     assert e.stats()["tc_mode"] == 3
@@ -330,3 +333,20 @@ def test_one_term_format_moves_to_split_after_a_redo(ex, oracle):
     assert st["tc_mode"] == 2 and st["tc_launches"] >= 2
     assert np.array_equal(b[0], ref[0]) and np.array_equal(b[1], ref[1])
     e.close()
+
+
+def test_build_probe_picks_the_operand_format(ex):
+    """build() probes the one-term format with the first rows of the base as queries: data whose distances are too
+    concentrated for its slack (GIST-like d = 960; u8 values at d = 512) starts in the two-term split, Deep- and
+    Gaussian-like data stays in the one-term format; no user batch is redone either way"""
+    rng = np.random.default_rng(55)
+    cases = [("unit960", rng.random((30000, 960), dtype=np.float32), 2), ("u8_512", rng.integers(0, 256, (30000, 512)).astype(np.float32), 2),
+             ("gauss128", rng.standard_normal((30000, 128)).astype(np.float32), 3)]
+    x = rng.standard_normal((30000, 96)).astype(np.float32)
+    cases.append(("deep96", x / np.linalg.norm(x, axis=1, keepdims=True), 3))
+    for name, base, mode in cases:
+        q = base[rng.integers(0, len(base), 300)] + (0.01 * rng.standard_normal((300, base.shape[1]))).astype(np.float32)
+        a = run(ex, base, q, 10)
+        assert a[3]["tc_mode"] == mode and a[3]["tc_launches"] >= 1 and a[3]["tc_fallbacks"] == 0, (name, a[3])
+        b = run(ex, base, q, 10, tc=0)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]), name

@@ -89,3 +89,27 @@ def test_live_reference_matches_oracle(oracle, reference_dyn):
         i1, d1, _ = oracle.bf_query(base, q, 7)
         i2, d2, _ = reference_dyn.bf(base).query(q, 7)
         assert np.array_equal(i1, i2) and np.array_equal(d1, d2)
+
+
+def test_primitives_wide_goldens(oracle):
+    """256 pairs per dimension incl. d = 832 and rows of extreme values (tests/golden/make_golden_wide.py): the oracle's
+    restatements of the reference kernels are bit-exact against what the UNMODIFIED reference computed"""
+    from tests.util import WIDE_DIMS, wide_primitive_inputs
+    g, inp = gold("primitives_wide"), wide_primitive_inputs()
+    for d in WIDE_DIMS:
+        a, b = inp[f"a{d}"], inp[f"b{d}"]
+        got = np.array([oracle.dist2(a[i], b[i]) for i in range(256)], np.float32)
+        assert np.array_equal(got, g[f"avx_dist2_{d}"]), d                   # src/distance.h:112-148
+        if d % 128 == 0:
+            assert np.array_equal(got, g[f"avx128_dist2_{d}"]), d            # src/distance.h:86-111
+        got = np.array([oracle.dot(a[i], b[i]) for i in range(256)], np.float32)
+        assert np.array_equal(got, g[f"avx_dot_{d}"]), d                     # src/distance.h:181-190
+        for i in range(256):
+            assert oracle.dist2_u8(inp[f"cq{d}"][i], inp[f"cc{d}"][i]) == g[f"compressed_{d}"][i]          # antitopo_engine.h:38-61
+            assert oracle.int_dist("orc_dist2_i8_asref", np.ascontiguousarray(inp[f"i8a{d}"][i]),
+                                   np.ascontiguousarray(inp[f"i8b{d}"][i])) == g[f"i8_asref_{d}"][i]       # distance.h:29-53 as written
+            assert oracle.int_dist("orc_dist2_i16_asref", np.ascontiguousarray(inp[f"i16a{d}"][i]),
+                                   np.ascontiguousarray(inp[f"i16b{d}"][i])) == g[f"i16_asref_{d}"][i]     # distance.h:14-27 as written
+        # the reference's 16-bit mullo wraps for |diff| > 181 (rows 240-247: diff 362): as-written differs from the true value
+        t = ((inp[f"i16a{d}"][240].astype(np.int64) - inp[f"i16b{d}"][240].astype(np.int64)) ** 2).sum()
+        assert int(g[f"i16_asref_{d}"][240]) != int(t)

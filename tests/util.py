@@ -54,3 +54,36 @@ def assert_topk_parity(ids, dists, exp_ids, exp_dists, base, q, metric="l2", exa
         rel = np.abs(d[fin] - e[fin]) / np.maximum(np.abs(e[fin]), 1e-30)
         assert rel.max(initial=0.0) <= REL_TOL, f"{tag}: distance rel err {rel.max()}"
     return swaps
+
+
+WIDE_DIMS = (64, 128, 832, 960)
+
+
+def wide_primitive_inputs():
+    """seeded inputs of tests/golden/primitives_wide.npz (256 pairs per dimension; rows of extreme values: 1e15-scale,
+    denormal-scale squares, u8-valued, identical vectors, zeros; largest u8 / int8 differences; int16 differences past the
+    reference's 16-bit mullo range). tests/golden/make_golden_wide.py runs the reference on exactly these arrays."""
+    NP = 256
+    rng = np.random.default_rng(2026)
+    out = {}
+    for d in WIDE_DIMS:
+        a = rng.standard_normal((NP, d)).astype(np.float32) * 3
+        b = rng.standard_normal((NP, d)).astype(np.float32) * 3
+        a[200:216] *= np.float32(1e15); b[200:216] *= np.float32(1e15)
+        a[216:232] *= np.float32(1e-20); b[216:232] *= np.float32(1e-20)
+        a[232:248] = rng.integers(0, 256, (16, d)); b[232:248] = rng.integers(0, 256, (16, d))
+        b[248:252] = a[248:252]
+        a[252:256] = 0; b[254:256] = 0
+        out[f"a{d}"], out[f"b{d}"] = a, b
+        qi = rng.integers(0, 256, (NP, d)).astype(np.float32) + rng.random((NP, d)).astype(np.float32) * 0.9
+        ci = rng.integers(0, 256, (NP, d)).astype(np.uint8)
+        qi[240:248] = 255.0; ci[240:244] = 0; ci[244:248] = 255
+        qi[248:256] = 0.0; ci[248:252] = 255
+        out[f"cq{d}"], out[f"cc{d}"] = qi, ci
+        i8a = rng.integers(-128, 128, (NP, d)).astype(np.int8); i8b = rng.integers(-128, 128, (NP, d)).astype(np.int8)
+        i8a[240:248] = 127; i8b[240:248] = -128
+        out[f"i8a{d}"], out[f"i8b{d}"] = i8a, i8b
+        i16a = rng.integers(-300, 300, (NP, d)).astype(np.int16); i16b = rng.integers(-300, 300, (NP, d)).astype(np.int16)
+        i16a[240:248] = 181; i16b[240:248] = -181
+        out[f"i16a{d}"], out[f"i16b{d}"] = i16a, i16b
+    return out
