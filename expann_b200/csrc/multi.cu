@@ -23,12 +23,65 @@
 // All kids are driven from the calling thread; every launch is asynchronous, cross-device ordering is by CUDA events.
 #include "engine.h"
 #include <algorithm>
+#include <condition_variable>
 #include <cstring>
+#include <functional>
+#include <memory>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <utility>
 
 namespace expann {
+
+// One parked host thread per kid: a call's per-kid launches (a dozen driver calls each) are issued side by side instead
+// of one kid after the other, so the last GPU starts its filter microseconds, not G x 30 us, after the first.
+struct MgWorker {
+	std::thread th;
+	std::mutex mu;
+	std::condition_variable cv;
+	std::function<int()> task;
+	bool has_task = false, done = true, quit = false;
+	int rc = 0;
+	void start(int device) {
+		th = std::thread([this, device] {
+			cudaSetDevice(device);
+			cudaFree(nullptr); // bind the primary context: driver entry points (cuTensorMapEncodeTiled) need one
+			std::unique_lock<std::mutex> lk(mu);
+			for (;;) {
+				cv.wait(lk, [this] { return has_task || quit; });
+				if (quit) return;
+				has_task = false;
+				lk.unlock();
+				const int r = task();
+				lk.lock();
+				rc = r;
+				done = true;
+				cv.notify_all();
+			}
+		});
+	}
+	void post(std::function<int()> f) {
+		std::lock_guard<std::mutex> lk(mu);
+		task = std::move(f);
+		has_task = true;
+		done = false;
+		cv.notify_all();
+	}
+	int wait() {
+		std::unique_lock<std::mutex> lk(mu);
+		cv.wait(lk, [this] { return done; });
+		return rc;
+	}
+	void stop() {
+		{
+			std::lock_guard<std::mutex> lk(mu);
+			quit = true;
+			cv.notify_all();
+		}
+		if (th.joinable()) th.join();
+	}
+};
 
 struct Multi {
 	std::vector<int> devices;        // one entry per kid slot; an ordinal may repeat (several shards on one GPU: tests)
@@ -48,6 +101,8 @@ struct Multi {
 	std::vector<DevBuf> kid_q, kid_keys;
 	std::vector<char> direct, same_dev;
 	uint64_t step = 0, peer_bytes = 0;
+	std::vector<std::unique_ptr<MgWorker>> workers; // [kid]; kid 0's work runs on the calling thread
+	std::vector<std::string> kid_err;
 };
 
 static size_t round_up_sz(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -88,6 +143,9 @@ int mg_create(const expann_gpu_cfg* cfg, const int32_t* devices, size_t ndev, ex
 void mg_destroy(expann_gpu* h) {
 	Multi* g = h->mg;
 	if (!g) return;
+	for (auto& w : g->workers)
+		if (w) w->stop();
+	g->workers.clear();
 	for (expann_gpu* kid : g->kids)
 		if (kid) { DeviceGuard kg(kid->device); cudaStreamSynchronize(kid->stream); }
 	for (size_t c = 0; c < g->kids.size(); ++c) {
@@ -211,6 +269,12 @@ static int mg_materialize(expann_gpu* h) {
 	DeviceGuard rg(h->device);
 	EXPANN_CUDA(h, cudaEventCreateWithFlags(&g.ev_q, cudaEventDisableTiming));
 	for (int p = 0; p < 2; ++p) EXPANN_CUDA(h, cudaEventCreateWithFlags(&g.ev_merged[p], cudaEventDisableTiming));
+	g.workers.resize(nk);
+	g.kid_err.assign(nk, std::string());
+	for (size_t c = 1; c < nk; ++c) {
+		g.workers[c].reset(new MgWorker());
+		g.workers[c]->start(g.kids[c]->device);
+	}
 	g.materialized = true;
 	return EXPANN_OK;
 }
@@ -307,37 +371,60 @@ int mg_query_device(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t 
 		gat = g.gather[par].as<uint64_t>();
 	}
 	EXPANN_CUDA(h, cudaEventRecord(g.ev_q, st)); // the queries are in place / earlier users of d_keys_out are done
-	std::vector<size_t> active;
-	for (size_t c = 0; c < g.kids.size(); ++c) {
-		const size_t iq = c / gr, ir = c % gr;
-		size_t q_lo, q_hi;
-		mg_query_block(g, m, iq, &q_lo, &q_hi);
-		if (q_lo >= q_hi) continue;
-		const size_t mq = q_hi - q_lo;
+	const bool wait_merged = gr > 1 && g.merged_pending[par];
+	// everything one kid needs for this call, issued on ITS stream; runs on the kid's own host thread (kid 0: this thread)
+	auto kid_step = [&g, h, d_q, m, k, ef, gat, gr, d, par, wait_merged](size_t c, size_t q_lo, size_t mq) -> int {
+		const size_t ir = c % gr;
 		expann_gpu* kid = g.kids[c];
 		DeviceGuard kg(kid->device);
-		EXPANN_CUDA(h, cudaStreamWaitEvent(kid->stream, g.ev_q, 0));
-		if (gr > 1 && g.merged_pending[par]) EXPANN_CUDA(h, cudaStreamWaitEvent(kid->stream, g.ev_merged[par], 0)); // last reader of this gather buffer
+#define MG_CUDA(call)                                                                            \
+	do {                                                                                         \
+		cudaError_t e_ = (call);                                                                 \
+		if (e_ != cudaSuccess) { kid->err = std::string(#call) + ": " + cudaGetErrorString(e_); return EXPANN_ERR_CUDA; } \
+	} while (0)
+		MG_CUDA(cudaStreamWaitEvent(kid->stream, g.ev_q, 0));
+		if (wait_merged) MG_CUDA(cudaStreamWaitEvent(kid->stream, g.ev_merged[par], 0)); // last reader of this gather buffer
 		const float* qk = d_q + q_lo * d;
 		if (!g.same_dev[c]) { // this kid's block of the queries comes over NVLink from GPU 0
-			EXPANN_CUDA(h, g.kid_q[c].ensure(mq * d * sizeof(float)));
-			EXPANN_CUDA(h, cudaMemcpyPeerAsync(g.kid_q[c].p, kid->device, qk, h->device, mq * d * sizeof(float), kid->stream));
+			MG_CUDA(g.kid_q[c].ensure(mq * d * sizeof(float)));
+			MG_CUDA(cudaMemcpyPeerAsync(g.kid_q[c].p, kid->device, qk, h->device, mq * d * sizeof(float), kid->stream));
 			qk = g.kid_q[c].as<float>();
-			g.peer_bytes += mq * d * sizeof(float) + mq * k * 8;
 		}
 		uint64_t* out = gat + (ir * m + q_lo) * k;
 		int rc;
 		if (g.direct[c])
 			rc = query_device_impl(kid, qk, mq, k, ef, out, kid->stream); // the kid's last kernel stores into GPU 0's memory
 		else {
-			EXPANN_CUDA(h, g.kid_keys[c].ensure(mq * k * 8));
+			MG_CUDA(g.kid_keys[c].ensure(mq * k * 8));
 			rc = query_device_impl(kid, qk, mq, k, ef, g.kid_keys[c].as<uint64_t>(), kid->stream);
-			if (!rc) EXPANN_CUDA(h, cudaMemcpyPeerAsync(out, h->device, g.kid_keys[c].p, kid->device, mq * k * 8, kid->stream));
+			if (!rc) MG_CUDA(cudaMemcpyPeerAsync(out, h->device, g.kid_keys[c].p, kid->device, mq * k * 8, kid->stream));
 		}
-		if (rc) return kid_fail(h, kid, rc, c);
-		EXPANN_CUDA(h, cudaEventRecord(g.ev_done[c], kid->stream));
+		if (rc) return rc;
+		MG_CUDA(cudaEventRecord(g.ev_done[c], kid->stream));
+#undef MG_CUDA
+		return EXPANN_OK;
+	};
+	std::vector<size_t> active;
+	size_t q_lo0 = 0, mq0 = 0;
+	bool run0 = false;
+	for (size_t c = 0; c < g.kids.size(); ++c) {
+		size_t q_lo, q_hi;
+		mg_query_block(g, m, c / gr, &q_lo, &q_hi);
+		if (q_lo >= q_hi) continue;
+		const size_t mq = q_hi - q_lo;
+		if (!g.same_dev[c]) g.peer_bytes += mq * d * sizeof(float) + mq * k * 8;
 		active.push_back(c);
+		if (c == 0) { run0 = true; q_lo0 = q_lo; mq0 = mq; }
+		else g.workers[c]->post([kid_step, c, q_lo, mq] { return kid_step(c, q_lo, mq); });
 	}
+	int rc_all = run0 ? kid_step(0, q_lo0, mq0) : EXPANN_OK;
+	size_t bad = 0;
+	for (size_t c : active) {
+		if (c == 0) continue;
+		const int rc = g.workers[c]->wait(); // every kid's launches (and its done event) are issued before GPU 0's stream waits on them
+		if (rc && !rc_all) { rc_all = rc; bad = c; }
+	}
+	if (rc_all) return kid_fail(h, g.kids[bad], rc_all, bad);
 	for (size_t c : active) EXPANN_CUDA(h, cudaStreamWaitEvent(st, g.ev_done[c], 0));
 	if (gr > 1) {
 		if (int rc = launch_merge(h, gat, m, gr, k, k, m * k, k, 0, d_keys_out, st)) return rc;

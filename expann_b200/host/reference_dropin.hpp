@@ -6,8 +6,8 @@
 // and driven by the unmodified basic_bench::get_benchmark_data (src/basic_bench.h:58-149). Everything forwards to the C
 // ABI in include/expann_gpu.h; nothing is computed on the host.
 //
-// oracle/dropin_harness.cpp compiles exactly this against /root/reference (oracle/Makefile, target dropin) and
-// tests/test_gpu_dropin.py runs the reference's own harness over it.
+// The repo's test infrastructure compiles exactly this against /root/reference (dropin_harness.cpp, make target
+// `dropin`) and tests/test_gpu_dropin.py runs the reference's own harness over it.
 #pragma once
 #include <stdexcept>
 #include <string>
