@@ -15,8 +15,10 @@ A "step" is one pass of the hot path over one batch of m synthetic queries again
 N > 1: ONE process drives all N GPUs through ONE multi-device handle (expann_gpu_create_multi, csrc/multi.cu): the base
 set is sharded by contiguous row ranges inside the library, the queries fan out over NVLink, every GPU's last kernel
 stores its [m][k] keys into GPU 0's gather buffer and K7 merges there — the path a reference-side caller gets. Under the
-driver's torchrun launch rank 0 owns the handle; the other ranks only join the NCCL barriers that bracket the timed
-region (they hold no data and launch nothing), so `value` is the whole job's throughput.
+driver's torchrun launch rank 0 owns the handle; the other ranks initialise the N-rank NCCL communicator with it and then
+only join the CPU-side barriers that bracket the timed region (they hold no data and launch nothing: an NCCL barrier
+kernel spinning on GPU r would be time-sliced against the handle's own kernels there), so `value` is the whole job's
+throughput.
 """
 from __future__ import annotations
 
@@ -247,25 +249,47 @@ def tensor_roofline(st0, st1, m, n_rows_per_gpu, d, G, gq, workload, hot_ms):
                     "frac_of_sustained_peak uses the seconds-long figure"}
 
 
-def timed_steps(torch, dist, world, dev, fn, steps):
+def timed_steps(torch, sync, fn, steps):
     """K steps bracketed by barrier + synchronize on both sides, CUDA events on the launching stream, max over ranks"""
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-    barrier()
+    sync.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     e0.record()
     for _ in range(steps):
         fn()
     e1.record()
-    barrier()
+    sync.barrier()
     t1 = time.perf_counter()
-    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    return float(ms.item()), t0, t1
+    return sync.max(e0.elapsed_time(e1)), t0, t1
+
+
+class RankSync:
+    """Barrier / max-over-ranks for the torchrun launch. NCCL is initialised and used ONCE (an all-reduce that proves the
+    N-rank communicator), after that the ranks meet on a gloo group: an NCCL barrier is a kernel that spins on its GPU
+    until every rank has arrived, and ranks > 0 reach each barrier long before rank 0 does -- their spinning kernels would
+    sit on GPUs 1..N-1 (another process's context: time-sliced against rank 0's kernels there) through the whole timed
+    region. A gloo barrier blocks on the CPU and leaves those GPUs to the multi-device handle."""
+
+    def __init__(self, torch, dist, world, dev):
+        self.torch, self.dist, self.world, self.dev, self.cpu = torch, dist, world, dev, None
+        if world > 1:
+            t = torch.ones(1, device=dev)
+            dist.all_reduce(t)                      # NCCL communicator over all N ranks
+            torch.cuda.synchronize()
+            assert int(t.item()) == world
+            self.cpu = dist.new_group(backend="gloo")
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier(group=self.cpu)
+
+    def max(self, v):
+        if self.world == 1:
+            return float(v)
+        t = self.torch.tensor([float(v)], dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.cpu)
+        return float(t.item())
 
 
 def extra_leg(expann_b200, torch, name, G, budget_left, steps=5):
@@ -408,15 +432,15 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
 
+    sync = RankSync(torch, dist, world, dev)
     if rank != 0:
         # ONE process (rank 0) drives all N GPUs through one multi-device handle; this rank only joins the barriers and the
-        # max-over-ranks reductions that bracket rank 0's timed regions, in the same order (headline, then e2e)
+        # max-over-ranks reductions that bracket rank 0's timed regions, in the same order (headline, then e2e), on the CPU
         for _ in range(2):
-            dist.barrier(); torch.cuda.synchronize()
-            dist.barrier(); torch.cuda.synchronize()
-            z = torch.zeros(1, device=dev)
-            dist.all_reduce(z, op=dist.ReduceOp.MAX)
-        dist.barrier()
+            sync.barrier()
+            sync.barrier()
+            sync.max(0.0)
+        sync.barrier()
         dist.destroy_process_group()
         return 0
 
@@ -479,7 +503,7 @@ def main():
     eng.set_timing(True)
     sampler = ClockSampler(local_rank)
     sampler.start()
-    ms, tw0, tw1 = timed_steps(torch, dist, world, dev, step_device, args.steps)
+    ms, tw0, tw1 = timed_steps(torch, sync, step_device, args.steps)
     st1 = eng.stats()
     eng.set_timing(False)
     # sustained region: the same step for >= 0.5 s, so that the clock sampler sees the loaded clock and the seconds-long tensor
@@ -500,9 +524,7 @@ def main():
     # e2e leg (host buffers): its own warm-up, then K timed steps by wall clock bracketed by barriers
     for _ in range(max(1, min(args.warmup, 2))):
         step_e2e()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
+    sync.barrier()
     p0 = eng.stats()["peer_bytes"]
     t0 = time.perf_counter()
     for _ in range(args.steps):
@@ -510,11 +532,8 @@ def main():
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     peer_per_step = (eng.stats()["peer_bytes"] - p0) / max(1, args.steps)
-    if world > 1:
-        dist.barrier()
-        t = torch.tensor([e2e_s], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
+    sync.barrier()
+    e2e_s = sync.max(e2e_s)
     step_e2e_pageable()
     nrep = max(3, min(args.steps, 20))
     t0 = time.perf_counter()
@@ -581,7 +600,7 @@ def main():
                       "step_minus_kernel_ms": ms_step - hot_ms,
                       "parallelism": ("one process, one multi-device handle over %d GPUs: %d row shards x %d query groups, queries fanned out over "
                                       "NVLink, per-GPU [m][k] keys stored by each GPU's last kernel into GPU 0's gather buffer, K7 merge "
-                                      "(no NCCL on the data path; torchrun ranks > 0 only join the barriers)" % (G, gr, gq)) if G > 1 else "single GPU"},
+                                      "(no NCCL on the data path; torchrun ranks > 0 only join the CPU-side barriers)" % (G, gr, gq)) if G > 1 else "single GPU"},
            "e2e": {"value": m * args.steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(m * d * 4),
                    "d2h_bytes_per_step": int(m * k * 8 + m * k * 4 + m * 8),
                    "api": "expann_gpu_query (page-locked caller buffers)", "pageable_value": m / e2e_pageable_s,
@@ -650,7 +669,7 @@ def main():
     out["run_s"] = time.perf_counter() - T_START
     emit(out)
     if world > 1:
-        dist.barrier()
+        sync.barrier()
         dist.destroy_process_group()
     return 0
 

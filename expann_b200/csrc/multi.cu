@@ -20,7 +20,8 @@
 //                  [m][k] block and nothing is merged. The gather buffer is double-buffered by call parity, so the kids
 //                  of call s+1 overlap GPU 0's merge of call s.
 //   result         keys carry (key, id), so the merged result is bit-identical to the one-GPU result whatever G, gq, gr.
-// All kids are driven from the calling thread; every launch is asynchronous, cross-device ordering is by CUDA events.
+// Every kid's launches are issued by its own parked host thread (kid 0: the calling thread); every launch is asynchronous,
+// cross-device ordering is by CUDA events.
 #include "engine.h"
 #include <algorithm>
 #include <condition_variable>
