@@ -376,7 +376,7 @@ def main():
                     help="bf: exact brute force (K1/K3+K4); quant: quantizer compressed scan + fp32 rerank (K6+K4); auto: quant for c5")
     ap.add_argument("--qtile", type=int, default=0)
     ap.add_argument("--m", type=int, default=0, help="override the query count")
-    ap.add_argument("--row-groups", type=int, default=0, help="N > 1: row shards (0 = one per GPU); N / row_groups GPUs split the queries")
+    ap.add_argument("--row-groups", type=int, default=0, help="N > 1: row shards (0 = automatic: shards of up to 2^20 rows; N = one per GPU); N / row_groups GPUs split the queries")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extras", action="store_true", help="skip the extra legs (hbm scan, graph engine sweep, c4 / c5)")
     ap.add_argument("--extras-budget-s", type=float, default=300.0, help="extra legs start only while the run is younger than this")
@@ -592,6 +592,7 @@ def main():
            "n_gpus": G, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": desc, "n": n, "m": m, "d": d, "k": k, "metric": metric, "qtile": int(qt),
+                      "decomposition": ("automatic: %d row shard(s) of up to 2^20 rows x %d query group(s)" % (gr, gq)) if (G > 1 and not args.row_groups) else None,
                       "path": "K5 graph beam search (one GPU-built graph per shard, M0=32)" if use_graph else
                               "K6 8-bit code scan + K4 fp32 rerank of 100 survivors" if use_quant else
                               ("K3 tcgen05 filter + K4 fp32 rerank" if used_tc else "K1 fp32 SIMT scan"),
@@ -637,6 +638,42 @@ def main():
     def young():
         return time.perf_counter() - T_START < args.extras_budget_s
 
+    if extras and G > 1 and gr != G and young():
+        # the decomposition the north star names beside the automatic one of the headline: ONE row shard per GPU, all queries
+        # on every GPU, K7 merge of G lists (not the headline: the same numbers for the other decomposition)
+        try:
+            e2 = expann_b200.BruteForceEngine(metric=mt, qtile=args.qtile, devices=devs, row_groups=G)
+            e2.store_many_vectors(base)
+            e2.build()
+            for _ in range(args.warmup):
+                e2.query_device(dq.data_ptr(), m, k, final_keys.data_ptr(), stream)
+            torch.cuda.synchronize()
+            s0 = e2.stats()
+            e2.set_timing(True)
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record()
+            for _ in range(args.steps):
+                e2.query_device(dq.data_ptr(), m, k, final_keys.data_ptr(), stream)
+            ev1.record()
+            torch.cuda.synchronize()
+            s1 = e2.stats()
+            e2.set_timing(False)
+            ms2 = ev0.elapsed_time(ev1) / args.steps
+            hot2 = (s1["hot_time_ns"] - s0["hot_time_ns"]) / 1e6 / max(1, s1["hot_timed_launches"] - s0["hot_timed_launches"])
+            e2.query_k_batch(hq_np, k, out=out_pinned)
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                e2.query_k_batch(hq_np, k, out=out_pinned)
+            e2e2 = (time.perf_counter() - t0) / args.steps
+            rs = tensor_roofline(s0, s1, m, (n + G - 1) // G, d, G, 1, args.workload, hot2)
+            rs.update({"decomposition": "%d row shards x 1 query group (one shard per GPU, K7 merge of %d lists)" % (G, G),
+                       "qps": m / ms2 * 1e3, "ms_per_step": ms2, "step_minus_kernel_ms": ms2 - hot2, "e2e_qps": m / e2e2,
+                       "ids_equal_headline": bool(np.array_equal(e2.query_k_batch(q[:256], k)[0], got[:256]))})
+            roof["row_sharded"] = rs
+            e2.close()
+            del e2
+        except Exception as ex:  # noqa: BLE001
+            roof["row_sharded"] = {"error": repr(ex)[:300]}
     if extras and G == 1:
         try:
             roof["hbm_scan"] = scan_hbm_leg(eng, torch, dq, k, n, d, stream, peak, peak_src, args.steps)

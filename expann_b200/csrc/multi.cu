@@ -8,9 +8,10 @@
 //   decomposition  G = gq x gr: the rows are cut into gr contiguous shards (rows [ir*ceil(n/gr), ...), global id =
 //                  local id + offset, added on the device), each shard is held by gq GPUs, and query group iq of a call
 //                  (a contiguous block of the m queries) is served by the gr kids (iq, *). gr = G is the plain row
-//                  sharding of §8(e); gr < G ("mgpu_row_groups") keeps the per-GPU row streams long when the base is
-//                  small against G (the tensor-core filter warms a bound up per row stream); a graph index read from a
-//                  file is replicated (gr = 1: queries split, no merge).
+//                  sharding of §8(e) ("mgpu_row_groups" = G); by default a shard holds up to 2^20 rows and the GPUs that
+//                  are not needed to hold the base split the queries (the tensor-core filter warms a bound up per row
+//                  stream: slivers of a small base cost more than they save); a graph index read from a file is
+//                  replicated (gr = 1: queries split, no merge).
 //   query fan-out  the queries reach GPU 0 once (one H2D copy, or the caller's device buffer); every other kid pulls ITS
 //                  block over NVLink (cudaMemcpyPeerAsync on its own stream) — not G copies over PCIe.
 //   fused tail     the last kernel of a kid's path (K4 rerank / the fused split merge of K1 / the graph search) stores
@@ -88,7 +89,7 @@ struct Multi {
 	std::vector<int> devices;        // one entry per kid slot; an ordinal may repeat (several shards on one GPU: tests)
 	std::vector<expann_gpu*> kids;   // kid (iq, ir) at [iq * gr + ir]
 	int gq = 1, gr = 1;
-	int opt_row_groups = 0;          // 0 = one row shard per GPU
+	int opt_row_groups = 0;          // 0 = automatic (shards of up to MG_SHARD_ROWS rows), R = R row shards
 	std::vector<float> rows;         // host copy of the stored rows until the shards are uploaded (store_vector copies too)
 	std::vector<std::pair<std::string, int64_t>> options; // replayed on the kids when they are created
 	std::string index_path;          // graph engine: every kid reads the same index file (replicas)
@@ -105,6 +106,8 @@ struct Multi {
 	std::vector<std::unique_ptr<MgWorker>> workers; // [kid]; kid 0's work runs on the calling thread
 	std::vector<std::string> kid_err;
 };
+
+constexpr size_t MG_SHARD_ROWS = (size_t)1 << 20; // automatic decomposition: rows per shard before another shard is opened
 
 static size_t round_up_sz(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -205,7 +208,18 @@ static int mg_materialize(expann_gpu* h) {
 	const size_t G = g.devices.size();
 	const bool replicas = !g.index_path.empty();
 	if (!replicas && h->n == 0) return fail(h, EXPANN_ERR_STATE, "build() on an empty engine (the reference asserts n > 0)");
-	size_t gr = replicas ? 1 : (g.opt_row_groups > 0 ? std::min<size_t>(G, (size_t)g.opt_row_groups) : G);
+	// Row shards. Explicit ("mgpu_row_groups" = R): R shards. Automatic (0): shards of up to MG_SHARD_ROWS rows -- a base that
+	// is small against the GPU count is NOT cut into slivers: the tensor-core filter warms a bound up per row stream, and on
+	// a 125k-row shard (C2 over 8 GPUs) that warm-up is half the kernel time, so the GPUs that are not needed to hold the rows
+	// split the QUERIES of a call instead (same rows on each GPU of a group; measured, profiles/r2_notes.md). C4 (10M rows) is
+	// cut into one shard per GPU either way.
+	size_t gr;
+	if (replicas) gr = 1;
+	else if (g.opt_row_groups > 0) gr = std::min<size_t>(G, (size_t)g.opt_row_groups);
+	else {
+		gr = std::min<size_t>(G, std::max<size_t>(1, (h->n + MG_SHARD_ROWS - 1) / MG_SHARD_ROWS));
+		while (G % gr) ++gr; // the next count of shards that leaves whole query groups
+	}
 	while (G % gr) --gr; // whole query groups
 	size_t per = 0;
 	if (!replicas) {
@@ -481,7 +495,7 @@ int mg_set_option(expann_gpu* h, const char* name, int64_t value) {
 	Multi& g = *h->mg;
 	const std::string nm(name);
 	if (nm == "mgpu_row_groups") {
-		if (value < 0) return fail(h, EXPANN_ERR_ARG, "mgpu_row_groups must be >= 0 (0 = one row shard per GPU)");
+		if (value < 0) return fail(h, EXPANN_ERR_ARG, "mgpu_row_groups must be >= 0 (0 = automatic)");
 		if (g.materialized) return fail(h, EXPANN_ERR_STATE, "mgpu_row_groups must be set before the shards are created (build / build_graph / load_index)");
 		g.opt_row_groups = (int)value;
 		return EXPANN_OK;

@@ -30,8 +30,9 @@ class GpuEngine:
     def __init__(self, metric: int = METRIC_L2, device: int = -1, qtile: int = 0, id_offset: int = 0, devices=None,
                  row_groups: int = 0, **kw):
         """devices: list of CUDA ordinals -> ONE engine over several GPUs of this process (rows sharded by contiguous
-        ranges, per-GPU top-k merged on devices[0]; an ordinal may repeat); row_groups: 0 = one row shard per GPU, R = R
-        row shards each held by len(devices) / R GPUs that split the queries. Results do not depend on either."""
+        ranges, per-GPU top-k merged on devices[0]; an ordinal may repeat); row_groups: R = R row shards each held by
+        len(devices) / R GPUs that split the queries (R = len(devices): one shard per GPU), 0 = automatic (shards of up to
+        2^20 rows). Results do not depend on either."""
         self._lib = _lib.load()
         cfg = _lib.Cfg()
         cfg.engine = self._engine_kind

@@ -41,9 +41,10 @@ typedef struct expann_gpu_cfg {
 	                            1 = quantizer_ranged_q8 (src/quantizer.h:186-238) */
 	/* device list: n_devices > 1 puts GPUs device .. device + n_devices - 1 behind this ONE handle; the
 	   base set is sharded by contiguous row ranges, every call fans out and the per-GPU top-k lists are merged on the
-	   first GPU. expann_gpu_create_multi takes an explicit list instead. row_groups: 0 = one row shard per GPU; R > 0 = R
-	   row shards, each held by n_devices / R GPUs that split the queries of a call between them (option
-	   "mgpu_row_groups"). The result does not depend on either. */
+	   first GPU. expann_gpu_create_multi takes an explicit list instead. row_groups: R > 0 = R row shards, each held by
+	   n_devices / R GPUs that split the queries of a call between them (R = n_devices: one shard per GPU, nothing
+	   replicated); 0 = automatic: shards of up to 2^20 rows, the GPUs that are not needed to hold the base split the
+	   queries (option "mgpu_row_groups"). The result does not depend on either. */
 	int32_t n_devices, row_groups;
 	int32_t reserved[4];
 } expann_gpu_cfg;
@@ -155,8 +156,8 @@ int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
  * Quantised scan engine: "quant_tc" (0/1, default 1: batches of at least "quant_tc_min_batch" queries (default 32) run the
  * code scan as a tensor-core candidate filter, tcgen05.mma.kind::i8 on the 8-bit codes, with the SIMT scan as its queued
  * redo; same result).
- * Multi-device handles: "mgpu_row_groups" (0 (default) one row shard per GPU | R row shards, each on n_devices / R GPUs that
- * split the queries of a call; before build()); every other knob is applied to each GPU's engine.
+ * Multi-device handles: "mgpu_row_groups" (0 (default) automatic: shards of up to 2^20 rows | R row shards, each on
+ * n_devices / R GPUs that split the queries of a call; R = n_devices: one shard per GPU; before build()); every other knob is applied to each GPU's engine.
  * Unknown names: EXPANN_ERR_ARG. */
 int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value);
 /* library build info: "sm_100a;..." */

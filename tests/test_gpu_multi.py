@@ -51,13 +51,13 @@ def test_brute_force_identical_to_one_gpu(ex, kind):
         base = rng.integers(0, 256, (20_001, 100)).astype(np.float32); q = rng.integers(0, 256, (700, 100)).astype(np.float32)
     want = {m: single(ex, base, q[:m], 10) for m in (1, 4, 300, len(q))}
     for name, devs in device_lists():
-        for rg in sorted({0, 1, 2} & {0, 1, 2 if len(devs) % 2 == 0 else 0}):
+        for rg in sorted({0, len(devs), 2 if len(devs) % 2 == 0 else 0}):   # automatic / one shard per GPU / 2 shards x G/2 query groups
             e = ex.BruteForceEngine(devices=devs, row_groups=rg)
             e.store_many_vectors(base[:30_000]); e.store_many_vectors(base[30_000:])   # two add() calls
             e.build()
             st = e.stats()
             assert st["n"] == len(base) and st["query_groups"] * st["row_groups"] <= len(devs)
-            assert st["row_groups"] == (len(devs) if rg == 0 else rg)
+            assert st["row_groups"] == (1 if rg == 0 else rg)        # automatic: a base below 2^20 rows is not cut, the GPUs split the queries
             for m, w in want.items():
                 got = e.query_k_batch(q[:m], 10)
                 assert np.array_equal(got[0], w[0]) and np.array_equal(got[1], w[1]) and np.array_equal(got[2], w[2]), (name, rg, m)
@@ -75,7 +75,7 @@ def test_ip_metric_k100_and_tiny_bases(ex):
     for k, metric in ((100, 0), (10, 1), (1, 1)):
         w = single(ex, base, q, k, metric=metric)
         for name, devs in device_lists():
-            e = ex.BruteForceEngine(metric=metric, devices=devs)
+            e = ex.BruteForceEngine(metric=metric, devices=devs, row_groups=len(devs))
             e.store_many_vectors(base); e.build()
             got = e.query_k_batch(q, k)
             e.close()
@@ -83,7 +83,7 @@ def test_ip_metric_k100_and_tiny_bases(ex):
     # fewer rows than GPUs / than k: no empty shard is created, short lists are padded exactly like the one-GPU result
     tiny = base[:5]
     w = single(ex, tiny, q[:7], 10)
-    e = ex.BruteForceEngine(devices=[0] * 8)
+    e = ex.BruteForceEngine(devices=[0] * 8, row_groups=8)
     e.store_many_vectors(tiny); e.build()
     got = e.query_k_batch(q[:7], 10)
     st = e.stats()
@@ -111,7 +111,7 @@ def test_device_pointer_entry_and_back_to_back_calls(ex):
     torch.cuda.synchronize()
     one.close()
     for name, devs in device_lists():
-        e = ex.BruteForceEngine(devices=devs)
+        e = ex.BruteForceEngine(devices=devs, row_groups=len(devs))
         e.store_many_vectors(base); e.build()
         got = [torch.empty((900, 10), dtype=torch.int64, device=dev) for _ in qs]
         for a, g in zip(dq, got):
@@ -166,7 +166,7 @@ def test_quant_scan_does_not_depend_on_the_partitioning(ex):
         wp = one.quantizer_params()
         one.close()
         for name, devs in device_lists():
-            e = ex.QuantScanEngine(quantizer=quantizer, kprime=50, devices=devs)
+            e = ex.QuantScanEngine(quantizer=quantizer, kprime=50, devices=devs, row_groups=len(devs))
             e.store_many_vectors(b); e.build()
             got = e.query_k_batch(qq, 10)
             gp = e.quantizer_params()
@@ -205,7 +205,7 @@ def test_graph_replicas_and_sharded_subgraphs(ex):
     r1 = rec(one.query_k_batch(qq, 10)[0])
     one.close()
     for name, devs in device_lists()[:2] + device_lists()[3:4]:
-        e = ex.GraphEngine(devices=devs)
+        e = ex.GraphEngine(devices=devs, row_groups=len(devs))     # one sub-graph per row shard
         e.store_many_vectors(base); e.build_graph(M=12, M0=24, K=48); e.build(); e.set_ef_search(30)
         ids, dists, counts = e.query_k_batch(qq, 10)
         e.close()
