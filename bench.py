@@ -249,14 +249,17 @@ def tensor_roofline(st0, st1, m, n_rows_per_gpu, d, G, gq, workload, hot_ms):
                     "frac_of_sustained_peak uses the seconds-long figure"}
 
 
-def timed_steps(torch, sync, fn, steps):
-    """K steps bracketed by barrier + synchronize on both sides, CUDA events on the launching stream, max over ranks"""
+def timed_steps(torch, sync, fn, steps, join=None):
+    """K steps bracketed by barrier + synchronize on both sides, CUDA events on the launching stream, max over ranks.
+    join(): makes the launching stream wait for the side streams the steps were issued on (N > 1: two batches in flight)"""
     sync.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     e0.record()
     for _ in range(steps):
         fn()
+    if join:
+        join()
     e1.record()
     sync.barrier()
     t1 = time.perf_counter()
@@ -486,8 +489,27 @@ def main():
     out_pageable = (np.empty((m, k), np.uint64), np.empty((m, k), np.float32), np.empty((m,), np.uint64))
     q_pageable = np.array(q, copy=True)
 
+    # N > 1: consecutive steps are issued on two alternating streams with their own result buffers -- two batches in flight,
+    # the way a serving loop double-buffers: a call's results are ordered on ITS stream, so on one stream step s+1 could
+    # not start on any GPU before the slowest GPU had finished step s. (Every GPU's own work stays in order on the handle's
+    # per-GPU stream; the single-device handle at N = 1 has one set of work buffers and takes one stream.)
+    alt = None
+    if G > 1:
+        alt = {"streams": [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)],
+               "keys": [final_keys, torch.empty_like(final_keys)], "i": 0}
+        torch.cuda.synchronize()
+
     def step_device():
-        eng.query_device(dq.data_ptr(), m, k, final_keys.data_ptr(), stream)
+        if alt is None:
+            eng.query_device(dq.data_ptr(), m, k, final_keys.data_ptr(), stream)
+        else:
+            i = alt["i"] = alt["i"] ^ 1
+            eng.query_device(dq.data_ptr(), m, k, alt["keys"][i].data_ptr(), alt["streams"][i].cuda_stream)
+
+    def join_streams():
+        if alt is not None:
+            for s_ in alt["streams"]:
+                torch.cuda.current_stream().wait_stream(s_)
 
     def step_e2e():
         # the C-ABI host call: H2D of the pinned queries, scan (all GPUs), merge, decode, D2H into pinned result buffers
@@ -503,7 +525,7 @@ def main():
     eng.set_timing(True)
     sampler = ClockSampler(local_rank)
     sampler.start()
-    ms, tw0, tw1 = timed_steps(torch, sync, step_device, args.steps)
+    ms, tw0, tw1 = timed_steps(torch, sync, step_device, args.steps, join=join_streams)
     st1 = eng.stats()
     eng.set_timing(False)
     # sustained region: the same step for >= 0.5 s, so that the clock sampler sees the loaded clock and the seconds-long tensor
@@ -516,6 +538,7 @@ def main():
         e0.record()
         for _ in range(reps):
             step_device()
+        join_streams()
         e1.record()
         torch.cuda.synchronize()
         tw1 = time.perf_counter()
@@ -542,6 +565,8 @@ def main():
     e2e_pageable_s = (time.perf_counter() - t0) / nrep
 
     # correctness (not timed): keys decode to the ids of the host call; N > 1: ids of 256 queries equal a ONE-GPU scan of the whole base
+    torch.cuda.synchronize()
+    eng.query_device(dq.data_ptr(), m, k, final_keys.data_ptr(), stream)
     eng.decode_device(final_keys.data_ptr(), m, k, ids_dev.data_ptr(), 0, 0, stream)
     torch.cuda.synchronize()
     got = ids_dev.cpu().numpy().view(np.uint64)
@@ -598,7 +623,7 @@ def main():
                               ("K3 tcgen05 filter + K4 fp32 rerank" if used_tc else "K1 fp32 SIMT scan"),
                       "nsplit": int(st1["last_nsplit"]), "rows_per_gpu": rows_gpu, "row_groups": gr, "query_groups": gq,
                       "l2": "base shard (%.0f MB) %s L2 (126 MB); no explicit flush" % (rows_gpu * d * 4 / 1e6, "larger than" if rows_gpu * d * 4 > 126e6 else "fits in"),
-                      "step_minus_kernel_ms": ms_step - hot_ms,
+                      "step_minus_kernel_ms": ms_step - hot_ms, "batches_in_flight": 2 if G > 1 else 1,
                       "parallelism": ("one process, one multi-device handle over %d GPUs: %d row shards x %d query groups, queries fanned out over "
                                       "NVLink, per-GPU [m][k] keys stored by each GPU's last kernel into GPU 0's gather buffer, K7 merge "
                                       "(no NCCL on the data path; torchrun ranks > 0 only join the CPU-side barriers)" % (G, gr, gq)) if G > 1 else "single GPU"},
@@ -652,8 +677,9 @@ def main():
             e2.set_timing(True)
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             ev0.record()
-            for _ in range(args.steps):
-                e2.query_device(dq.data_ptr(), m, k, final_keys.data_ptr(), stream)
+            for i in range(args.steps):   # two batches in flight, like the headline
+                e2.query_device(dq.data_ptr(), m, k, alt["keys"][i & 1].data_ptr(), alt["streams"][i & 1].cuda_stream)
+            join_streams()
             ev1.record()
             torch.cuda.synchronize()
             s1 = e2.stats()

@@ -366,7 +366,10 @@ static void mg_query_block(const Multi& g, size_t m, size_t iq, size_t* q_lo, si
 	*q_hi = std::min(m, *q_lo + per);
 }
 
-int mg_query_device(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out, cudaStream_t st) {
+// d_q: the queries on GPU 0 (kids on other GPUs pull their block over NVLink), or -- host_q -- in page-locked host memory:
+// every kid then copies ITS block straight from the host on its own stream (with query groups each GPU needs only 1/gq of
+// the queries, and every GPU has its own PCIe link: G small copies side by side instead of one large one plus a fan-out)
+static int mg_query_impl(expann_gpu* h, const float* d_q, const float* host_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out, cudaStream_t st) {
 	Multi& g = *h->mg;
 	if (!h->built) return fail(h, EXPANN_ERR_STATE, "query before build()");
 	if (k == 0) return fail(h, EXPANN_ERR_ARG, "k must be > 0");
@@ -388,7 +391,7 @@ int mg_query_device(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t 
 	EXPANN_CUDA(h, cudaEventRecord(g.ev_q, st)); // the queries are in place / earlier users of d_keys_out are done
 	const bool wait_merged = gr > 1 && g.merged_pending[par];
 	// everything one kid needs for this call, issued on ITS stream; runs on the kid's own host thread (kid 0: this thread)
-	auto kid_step = [&g, h, d_q, m, k, ef, gat, gr, d, par, wait_merged](size_t c, size_t q_lo, size_t mq) -> int {
+	auto kid_step = [&g, h, d_q, host_q, m, k, ef, gat, gr, d, par, wait_merged](size_t c, size_t q_lo, size_t mq) -> int {
 		const size_t ir = c % gr;
 		expann_gpu* kid = g.kids[c];
 		DeviceGuard kg(kid->device);
@@ -400,7 +403,11 @@ int mg_query_device(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t 
 		MG_CUDA(cudaStreamWaitEvent(kid->stream, g.ev_q, 0));
 		if (wait_merged) MG_CUDA(cudaStreamWaitEvent(kid->stream, g.ev_merged[par], 0)); // last reader of this gather buffer
 		const float* qk = d_q + q_lo * d;
-		if (!g.same_dev[c]) { // this kid's block of the queries comes over NVLink from GPU 0
+		if (host_q) { // this kid's block of the queries comes straight from the caller's page-locked memory
+			MG_CUDA(g.kid_q[c].ensure(mq * d * sizeof(float)));
+			MG_CUDA(cudaMemcpyAsync(g.kid_q[c].p, host_q + q_lo * d, mq * d * sizeof(float), cudaMemcpyHostToDevice, kid->stream));
+			qk = g.kid_q[c].as<float>();
+		} else if (!g.same_dev[c]) { // this kid's block of the queries comes over NVLink from GPU 0
 			MG_CUDA(g.kid_q[c].ensure(mq * d * sizeof(float)));
 			MG_CUDA(cudaMemcpyPeerAsync(g.kid_q[c].p, kid->device, qk, h->device, mq * d * sizeof(float), kid->stream));
 			qk = g.kid_q[c].as<float>();
@@ -427,7 +434,7 @@ int mg_query_device(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t 
 		mg_query_block(g, m, c / gr, &q_lo, &q_hi);
 		if (q_lo >= q_hi) continue;
 		const size_t mq = q_hi - q_lo;
-		if (!g.same_dev[c]) g.peer_bytes += mq * d * sizeof(float) + mq * k * 8;
+		if (!g.same_dev[c]) g.peer_bytes += (host_q ? 0 : mq * d * sizeof(float)) + mq * k * 8;
 		active.push_back(c);
 		if (c == 0) { run0 = true; q_lo0 = q_lo; mq0 = mq; }
 		else g.workers[c]->post([kid_step, c, q_lo, mq] { return kid_step(c, q_lo, mq); });
@@ -449,6 +456,10 @@ int mg_query_device(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t 
 	return EXPANN_OK;
 }
 
+int mg_query_device(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out, cudaStream_t st) {
+	return mg_query_impl(h, d_q, nullptr, m, k, ef, d_keys_out, st);
+}
+
 int mg_query(expann_gpu* h, const float* q, size_t m, size_t k, size_t ef, uint64_t* ids_out, float* dist_out, uint64_t* counts_out) {
 	Multi& g = *h->mg;
 	if (!h->built) return fail(h, EXPANN_ERR_STATE, "query before build()");
@@ -468,8 +479,15 @@ int mg_query(expann_gpu* h, const float* q, size_t m, size_t k, size_t ef, uint6
 		EXPANN_CUDA(h, h->h_q.ensure(qbytes));
 		std::memcpy(h->h_q.p, q, qbytes);
 	}
-	EXPANN_CUDA(h, cudaMemcpyAsync(g.q_dev.p, q_pinned ? (const void*)q : h->h_q.p, qbytes, cudaMemcpyHostToDevice, st)); // ONE H2D copy
-	if (int rc = mg_query_device(h, g.q_dev.as<float>(), m, k, ef, g.keys.as<uint64_t>(), st)) return rc;
+	const float* hq = q_pinned ? q : static_cast<const float*>(h->h_q.p);
+	if (g.gq > 1) {
+		// query groups: every GPU needs only its block -- copied from the host by each GPU itself, all PCIe links side by side
+		if (int rc = mg_query_impl(h, nullptr, hq, m, k, ef, g.keys.as<uint64_t>(), st)) return rc;
+	} else {
+		// every GPU needs every query: ONE H2D copy to GPU 0, the others pull it over NVLink
+		EXPANN_CUDA(h, cudaMemcpyAsync(g.q_dev.p, hq, qbytes, cudaMemcpyHostToDevice, st));
+		if (int rc = mg_query_impl(h, g.q_dev.as<float>(), nullptr, m, k, ef, g.keys.as<uint64_t>(), st)) return rc;
+	}
 	if (int rc = launch_decode(h, g.keys.as<uint64_t>(), m, k, 0, reinterpret_cast<uint64_t*>(d_res), reinterpret_cast<float*>(d_res + off_d),
 	                           reinterpret_cast<uint64_t*>(d_res + off_c), st))
 		return rc;
