@@ -359,6 +359,14 @@ def extra_leg(expann_b200, torch, name, G, budget_left, steps=5):
             qe.store_many_vectors(base)
             qe.build()
             qids, s0, s1, hot = run(qe, "code_scan")
+            dcp = (d + 127) // 128 * 128
+            gr_q, gq_q = out["code_scan"]["row_groups"], out["code_scan"]["query_groups"]
+            ops = 2.0 * ((m + gq_q - 1) // gq_q) * ((n + gr_q - 1) // gr_q) * dcp
+            tpk = tensor_peaks()[0]
+            out["code_scan"]["roofline"] = {"bound": "tensor", "kernel": "tc_filter_pair_kernel KIND = 1 (tcgen05.mma.kind::i8)", "achieved": ops / (hot * 1e-3) / 1e12,
+                                            "peak": 2.0 * tpk, "unit": "Tera-op/s", "frac": ops / (hot * 1e-3) / 1e12 / (2.0 * tpk),
+                                            "frac_of_nominal": ops / (hot * 1e-3) / 1e12 / 4500.0, "algorithmic_ops_per_launch": ops, "kernel_ms_per_launch": hot,
+                                            "peak_source": "2 x measured bf16 burst peak; nominal dense int8 4500"}
             hit = sum(len(set(a.tolist()) & set(b.tolist())) for a, b in zip(qids, eids))
             out["code_scan"]["recall_at_k_vs_exact"] = hit / float(m * k)
             out["code_scan"]["path"] = "quantizer_ranged_q8 codes (src/quantizer.h:186-238), k' = 100 survivors re-ranked in fp32"
@@ -598,6 +606,23 @@ def main():
                 "traffic": None, "traffic_source": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": int(alg_bytes), "kernel_ms_per_launch": hot_ms,
                 "distcomps_per_query_all_gpus": dcq,
                 "note": "algorithmic bytes = distance evaluations x d x 4 per GPU (random row gathers); latency-bound"}
+    elif used_tc and use_quant:
+        # K6-TC: tcgen05.mma.kind::i8 over the 8-bit codes; ops = 2 * m * n_shard * dc_pad (code row stride: d rounded up to 128)
+        dcp = (d + 127) // 128 * 128
+        m_gpu = (m + gq - 1) // gq
+        ops = 2.0 * m_gpu * rows_gpu * dcp
+        tpeak, tpeak_sus, tsrc = tensor_peaks()
+        achieved = ops / (hot_ms * 1e-3) / 1e12
+        code_gbs = rows_gpu * dcp / (hot_ms * 1e-3) / 1e9
+        roof = {"bound": "tensor", "kernel": "tc_filter_pair_kernel<.., KIND = 1> (tcgen05.mma.cta_group::2.kind::i8, u8 x u8 -> s32 in TMEM)",
+                "achieved": achieved, "peak": 2.0 * tpeak, "unit": "Tera-op/s", "frac": achieved / (2.0 * tpeak),
+                "peak_source": "2 x the measured bf16 burst peak (MEASURED_PEAKS.json has no int8 figure; an int8 instruction moves twice the K of a bf16 one "
+                               "in the same time); nominal dense int8 = 4500 Tera-op/s (B200_PROFILING.md): frac_of_nominal beside it",
+                "frac_of_nominal": achieved / 4500.0, "algorithmic_ops_per_launch": ops, "useful_ops_per_launch": 2.0 * m_gpu * rows_gpu * d,
+                "kernel_ms_per_launch": hot_ms, "code_bytes_per_launch": int(rows_gpu * dcp), "code_GBs": code_gbs, "code_frac_of_hbm": code_gbs / peak,
+                "traffic": None, "traffic_source": None, "per_gpu": G > 1,
+                "note": "the quantizer's compressed scan as a tensor-core candidate filter over the code matrix; the k' = 100 best codes per query "
+                        "(bit-identical to the SIMT scan's) are re-ranked in fp32 by K4"}
     elif used_tc:
         roof = tensor_roofline(st0, st1, m, rows_gpu, d, G, gq, args.workload, hot_ms)
     else:
@@ -619,7 +644,7 @@ def main():
            "config": {"workload": desc, "n": n, "m": m, "d": d, "k": k, "metric": metric, "qtile": int(qt),
                       "decomposition": ("automatic: %d row shard(s) of up to 2^20 rows x %d query group(s)" % (gr, gq)) if (G > 1 and not args.row_groups) else None,
                       "path": "K5 graph beam search (one GPU-built graph per shard, M0=32)" if use_graph else
-                              "K6 8-bit code scan + K4 fp32 rerank of 100 survivors" if use_quant else
+                              ("K6-TC 8-bit code filter (tcgen05 kind::i8) + K4 fp32 rerank of 100 survivors" if used_tc else "K6 8-bit code scan (dp4a) + K4 fp32 rerank of 100 survivors") if use_quant else
                               ("K3 tcgen05 filter + K4 fp32 rerank" if used_tc else "K1 fp32 SIMT scan"),
                       "nsplit": int(st1["last_nsplit"]), "rows_per_gpu": rows_gpu, "row_groups": gr, "query_groups": gq,
                       "l2": "base shard (%.0f MB) %s L2 (126 MB); no explicit flush" % (rows_gpu * d * 4 / 1e6, "larger than" if rows_gpu * d * 4 > 126e6 else "fits in"),
