@@ -7,6 +7,13 @@
  * binds; the *_device entry points take HBM-resident buffers and a CUDA stream for
  * callers that already own device memory (bench.py / the multi-GPU merge).
  *
+ * Limits (the reference's query_k takes any k; beyond these a call returns EXPANN_ERR_UNSUPPORTED, nothing is truncated
+ * silently): scans k <= 128; quantised scan k' (survivors re-ranked in fp32) <= 128; graph engine max(k, ef) <= 256 and
+ * vertex degree <= 256; GPU graph build 2 <= M, M0 <= 96 and at most 127 candidates per vertex; ids: n + id_offset <
+ * 2^32 - 1 per handle or per GPU shard (graph engine: n < 2^31). Memory beyond the vectors: the graph engine keeps one
+ * visited byte per vertex per resident search slot (about 2960 slots: 3 GB at n = 1M) — shard larger bases over several
+ * GPUs (device list below); the brute-force engine keeps a bf16 copy of the rows (2 or 6 bytes per component).
+ *
  * One handle = one engine instance on one GPU (or, with a device list, on several GPUs of this process) = one host thread at a time (the reference engines are not
  * re-entrant either: src/antitopo_engine.h:208-209). Distinct handles are independent.
  */
