@@ -485,6 +485,8 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 	} else if (nm == "graph_cta_width") {
 		if (value != 1 && value != 2) return fail(h, EXPANN_ERR_ARG, "graph_cta_width must be 1 or 2");
 		h->opt_graph_cta_width = (int)value;
+	} else if (nm == "graph_hash") {
+		h->opt_graph_hash = value != 0;
 	} else if (nm == "graph_upper_compact") {
 		h->opt_graph_upper_compact = value != 0;
 	} else if (nm == "tc_boot") {

@@ -289,8 +289,16 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 		h->stats.graph_launches++;
 		return EXPANN_OK;
 	}
-	const size_t smem = ((size_t)h->d_pad * 5 + GS_MAXNB * 8) * GS_WARPS;
+	size_t smem = ((size_t)h->d_pad * 5 + GS_MAXNB * 8) * GS_WARPS;
 	if (smem > 200 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "graph search: d too large");
+	{
+		// per-warp visited hash in shared memory (graph_search.cuh): 2048 ids per warp when that leaves the resident CTAs
+		// per SM the kernel is launched for (d = 128: 43.5 KB per CTA, five CTAs per SM); else the HBM bytes only
+		const size_t occ = std::max<size_t>(1, h->g_ctas / (size_t)std::max(1, sms));
+		const size_t with_hash = smem + (size_t)GS_HASH * 4 * GS_WARPS;
+		p.hash = h->opt_graph_hash && (with_hash + 1024) * occ <= 227 * 1024 ? GS_HASH : 0;
+		if (p.hash) smem = with_hash;
+	}
 	const unsigned grid = (unsigned)std::min<size_t>(h->g_ctas, (m + GS_WARPS - 1) / GS_WARPS);
 	cudaEvent_t t0 = timing_begin(h, st);
 #define GS_LAUNCH_B(L, B)                                                                                         \

@@ -25,6 +25,7 @@ namespace expann {
 constexpr uint32_t NO_VERTEX = 0xFFFFFFFFu;
 constexpr int GS_WARPS = 4;      // warps per CTA
 constexpr int GS_MAXNB = 256;    // max neighbours of one vertex (bottom stride / upper stride)
+constexpr uint32_t GS_HASH = 2048; // entries of a warp's visited hash in shared memory (8 KB; moves to HBM at 3/4 full)
 
 struct GraphParams {
 	const float* base;        // [n][d_pad]
@@ -42,6 +43,7 @@ struct GraphParams {
 	uint32_t start, max_layer, id_add;
 	int compressed;
 	int width; // latency form: vertices expanded per hop (1 or 2)
+	uint32_t hash; // warp form: entries of the per-warp visited hash in shared memory (power of two; 0 = visited bytes in HBM only)
 	// latency form, upper layers in compact form (null = off): the vertices that have upper layers (~n/M of them) get a
 	// dense index c; up_meta[c] = {first upper row, number of layers, global id, 0}; upper_c = the upper rows with
 	// neighbours as dense indices; up_vec[c] = a copy of the vertex's vector. A step of the descent is then row ->
@@ -150,8 +152,39 @@ __global__ void __launch_bounds__(32 * GS_WARPS, MINB) graph_search_kernel(const
 	uint8_t* vis = p.visited + (size_t)slot * p.vis_stride;
 	uint32_t epoch = p.epoch[slot];
 	unsigned long long dc_total = 0;
+	// Visited set in SHARED memory (exact form): an open-addressing table of vertex ids per warp. A hop is
+	// then adjacency row -> neighbour vectors, two dependent global round trips instead of three (row -> visited bytes ->
+	// vectors): the search is latency-bound, the visited bytes were a third of every hop's chain. Exactness is kept: a query
+	// that fills the table past 3/4 writes its entries into the HBM byte array and carries on there.
+	// MEASURED (1M x 128, 10 000 queries, profiles/r2_graph_hash.json): identical ids and distance-evaluation counts, but
+	// SLOWER than the bytes in HBM at every beam width (ef 20 / 40 / 60 / 120: 8.50 / 5.28 / 3.63 / 1.64 against 9.22 / 5.81 /
+	// 4.23 / 2.10 M QPS): the bytes mostly hit L2 and their round trip overlaps across the 20 resident warps, while the
+	// table costs an 8 KB clear per query and divergent compare-and-swap probing per hop. Kept behind option graph_hash = 1.
+	uint32_t* htab = reinterpret_cast<uint32_t*>(gs_smem + per_warp * GS_WARPS) + (size_t)wib * p.hash;
+	const uint32_t hmask = p.hash - 1, hshift = 32 - __popc(hmask);
 
 	for (uint32_t qi = slot; qi < p.m; qi += nslots) {
+		bool use_hash = p.hash != 0;
+		uint32_t hcount = 0;
+		if (use_hash) {
+			for (uint32_t i = lane * 4; i < p.hash; i += 128) *reinterpret_cast<uint4*>(htab + i) = make_uint4(NO_VERTEX, NO_VERTEX, NO_VERTEX, NO_VERTEX);
+			__syncwarp();
+		}
+		// true if v had not been seen by this query; marks it seen
+		auto first_visit = [&](uint32_t v) -> bool {
+			if (use_hash) {
+				uint32_t hs = (v * 2654435761u) >> hshift;
+				for (;;) {
+					const uint32_t old = atomicCAS(htab + hs, NO_VERTEX, v);
+					if (old == NO_VERTEX) return true;
+					if (old == v) return false;
+					hs = (hs + 1) & hmask;
+				}
+			}
+			const bool fresh = vis[v] != (uint8_t)((epoch + 0u) & 0xFF);
+			if (fresh) vis[v] = (uint8_t)(epoch & 0xFF);
+			return fresh;
+		};
 		// ---- new epoch for the visited bytes (clear the slot when the 8-bit epoch wraps)
 		epoch++;
 		if ((epoch & 0xFF) == 0) {
@@ -221,7 +254,9 @@ __global__ void __launch_bounds__(32 * GS_WARPS, MINB) graph_search_kernel(const
 		else gather_dist_f32(p.base, p.d_pad, qsm, nb, nbd, 1, lane);
 		dc++;
 		beam.insert(beam_key(nbd[0], ep), lane);
-		if (lane == 0) vis[ep] = ep8;
+		if (lane == 0) first_visit(ep);
+		hcount = 1;
+		__syncwarp();
 		float thr = __int_as_float(0x7f800000); // distance at position ef-1 (inf while the beam is not full)
 		bool full = false;
 		if (p.ef == 1) { full = true; thr = nbd[0]; }
@@ -254,15 +289,22 @@ __global__ void __launch_bounds__(32 * GS_WARPS, MINB) graph_search_kernel(const
 			for (uint32_t j0 = 0; j0 < p.m0s; j0 += 32) {
 				const uint32_t v = j0 + lane < p.m0s ? __ldg(row + j0 + lane) : NO_VERTEX;
 				bool fresh = false;
-				if (v != NO_VERTEX) {
-					fresh = vis[v] != ep8;
-					if (fresh) vis[v] = ep8;
-				}
+				if (v != NO_VERTEX) fresh = first_visit(v);
 				const unsigned mk = __ballot_sync(FULL, fresh);
 				if (fresh) nb[cnt + __popc(mk & ((1u << lane) - 1))] = v;
 				cnt += __popc(mk);
 			}
 			__syncwarp();
+			hcount += cnt;
+			if (use_hash && hcount > (p.hash >> 2) * 3) {
+				// the table is three quarters full: its entries move to the visited bytes in HBM, which take over for this query
+				for (uint32_t i = lane; i < p.hash; i += 32) {
+					const uint32_t v = htab[i];
+					if (v != NO_VERTEX) vis[v] = ep8;
+				}
+				use_hash = false;
+				__syncwarp();
+			}
 			if (cnt == 0) continue;
 			if (cnt > 8) {
 				// the gather below works through 8 vertices per round: ask for the rows of the later rounds now, so that only

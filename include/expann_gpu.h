@@ -153,7 +153,9 @@ int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
  * of the search, one CTA per query; -1 automatic = twice the SM count, 0 never), "graph_cta_width" (vertices the latency form expands per hop: 1 (default) =
  * exactly the reference's visit order, 2 = the two closest unexpanded beam entries together: half the dependent hops,
  * measured recall >= at every beam width for 2 % more distance evaluations), "graph_upper_compact" (0/1, before build():
- * compact copy of the upper layers for the latency form, default 1).
+ * compact copy of the upper layers for the latency form, default 1), "graph_hash" (0/1, default 0: the one-warp-per-query form
+ * keeps the visited set in a per-warp shared-memory hash, exact, moving to the per-vertex bytes in HBM when a query fills it;
+ * measured 9-20 % slower than the bytes in HBM, which mostly hit L2).
  * Tensor-core candidate filter of the brute-force engine: "tc" (0/1; operands are prepared by build(), so enabling
  * needs to precede it), "tc_min_batch" (default 5: measured crossover with the SIMT scan on 1M x 128), "tc_pair" (0/1:
  * clusters of two CTAs for batches > 128, default 1), "tc_astream" (0 off | 1 when the query tile cannot stay resident
