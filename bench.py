@@ -227,22 +227,25 @@ def tensor_roofline(st0, st1, m, n_rows_per_gpu, d, G, gq, workload, hot_ms):
     2*m*n*d only (the two-term split issues 3x that)"""
     seg = (d + 63) // 64 * 64
     mode = int(st1["tc_mode"])
-    kd = 3 * seg if mode == 2 else seg
+    kd = 3 * seg if mode == 2 else ((d + 31) // 32 * 32 if mode == 4 else seg)
     m_gpu = (m + gq - 1) // gq
     flops = 2.0 * m_gpu * n_rows_per_gpu * kd
     useful = 2.0 * m_gpu * n_rows_per_gpu * d
     achieved = flops / (hot_ms * 1e-3) / 1e12
     tpeak, tpeak_sus, tsrc = tensor_peaks()
+    if mode == 4:   # kind::tf32 runs at half the bf16 rate (K = 8 per instruction instead of 16): half the measured bf16 peaks
+        tpeak, tpeak_sus, tsrc = tpeak / 2, tpeak_sus / 2, tsrc + " / 2 for tf32"
     qt = int(st1["last_qtile"])
     kname = "tc_filter_pair_kernel" if qt == 256 else "tc_filter2_kernel"
     traffic, trsrc = ncu_traffic(kname) if (workload == "c2" and G == 1 and m == 10000) else (None, None)
-    return {"bound": "tensor", "kernel": kname + (" (tcgen05.mma.cta_group::2 bf16, fp32 accumulate in TMEM)" if qt == 256 else
+    return {"bound": "tensor", "kernel": kname + ((" (tcgen05.mma.cta_group::2 %s, fp32 accumulate in TMEM)" % ("tf32" if mode == 4 else "bf16")) if qt == 256 else
                                                   " (tcgen05.mma bf16, fp32 accumulate in TMEM)"),
             "achieved": achieved, "peak": tpeak, "unit": "TFLOP/s", "frac": achieved / tpeak, "frac_of_sustained_peak": achieved / tpeak_sus,
             "useful_flops_per_launch": useful, "achieved_useful": useful / (hot_ms * 1e-3) / 1e12, "frac_useful": useful / (hot_ms * 1e-3) / 1e12 / tpeak,
             "traffic": traffic, "traffic_source": trsrc, "traffic_unit": "DRAM bytes per launch (read + write)",
             "peak_source": tsrc, "algorithmic_flops_per_launch": flops, "kernel_ms_per_launch": hot_ms,
-            "tc_mode": {1: "bf16-exact (integer rows)", 2: "two-term bf16 split (3x the flops)", 3: "one bf16 term per value (real-valued rows)"}.get(mode, str(mode)),
+            "tc_mode": {1: "bf16-exact (integer rows)", 2: "two-term bf16 split (3x the flops)", 3: "one bf16 term per value (real-valued rows)",
+                        4: "tf32 on the fp32 rows (kind::tf32)"}.get(mode, str(mode)),
             "kd": kd, "per_gpu": G > 1,
             "note": "flops = 2*m*n*kd of the candidate filter on ONE GPU's shard (the slowest GPU's kernel time when several run side by "
                     "side); useful = 2*m*n*d; survivors (about k per query) are re-ranked in fp32 by K4. peak = cuBLAS bf16 burst figure; "

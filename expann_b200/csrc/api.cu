@@ -221,7 +221,7 @@ void expann_gpu_destroy(expann_gpu_t* h) {
 	if (h->tc_flag_event) cudaEventDestroy(h->tc_flag_event);
 	h->tc_flag_host.release();
 	if (h->base) cudaFree(h->base);
-	for (DevBuf* b : { &h->tc_xb, &h->tc_xn, &h->tc_stats, &h->tc_qstats, &h->tc_qb, &h->tc_qn, &h->tc_thr, &h->tc_cnt, &h->tc_cand, &h->tc_gthr, &h->tc_sel, &h->tc_xx, &h->tc_seed, &h->tc_fbcount, &h->scan_cnt })
+	for (DevBuf* b : { &h->tc_xb, &h->tc_xn, &h->tc_stats, &h->tc_qstats, &h->tc_qb, &h->tc_qn, &h->tc_thr, &h->tc_cnt, &h->tc_cand, &h->tc_gthr, &h->tc_sel, &h->tc_xx, &h->tc_xx32, &h->tc_seed, &h->tc_fbcount, &h->scan_cnt })
 		b->release();
 	for (DevBuf* b : { &h->q_codes, &h->q_cnorm, &h->q_mm, &h->qq_codes, &h->qq_norm, &h->q_cand, &h->q_cnb, &h->q_thrfin, &h->q_zero }) b->release();
 	for (DevBuf* b : { &h->g_bottom, &h->g_upper, &h->g_upper_idx, &h->g_upper_nl, &h->g_visited, &h->g_epoch, &h->g_codes, &h->g_up_meta,
@@ -500,6 +500,9 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 	} else if (nm == "quant_tc_min_batch") {
 		if (value < 1) return fail(h, EXPANN_ERR_ARG, "quant_tc_min_batch must be >= 1");
 		h->opt_quant_tc_min_batch = (int)value;
+	} else if (nm == "tc_tf32") {
+		if (h->built) return fail(h, EXPANN_ERR_STATE, "tc_tf32 must be set before build()");
+		h->opt_tc_tf32 = value != 0;
 	} else if (nm == "tc_v1") {
 		h->opt_tc_v1 = value != 0;
 	} else if (nm == "tc") {

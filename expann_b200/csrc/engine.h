@@ -66,7 +66,7 @@ struct expann_gpu {
 	expann_gpu_stats_t stats{};
 	// tensor-core candidate filter (K3)
 	int opt_tc = 1, opt_tc_min_batch = 5; // from 5 queries on K3 is level with or ahead of K1 (1M x 128: 0.12 vs 0.15 ms at 6, 0.13 vs 0.22 at 12)
-	int tc_mode = 0; // 0 off, 1 bf16-exact single GEMM, 2 two-term bf16 split, 3 one bf16 term per value (real-valued data, wider slack)
+	int tc_mode = 0; // 0 off, 1 bf16-exact single GEMM, 2 two-term bf16 split, 3 one bf16 term per value (real-valued data, wider slack), 4 tf32 on the fp32 rows
 	int opt_tc_real = 1; // real-valued data: 1 = start in the one-term format (mode 3) and move to the split when a batch is redone, 0 = split from the start
 	bool tc_flag_pending = false; // mode 3: a copy of the last batch's flag word is on its way to tc_flag_host
 	cudaEvent_t tc_flag_event = nullptr;
@@ -74,7 +74,9 @@ struct expann_gpu {
 	uint32_t tc_kd = 0;
 	float tc_xmin = 0.f, tc_xmax = 0.f, tc_xnorm_max = 0.f;
 	expann::DevBuf tc_xb, tc_xn, tc_stats, tc_qstats, tc_qb, tc_qn, tc_thr, tc_cnt, tc_cand, tc_gthr, tc_sel, tc_xx, tc_seed, tc_fbcount;
-	CUtensorMap tmap_xb{}, tmap_xb128{}, tmap_xx{};
+	CUtensorMap tmap_xb{}, tmap_xb128{}, tmap_xx{}, tmap_x32{}, tmap_xx32{}; // (x32 / xx32: format 4, fp32 maps over the base rows / tf32 norm terms)
+	expann::DevBuf tc_xx32;
+	int opt_tc_tf32 = 1; // real-valued rows: try kind::tf32 (format 4) between the one-term format and the split
 	int opt_tc_v1 = 0; // force the chunked first form of K3 (tests)
 	int opt_tc_pair = 1; // pair form of K3 (clusters of two CTAs, tcgen05.mma.cta_group::2)
 	int opt_tc_astream = 1; // pair form with the query operand streamed through the ring: 0 off, 1 when nothing else fits, 2 always
@@ -143,6 +145,9 @@ int mg_stats(expann_gpu* h, expann_gpu_stats_t* out);
 int launch_scan_f32(expann_gpu* h, const float* d_q_padded, size_t m, size_t k, uint64_t* d_keys_out,
                     cudaStream_t st);
 int make_base_tensor_map(expann_gpu* h);
+// 2D tiled tensor map over fp32 (dtype_u8 = 0) or byte (1) rows; 128-byte swizzle, or 32-byte for 32-byte box rows
+int encode_tensor_map_2d(expann_gpu* h, CUtensorMap* out, int dtype_u8, void* base, uint64_t inner, uint64_t rows,
+                         uint64_t row_bytes, uint32_t box_inner, uint32_t box_rows, int swizzle32 = 0);
 // graph.cu
 int graph_set_csr(expann_gpu* h, size_t n, const uint32_t* nlayers, const uint64_t* offsets, const uint32_t* edges,
                   uint64_t start, uint64_t max_layer);

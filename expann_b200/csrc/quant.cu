@@ -9,8 +9,6 @@ namespace expann {
 constexpr int QS_TR = 2, QS_NWARP = 8, QS_STAGES = 3;
 constexpr int QS_ROWS = 32 * QS_TR * QS_NWARP;
 
-int encode_tensor_map_2d(expann_gpu* h, CUtensorMap* out, int dtype_u8, void* base, uint64_t inner, uint64_t rows,
-                         uint64_t row_bytes, uint32_t box_inner, uint32_t box_rows);
 
 static int quantize_rows(expann_gpu* h, const float* src, size_t src_stride, size_t n, uint8_t* dst, int32_t* norm,
                          cudaStream_t st) {

@@ -29,7 +29,7 @@ static encode_tiled_fn get_encode_tiled() {
 
 // 2D tiled tensor map with 128B swizzle (16-byte chunk c of box row r lands at chunk c ^ (r & 7) of its line)
 int encode_tensor_map_2d(expann_gpu* h, CUtensorMap* out, int dtype_u8, void* base, uint64_t inner, uint64_t rows,
-                         uint64_t row_bytes, uint32_t box_inner, uint32_t box_rows) {
+                         uint64_t row_bytes, uint32_t box_inner, uint32_t box_rows, int swizzle32) {
 	encode_tiled_fn enc = get_encode_tiled();
 	if (!enc) return fail(h, EXPANN_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
 	cuuint64_t gdim[2] = { (cuuint64_t)inner, (cuuint64_t)rows };
@@ -37,8 +37,8 @@ int encode_tensor_map_2d(expann_gpu* h, CUtensorMap* out, int dtype_u8, void* ba
 	cuuint32_t box[2] = { box_inner, box_rows };
 	cuuint32_t estr[2] = { 1, 1 };
 	CUresult r = enc(out, dtype_u8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, gdim, gstride,
-	                 box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-	                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+	                 box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+	                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 	if (r != CUDA_SUCCESS) return fail(h, EXPANN_ERR_CUDA, "cuTensorMapEncodeTiled failed: " + std::to_string((int)r));
 	return EXPANN_OK;
 }

@@ -65,7 +65,35 @@ static int reset_stats(expann_gpu* h, DevBuf& buf, cudaStream_t st) {
 // [xh | xl | xh] in the two-term split (2)
 static uint32_t tc_kd_of(const expann_gpu* h, int mode) {
 	const uint32_t seg = (uint32_t)((h->d + 63) / 64 * 64);
+	if (mode == 4) return (uint32_t)(2 * h->d_pad); // tf32: the fp32 rows themselves, counted in 2-byte units like the others
 	return mode == 2 ? 3 * seg : seg;
+}
+
+int launch_filter_pair_tf32(expann_gpu* h, const CUtensorMap& tq, const Tc2Params& p, dim3 grid, cudaStream_t st); // tc_tf32.cu
+
+// format 4 (kind::tf32): no operand copy -- ||x||^2, its three tf32 terms, statistics, tensor maps over the fp32 base rows
+static int tc_prepare_tf32(expann_gpu* h) {
+	cudaStream_t st = h->stream;
+	const size_t n_pad = (h->n + TC_BN - 1) / TC_BN * TC_BN;
+	EXPANN_CUDA(h, h->tc_xn.ensure(n_pad * 4));
+	EXPANN_CUDA(h, h->tc_xx32.ensure(h->n * 32));
+	if (int rc = reset_stats(h, h->tc_stats, st)) return rc;
+	tc_norm_tf32_kernel<<<(unsigned)((h->n + 7) / 8), 256, 0, st>>>(h->base, h->d_pad, (uint32_t)h->d, h->n, h->tc_xn.as<float>(),
+	                                                               h->tc_xx32.as<float>(), h->cfg.metric == EXPANN_METRIC_IP ? 0 : 1,
+	                                                               h->tc_stats.as<TcStats>());
+	EXPANN_CUDA(h, cudaGetLastError());
+	h->stats.aux_launches++;
+	TcStats s;
+	if (int rc = read_stats(h, h->tc_stats, &s, st)) return rc;
+	h->tc_xmin = f32_from_orderable(s.vmin);
+	h->tc_xmax = f32_from_orderable(s.vmax);
+	h->tc_xnorm_max = std::sqrt(f32_from_orderable(s.nmax));
+	h->tc_kd = tc_kd_of(h, 4);
+	if (int rc = encode_tensor_map_2d(h, &h->tmap_x32, 0, h->base, h->d_pad, h->n, h->d_pad * 4, 32, TC2_TN)) return rc;
+	if (int rc = encode_tensor_map_2d(h, &h->tmap_xx32, 0, h->tc_xx32.p, 8, h->n, 32, 8, TC2_TN, 1)) return rc;
+	h->tc_xb.release(); // the bf16 operand of the probed format is not needed any more
+	h->tc_xx.release();
+	return EXPANN_OK;
 }
 
 // materialise the bf16 operand of `fmt` (1 = one bf16 term per value, 2 = two-term split), ||x||^2 and its three-term
@@ -145,11 +173,28 @@ int tc_finalize(expann_gpu* h) {
 			EXPANN_CUDA(h, cudaMemcpy(&redone, h->tc_fbcount.p, 4, cudaMemcpyDeviceToHost));
 			EXPANN_CUDA(h, cudaMemset(h->tc_fbcount.p, 0, 4)); // the probe is not a user batch: not counted in tc_fallbacks
 		}
-		probe_keys.release();
 		h->tc_flag_pending = false;
 		h->stats.tc_launches = 0;
-		if (rc) return rc;
-		if (!redone) return EXPANN_OK;
+		if (rc) { probe_keys.release(); return rc; }
+		if (!redone) { probe_keys.release(); return EXPANN_OK; }
+		// next: tf32 on the fp32 rows (slack 5x tighter, twice the MMA time of one bf16 term, no operand copy), probed alike
+		if (h->opt_tc_tf32) {
+			if (int r2 = tc_prepare_tf32(h)) { probe_keys.release(); return r2; }
+			h->tc_mode = 4;
+			rc = tc_batch2(h, h->base, pm, pk, probe_keys.as<uint64_t>(), h->stream, &fb);
+			redone = 0;
+			if (!rc) {
+				EXPANN_CUDA(h, cudaStreamSynchronize(h->stream));
+				EXPANN_CUDA(h, cudaMemcpy(&redone, h->tc_fbcount.p, 4, cudaMemcpyDeviceToHost));
+				EXPANN_CUDA(h, cudaMemset(h->tc_fbcount.p, 0, 4));
+			}
+			h->tc_flag_pending = false;
+			h->stats.tc_launches = 0;
+			probe_keys.release();
+			if (rc) return rc;
+			if (!redone) return EXPANN_OK;
+		} else
+			probe_keys.release();
 	}
 	if (int rc = tc_prepare(h, 2, nullptr)) return rc;
 	h->tc_mode = 2;
@@ -162,7 +207,11 @@ static void tc_eps(const expann_gpu* h, float* eps_rel, float* eps_abs) {
 	*eps_abs = 0.f;
 	if (h->tc_mode == 1) return;
 	const float acc = (float)h->tc_kd / 16.f * (1.0f / 8388608.0f); // fp32 accumulation over kd/16 MMA steps, 2^-23 each
-	if (h->tc_mode == 3)
+	if (h->tc_mode == 4)
+		// tf32: the tensor core reads the fp32 rows' top 19 bits (truncation: 2^-10), the queries were rounded to tf32 (2^-11);
+		// the query operand carries the factor -2; K = 8 per step: d_pad / 8 accumulation steps
+		*eps_rel = 2.0f * (1.0f / 1024.0f + 1.0f / 2048.0f + 1.0f / 1048576.0f) + (float)h->d_pad / 8.f * (1.0f / 8388608.0f);
+	else if (h->tc_mode == 3)
 		// one bf16 term per operand: unit roundoff 2^-8 each, so a product is off by at most (2^-7 + 2^-16) |q_i x_i|; the
 		// query operand carries the factor -2 (L2; -1 for the inner product, where this is twice what is needed)
 		*eps_rel = 2.0f * (1.0f / 128.0f + 1.0f / 65536.0f) + acc;
@@ -175,18 +224,23 @@ static void tc_eps(const expann_gpu* h, float* eps_rel, float* eps_abs) {
 // one-term format: has an earlier batch been redone? (its flag word was copied to page-locked memory behind the batch;
 // looked at here without waiting) -> the handle moves to the two-term split for good
 static int tc_adapt_format(expann_gpu* h) {
-	if (h->tc_mode != 3 || !h->tc_flag_pending) return EXPANN_OK;
+	if ((h->tc_mode != 3 && h->tc_mode != 4) || !h->tc_flag_pending) return EXPANN_OK;
 	if (cudaEventQuery(h->tc_flag_event) != cudaSuccess) { cudaGetLastError(); return EXPANN_OK; }
 	h->tc_flag_pending = false;
 	if (*h->tc_flag_host.as<uint32_t>() == 0) return EXPANN_OK;
 	EXPANN_CUDA(h, cudaDeviceSynchronize()); // operand buffers are about to be rewritten
-	if (int rc = tc_prepare(h, 2, nullptr)) return rc;
-	h->tc_mode = 2;
-	h->stats.tc_mode = 2;
+	if (h->tc_mode == 3 && h->opt_tc_tf32) { // one bf16 term -> tf32 -> two-term split
+		if (int rc = tc_prepare_tf32(h)) return rc;
+		h->tc_mode = 4;
+	} else {
+		if (int rc = tc_prepare(h, 2, nullptr)) return rc;
+		h->tc_mode = 2;
+	}
+	h->stats.tc_mode = (uint64_t)h->tc_mode;
 	return EXPANN_OK;
 }
 static int tc_watch_flag(expann_gpu* h, const uint32_t* flags, cudaStream_t st) {
-	if (h->tc_mode != 3 || h->tc_flag_pending) return EXPANN_OK;
+	if ((h->tc_mode != 3 && h->tc_mode != 4) || h->tc_flag_pending) return EXPANN_OK;
 	if (!h->tc_flag_event) {
 		EXPANN_CUDA(h, h->tc_flag_host.ensure(4));
 		EXPANN_CUDA(h, cudaEventCreateWithFlags(&h->tc_flag_event, cudaEventDisableTiming));
@@ -366,7 +420,8 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	// candidate buffers per row split (one per half tile)
 	// streamed-A pair form: the only one for operand rows too long for a resident query tile (any batch size then)
 	const bool astream = Tc2Cfg<1>::smem_bytes(kd, 4) > 227 * 1024 || h->opt_tc_astream == 2;
-	const bool pair = astream || (h->opt_tc_pair && m > TC_BM && Tc3Cfg::smem_bytes(kd, 4) <= 227 * 1024);
+	const bool tf32 = h->tc_mode == 4; // pair form only (any batch size)
+	const bool pair = tf32 || astream || (h->opt_tc_pair && m > TC_BM && Tc3Cfg::smem_bytes(kd, 4) <= 227 * 1024);
 	const uint32_t qblocks = pair ? 2 * (uint32_t)((m + 255) / 256) : (uint32_t)((m + TC_BM * nqb - 1) / (TC_BM * nqb));
 	const uint32_t ntiles = (uint32_t)((h->n + (pair ? TC3_TN : TC2_TN) - 1) / (pair ? TC3_TN : TC2_TN));
 	// pair form, large bases: a short first launch over the leading boot_tiles tiles seeds every stream of the main launch
@@ -391,8 +446,12 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	uint32_t* flags = reinterpret_cast<uint32_t*>(h->tc_sel.as<uint64_t>() + m * (size_t)TC_PAD);
 	EXPANN_CUDA(h, h->tc_qstats.ensure(sizeof(TcStats)));
 	tc_batch_init_kernel<<<(unsigned)((std::max<size_t>(m, 4) + 255) / 256), 256, 0, st>>>(h->tc_qstats.as<TcStats>(), flags, h->tc_gthr.as<uint32_t>(), (uint32_t)m);
-	tc_convert_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(d_q, h->d_pad, (uint32_t)h->d, m, h->tc_qb.as<__nv_bfloat16>(), kd,
-	                                                          h->tc_mode == 2 ? 2 : 1, 1, h->tc_qn.as<float>(), h->tc_qstats.as<TcStats>(), ip ? -1.f : -2.f);
+	if (tf32) // the query operand of format 4: fp32 rows, scaled by -2 (-1) and rounded to tf32, [m][d_pad]
+		tc_query_tf32_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(d_q, h->d_pad, (uint32_t)h->d, (uint32_t)h->d_pad, m, h->tc_qb.as<float>(),
+		                                                             ip ? -1.f : -2.f, h->tc_qn.as<float>());
+	else
+		tc_convert_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(d_q, h->d_pad, (uint32_t)h->d, m, h->tc_qb.as<__nv_bfloat16>(), kd,
+		                                                          h->tc_mode == 2 ? 2 : 1, 1, h->tc_qn.as<float>(), h->tc_qstats.as<TcStats>(), ip ? -1.f : -2.f);
 	EXPANN_CUDA(h, cudaGetLastError());
 	h->stats.aux_launches += 2;
 	float eps_rel = 0.f, eps_abs = 0.f;
@@ -404,7 +463,10 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	} else
 		tc_eps(h, &eps_rel, &eps_abs);
 	CUtensorMap tq;
-	if (int rc = encode_tensor_map_bf16(h, &tq, h->tc_qb.p, kd, m, TC_BM)) return rc;
+	if (tf32) {
+		if (int rc = encode_tensor_map_2d(h, &tq, 0, h->tc_qb.p, h->d_pad, m, h->d_pad * 4, 32, TC_BM)) return rc;
+	} else if (int rc = encode_tensor_map_bf16(h, &tq, h->tc_qb.p, kd, m, TC_BM))
+		return rc;
 	Tc2Params p{};
 	p.xn = h->tc_xn.as<float>();
 	p.qn = h->tc_qn.as<float>();
@@ -440,13 +502,15 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 		b.seed_in = nullptr;
 		b.seed_out = h->tc_seed.as<float>();
 		const dim3 bgrid(qblocks, 1);
-		int brc = astream                                              ? launch_filter_pair<5, true>(h, tq, b, bgrid, st)
+		int brc = tf32                                                 ? launch_filter_pair_tf32(h, tq, b, bgrid, st)
+		          : astream                                            ? launch_filter_pair<5, true>(h, tq, b, bgrid, st)
 		          : Tc3Cfg::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024 ? launch_filter_pair<TC2_NSTAGE>(h, tq, b, bgrid, st)
 		                                                              : launch_filter_pair<4>(h, tq, b, bgrid, st);
 		if (brc) return brc;
 		h->stats.tc_launches++;
 	}
-	int rc = astream  ? launch_filter_pair<5, true>(h, tq, p, grid, st)
+	int rc = tf32     ? launch_filter_pair_tf32(h, tq, p, grid, st)
+	         : astream  ? launch_filter_pair<5, true>(h, tq, p, grid, st)
 	         : pair   ? (Tc3Cfg::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024 ? launch_filter_pair<TC2_NSTAGE>(h, tq, p, grid, st)
 	                                                                     : launch_filter_pair<4>(h, tq, p, grid, st))
 	         : nqb == 2 ? launch_filter2<2, TC2_NSTAGE>(h, tq, p, grid, st)
@@ -495,7 +559,9 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 }
 
 // entry used by the brute-force engine for large batches
-bool tc_first_form_fits(const expann_gpu* h) { return tc_smem_bytes(h->tc_kd, h->tc_mode != 2 ? TC_NSTAGE_EXACT : TC_NSTAGE_SPLIT) <= 227 * 1024; }
+bool tc_first_form_fits(const expann_gpu* h) { // (the chunked first form has no tf32 variant)
+	return h->tc_mode != 4 && tc_smem_bytes(h->tc_kd, h->tc_mode != 2 ? TC_NSTAGE_EXACT : TC_NSTAGE_SPLIT) <= 227 * 1024;
+}
 
 int launch_scan_tc(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st) {
 	for (size_t q0 = 0; q0 < m; q0 += TC_QBATCH) {

@@ -56,6 +56,7 @@ __device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const void* tmap
 	    "l"(tmap), "r"(mbar_cluster_addr), "r"(c0), "r"(c1)
 	    : "memory");
 }
+// KIND 2: kind::tf32 (fp32 rows read as tf32, K = 8 per instruction = the same 32 bytes; the fp32 base rows are the operand).
 // KIND 0: kind::f16 (bf16 x bf16 -> fp32). KIND 1: kind::i8 (u8 x u8 -> s32, K = 32 per instruction: the same 32 bytes
 // of every operand row as a bf16 step, so descriptors and k-block layout are unchanged).
 template <int KIND>
@@ -66,10 +67,16 @@ __device__ __forceinline__ void tc_mma_2sm(uint32_t d_tmem, uint64_t adesc, uint
 		    "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
 		    "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
 		    : "memory");
-	else
+	else if (KIND == 1)
 		asm volatile(
 		    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
 		    "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+		    "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+		    : "memory");
+	else
+		asm volatile(
+		    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+		    "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
 		    "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
 		    : "memory");
 }
@@ -82,7 +89,8 @@ __device__ __forceinline__ void tc_commit_2sm(uint64_t* bar) {
 template <int KIND>
 __device__ __forceinline__ uint32_t tc3_instr_desc() { // K-major operands, M = 256 (pair), N = 256
 	// KIND 0: D = fp32 (bits 4-5 = 1), A = B = bf16 (format 1 at bits 7-9 / 10-12); KIND 1: D = s32 (2), A = B = unsigned 8 bit (0)
-	const uint32_t fmt = KIND == 0 ? (1u << 4) | (1u << 7) | (1u << 10) : (2u << 4);
+	// KIND 2: D = fp32, A = B = tf32 (format 2)
+	const uint32_t fmt = KIND == 0 ? (1u << 4) | (1u << 7) | (1u << 10) : KIND == 1 ? (2u << 4) : (1u << 4) | (2u << 7) | (2u << 10);
 	return fmt | ((uint32_t)(TC3_TN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
 }
 
@@ -128,7 +136,7 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 	uint8_t* smem = (uint8_t*)(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
 	const uint32_t nkb = p.kd / TC_BK;
 	constexpr uint32_t STG = TC2_STAGE_BYTES + (ASTREAM ? TC_A_KB_BYTES : 0); // ring slot
-	constexpr int KMUL = KIND == 1 ? 2 : 1; // tensor-map elements per 2-byte unit of the operand rows (u8 codes: 2)
+	constexpr int KELEM = KIND == 0 ? TC_BK : KIND == 1 ? 2 * TC_BK : TC_BK / 2; // tensor-map elements per 128-byte k-block: 64 bf16 | 128 codes | 32 floats
 	constexpr uint32_t BOFF = ASTREAM ? TC_A_KB_BYTES : 0;                    // B inside the slot; norm terms follow B
 	uint8_t* smA = smem;                                                    // [nkb][128 q][64 bf16] (resident form)
 	uint8_t* smOnes = smA + (ASTREAM ? 0 : (size_t)nkb * TC_A_KB_BYTES);    // [128 q][16 bf16]
@@ -158,8 +166,12 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 		for (int s = 0; s < 2; ++s) { mbar_init(&tm_full[s], 1); mbar_init(&tm_empty[s], 2 * Tc3Cfg::EPI_WARPS); }
 		mbar_fence_init();
 	}
-	for (int i = tid; i < 128 * 16; i += Tc3Cfg::THREADS)
-		reinterpret_cast<__nv_bfloat16*>(smOnes)[i] = __float2bfloat16_rn((i & 7) < 3 ? 1.f : 0.f);
+	if (KIND == 2) { // constant A rows of the norm step: 32-byte rows of 8 floats [1 1 1 0 | 1 1 1 0]
+		for (int i = tid; i < 128 * 8; i += Tc3Cfg::THREADS) reinterpret_cast<float*>(smOnes)[i] = (i & 3) < 3 ? 1.f : 0.f;
+	} else {
+		for (int i = tid; i < 128 * 16; i += Tc3Cfg::THREADS)
+			reinterpret_cast<__nv_bfloat16*>(smOnes)[i] = __float2bfloat16_rn((i & 7) < 3 ? 1.f : 0.f);
+	}
 	fence_proxy_async();
 	if (warp == Tc3Cfg::EPI_WARPS + 1) { // the same logical warp of both CTAs
 		asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)) : "memory");
@@ -181,7 +193,7 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 				if (!ASTREAM) {
 					if (leader) mbar_expect_tx(a_full, 2 * nkb * TC_A_KB_BYTES);
 					for (uint32_t kb = 0; kb < nkb; ++kb)
-						tma_load_2d_2sm(smA + (size_t)kb * TC_A_KB_BYTES, &tmap_q, (int)(kb * TC_BK * KMUL), (int)q0, a_full_l);
+						tma_load_2d_2sm(smA + (size_t)kb * TC_A_KB_BYTES, &tmap_q, (int)(kb * KELEM), (int)q0, a_full_l);
 				}
 			}
 			__syncwarp();
@@ -192,11 +204,11 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 					const uint32_t s = it % NSTAGE, use = it / NSTAGE;
 					if (use > 0) mbar_wait(&empty[s], (use - 1) & 1);
 					if (elect_one()) {
-						const bool last = KIND == 0 && kb + 1 == nkb; // the norm terms of the tile travel with its last k-block
+						const bool last = KIND != 1 && kb + 1 == nkb; // the norm terms of the tile travel with its last k-block
 						const uint32_t full_l = mapa_u32(&full[s], 0);
 						if (leader) mbar_expect_tx(&full[s], 2 * (BOFF + TC2_B_STAGE_BYTES + (last ? TC2_X_BYTES : 0)));
-						if (ASTREAM) tma_load_2d_2sm(smB + (size_t)s * STG, &tmap_q, (int)(kb * TC_BK * KMUL), (int)q0, full_l);
-						tma_load_2d_2sm(smB + (size_t)s * STG + BOFF, &tmap_x, (int)(kb * TC_BK * KMUL), (int)row, full_l);
+						if (ASTREAM) tma_load_2d_2sm(smB + (size_t)s * STG, &tmap_q, (int)(kb * KELEM), (int)q0, full_l);
+						tma_load_2d_2sm(smB + (size_t)s * STG + BOFF, &tmap_x, (int)(kb * KELEM), (int)row, full_l);
 						if (last) tma_load_2d_2sm(smB + (size_t)s * STG + BOFF + TC2_B_STAGE_BYTES, &tmap_xx, 0, (int)row, full_l);
 					}
 					__syncwarp();
@@ -258,7 +270,7 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 #pragma unroll
 						for (int k = 0; k < TC_BK / TC_UMMA_K; ++k)
 							tc_mma_2sm<KIND>(d_tmem, ad0 + 2 * k, bd0 + 2 * k, idesc, (kb | (uint32_t)k) != 0 ? 1u : 0u);
-						if (KIND == 0 && kb + 1 == nkb) tc_mma_2sm<0>(d_tmem, ones_desc, x_desc0 + (uint64_t)((s * STG) >> 4), idesc, 1u);
+						if (KIND != 1 && kb + 1 == nkb) tc_mma_2sm<KIND>(d_tmem, ones_desc, x_desc0 + (uint64_t)((s * STG) >> 4), idesc, 1u);
 						tc_commit_2sm(&empty[s]);
 						if (kb + 1 == nkb) tc_commit_2sm(&tm_full[acc]);
 					}
@@ -314,7 +326,7 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 			mbar_wait(&tm_full[acc], (lt >> 1) & 1);
 			tc_fence_after();
 			const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * TC3_TN + half * TC2_TN;
-			if (KIND == 0) {
+			if (KIND != 1) {
 				// the thread's 128 accumulator columns go to registers in one go and the accumulator is handed back to the MMA
 				// warp BEFORE they are looked at: a warp that has hits to work through no longer holds the other 15 warps of
 				// the pair (and the next MMA) up, it only has to be back in time for its next tile

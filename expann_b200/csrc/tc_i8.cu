@@ -20,8 +20,6 @@
 
 namespace expann {
 
-int encode_tensor_map_2d(expann_gpu* h, CUtensorMap* out, int dtype_u8, void* base, uint64_t inner, uint64_t rows,
-                         uint64_t row_bytes, uint32_t box_inner, uint32_t box_rows);
 
 constexpr int32_t CODE_BIAS = 0x40000000; // a'' = bias + sum c^2 - 2 sum q c stays a positive normal float bit pattern
 constexpr uint32_t CODE_PAD_NORM = 0x7F000000u;

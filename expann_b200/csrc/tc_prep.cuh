@@ -143,3 +143,75 @@ __global__ void __launch_bounds__(128) tc_select_kernel(uint64_t* __restrict__ c
 }
 
 } // namespace expann
+
+namespace expann {
+
+// ---- operand format 4 (tcgen05.mma.kind::tf32): the fp32 rows themselves are the operand -----------------------------
+// a float whose low 13 mantissa bits are zero is read by the tensor core without loss
+__device__ __forceinline__ float tf32_trunc(float v) { return __uint_as_float(__float_as_uint(v) & 0xFFFFE000u); }
+__device__ __forceinline__ float tf32_round(float v) { // round to nearest even at 10 mantissa bits
+	uint32_t u = __float_as_uint(v);
+	u += 0xFFFu + ((u >> 13) & 1u);
+	return __uint_as_float(u & 0xFFFFE000u);
+}
+
+// base rows: ||x||^2 (fp32) and its three tf32 terms for the norm step of the GEMM, as a 32-byte row of 8 floats
+// [h/2 m/2 l/2 0 | h/2 m/2 l/2 0] (both 16-byte halves alike, see tc_convert_kernel); value statistics like tc_convert.
+static __global__ void tc_norm_tf32_kernel(const float* __restrict__ src, size_t src_stride, uint32_t d, size_t rows,
+                                           float* __restrict__ norm2, float* __restrict__ xx, int xx_norm, TcStats* __restrict__ stats) {
+	const size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	const int lane = threadIdx.x & 31;
+	if (row >= rows) return;
+	const float* x = src + row * src_stride;
+	float s = 0.f, mn = 3.4e38f, mx = -3.4e38f;
+	for (uint32_t i = lane; i < d; i += 32) {
+		const float v = x[i];
+		s = fmaf(v, v, s);
+		mn = fminf(mn, v);
+		mx = fmaxf(mx, v);
+	}
+#pragma unroll
+	for (int of = 16; of >= 1; of >>= 1) {
+		s += __shfl_xor_sync(FULL, s, of);
+		mn = fminf(mn, __shfl_xor_sync(FULL, mn, of));
+		mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, of));
+	}
+	if (lane < 8) {
+		float t = 0.f;
+		if (xx_norm) {
+			const float h = tf32_trunc(s), r1 = s - h, mm = tf32_trunc(r1), ll = r1 - mm; // 11 + 11 + 2 bits: exact
+			const int j = lane & 3;
+			t = 0.5f * (j == 0 ? h : j == 1 ? mm : j == 2 ? ll : 0.f);
+		}
+		xx[row * 8 + lane] = t;
+	}
+	if (lane == 0) {
+		if (norm2) norm2[row] = s;
+		if (stats) {
+			volatile TcStats* vs = stats;
+			const uint32_t omn = f32_orderable(mn), omx = f32_orderable(mx), os = f32_orderable(s);
+			if (omn < vs->vmin) atomicMin(&stats->vmin, omn);
+			if (omx > vs->vmax) atomicMax(&stats->vmax, omx);
+			if (os > vs->nmax) atomicMax(&stats->nmax, os);
+		}
+	}
+}
+
+// queries: dst[row][d_pad] = tf32(scale * q) rounded to nearest (zero padded), norm2[row] = ||q||^2
+static __global__ void tc_query_tf32_kernel(const float* __restrict__ src, size_t src_stride, uint32_t d, uint32_t d_pad, size_t rows,
+                                            float* __restrict__ dst, float scale, float* __restrict__ norm2) {
+	const size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	const int lane = threadIdx.x & 31;
+	if (row >= rows) return;
+	float s = 0.f;
+	for (uint32_t i = lane; i < d_pad; i += 32) {
+		const float v = i < d ? src[row * src_stride + i] : 0.f;
+		s = fmaf(v, v, s);
+		dst[row * d_pad + i] = tf32_round(scale * v);
+	}
+#pragma unroll
+	for (int of = 16; of >= 1; of >>= 1) s += __shfl_xor_sync(FULL, s, of);
+	if (lane == 0 && norm2) norm2[row] = s;
+}
+
+} // namespace expann

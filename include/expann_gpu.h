@@ -66,8 +66,10 @@ typedef struct expann_gpu_stats {
 	                                             the device: expann_gpu_stats() synchronises the device to read it) */
 	uint64_t tc_mode;                         /* operand format of the tensor-core filter: 0 off, 1 bf16-exact integers (error 0),
 	                                             3 one bf16 term per value (real-valued data; slack 2^-6 |q| max|x|), 2 two-term bf16
-	                                             split (3x the flops, slack 2^-14 |q| max|x|). build() picks 1 or 3; a batch of
-	                                             format 3 that had to be redone moves the handle to 2 */
+	                                             split (3x the flops, slack 2^-14 |q| max|x|), 4 tf32 on the fp32 rows themselves (twice
+	                                             the MMA time of 3, slack 2^-8.4 |q| max|x|, no operand copy). build() picks 1, else
+	                                             probes 3, then 4, then takes 2; a batch that had to be redone moves the handle on
+	                                             (3 -> 4 -> 2) */
 	uint64_t peer_bytes;                      /* multi-device handle: bytes moved between GPUs so far (query blocks out over
 	                                             NVLink, [m][k] key lists stored into the first GPU's gather buffer) */
 	uint64_t query_groups, row_groups;        /* multi-device handle: decomposition n_devices = query_groups x row_groups (else 0) */
@@ -161,7 +163,8 @@ int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
  * clusters of two CTAs for batches > 128, default 1), "tc_astream" (0 off | 1 when the query tile cannot stay resident
  * | 2 always), "tc_boot" (seeding launch: 0 off | 1 one-term formats and >= 8192 queries | 2 always), "tc_v1" (force the
  * chunked first form), "tc_real" (real-valued rows, before build(): 1 (default) one bf16 term per value, falling back to the
- * two-term split when a batch had to be redone | 0 the split from the start).
+ * next format when a batch had to be redone | 0 the split from the start), "tc_tf32" (0/1, default 1, before build(): tf32 on the
+ * fp32 rows (format 4) is the format between the one-term one and the split).
  * Quantised scan engine: "quant_tc" (0/1, default 1: batches of at least "quant_tc_min_batch" queries (default 32) run the
  * code scan as a tensor-core candidate filter, tcgen05.mma.kind::i8 on the 8-bit codes, with the SIMT scan as its queued
  * redo; same result).

@@ -41,7 +41,7 @@ def test_fuzz_tc_vs_simt():
             base = np.ascontiguousarray(base[np.argsort(-((base - c) ** 2).sum(1))])
             q = np.tile(c, (m, 1)).astype(np.float32)
         opts = {"tc_pair": int(rng.integers(0, 2)), "tc_boot": int(rng.choice([0, 1, 2])), "tc_astream": int(rng.choice([1, 1, 2])),
-                "tc_real": int(rng.integers(0, 2))}
+                "tc_real": int(rng.integers(0, 2)), "tc_tf32": int(rng.integers(0, 2))}
         res = []
         for tc in (1, 0):
             e = expann_b200.BruteForceEngine(metric=metric)

@@ -14,9 +14,11 @@ def ex():
     return expann_b200
 
 
-def run(ex, base, q, k, metric=0, tc=1, id_offset=0, v1=0, pair=1, boot=None, real=None):
+def run(ex, base, q, k, metric=0, tc=1, id_offset=0, v1=0, pair=1, boot=None, real=None, tf32=None):
     e = ex.BruteForceEngine(metric=metric, id_offset=id_offset)
     e.set_option("tc", tc)
+    if tf32 is not None:
+        e.set_option("tc_tf32", tf32)  # 1 (default): tf32 on the fp32 rows (format 4) is tried between the one-term format and the split
     if real is not None:
         e.set_option("tc_real", real)  # real-valued rows: 1 (default) one bf16 term per value (mode 3), 0 two-term split (mode 2)
     e.set_option("tc_pair", pair)  # 1 (default): clusters of two CTAs, tcgen05.mma.cta_group::2; 0: single-CTA form
@@ -309,10 +311,11 @@ def test_signed_integer_rows(ex, oracle, amp):
         assert a[3]["tc_mode"] == 1 and a[3]["tc_fallbacks"] == 0
 
 
-def test_one_term_format_moves_to_split_after_a_redo(ex, oracle):
-    """mode 3 (one bf16 term per value) passes the build probe on this base, but the QUERIES carry a large component
+def test_operand_format_moves_on_after_a_redo(ex, oracle):
+    """format 3 (one bf16 term per value) passes the build probe on this base, but the QUERIES carry a large component
     orthogonal to the data: the slack (2^-6 |q| max|x|) then dwarfs the spread of the distances, every row survives, the
-    batch is redone by the SIMT scan (exact answer), and the NEXT batch runs in the two-term split (tc_mode 2)"""
+    batch is redone by the SIMT scan (exact answer) and the handle moves to tf32 (format 4: slack 5x tighter, still too
+    wide here: redone again) and then to the two-term split (format 2), where the third batch runs without a redo"""
     rng = np.random.default_rng(31)
     n, d = 60_000, 64
     base = np.zeros((n, d), np.float32)
@@ -324,23 +327,23 @@ def test_one_term_format_moves_to_split_after_a_redo(ex, oracle):
     e.store_many_vectors(base); e.build()
     assert e.stats()["tc_mode"] == 3
     ref = run(ex, base, q, 10, tc=0)
-    a = e.query_k_batch(q, 10)
-    st = e.stats()
-    assert st["tc_fallbacks"] == 1
-    assert np.array_equal(a[0], ref[0]) and np.array_equal(a[1], ref[1])
-    b = e.query_k_batch(q, 10)          # the flag word of the first batch has arrived by now (the host call synchronised)
-    st = e.stats()
-    assert st["tc_mode"] == 2 and st["tc_launches"] >= 2
-    assert np.array_equal(b[0], ref[0]) and np.array_equal(b[1], ref[1])
+    seen = []
+    for step in range(4):               # (each host call synchronises: the flag word of a batch has arrived before the next one)
+        a = e.query_k_batch(q, 10)
+        st = e.stats()
+        seen.append((int(st["tc_mode"]), int(st["tc_fallbacks"])))
+        assert np.array_equal(a[0], ref[0]) and np.array_equal(a[1], ref[1]), seen
+    assert seen[0] == (3, 1) and seen[1] == (4, 2) and seen[2] == (2, 2) and seen[3] == (2, 2), seen
     e.close()
 
 
 def test_build_probe_picks_the_operand_format(ex):
     """build() probes the one-term format with the first rows of the base as queries: data whose distances are too
-    concentrated for its slack (GIST-like d = 960; u8 values at d = 512) starts in the two-term split, Deep- and
-    Gaussian-like data stays in the one-term format; no user batch is redone either way"""
+    concentrated for its slack (GIST-like d = 960; u8 values at d = 512) goes on to tf32 on the fp32 rows (format 4, probed
+    the same way; the two-term split only if that fails too), Deep- and Gaussian-like data stays in the one-term format; no
+    user batch is redone either way. With tc_tf32 = 0 the second choice is the split."""
     rng = np.random.default_rng(55)
-    cases = [("unit960", rng.random((30000, 960), dtype=np.float32), 2), ("u8_512", rng.integers(0, 256, (30000, 512)).astype(np.float32), 2),
+    cases = [("unit960", rng.random((30000, 960), dtype=np.float32), 4), ("u8_512", rng.integers(0, 256, (30000, 512)).astype(np.float32), 4),
              ("gauss128", rng.standard_normal((30000, 128)).astype(np.float32), 3)]
     x = rng.standard_normal((30000, 96)).astype(np.float32)
     cases.append(("deep96", x / np.linalg.norm(x, axis=1, keepdims=True), 3))
@@ -350,3 +353,8 @@ def test_build_probe_picks_the_operand_format(ex):
         assert a[3]["tc_mode"] == mode and a[3]["tc_launches"] >= 1 and a[3]["tc_fallbacks"] == 0, (name, a[3])
         b = run(ex, base, q, 10, tc=0)
         assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]), name
+        if mode == 4:
+            c = run(ex, base, q, 10, tf32=0)
+            assert c[3]["tc_mode"] == 2 and c[3]["tc_fallbacks"] == 0 and np.array_equal(c[0], b[0]) and np.array_equal(c[1], b[1]), name
+            c = run(ex, base, q[:40], 10)        # a small batch in format 4: still the pair form
+            assert c[3]["tc_mode"] == 4 and c[3]["last_qtile"] == 256 and np.array_equal(c[0], b[0][:40]) and np.array_equal(c[1], b[1][:40])
