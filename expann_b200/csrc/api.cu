@@ -127,23 +127,72 @@ static int padded_queries(expann_gpu* h, const float* d_q, size_t m, cudaStream_
 	return EXPANN_OK;
 }
 
+static void swap_scratch(expann_gpu* h) {
+	expann_gpu::Scratch& s = h->spare;
+	std::swap(h->qpad, s.qpad);
+	std::swap(h->partial, s.partial);
+	std::swap(h->scan_cnt, s.scan_cnt);
+	std::swap(h->tc_qstats, s.tc_qstats);
+	std::swap(h->tc_qb, s.tc_qb);
+	std::swap(h->tc_qn, s.tc_qn);
+	std::swap(h->tc_thr, s.tc_thr);
+	std::swap(h->tc_cnt, s.tc_cnt);
+	std::swap(h->tc_cand, s.tc_cand);
+	std::swap(h->tc_gthr, s.tc_gthr);
+	std::swap(h->tc_sel, s.tc_sel);
+	std::swap(h->tc_seed, s.tc_seed);
+	h->set_active ^= 1;
+}
+
+// Which set of work buffers does a call on stream `st` use? The set this stream used last (stream order protects it);
+// otherwise the set used longest ago, behind the event of its last call. The brute-force engine has two sets, so two
+// streams never wait for one another; the other engines have one (a call on another stream waits for the last call).
+static int scratch_for_stream(expann_gpu* h, cudaStream_t st) {
+	const bool two = h->cfg.engine == EXPANN_ENGINE_BRUTE_FORCE;
+	int a = h->set_active;
+	if (h->set_used[a] && h->set_stream[a] == st) return EXPANN_OK;
+	if (two) {
+		const int o = a ^ 1;
+		swap_scratch(h); // the other set: this stream's own from an earlier call, or the one used longest ago
+		a = o;
+		if (h->set_used[a] && h->set_stream[a] == st) return EXPANN_OK;
+	}
+	if (h->set_used[a]) EXPANN_CUDA(h, cudaStreamWaitEvent(st, h->set_done[a], 0));
+	h->set_stream[a] = st;
+	return EXPANN_OK;
+}
+
 int query_device_impl(expann_gpu* h, const float* d_q, size_t m, size_t k, size_t ef, uint64_t* d_keys_out,
                       cudaStream_t st) {
 	if (!h->built) return fail(h, EXPANN_ERR_STATE, "query before build()");
 	if (k == 0) return fail(h, EXPANN_ERR_ARG, "k must be > 0");
 	if (m == 0) return EXPANN_OK;
+	if (int rc = scratch_for_stream(h, st)) return rc;
 	const float* qp = nullptr;
-	if (int rc = padded_queries(h, d_q, m, st, &qp)) return rc;
-	switch (h->cfg.engine) {
-	case EXPANN_ENGINE_BRUTE_FORCE:
-		return launch_scan_f32(h, qp, m, k, d_keys_out, st);
-	case EXPANN_ENGINE_GRAPH:
-		return launch_graph_search(h, qp, m, k, ef, d_keys_out, st);
-	case EXPANN_ENGINE_QUANT_SCAN:
-		return launch_quant_scan(h, qp, m, k, d_keys_out, st);
-	default:
-		return fail(h, EXPANN_ERR_UNSUPPORTED, "engine kind not implemented");
+	int rc = padded_queries(h, d_q, m, st, &qp);
+	if (!rc) switch (h->cfg.engine) {
+		case EXPANN_ENGINE_BRUTE_FORCE:
+			rc = launch_scan_f32(h, qp, m, k, d_keys_out, st);
+			break;
+		case EXPANN_ENGINE_GRAPH:
+			rc = launch_graph_search(h, qp, m, k, ef, d_keys_out, st);
+			break;
+		case EXPANN_ENGINE_QUANT_SCAN:
+			rc = launch_quant_scan(h, qp, m, k, d_keys_out, st);
+			break;
+		default:
+			rc = fail(h, EXPANN_ERR_UNSUPPORTED, "engine kind not implemented");
+		}
+	// whatever was queued (even by a call that failed half way) is the set's last user
+	const int a = h->set_active;
+	if (!h->set_done[a] && cudaEventCreateWithFlags(&h->set_done[a], cudaEventDisableTiming) != cudaSuccess) {
+		h->set_done[a] = nullptr;
+		return rc ? rc : cuda_fail(h, cudaGetLastError(), "cudaEventCreate");
 	}
+	const cudaError_t e = cudaEventRecord(h->set_done[a], st);
+	h->set_used[a] = true;
+	if (e != cudaSuccess && !rc) return cuda_fail(h, e, "cudaEventRecord");
+	return rc;
 }
 
 bool is_pinned_host(const void* p) {
@@ -230,6 +279,11 @@ void expann_gpu_destroy(expann_gpu_t* h) {
 	for (DevBuf* b : { &h->qpad, &h->partial, &h->keys, &h->ids, &h->dists, &h->counts, &h->h_q, &h->h_ids, &h->h_dists,
 	                   &h->h_counts })
 		b->release();
+	for (DevBuf* b : { &h->spare.qpad, &h->spare.partial, &h->spare.scan_cnt, &h->spare.tc_qstats, &h->spare.tc_qb, &h->spare.tc_qn, &h->spare.tc_thr,
+	                   &h->spare.tc_cnt, &h->spare.tc_cand, &h->spare.tc_gthr, &h->spare.tc_sel, &h->spare.tc_seed })
+		b->release();
+	for (cudaEvent_t e : h->set_done)
+		if (e) cudaEventDestroy(e);
 	delete h;
 }
 

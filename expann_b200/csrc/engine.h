@@ -63,6 +63,14 @@ struct expann_gpu {
 	cudaStream_t stream = nullptr;
 	expann::DevBuf qpad, partial, keys, ids, dists, counts, scan_cnt; // device work buffers (grow-only)
 	expann::DevBuf h_q, h_ids, h_dists, h_counts;            // pinned host staging for the host-pointer API
+	// The per-call work buffers of the scans exist twice (brute-force engine): calls issued on two streams use one set each
+	// and overlap on the GPU (one batch's conversion / select / re-rank beside the other's filter); a third stream takes over
+	// the set used longest ago behind an event. The members above / below are the ACTIVE set, `spare` holds the other one's.
+	struct Scratch { expann::DevBuf qpad, partial, scan_cnt, tc_qstats, tc_qb, tc_qn, tc_thr, tc_cnt, tc_cand, tc_gthr, tc_sel, tc_seed; } spare;
+	int set_active = 0;
+	bool set_used[2] = { false, false };
+	cudaStream_t set_stream[2] = { nullptr, nullptr };
+	cudaEvent_t set_done[2] = { nullptr, nullptr }; // recorded behind the last call that used the set
 	expann_gpu_stats_t stats{};
 	// tensor-core candidate filter (K3)
 	int opt_tc = 1, opt_tc_min_batch = 5; // from 5 queries on K3 is level with or ahead of K1 (1M x 128: 0.12 vs 0.15 ms at 6, 0.13 vs 0.22 at 12)

@@ -99,8 +99,11 @@ struct Multi {
 	DevBuf gather[2], q_dev, keys, res;
 	cudaEvent_t ev_q = nullptr, ev_merged[2] = { nullptr, nullptr };
 	bool merged_pending[2] = { false, false };
+	// per kid, twice (index 2*kid + parity of the call): consecutive calls alternate, so that a brute-force kid can work on
+	// two calls side by side (its second stream + the handle's second set of work buffers, api.cu scratch_for_stream)
 	std::vector<cudaEvent_t> ev_done;
 	std::vector<DevBuf> kid_q, kid_keys;
+	std::vector<cudaStream_t> kid_stream2; // second stream of a brute-force kid (nullptr: one stream, calls run in order)
 	std::vector<char> direct, same_dev;
 	uint64_t step = 0, peer_bytes = 0;
 	std::vector<std::unique_ptr<MgWorker>> workers; // [kid]; kid 0's work runs on the calling thread
@@ -152,13 +155,18 @@ void mg_destroy(expann_gpu* h) {
 	g->workers.clear();
 	for (expann_gpu* kid : g->kids)
 		if (kid) { DeviceGuard kg(kid->device); cudaStreamSynchronize(kid->stream); }
+	for (size_t c = 0; c < g->kid_stream2.size(); ++c)
+		if (g->kid_stream2[c] && g->kids[c]) { DeviceGuard kg(g->kids[c]->device); cudaStreamSynchronize(g->kid_stream2[c]); }
 	for (size_t c = 0; c < g->kids.size(); ++c) {
 		if (!g->kids[c]) continue;
 		{
 			DeviceGuard kg(g->kids[c]->device);
-			if (c < g->ev_done.size() && g->ev_done[c]) cudaEventDestroy(g->ev_done[c]);
-			if (c < g->kid_q.size()) g->kid_q[c].release();
-			if (c < g->kid_keys.size()) g->kid_keys[c].release();
+			for (size_t j = 2 * c; j < 2 * c + 2; ++j) {
+				if (j < g->ev_done.size() && g->ev_done[j]) cudaEventDestroy(g->ev_done[j]);
+				if (j < g->kid_q.size()) g->kid_q[j].release();
+				if (j < g->kid_keys.size()) g->kid_keys[j].release();
+			}
+			if (c < g->kid_stream2.size() && g->kid_stream2[c]) cudaStreamDestroy(g->kid_stream2[c]);
 		}
 		expann_gpu_destroy(g->kids[c]);
 	}
@@ -232,9 +240,10 @@ static int mg_materialize(expann_gpu* h) {
 	g.per_rows = per;
 	const size_t nk = gq * gr;
 	g.kids.assign(nk, nullptr);
-	g.ev_done.assign(nk, nullptr);
-	g.kid_q.resize(nk);
-	g.kid_keys.resize(nk);
+	g.ev_done.assign(2 * nk, nullptr);
+	g.kid_q.resize(2 * nk);
+	g.kid_keys.resize(2 * nk);
+	g.kid_stream2.assign(nk, nullptr);
 	g.direct.assign(nk, 1);
 	g.same_dev.assign(nk, 0);
 	for (size_t c = 0; c < nk; ++c) {
@@ -257,7 +266,9 @@ static int mg_materialize(expann_gpu* h) {
 			return kid_fail(h, kid, rc, c);
 		g.same_dev[c] = kid->device == h->device;
 		DeviceGuard kg(kid->device);
-		EXPANN_CUDA(h, cudaEventCreateWithFlags(&g.ev_done[c], cudaEventDisableTiming));
+		EXPANN_CUDA(h, cudaEventCreateWithFlags(&g.ev_done[2 * c], cudaEventDisableTiming));
+		EXPANN_CUDA(h, cudaEventCreateWithFlags(&g.ev_done[2 * c + 1], cudaEventDisableTiming));
+		if (h->cfg.engine == EXPANN_ENGINE_BRUTE_FORCE) EXPANN_CUDA(h, cudaStreamCreateWithFlags(&g.kid_stream2[c], cudaStreamNonBlocking));
 		if (!g.same_dev[c]) {
 			// the kid's kernels store their keys into GPU 0's gather buffer: needs the peer mapping kid -> GPU 0
 			int can = 0;
@@ -382,7 +393,11 @@ static int mg_query_impl(expann_gpu* h, const float* d_q, const float* host_q, s
 	if (gr > 1) {
 		if (g.gather[par].cap < gr * m * k * 8) {
 			EXPANN_CUDA(h, cudaDeviceSynchronize()); // growing: nobody may still be writing into the old buffer
-			for (size_t c = 0; c < g.kids.size(); ++c) { DeviceGuard kg(g.kids[c]->device); EXPANN_CUDA(h, cudaStreamSynchronize(g.kids[c]->stream)); }
+			for (size_t c = 0; c < g.kids.size(); ++c) {
+				DeviceGuard kg(g.kids[c]->device);
+				EXPANN_CUDA(h, cudaStreamSynchronize(g.kids[c]->stream));
+				if (g.kid_stream2[c]) EXPANN_CUDA(h, cudaStreamSynchronize(g.kid_stream2[c]));
+			}
 			EXPANN_CUDA(h, g.gather[par].ensure(gr * m * k * 8));
 			g.merged_pending[par] = false;
 		}
@@ -400,29 +415,31 @@ static int mg_query_impl(expann_gpu* h, const float* d_q, const float* host_q, s
 		cudaError_t e_ = (call);                                                                 \
 		if (e_ != cudaSuccess) { kid->err = std::string(#call) + ": " + cudaGetErrorString(e_); return EXPANN_ERR_CUDA; } \
 	} while (0)
-		MG_CUDA(cudaStreamWaitEvent(kid->stream, g.ev_q, 0));
-		if (wait_merged) MG_CUDA(cudaStreamWaitEvent(kid->stream, g.ev_merged[par], 0)); // last reader of this gather buffer
+		const size_t cp = 2 * c + (size_t)par;
+		cudaStream_t ks = par && g.kid_stream2[c] ? g.kid_stream2[c] : kid->stream;
+		MG_CUDA(cudaStreamWaitEvent(ks, g.ev_q, 0));
+		if (wait_merged) MG_CUDA(cudaStreamWaitEvent(ks, g.ev_merged[par], 0)); // last reader of this gather buffer
 		const float* qk = d_q + q_lo * d;
 		if (host_q) { // this kid's block of the queries comes straight from the caller's page-locked memory
-			MG_CUDA(g.kid_q[c].ensure(mq * d * sizeof(float)));
-			MG_CUDA(cudaMemcpyAsync(g.kid_q[c].p, host_q + q_lo * d, mq * d * sizeof(float), cudaMemcpyHostToDevice, kid->stream));
-			qk = g.kid_q[c].as<float>();
+			MG_CUDA(g.kid_q[cp].ensure(mq * d * sizeof(float)));
+			MG_CUDA(cudaMemcpyAsync(g.kid_q[cp].p, host_q + q_lo * d, mq * d * sizeof(float), cudaMemcpyHostToDevice, ks));
+			qk = g.kid_q[cp].as<float>();
 		} else if (!g.same_dev[c]) { // this kid's block of the queries comes over NVLink from GPU 0
-			MG_CUDA(g.kid_q[c].ensure(mq * d * sizeof(float)));
-			MG_CUDA(cudaMemcpyPeerAsync(g.kid_q[c].p, kid->device, qk, h->device, mq * d * sizeof(float), kid->stream));
-			qk = g.kid_q[c].as<float>();
+			MG_CUDA(g.kid_q[cp].ensure(mq * d * sizeof(float)));
+			MG_CUDA(cudaMemcpyPeerAsync(g.kid_q[cp].p, kid->device, qk, h->device, mq * d * sizeof(float), ks));
+			qk = g.kid_q[cp].as<float>();
 		}
 		uint64_t* out = gat + (ir * m + q_lo) * k;
 		int rc;
 		if (g.direct[c])
-			rc = query_device_impl(kid, qk, mq, k, ef, out, kid->stream); // the kid's last kernel stores into GPU 0's memory
+			rc = query_device_impl(kid, qk, mq, k, ef, out, ks); // the kid's last kernel stores into GPU 0's memory
 		else {
-			MG_CUDA(g.kid_keys[c].ensure(mq * k * 8));
-			rc = query_device_impl(kid, qk, mq, k, ef, g.kid_keys[c].as<uint64_t>(), kid->stream);
-			if (!rc) MG_CUDA(cudaMemcpyPeerAsync(out, h->device, g.kid_keys[c].p, kid->device, mq * k * 8, kid->stream));
+			MG_CUDA(g.kid_keys[cp].ensure(mq * k * 8));
+			rc = query_device_impl(kid, qk, mq, k, ef, g.kid_keys[cp].as<uint64_t>(), ks);
+			if (!rc) MG_CUDA(cudaMemcpyPeerAsync(out, h->device, g.kid_keys[cp].p, kid->device, mq * k * 8, ks));
 		}
 		if (rc) return rc;
-		MG_CUDA(cudaEventRecord(g.ev_done[c], kid->stream));
+		MG_CUDA(cudaEventRecord(g.ev_done[cp], ks));
 #undef MG_CUDA
 		return EXPANN_OK;
 	};
@@ -447,7 +464,7 @@ static int mg_query_impl(expann_gpu* h, const float* d_q, const float* host_q, s
 		if (rc && !rc_all) { rc_all = rc; bad = c; }
 	}
 	if (rc_all) return kid_fail(h, g.kids[bad], rc_all, bad);
-	for (size_t c : active) EXPANN_CUDA(h, cudaStreamWaitEvent(st, g.ev_done[c], 0));
+	for (size_t c : active) EXPANN_CUDA(h, cudaStreamWaitEvent(st, g.ev_done[2 * c + (size_t)par], 0));
 	if (gr > 1) {
 		if (int rc = launch_merge(h, gat, m, gr, k, k, m * k, k, 0, d_keys_out, st)) return rc;
 		EXPANN_CUDA(h, cudaEventRecord(g.ev_merged[par], st));

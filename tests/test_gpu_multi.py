@@ -122,6 +122,45 @@ def test_device_pointer_entry_and_back_to_back_calls(ex):
         e.close()
 
 
+def test_calls_on_several_streams_overlap_safely(ex):
+    """calls issued on different streams without a host synchronisation: the brute-force handle keeps two sets of work
+    buffers (one per stream, csrc/api.cu scratch_for_stream), a third stream takes over the set used longest ago behind
+    an event; a multi-device handle alternates two streams per GPU. Every call must give the keys of the same call made
+    alone, whatever else is in flight; also for the engines that have one set (quantised scan)."""
+    import torch
+    rng = np.random.default_rng(47)
+    base = rng.integers(0, 256, (60_000, 64)).astype(np.float32)
+    sizes = (700, 300, 1000, 40, 3, 513)
+    qs = [rng.integers(0, 256, (m, 64)).astype(np.float32) for m in sizes]
+    dev = torch.device("cuda", 0)
+    dq = [torch.from_numpy(x).to(dev) for x in qs]
+    streams = [torch.cuda.Stream(device=dev) for _ in range(3)]
+    makers = [("bf", lambda: ex.BruteForceEngine()), ("bf_real", lambda: ex.BruteForceEngine()),
+              ("quant", lambda: ex.QuantScanEngine(quantizer=0, kprime=30)),
+              ("multi", lambda: ex.BruteForceEngine(devices=[0, 0, 0], row_groups=0)),
+              ("multi_rows", lambda: ex.BruteForceEngine(devices=[0, 0], row_groups=2))]
+    for name, mk in makers:
+        b = base + 0.25 if name == "bf_real" else base
+        e = mk()
+        e.store_many_vectors(b); e.build()
+        main = torch.cuda.current_stream(dev).cuda_stream
+        want = [torch.empty((m, 10), dtype=torch.int64, device=dev) for m in sizes]
+        for a, w, m in zip(dq, want, sizes):
+            e.query_device(a.data_ptr(), m, 10, w.data_ptr(), main)
+            torch.cuda.synchronize()
+        for nstreams in (2, 3):
+            got = [[torch.zeros((m, 10), dtype=torch.int64, device=dev) for m in sizes] for _ in range(3)]
+            for rep in range(3):
+                for i, (a, m) in enumerate(zip(dq, sizes)):
+                    stm = streams[(i + rep) % nstreams]
+                    e.query_device(a.data_ptr(), m, 10, got[rep][i].data_ptr(), stm.cuda_stream)
+            torch.cuda.synchronize()
+            for rep in range(3):
+                for i in range(len(sizes)):
+                    assert torch.equal(got[rep][i], want[i]), (name, nstreams, rep, i)
+        e.close()
+
+
 def test_immutable_after_build_and_errors(ex):
     from expann_b200._lib import ExpannError, ERR_STATE, ERR_UNSUPPORTED, ERR_ARG
     rng = np.random.default_rng(44)
