@@ -47,6 +47,7 @@ SYMBOLS = {
     "expann_gpu_build": (C.c_int, [_vp]),
     "expann_gpu_query": (C.c_int, [_vp, _vp, _sz, _sz, _sz, _vp, _vp, _vp]),
     "expann_gpu_query_device": (C.c_int, [_vp, _vp, _sz, _sz, _sz, _vp, _vp]),
+    "expann_gpu_scan_device_noalloc": (C.c_int, [_vp, _vp, _sz, _sz, _vp, _vp]),
     "expann_gpu_merge_device": (C.c_int, [_vp, _vp, _sz, _sz, _sz, _sz, _sz, _sz, _vp, _vp]),
     "expann_gpu_decode_device": (C.c_int, [_vp, _vp, _sz, _sz, _vp, _vp, _vp, _vp]),
     "expann_gpu_get_quantizer": (C.c_int, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),

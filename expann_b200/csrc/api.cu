@@ -332,6 +332,7 @@ int expann_gpu_build(expann_gpu_t* h) {
 	if (h->cfg.engine == EXPANN_ENGINE_QUANT_SCAN)
 		if (int rc = quant_finalize(h)) return rc;
 	if (int rc = tc_finalize(h)) return rc;
+	if (h->cfg.engine == EXPANN_ENGINE_BRUTE_FORCE) scan_noalloc_setup(h); // address of the static scratch array on this device
 	h->stats.n = h->n;
 	h->stats.tc_mode = h->tc_mode;
 	h->stats.d = h->d;
@@ -346,6 +347,13 @@ int expann_gpu_query_device(expann_gpu_t* h, const float* d_q, size_t m, size_t 
 	if (h->mg) return mg_query_device(h, d_q, m, k, ef, d_keys_out, (cudaStream_t)stream);
 	DeviceGuard g(h->device);
 	return query_device_impl(h, d_q, m, k, ef, d_keys_out, (cudaStream_t)stream);
+}
+
+int expann_gpu_scan_device_noalloc(expann_gpu_t* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, void* stream) {
+	if (!h || (m && (!d_q || !d_keys_out))) return fail(h, EXPANN_ERR_ARG, "null argument");
+	if (h->mg) return fail(h, EXPANN_ERR_UNSUPPORTED, "scan_device_noalloc: single-device handles only");
+	DeviceGuard g(h->device);
+	return scan_noalloc(h, d_q, m, k, d_keys_out, (cudaStream_t)stream);
 }
 
 constexpr size_t SMALL_CALL_BYTES = 16 << 10; // queries / results of a call up to this size skip the copy engines

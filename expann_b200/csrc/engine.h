@@ -153,6 +153,9 @@ int mg_stats(expann_gpu* h, expann_gpu_stats_t* out);
 int launch_scan_f32(expann_gpu* h, const float* d_q_padded, size_t m, size_t k, uint64_t* d_keys_out,
                     cudaStream_t st);
 int make_base_tensor_map(expann_gpu* h);
+// K1 with its scratch memory in a static device array (no allocation in the call): expann_gpu_scan_device_noalloc
+void scan_noalloc_setup(expann_gpu* h);
+int scan_noalloc(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st);
 // 2D tiled tensor map over fp32 (dtype_u8 = 0) or byte (1) rows; 128-byte swizzle, or 32-byte for 32-byte box rows
 int encode_tensor_map_2d(expann_gpu* h, CUtensorMap* out, int dtype_u8, void* base, uint64_t inner, uint64_t rows,
                          uint64_t row_bytes, uint32_t box_inner, uint32_t box_rows, int swizzle32 = 0);

@@ -171,4 +171,118 @@ int launch_scan_f32_simt(expann_gpu* h, const float* d_q, size_t m, size_t k, ui
 	return EXPANN_OK; // split merge is fused into the scan (last writer of each query)
 }
 
+// ---- K1 without allocations: expann_gpu_scan_device_noalloc (include/expann_gpu.h) -----------------------------------
+// The scan's scratch memory -- the per-row-split key lists and the tickets of the fused merge -- lives in ONE file-scope
+// array instead of the handle's grow-only buffers, so the call makes no cudaMalloc / cudaFree (callers under CUDA graph
+// capture, serving loops and harnesses that forbid allocation). Every GPU that loads the library holds the array until
+// exit: 8 MiB of key lists + 64 KiB of tickets. ALL calls on a device share it: calls that overlap on the GPU race.
+constexpr size_t NOALLOC_MAX_KEYS = (size_t)1 << 20;  // m * row splits * k keys of 8 bytes
+constexpr size_t NOALLOC_MAX_QUERIES = 16384;         // one 4-byte ticket per query
+static __device__ __align__(256) unsigned long long g_scan_scratch[NOALLOC_MAX_KEYS + NOALLOC_MAX_QUERIES / 2];
+
+// In host code `g_scan_scratch` is a stand-in, not a device address: the address is asked for once per device, with that
+// device current, and kept here.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static std::mutex g_noalloc_mu;
+static unsigned long long* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+static cudaError_t g_noalloc_err[NOALLOC_MAX_DEVICES] = {};
+
+template <int QT, int METRIC, int LPL> static void noalloc_raise_smem(expann_gpu* h) {
+	using Cfg = ScanCfg<QT, SCAN_TR, SCAN_NWARP, SCAN_STAGES, METRIC, LPL>;
+	const size_t smem = Cfg::smem_bytes((uint32_t)h->d_pad);
+	if (smem <= 227 * 1024) ensure_dyn_smem(h, (const void*)scan_topk_f32_kernel<QT, SCAN_TR, SCAN_NWARP, SCAN_STAGES, METRIC, LPL>, smem);
+}
+template <int METRIC> static void noalloc_raise_smem_all(expann_gpu* h) {
+	noalloc_raise_smem<1, METRIC, 1>(h);
+	noalloc_raise_smem<1, METRIC, 4>(h);
+	noalloc_raise_smem<4, METRIC, 1>(h);
+	noalloc_raise_smem<4, METRIC, 4>(h);
+	noalloc_raise_smem<8, METRIC, 1>(h);
+	noalloc_raise_smem<8, METRIC, 4>(h);
+}
+
+// set-up (expann_gpu_build of a brute-force handle, the handle's device current): resolve the scratch array's device
+// address for this device and raise the shared-memory limits the scan's instantiations need for this row length, so that
+// the call itself has nothing left to set up. A failure is kept and reported by the call, build() goes on.
+void scan_noalloc_setup(expann_gpu* h) {
+	if (h->device < 0 || h->device >= NOALLOC_MAX_DEVICES) return;
+	{
+		std::lock_guard<std::mutex> lk(g_noalloc_mu);
+		if (!g_noalloc_ptr[h->device]) {
+			unsigned long long* ptr = nullptr;
+			const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_scan_scratch);
+			g_noalloc_err[h->device] = e;
+			if (e == cudaSuccess) g_noalloc_ptr[h->device] = ptr;
+			else cudaGetLastError();
+		}
+	}
+	if (h->cfg.metric == EXPANN_METRIC_IP) noalloc_raise_smem_all<METRIC_IP>(h);
+	else noalloc_raise_smem_all<METRIC_L2>(h);
+}
+
+int scan_noalloc(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, cudaStream_t st) {
+	if (h->cfg.engine != EXPANN_ENGINE_BRUTE_FORCE) return fail(h, EXPANN_ERR_UNSUPPORTED, "scan_device_noalloc: brute-force handles only");
+	if (!h->built) return fail(h, EXPANN_ERR_STATE, "query before build()");
+	if (k == 0) return fail(h, EXPANN_ERR_ARG, "k must be > 0");
+	if (k > 128) return fail(h, EXPANN_ERR_UNSUPPORTED, "scan: k > 128 not supported");
+	if (m == 0) return EXPANN_OK;
+	if (h->d != h->d_pad)
+		return fail(h, EXPANN_ERR_UNSUPPORTED, "scan_device_noalloc: d must be a multiple of 32 (padding the queries would need a work buffer)");
+	if (m > NOALLOC_MAX_QUERIES)
+		return fail(h, EXPANN_ERR_UNSUPPORTED, "scan_device_noalloc: at most " + std::to_string(NOALLOC_MAX_QUERIES) + " queries per call (static ticket array)");
+	if (h->device < 0 || h->device >= NOALLOC_MAX_DEVICES) return fail(h, EXPANN_ERR_UNSUPPORTED, "scan_device_noalloc: device ordinal beyond 63");
+	unsigned long long* scratch = nullptr;
+	{
+		std::lock_guard<std::mutex> lk(g_noalloc_mu);
+		scratch = g_noalloc_ptr[h->device];
+		if (!scratch) return cuda_fail(h, g_noalloc_err[h->device] == cudaSuccess ? cudaErrorNotReady : g_noalloc_err[h->device],
+		                               "scan_device_noalloc: cudaGetSymbolAddress of the static scratch array (set-up at build())");
+	}
+	// grid: the rule of launch_scan_f32_simt
+	int qt = h->cfg.qtile;
+	if (qt == 0) qt = m >= 8 ? 8 : (m >= 3 ? 4 : 1);
+	if (qt != 1 && qt != 4 && qt != 8) return fail(h, EXPANN_ERR_ARG, "qtile must be 0, 1, 4 or 8");
+	const uint32_t dp = (uint32_t)h->d_pad;
+	if (qt == 8 && ScanCfg<8, SCAN_TR, SCAN_NWARP, SCAN_STAGES, 0, 1>::smem_bytes(dp) > 227 * 1024) qt = 4;
+	if (qt == 4 && ScanCfg<4, SCAN_TR, SCAN_NWARP, SCAN_STAGES, 0, 1>::smem_bytes(dp) > 227 * 1024) qt = 1;
+	const uint32_t qtiles = (uint32_t)((m + qt - 1) / qt);
+	const uint32_t groups = (uint32_t)((h->n + SCAN_ROWS - 1) / SCAN_ROWS);
+	int dev_sms = 148;
+	cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, h->device);
+	const uint32_t waves = std::max(1u, (qtiles + dev_sms - 1) / (uint32_t)dev_sms);
+	const uint32_t want = std::max(1u, (uint32_t)((uint64_t)dev_sms * waves / qtiles));
+	uint32_t nsplit = std::max(1u, std::min(want, std::max(1u, groups / 2u)));
+	uint32_t rps = (uint32_t)(((h->n + nsplit - 1) / nsplit + 63) / 64 * 64);
+	nsplit = (uint32_t)((h->n + rps - 1) / rps);
+	ScanParams p{};
+	p.queries = d_q;
+	p.m = (uint32_t)m;
+	p.k = (uint32_t)k;
+	p.d_pad = dp;
+	p.n = (uint32_t)h->n;
+	p.rows_per_split = rps;
+	p.nsplit = nsplit;
+	p.partial = d_keys_out;
+	if (nsplit > 1 || (uint32_t)h->cfg.id_offset != 0) {
+		if (m * (size_t)nsplit * k > NOALLOC_MAX_KEYS)
+			return fail(h, EXPANN_ERR_UNSUPPORTED, "scan_device_noalloc: m * row splits * k = " + std::to_string(m * (size_t)nsplit * k) +
+			                                           " keys exceed the static scratch array (" + std::to_string(NOALLOC_MAX_KEYS) + " keys)");
+		uint32_t* tickets = reinterpret_cast<uint32_t*>(scratch + NOALLOC_MAX_KEYS);
+		// the array keeps the last call's contents: the key lists are overwritten before they are read, the tickets must
+		// start at zero (a call that ran to its end leaves them zero; cleared anyway, behind earlier work of this stream)
+		EXPANN_CUDA(h, cudaMemsetAsync(tickets, 0, m * 4, st));
+		p.partial = reinterpret_cast<uint64_t*>(scratch);
+		p.final_out = d_keys_out;
+		p.counters = tickets;
+		p.id_add = (uint32_t)h->cfg.id_offset;
+	}
+	const dim3 grid(qtiles, nsplit);
+	const int rc = qt == 8 ? launch_m<8>(h, p, grid, st) : qt == 4 ? launch_m<4>(h, p, grid, st) : launch_m<1>(h, p, grid, st);
+	if (rc) return rc;
+	h->stats.scan_launches++;
+	h->stats.last_nsplit = nsplit;
+	h->stats.last_qtile = qt;
+	return EXPANN_OK;
+}
+
 } // namespace expann

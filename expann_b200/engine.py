@@ -150,6 +150,11 @@ class GpuEngine:
         self._check(self._lib.expann_gpu_query_device(self._h, q_ptr, m, k, self.ef_search if ef is None else ef,
                                                       keys_out_ptr, stream))
 
+    def scan_device_noalloc(self, q_ptr: int, m: int, k: int, keys_out_ptr: int, stream: int = 0):
+        """the exact fp32 scan with its scratch memory in the library's static device array: no allocation in the call
+        (expann_gpu_scan_device_noalloc; limits in include/expann_gpu.h)"""
+        self._check(self._lib.expann_gpu_scan_device_noalloc(self._h, q_ptr, m, k, keys_out_ptr, stream))
+
     def merge_device(self, keys_in_ptr: int, m: int, nlists: int, klist: int, stride_q: int, stride_s: int, k: int,
                      keys_out_ptr: int, stream: int = 0):
         self._check(self._lib.expann_gpu_merge_device(self._h, keys_in_ptr, m, nlists, klist, stride_q, stride_s, k,

@@ -127,6 +127,20 @@ int expann_gpu_query(expann_gpu_t* h, const float* q, size_t m, size_t k, size_t
  * (orderable(dist) << 32 | local id + id_offset), asynchronous on `stream`. */
 int expann_gpu_query_device(expann_gpu_t* h, const float* d_q, size_t m, size_t k, size_t ef,
                             uint64_t* d_keys_out, void* stream);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it). The exact fp32 scan (K1,
+ * scan_topk_f32_kernel) of expann_gpu_query_device on a built single-device brute-force handle, with the kernel's
+ * scratch memory -- the per-row-split key lists and the tickets of its fused merge -- in a static device array of the
+ * library (8 MiB + 64 KiB, held by every GPU that loads the library until exit) instead of the handle's grow-only
+ * buffers: the call makes no cudaMalloc / cudaFree and uses no allocating library routine. d_q device [m][d], d_keys_out
+ * device [m][k], keys bit-identical to expann_gpu_query_device's, asynchronous on `stream`. Limits, beyond which the
+ * call returns EXPANN_ERR_UNSUPPORTED with the reason in last_error and launches nothing: m <= 16384 queries;
+ * m * row_splits * k <= 2^20 keys whenever the lists pass through the scratch array, i.e. with more than one row split
+ * (row_splits = SM count / ceil(m / 8) for batches below ~1184 queries: at most ~1184 * k keys) or on a handle with an
+ * id offset (m * k keys); k <= 128; d a multiple of 32 (no padded copy of the queries is made). ALL calls on one
+ * GPU share the array (across handles too): calls that overlap on the GPU -- different streams without an ordering
+ * between them -- race; calls on one stream, or ordered by events, are safe. */
+int expann_gpu_scan_device_noalloc(expann_gpu_t* h, const float* d_q, size_t m, size_t k, uint64_t* d_keys_out, void* stream);
 /* K7: merge nlists key lists per query (list s of query q at d_keys_in + q*stride_q + s*stride_s, klist keys
  * each) into the k smallest -> d_keys_out [m][k]. Used for the per-GPU lists gathered over NCCL. */
 int expann_gpu_merge_device(expann_gpu_t* h, const uint64_t* d_keys_in, size_t m, size_t nlists, size_t klist,
