@@ -552,7 +552,10 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 	} else if (nm == "graph_upper_compact") {
 		h->opt_graph_upper_compact = value != 0;
 	} else if (nm == "tc_boot") {
-		h->opt_tc_boot = (int)value; // 0 off, 1 bf16-exact mode only (default), 2 both modes
+		h->opt_tc_boot = (int)value; // 0 off, 1 every format but the split (default), 2 all formats
+	} else if (nm == "tc_boot_tiles") {
+		if (value < 1 || value > 4096) return fail(h, EXPANN_ERR_ARG, "tc_boot_tiles must be 1..4096");
+		h->opt_tc_boot_tiles = (int)value;
 	} else if (nm == "tc_real") {
 		if (value != 0 && value != 1) return fail(h, EXPANN_ERR_ARG, "tc_real must be 0 or 1");
 		if (h->built) return fail(h, EXPANN_ERR_STATE, "tc_real must be set before build()");

@@ -426,20 +426,31 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	const uint32_t ntiles = (uint32_t)((h->n + (pair ? TC3_TN : TC2_TN) - 1) / (pair ? TC3_TN : TC2_TN));
 	// pair form, large bases: a short first launch over the leading boot_tiles tiles seeds every stream of the main launch
 	// with the k smallest a' found there (Tc2Params::seed_in): fewer bound-tightening events in the main launch. Worth it
-	// only in the bf16-exact mode, whose epilogue is the limiter (the split mode is MMA-bound: 9.70 ms without, 9.94 with),
-	// and only for batches that fill the GPU with the seeding launch's one cluster per 256 queries (it costs ~0.14 ms
-	// whatever the batch: measured break-even at ~8000 queries on 1M rows)
-	const uint32_t boot_tiles = pair && (h->opt_tc_boot == 2 || (h->opt_tc_boot == 1 && h->tc_mode != 2 && m >= 8192)) && ntiles >= 128 ? std::max(8u, std::min(64u, ntiles / 32u)) : 0u;
+	// only where the epilogue is the limiter (the split mode is MMA-bound: 9.70 ms without, 9.94 with). The seeding launch
+	// is ONE wave of clusters: (blocks of 256 queries) x (boot_split row splits of boot_each tiles); its 2 * boot_split
+	// lists per query are merged into one by tc_seed_merge_kernel. (Round 1 ran it with one cluster per 256 queries over
+	// 64 tiles: ~0.14 ms whatever the batch, break-even at ~8000 queries; split over the idle SMs it pays from small
+	// batches on, where a query has the most cold streams -- one GPU's share of C2 at 8 GPUs.)
+	const uint32_t qclusters = qblocks / 2u;
+	const bool boot_on = pair && (h->opt_tc_boot == 2 || (h->opt_tc_boot == 1 && h->tc_mode != 2)) && ntiles >= 128;
+	uint32_t boot_split = boot_on ? std::max(1u, std::min(32u, (uint32_t)(sms / 2) / std::max(1u, qclusters))) : 0u;
+	uint32_t boot_each = 0;
+	if (boot_on) {
+		const uint32_t want_tiles = std::max(8u, std::min((uint32_t)std::max(1, h->opt_tc_boot_tiles), ntiles / 32u));
+		boot_each = std::max(2u, (want_tiles + boot_split - 1) / boot_split);
+		boot_split = std::max(1u, std::min(boot_split, (want_tiles + boot_each - 1) / boot_each));
+	}
+	const uint32_t boot_tiles = boot_split * boot_each;
 	const uint32_t main_tiles = ntiles - boot_tiles;
 	uint32_t rows_split = tc2_pick_rsplit(qblocks, main_tiles, sms);
 	if (h->opt_nsplit > 0) rows_split = std::max(1u, std::min({ (uint32_t)h->opt_nsplit, main_tiles, (uint32_t)TC2_MAX_SPLIT / 2u - 1u })); // experiments
 	const uint32_t tiles_per_cta = (main_tiles + rows_split - 1) / rows_split;
 	rows_split = (main_tiles + tiles_per_cta - 1) / tiles_per_cta;
-	const uint32_t rsplit = (pair ? 2 * rows_split : rows_split) + (boot_tiles ? 2u : 0u); // candidate buffers per query
+	const uint32_t rsplit = (pair ? 2 * rows_split : rows_split) + 2u * boot_split; // candidate buffers per query
 	EXPANN_CUDA(h, h->tc_qb.ensure(m * (size_t)kd * 2));
 	EXPANN_CUDA(h, h->tc_qn.ensure(m * 4));
 	EXPANN_CUDA(h, h->tc_gthr.ensure(m * 4));
-	if (boot_tiles) EXPANN_CUDA(h, h->tc_seed.ensure(m * 32 * 4));
+	if (boot_tiles) EXPANN_CUDA(h, h->tc_seed.ensure(m * (32 + (boot_split > 1 ? 2 * boot_split * 16 : 0)) * 4)); // [m][32] merged | [m][2 * boot_split][16]
 	EXPANN_CUDA(h, h->tc_cnt.ensure(m * (size_t)rsplit * 4 + 16));
 	EXPANN_CUDA(h, h->tc_cand.ensure(m * (size_t)rsplit * TC2_CAP * 8));
 	EXPANN_CUDA(h, h->tc_sel.ensure(m * (size_t)TC_PAD * 8 + 16));
@@ -482,7 +493,7 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	p.tiles_per_cta = tiles_per_cta;
 	p.rsplit = rsplit;
 	p.tile_first = boot_tiles;
-	p.buf_first = boot_tiles ? 2u : 0u;
+	p.buf_first = 2u * boot_split;
 	p.seed_in = boot_tiles ? h->tc_seed.as<float>() : nullptr;
 	p.seed_out = nullptr;
 	p.scale = ip ? -1.f : -2.f;
@@ -496,18 +507,24 @@ static int tc_batch2(expann_gpu* h, const float* d_q, size_t m, size_t k, uint64
 	if (boot_tiles) {
 		Tc2Params b = p;
 		b.ntiles = boot_tiles;
-		b.tiles_per_cta = boot_tiles;
+		b.tiles_per_cta = boot_each;
 		b.tile_first = 0;
 		b.buf_first = 0;
 		b.seed_in = nullptr;
-		b.seed_out = h->tc_seed.as<float>();
-		const dim3 bgrid(qblocks, 1);
+		b.seed_out = h->tc_seed.as<float>() + (boot_split > 1 ? m * 32 : 0);
+		b.seed_lists = 2u * boot_split;
+		const dim3 bgrid(qblocks, boot_split);
 		int brc = tf32                                                 ? launch_filter_pair_tf32(h, tq, b, bgrid, st)
 		          : astream                                            ? launch_filter_pair<5, true>(h, tq, b, bgrid, st)
 		          : Tc3Cfg::smem_bytes(kd, TC2_NSTAGE) <= 227 * 1024 ? launch_filter_pair<TC2_NSTAGE>(h, tq, b, bgrid, st)
 		                                                              : launch_filter_pair<4>(h, tq, b, bgrid, st);
 		if (brc) return brc;
 		h->stats.tc_launches++;
+		if (boot_split > 1) {
+			tc_seed_merge_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(b.seed_out, b.seed_lists, p.m, p.k, h->tc_seed.as<float>());
+			EXPANN_CUDA(h, cudaGetLastError());
+			h->stats.aux_launches++;
+		}
 	}
 	int rc = tf32     ? launch_filter_pair_tf32(h, tq, p, grid, st)
 	         : astream  ? launch_filter_pair<5, true>(h, tq, p, grid, st)

@@ -45,7 +45,8 @@ struct Tc2Params {
 	// launch starts its lists from them (seed_in), so its streams do not each warm a bound up from +inf
 	uint32_t tile_first, buf_first; // this launch covers tiles [tile_first, tile_first + ntiles), buffers from buf_first
 	const float* seed_in;           // [m][2][16] or null
-	float* seed_out;                // [m][2][16] or null
+	float* seed_out;                // [m][seed_lists][16] or null: list 2 * (row split of this launch) + half tile
+	uint32_t seed_lists;            // lists per query in seed_out (2 x the seeding launch's row splits)
 	// more than 16 results per query (the code scan's k' survivors): every stream still keeps ITS 16 smallest (k = 16) and
 	// reports the bound it ended with; the select kernel takes the k'-th smallest key T over all buffers and verifies
 	// T <= every stream's final bound -- then no stream has dropped a row at or below T and the buffers hold the exact top
@@ -376,6 +377,49 @@ tc_filter2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 // FLAT index space of all buffered keys (binary search of the prefix per key, 4 independent loads in flight per lane):
 // with up to 296 splits a split-by-split walk is a chain of dependent L2 round trips (180 us measured at 148 splits).
 constexpr int TC2_MAX_SPLIT = 296;
+
+// Seeding launch with several row splits: every (split, half tile) stream leaves its sorted list of 16; the main launch wants
+// ONE list per query (its seed_in: [m][2][16], second list unused = +inf). One warp per query: lane l holds lists l and
+// l + 32 (lists <= 64), k rounds of "smallest value left anywhere" by shuffles. Slots below 16 - k stay -inf.
+static __global__ void tc_seed_merge_kernel(const float* __restrict__ lists, uint32_t nlists, uint32_t m, uint32_t k, float* __restrict__ seed) {
+	const uint32_t q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	const int lane = threadIdx.x & 31;
+	if (q >= m) return;
+	const float INF = __int_as_float(0x7f800000);
+	float v[32];
+#pragma unroll
+	for (int h = 0; h < 2; ++h) {
+		const uint32_t l = (uint32_t)lane + 32u * h;
+		const float4* src = reinterpret_cast<const float4*>(lists + ((size_t)q * nlists + l) * 16);
+#pragma unroll
+		for (int j = 0; j < 4; ++j) {
+			const float4 x = l < nlists ? __ldg(src + j) : make_float4(INF, INF, INF, INF);
+			v[h * 16 + 4 * j] = x.x; v[h * 16 + 4 * j + 1] = x.y; v[h * 16 + 4 * j + 2] = x.z; v[h * 16 + 4 * j + 3] = x.w;
+		}
+	}
+	// the fixed -inf slots of a list (below 16 - k) are not values
+#pragma unroll
+	for (int j = 0; j < 32; ++j)
+		if ((j & 15) < TC2_KK - (int)k) v[j] = INF;
+	float* out = seed + (size_t)q * 32;
+	if (lane < 16) { out[16 + lane] = INF; if (lane < TC2_KK - (int)k) out[lane] = -INF; }
+	for (uint32_t r = 0; r < k; ++r) {
+		float mn = v[0];
+#pragma unroll
+		for (int j = 1; j < 32; ++j) mn = fminf(mn, v[j]);
+		float wm = mn;
+#pragma unroll
+		for (int of = 16; of >= 1; of >>= 1) wm = fminf(wm, __shfl_xor_sync(FULL, wm, of));
+		const uint32_t has = __ballot_sync(FULL, mn == wm);
+		if (lane == __ffs(has) - 1) { // one instance leaves
+			bool done = false;
+#pragma unroll
+			for (int j = 0; j < 32; ++j)
+				if (!done && v[j] == wm) { v[j] = INF; done = true; }
+			out[TC2_KK - k + r] = wm;
+		}
+	}
+}
 
 __device__ __forceinline__ uint64_t tc2_flat_key(const uint64_t* __restrict__ qbuf, const uint32_t* pre, uint32_t rsplit, uint32_t cap,
                                                  uint32_t i, uint32_t total) {

@@ -387,7 +387,7 @@ tc_filter_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_c
 			if (p.thr_out) p.thr_out[(size_t)qg * p.rsplit + bsplit] = f32_orderable(t.thr); // the bound this stream ended with
 			if (p.seed_out) {
 #pragma unroll
-				for (int j = 0; j < TC2_KK; ++j) p.seed_out[(size_t)qg * 32 + half * 16 + j] = t.v[j];
+				for (int j = 0; j < TC2_KK; ++j) p.seed_out[((size_t)qg * p.seed_lists + split * 2 + half) * 16 + j] = t.v[j];
 			}
 		}
 	}
