@@ -500,12 +500,13 @@ def main():
     out_pageable = (np.empty((m, k), np.uint64), np.empty((m, k), np.float32), np.empty((m,), np.uint64))
     q_pageable = np.array(q, copy=True)
 
-    # N > 1: consecutive steps are issued on two alternating streams with their own result buffers -- two batches in flight,
-    # the way a serving loop double-buffers: a call's results are ordered on ITS stream, so on one stream step s+1 could
-    # not start on any GPU before the slowest GPU had finished step s. (Every GPU's own work stays in order on the handle's
-    # per-GPU stream; the single-device handle at N = 1 has one set of work buffers and takes one stream.)
+    # Consecutive steps are issued on two alternating streams with their own result buffers -- two batches in flight, the way
+    # a serving loop double-buffers: a call's results are ordered on ITS stream, so on one stream step s+1 could not start on
+    # any GPU before the slowest GPU had finished step s, and one batch's conversion / select / re-rank could not run beside
+    # the other's filter. The brute-force handle keeps two sets of work buffers for this (csrc/api.cu scratch_for_stream; a
+    # multi-device handle alternates two streams per GPU); the graph and quantised engines have one set and take one stream.
     alt = None
-    if G > 1:
+    if G > 1 or (not use_graph and not use_quant):
         alt = {"streams": [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)],
                "keys": [final_keys, torch.empty_like(final_keys)], "i": 0}
         torch.cuda.synchronize()
@@ -670,7 +671,7 @@ def main():
                               ("K3 tcgen05 filter + K4 fp32 rerank" if used_tc else "K1 fp32 SIMT scan"),
                       "nsplit": int(st1["last_nsplit"]), "rows_per_gpu": rows_gpu, "row_groups": gr, "query_groups": gq,
                       "l2": "base shard (%.0f MB) %s L2 (126 MB); no explicit flush" % (rows_gpu * d * 4 / 1e6, "larger than" if rows_gpu * d * 4 > 126e6 else "fits in"),
-                      "step_minus_kernel_ms": ms_step - hot_ms, "batches_in_flight": 2 if G > 1 else 1,
+                      "step_minus_kernel_ms": ms_step - hot_ms, "batches_in_flight": 2 if alt is not None else 1,
                       "parallelism": ("one process, one multi-device handle over %d GPUs: %d row shards x %d query groups, queries fanned out over "
                                       "NVLink, per-GPU [m][k] keys stored by each GPU's last kernel into GPU 0's gather buffer, K7 merge "
                                       "(no NCCL on the data path; torchrun ranks > 0 only join the CPU-side barriers)" % (G, gr, gq)) if G > 1 else "single GPU"},

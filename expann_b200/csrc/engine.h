@@ -94,7 +94,7 @@ struct expann_gpu {
 	int opt_graph_hash = 0; // warp form of the search: visited set in a per-warp shared-memory hash (exact; falls back to the HBM bytes when full). Measured slower than the HBM bytes (5.28 vs 5.81 M QPS at ef 40): off by default
 	int opt_graph_upper_compact = 1; // latency form: upper layers in compact form (set before build())
 	int opt_tc_boot = 1; // pair form: seeding launch over the leading tiles of a large base
-	int opt_tc_boot_tiles = 64; // tiles (of 256 rows) the seeding launch covers, at most 1/32 of the base (experiments)
+	int opt_tc_boot_tiles = 128; // tiles (of 256 rows) the seeding launch covers, at most 1/32 of the base (experiments)
 	// quantised scan engine (K6 + K4)
 	int quantizer = 0;       // 0 = quantizer_simple<uint8_t>, 1 = quantizer_ranged_q8
 	int opt_kprime = 0;      // 0 = auto

@@ -175,7 +175,7 @@ int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
  * Tensor-core candidate filter of the brute-force engine: "tc" (0/1; operands are prepared by build(), so enabling
  * needs to precede it), "tc_min_batch" (default 5: measured crossover with the SIMT scan on 1M x 128), "tc_pair" (0/1:
  * clusters of two CTAs for batches > 128, default 1), "tc_astream" (0 off | 1 when the query tile cannot stay resident
- * | 2 always), "tc_boot" (seeding launch over the leading rows, one wave of clusters: 0 off | 1 every format but the split, default | 2 always), "tc_boot_tiles" (its 256-row tiles, default 64), "tc_v1" (force the
+ * | 2 always), "tc_boot" (seeding launch over the leading rows, one wave of clusters: 0 off | 1 every format but the split, default | 2 always), "tc_boot_tiles" (its 256-row tiles, default 128), "tc_v1" (force the
  * chunked first form), "tc_real" (real-valued rows, before build(): 1 (default) one bf16 term per value, falling back to the
  * next format when a batch had to be redone | 0 the split from the start), "tc_tf32" (0/1, default 1, before build(): tf32 on the
  * fp32 rows (format 4) is the format between the one-term one and the split).

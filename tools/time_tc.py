@@ -10,7 +10,7 @@ ms_list = [int(x) for x in (sys.argv[1] if len(sys.argv) > 1 else "10000").split
 base, q = datasets.make(gen, n, max(ms_list), d, variant=variant)
 e = expann_b200.BruteForceEngine(metric=int(os.environ.get("METRIC", 0))); e.set_option("tc_real", int(os.environ.get("REAL", 1))); e.set_option("tc_tf32", int(os.environ.get("TF32", 1))); e.store_many_vectors(base); e.build()
 e.set_option("tc_v1", int(os.environ.get("V1", 0))); e.set_option("nsplit", int(os.environ.get("NSPLIT", 0)))
-e.set_option("tc_min_batch", int(os.environ.get("TCMIN", 5))); e.set_option("tc_pair", int(os.environ.get("PAIR", 1))); e.set_option("tc_boot", int(os.environ.get("BOOT", 1))); e.set_option("tc_boot_tiles", int(os.environ.get("BOOTTILES", 64)))
+e.set_option("tc_min_batch", int(os.environ.get("TCMIN", 5))); e.set_option("tc_pair", int(os.environ.get("PAIR", 1))); e.set_option("tc_boot", int(os.environ.get("BOOT", 1))); e.set_option("tc_boot_tiles", int(os.environ.get("BOOTTILES", 128)))
 dq = torch.from_numpy(q).cuda(); keys = torch.empty((max(ms_list), k), dtype=torch.int64, device="cuda")
 st = torch.cuda.current_stream().cuda_stream
 rows = []
