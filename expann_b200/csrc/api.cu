@@ -274,7 +274,7 @@ void expann_gpu_destroy(expann_gpu_t* h) {
 		b->release();
 	for (DevBuf* b : { &h->q_codes, &h->q_cnorm, &h->q_mm, &h->qq_codes, &h->qq_norm, &h->q_cand, &h->q_cnb, &h->q_thrfin, &h->q_zero }) b->release();
 	for (DevBuf* b : { &h->g_bottom, &h->g_upper, &h->g_upper_idx, &h->g_upper_nl, &h->g_visited, &h->g_epoch, &h->g_codes, &h->g_up_meta,
-	                   &h->g_upper_c, &h->g_up_vec })
+	                   &h->g_upper_c, &h->g_up_vec, &h->g_blk_bottom, &h->g_blk_upper })
 		b->release();
 	for (DevBuf* b : { &h->qpad, &h->partial, &h->keys, &h->ids, &h->dists, &h->counts, &h->h_q, &h->h_ids, &h->h_dists,
 	                   &h->h_counts })
@@ -549,6 +549,10 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 		h->opt_graph_cta_width = (int)value;
 	} else if (nm == "graph_hash") {
 		h->opt_graph_hash = value != 0;
+	} else if (nm == "graph_inline") {
+		if (value < -1 || value > 1) return fail(h, EXPANN_ERR_ARG, "graph_inline must be -1 (automatic), 0 or 1");
+		if (h->built) return fail(h, EXPANN_ERR_STATE, "graph_inline must be set before build()");
+		h->opt_graph_inline = (int)value;
 	} else if (nm == "graph_upper_compact") {
 		h->opt_graph_upper_compact = value != 0;
 	} else if (nm == "tc_boot") {

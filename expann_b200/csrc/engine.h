@@ -110,6 +110,11 @@ struct expann_gpu {
 	expann::HostGraph graph;
 	expann::DevBuf g_bottom, g_upper, g_upper_idx, g_upper_nl, g_visited, g_epoch, g_codes, g_up_meta, g_upper_c, g_up_vec;
 	size_t g_nup = 0; // vertices with upper layers in the compact form (0 = not built)
+	// latency form on neighbourhood blocks (graph_inline.cuh): block(v) = ids of v's neighbours + their vectors, contiguous
+	expann::DevBuf g_blk_bottom, g_blk_upper;
+	uint32_t g_bb_bytes = 0, g_bb_idb = 0, g_ub_bytes = 0, g_ub_idb = 0;
+	bool g_inline = false; // the blocks are built
+	int opt_graph_inline = -1; // -1 automatic (built when the blocks take at most a third of the free HBM), 0 off, 1 whenever they fit; before build()
 	float build_ortho_factor = 0.5f, build_ortho_bias = 0.f;
 	uint64_t build_prune_overflow = 0, build_K = 0;
 	uint32_t g_ctas = 0;

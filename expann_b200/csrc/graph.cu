@@ -1,6 +1,7 @@
 // Host side of K5: graph hand-off (the reference's index file, or CSR arrays), HBM layout, launch.
 #include "engine.h"
 #include "graph_search.cuh"
+#include "graph_inline.cuh"
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
@@ -158,6 +159,9 @@ int graph_load_index(expann_gpu* h, const char* path, std::vector<float>& vector
 	}
 }
 
+// shared memory of graph_search_inline_kernel next to its visited bitmap
+static size_t inline_fixed_smem(size_t d_pad) { return d_pad * 4 + 2 * GS_MAXNB * 8 + 256 * 8 + 32 * 8 + 8 * 8 + 128; }
+
 int graph_finalize(expann_gpu* h) {
 	HostGraph& g = h->graph;
 	if (!g.present) return fail(h, EXPANN_ERR_STATE, "graph engine: no graph loaded (expann_gpu_load_index / expann_gpu_set_graph)");
@@ -211,6 +215,41 @@ int graph_finalize(expann_gpu* h) {
 			h->g_nup = meta.size();
 		}
 	}
+	// neighbourhood blocks for the latency form (graph_inline.cuh): HBM capacity traded for one memory trip per hop
+	h->g_inline = false;
+	if (h->opt_graph_inline != 0 && !h->cfg.use_compression && (h->g_nup || g.max_layer <= 1)) {
+		const size_t bb_idb = (g.m0s * 4 + 127) / 128 * 128, bb = bb_idb + g.m0s * h->d_pad * 4;
+		const size_t ub_idb = (g.ms * 4 + 127) / 128 * 128, ub = (ub_idb + g.ms * 16 + g.ms * h->d_pad * 4 + 127) / 128 * 128;
+		const size_t urows = h->g_nup ? g.upper.size() / g.ms : 0;
+		const size_t total = g.n * bb + urows * ub;
+		size_t freeb = 0, totalb = 0;
+		EXPANN_CUDA(h, cudaMemGetInfo(&freeb, &totalb));
+		freeb += h->g_blk_bottom.cap + h->g_blk_upper.cap; // a rebuild reuses what the handle already holds
+		const bool fits_smem = inline_fixed_smem(h->d_pad) <= 200 * 1024;
+		const bool fits_hbm = h->opt_graph_inline == 1 ? total + ((size_t)1 << 30) <= freeb : total <= freeb / 3;
+		if (fits_smem && fits_hbm && bb < ((size_t)1 << 31) && ub < ((size_t)1 << 31)) {
+			for (auto pr : { std::make_pair(&h->g_blk_bottom, g.n * bb), std::make_pair(&h->g_blk_upper, std::max<size_t>(256, urows * ub)) })
+				if (pr.first->cap < pr.second) { // exact size: these are the largest allocations of the handle
+					pr.first->release();
+					EXPANN_CUDA(h, cudaMalloc(&pr.first->p, pr.second));
+					pr.first->cap = pr.second;
+				}
+			h->g_bb_bytes = (uint32_t)bb; h->g_bb_idb = (uint32_t)bb_idb; h->g_ub_bytes = (uint32_t)ub; h->g_ub_idb = (uint32_t)ub_idb;
+			const size_t wb = g.n * g.m0s;
+			build_bottom_blocks_kernel<<<(unsigned)((wb * 32 + 255) / 256), 256, 0, st>>>(h->base, h->g_bottom.as<uint32_t>(), h->g_blk_bottom.as<uint8_t>(),
+			                                                                           (uint32_t)g.n, (uint32_t)g.m0s, (uint32_t)h->d_pad, (uint32_t)bb, (uint32_t)bb_idb);
+			EXPANN_CUDA(h, cudaGetLastError());
+			if (urows) {
+				const size_t wu = urows * g.ms;
+				build_upper_blocks_kernel<<<(unsigned)((wu * 32 + 255) / 256), 256, 0, st>>>(h->g_up_vec.as<float>(), h->g_up_meta.as<uint4>(), h->g_upper_c.as<uint32_t>(),
+				                                                                          h->g_blk_upper.as<uint8_t>(), (uint32_t)urows, (uint32_t)g.ms, (uint32_t)h->d_pad, (uint32_t)ub, (uint32_t)ub_idb);
+				EXPANN_CUDA(h, cudaGetLastError());
+			}
+			h->stats.aux_launches += 2;
+			h->g_inline = true;
+		}
+	}
+	if (!h->g_inline) { h->g_blk_bottom.release(); h->g_blk_upper.release(); }
 	if (h->cfg.use_compression) {
 		const size_t total = h->n * h->d_pad;
 		EXPANN_CUDA(h, h->g_codes.ensure(total));
@@ -274,6 +313,33 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 			h->fused = true;
 		}
 		cudaEvent_t t0 = timing_begin(h, st);
+		if (h->g_inline && p.width == 1 && !p.compressed) {
+			// neighbourhood blocks (graph_inline.cuh): one bulk copy per hop
+			InlineParams ip{};
+			ip.g = p;
+			ip.blk_bottom = h->g_blk_bottom.as<uint8_t>();
+			ip.blk_upper = h->g_blk_upper.as<uint8_t>();
+			ip.bb_bytes = h->g_bb_bytes; ip.bb_idb = h->g_bb_idb; ip.ub_bytes = h->g_ub_bytes; ip.ub_idb = h->g_ub_idb;
+			const size_t fixed = inline_fixed_smem(h->d_pad), lim = 227 * 1024;
+			const size_t bitmap = ((h->n + 127) / 128) * 16; // bytes, whole uint4s
+			ip.bitmap_words = fixed + bitmap <= lim ? (uint32_t)(bitmap / 4) : 0;
+			ip.prefetch = 0; // measured: 79.8 -> 84.0 us per one-query call (the instruction sits on the scorers' path, the hop is bound by the controller)
+			const size_t smemi = fixed + (size_t)ip.bitmap_words * 4;
+#define GI_LAUNCH(L)                                                                                              \
+	do {                                                                                                          \
+		if (int rc_ = ensure_dyn_smem(h, (const void*)graph_search_inline_kernel<L>, smemi)) return rc_;                \
+		graph_search_inline_kernel<L><<<grid1, GI_THREADS, smemi, st>>>(ip);                                  \
+	} while (0)
+			if (cap <= 32) GI_LAUNCH(1);
+			else if (cap <= 64) GI_LAUNCH(2);
+			else if (cap <= 128) GI_LAUNCH(4);
+			else GI_LAUNCH(8);
+#undef GI_LAUNCH
+			timing_end(h, t0, st);
+			EXPANN_CUDA(h, cudaGetLastError());
+			h->stats.graph_launches++;
+			return EXPANN_OK;
+		}
 #define GC_LAUNCH(L)                                                                                              \
 	do {                                                                                                          \
 		if (int rc_ = ensure_dyn_smem(h, (const void*)graph_search_cta_kernel<L>, smem1)) return rc_;                    \
