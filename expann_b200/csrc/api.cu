@@ -550,7 +550,7 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 	} else if (nm == "graph_hash") {
 		h->opt_graph_hash = value != 0;
 	} else if (nm == "graph_inline") {
-		if (value < -1 || value > 1) return fail(h, EXPANN_ERR_ARG, "graph_inline must be -1 (automatic), 0 or 1");
+		if (value < -1 || value > 2) return fail(h, EXPANN_ERR_ARG, "graph_inline must be -1 (automatic), 0, 1 or 2");
 		if (h->built) return fail(h, EXPANN_ERR_STATE, "graph_inline must be set before build()");
 		h->opt_graph_inline = (int)value;
 	} else if (nm == "graph_upper_compact") {

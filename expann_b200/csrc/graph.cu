@@ -160,7 +160,7 @@ int graph_load_index(expann_gpu* h, const char* path, std::vector<float>& vector
 }
 
 // shared memory of graph_search_inline_kernel next to its visited bitmap
-static size_t inline_fixed_smem(size_t d_pad) { return d_pad * 4 + 2 * GS_MAXNB * 8 + 256 * 8 + 32 * 8 + 8 * 8 + 128; }
+static size_t inline_fixed_smem(size_t d_pad) { return d_pad * 4 + 2 * GS_MAXNB * 8 + 256 * 8 + 32 * 8 + 2 * 16 + 4 * 8 + 128; }
 
 int graph_finalize(expann_gpu* h) {
 	HostGraph& g = h->graph;
@@ -226,7 +226,7 @@ int graph_finalize(expann_gpu* h) {
 		EXPANN_CUDA(h, cudaMemGetInfo(&freeb, &totalb));
 		freeb += h->g_blk_bottom.cap + h->g_blk_upper.cap; // a rebuild reuses what the handle already holds
 		const bool fits_smem = inline_fixed_smem(h->d_pad) <= 200 * 1024;
-		const bool fits_hbm = h->opt_graph_inline == 1 ? total + ((size_t)1 << 30) <= freeb : total <= freeb / 3;
+		const bool fits_hbm = h->opt_graph_inline >= 1 ? total + ((size_t)1 << 30) <= freeb : total <= freeb / 3;
 		if (fits_smem && fits_hbm && bb < ((size_t)1 << 31) && ub < ((size_t)1 << 31)) {
 			for (auto pr : { std::make_pair(&h->g_blk_bottom, g.n * bb), std::make_pair(&h->g_blk_upper, std::max<size_t>(256, urows * ub)) })
 				if (pr.first->cap < pr.second) { // exact size: these are the largest allocations of the handle
@@ -322,18 +322,24 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 			ip.bb_bytes = h->g_bb_bytes; ip.bb_idb = h->g_bb_idb; ip.ub_bytes = h->g_ub_bytes; ip.ub_idb = h->g_ub_idb;
 			const size_t fixed = inline_fixed_smem(h->d_pad), lim = 227 * 1024;
 			const size_t bitmap = ((h->n + 127) / 128) * 16; // bytes, whole uint4s
-			ip.bitmap_words = fixed + bitmap <= lim ? (uint32_t)(bitmap / 4) : 0;
-			ip.prefetch = 0; // measured: 79.8 -> 84.0 us per one-query call (the instruction sits on the scorers' path, the hop is bound by the controller)
+			ip.bitmap_words = fixed + bitmap <= lim && h->opt_graph_inline != 2 ? (uint32_t)(bitmap / 4) : 0;
 			const size_t smemi = fixed + (size_t)ip.bitmap_words * 4;
+#define GI_LAUNCH_N(L, N)                                                                                         \
+	do {                                                                                                          \
+		if (int rc_ = ensure_dyn_smem(h, (const void*)graph_search_inline_kernel<L, N>, smemi)) return rc_;             \
+		graph_search_inline_kernel<L, N><<<grid1, GI_THREADS, smemi, st>>>(ip);                                  \
+	} while (0)
 #define GI_LAUNCH(L)                                                                                              \
 	do {                                                                                                          \
-		if (int rc_ = ensure_dyn_smem(h, (const void*)graph_search_inline_kernel<L>, smemi)) return rc_;                \
-		graph_search_inline_kernel<L><<<grid1, GI_THREADS, smemi, st>>>(ip);                                  \
+		if (h->d_pad == 128) GI_LAUNCH_N(L, 4);                                                                  \
+		else if (h->d_pad == 96) GI_LAUNCH_N(L, 3);                                                              \
+		else GI_LAUNCH_N(L, 0);                                                                                  \
 	} while (0)
 			if (cap <= 32) GI_LAUNCH(1);
 			else if (cap <= 64) GI_LAUNCH(2);
 			else if (cap <= 128) GI_LAUNCH(4);
 			else GI_LAUNCH(8);
+#undef GI_LAUNCH_N
 #undef GI_LAUNCH
 			timing_end(h, t0, st);
 			EXPANN_CUDA(h, cudaGetLastError());

@@ -26,7 +26,7 @@
 
 namespace expann {
 
-constexpr int GI_SCORERS = 8;                   // scorer warps
+constexpr int GI_SCORERS = 8;                   // scorer warps (warps 1..8); warp 0 is the controller
 constexpr int GI_THREADS = 32 * (GI_SCORERS + 1);
 
 struct InlineParams {
@@ -35,7 +35,6 @@ struct InlineParams {
 	const uint8_t* blk_upper;  // [upper rows] blocks of ub_bytes: dense indices (ms x u32, padded to ub_idb) | meta (ms x uint4) | vectors
 	uint32_t bb_bytes, bb_idb, ub_bytes, ub_idb;
 	uint32_t bitmap_words; // visited bitmap in shared memory (0: epoch-stamped bytes in HBM)
-	uint32_t prefetch;     // scorers ask the block of every neighbour that is under the beam's bound into L2 (calls with few queries)
 };
 
 __device__ __forceinline__ void bulk_prefetch_l2(const void* gsrc, uint32_t bytes) {
@@ -47,6 +46,28 @@ __device__ __forceinline__ uint64_t warp_min_u64(uint64_t v) {
 	return ((uint64_t)mh << 32) | ml;
 }
 
+// Rendezvous between the warps of the CTA: mbarrier arrive / try_wait (the waiter sleeps in hardware). -DGI_POLL: counters in
+// shared memory that the waiting warp polls instead — measured SLOWER (one query per call 78.8 -> 86.1 us at ef 40: the
+// polling warps take issue slots from the warps they wait for). The k-th use (k = 0, 1, ...) of a polled rendezvous with A
+// arrivals is complete when its word has reached (k + 1) * A.
+#ifndef GI_POLL
+#define GI_INIT(bar, arrivals) mbar_init(bar, arrivals)
+#define GI_WAIT(bar, k, arrivals) mbar_wait(bar, (k) & 1)
+#define GI_ARRIVE(bar) mbar_arrive(bar)
+#else
+#define GI_INIT(bar, arrivals) (*reinterpret_cast<volatile uint32_t*>(bar) = 0u)
+#define GI_WAIT(bar, k, arrivals)                                                            \
+	do {                                                                                     \
+		while (*reinterpret_cast<volatile uint32_t*>(bar) < ((k) + 1u) * (arrivals)) { }     \
+		__threadfence_block();                                                               \
+	} while (0)
+#define GI_ARRIVE(bar)                                                                       \
+	do {                                                                                     \
+		__threadfence_block();                                                               \
+		atomicAdd(reinterpret_cast<uint32_t*>(bar), 1u);                                     \
+	} while (0)
+#endif
+
 #ifdef GI_PROFILE
 __device__ unsigned gi_prof_calls;
 #define GI_T(slot) do { const long long t_ = clock64(); pf[slot] += t_ - pf_t; pf_t = t_; } while (0)
@@ -54,22 +75,25 @@ __device__ unsigned gi_prof_calls;
 #define GI_T(slot) do { } while (0)
 #endif
 
-template <int LPL>
+// The whole kernel is bound by instruction latency in whichever warp is on the critical path (every warp is alone or
+// nearly alone on its scheduler), so the per-hop paths are specialised: NSTEP = d_pad / 32 (3 or 4: the lane's share of the
+// query lives in registers and the loads are issued unconditionally; 0 = any dimension), rows of at most 32 neighbours
+// (one per team) take a path without loops.
+template <int LPL, int NSTEP>
 __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const InlineParams p) {
 	extern __shared__ __align__(128) uint8_t gi_smem[];
 	const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
 	const uint32_t slot = blockIdx.x;
 	const uint32_t d_pad = p.g.d_pad, m0s = p.g.m0s, ms = p.g.ms, ef = p.g.ef;
-	const bool qreg = d_pad <= 128;
-	// shared memory: query | scores of a hop (ids, distances) x 2 | beam copy | staged candidates | ctl x 2 | barriers | bitmap
+	const bool one_round = m0s <= 32 && ms <= 32;
+	// shared memory: query | keys of a hop's scores x 2 | beam copy | staged candidates | ctl x 2 | state x 2 | barriers | bitmap
 	float* qsm = reinterpret_cast<float*>(gi_smem);
-	uint32_t* res_id = reinterpret_cast<uint32_t*>(qsm + d_pad); // [2][GS_MAXNB]
-	float* res_d = reinterpret_cast<float*>(res_id + 2 * GS_MAXNB);
-	uint64_t* bm = reinterpret_cast<uint64_t*>(res_d + 2 * GS_MAXNB); // [32 * LPL] shared-memory copy of the beam
-	uint64_t* ck = bm + 256;                                          // [32] candidate keys of one admission round
-	uint64_t* ctl = ck + 32;                                          // [2][2]: block pointer, mode (0 stop, 1 upper, 2 bottom)
-	uint64_t* bar_go = ctl + 4;                                       // [2] controller -> scorers
-	uint64_t* bar_sc = bar_go + 2;                                    // [2] scorers -> controller
+	uint64_t* rk = reinterpret_cast<uint64_t*>(qsm + d_pad); // [2][GS_MAXNB] bottom: beam key of a fresh neighbour; upper: orderable(dist) << 32 | position; KEY_EMPTY
+	uint64_t* bm = rk + 2 * GS_MAXNB;                        // [32 * LPL] shared-memory copy of the beam
+	uint64_t* ck = bm + 256;                                 // [32] candidate keys of one admission round
+	uint4* ctl = reinterpret_cast<uint4*>(ck + 32);          // [2] job for the scorers: block pointer (lo, hi), mode (0 stop, 1 upper, 2 bottom), bound for their prefetch
+	uint64_t* bar_go = reinterpret_cast<uint64_t*>(ctl + 2); // [2] controller -> scorers
+	uint64_t* bar_sc = bar_go + 2;                           // [2] scorers -> controller
 	uint32_t* bits = p.bitmap_words ? reinterpret_cast<uint32_t*>(bar_sc + 2) : nullptr;
 	uint8_t* vis = p.g.visited + (size_t)slot * p.g.vis_stride;
 	uint32_t epoch = p.g.epoch[slot];
@@ -77,8 +101,10 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 	uint32_t h = 0; // jobs handed to the scorers so far: job h uses buffers / barriers h & 1, phase (h >> 1) & 1
 
 	if (tid == 0) {
-		for (int b = 0; b < 2; ++b) { mbar_init(&bar_go[b], 1); mbar_init(&bar_sc[b], GI_SCORERS); }
+		for (int b = 0; b < 2; ++b) { GI_INIT(&bar_go[b], 1); GI_INIT(&bar_sc[b], GI_SCORERS); }
+#ifndef GI_POLL
 		mbar_fence_init();
+#endif
 	}
 	__syncthreads();
 
@@ -102,46 +128,88 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 
 		if (wib != 0) {
 			// =============================== scorers ===============================
-			const int team = (tid - 32) >> 3, tl = tid & 7;
+			const uint32_t team = (uint32_t)(tid - 32) >> 3, tl = tid & 7;
 			const int nstep = d_pad >> 5;
-			float4 qr[4];
+			float4 qr[NSTEP > 0 ? NSTEP : 1];
 #pragma unroll
-			for (int s = 0; s < 4; ++s)
-				qr[s] = qreg && s < nstep ? *reinterpret_cast<const float4*>(qsm + s * 32 + tl * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+			for (int s = 0; s < NSTEP; ++s) qr[s] = *reinterpret_cast<const float4*>(qsm + s * 32 + tl * 4);
+			// where this lane reads in a block (rows of at most 32 neighbours: team t scores neighbour t)
+			const uint32_t off_b = p.bb_idb + team * d_pad * 4 + tl * 16, off_u = p.ub_idb + ms * 16 + team * d_pad * 4 + tl * 16;
+			const bool in_b = team < m0s, in_u = team < ms;
+#ifdef GI_PROFILE
+			long long sp[6] = { 0, 0, 0, 0, 0, 0 }, sp_t = clock64();
+			int sp_jobs = 0;
+#define GI_S(slot) do { const long long t_ = clock64(); sp[slot] += t_ - sp_t; sp_t = t_; } while (0)
+#else
+#define GI_S(slot) do { } while (0)
+#endif
 			for (;;) {
 				const uint32_t par = h & 1;
-				mbar_wait(&bar_go[par], (h >> 1) & 1);
-				const uint32_t mode = (uint32_t)ctl[par * 2 + 1], thr_pub = (uint32_t)(ctl[par * 2 + 1] >> 32);
-				if (mode == 0) { // end of the query (the arrival keeps the two barriers' phases in step)
-					if (lane == 0) mbar_arrive(&bar_sc[par]);
+				GI_WAIT(&bar_go[par], h >> 1, 1u);
+				GI_S(0);
+				const uint4 job = ctl[par];
+				const uint8_t* blk = reinterpret_cast<const uint8_t*>(((uint64_t)job.y << 32) | job.x);
+				uint64_t* out = rk + par * GS_MAXNB;
+				if (job.z == 0) { // end of the query (the arrival keeps the two barriers' phases in step)
+					if (lane == 0) GI_ARRIVE(&bar_sc[par]);
 					++h;
 					break;
 				}
-				const uint8_t* blk = reinterpret_cast<const uint8_t*>(ctl[par * 2]);
-				const bool bottom = mode == 2;
-				const uint32_t rowlen = bottom ? m0s : ms;
-				const uint8_t* vecs = blk + (bottom ? p.bb_idb : p.ub_idb + ms * 16);
-				uint32_t* rid = res_id + par * GS_MAXNB;
-				float* rd = res_d + par * GS_MAXNB;
-				for (uint32_t p0 = 0; p0 < rowlen; p0 += GI_SCORERS * 4) {
-					const uint32_t pos = p0 + team;
-					const bool in = pos < rowlen;
-					const uint32_t v = in ? __ldg(reinterpret_cast<const uint32_t*>(blk) + pos) : NO_VERTEX;
-					const float* pa = reinterpret_cast<const float*>(vecs) + (size_t)(in ? pos : 0) * d_pad + tl * 4;
+				const bool bottom = job.z == 2;
+				uint32_t pfv = NO_VERTEX; // a neighbour likely to be expanded next: its block is asked into L2
+				if (NSTEP > 0 && one_round) {
+					const bool in = bottom ? in_b : in_u;
+					const uint8_t* pv = blk + (bottom ? off_b : off_u);
+					uint32_t v = NO_VERTEX;
+					float4 xa[NSTEP > 0 ? NSTEP : 1];
+					if (in) {
+						v = __ldg(reinterpret_cast<const uint32_t*>(blk) + team);
+#pragma unroll
+						for (int s = 0; s < NSTEP; ++s) xa[s] = __ldg(reinterpret_cast<const float4*>(pv + s * 128));
+					}
+					// visited test-and-set (:596-605) as soon as the id is here, under the vector loads
+					bool seen = false;
+					uint8_t seenb = 0;
+					if (tl == 0 && bottom && v != NO_VERTEX) {
+						if (bits) seen = (atomicOr(bits + (v >> 5), 1u << (v & 31)) >> (v & 31)) & 1u;
+						else seenb = vis[v];
+					}
+					GI_S(1);
 					float sa = 0.f;
-					if (qreg) {
-						float4 xa[4];
+					if (in) {
 #pragma unroll
-						for (int s = 0; s < 4; ++s)
-							if (s < nstep) xa[s] = ldg128f(pa + s * 32);
+						for (int s = 0; s < NSTEP; ++s) { // same order of operations as gather_dist_f32
+							float t;
+							t = qr[s].x - xa[s].x; sa = fmaf(t, t, sa); t = qr[s].y - xa[s].y; sa = fmaf(t, t, sa);
+							t = qr[s].z - xa[s].z; sa = fmaf(t, t, sa); t = qr[s].w - xa[s].w; sa = fmaf(t, t, sa);
+						}
+					}
+					GI_S(2);
 #pragma unroll
-						for (int s = 0; s < 4; ++s)
-							if (s < nstep) { // same order of operations as gather_dist_f32
-								float t;
-								t = qr[s].x - xa[s].x; sa = fmaf(t, t, sa); t = qr[s].y - xa[s].y; sa = fmaf(t, t, sa);
-								t = qr[s].z - xa[s].z; sa = fmaf(t, t, sa); t = qr[s].w - xa[s].w; sa = fmaf(t, t, sa);
-							}
-					} else
+					for (int o = 4; o >= 1; o >>= 1) sa += __shfl_xor_sync(FULL, sa, o);
+					GI_S(3);
+					{ // (branch-free: every lane forms the key, the team's first lane stores it)
+						if (!bits && tl == 0 && bottom && v != NO_VERTEX) {
+							seen = seenb == ep8;
+							if (!seen) vis[v] = ep8;
+						}
+						const bool fresh = v != NO_VERTEX && !seen;
+						const uint32_t od = f32_orderable(sa);
+						const uint64_t key = fresh ? ((uint64_t)od << 32) | (bottom ? v << 1 : team) : KEY_EMPTY; // bottom: beam_key(sa, v)
+						if (tl == 0 && in) {
+							out[team] = key;
+							if (bottom && fresh && od < job.w) pfv = v;
+						}
+					}
+				} else {
+					const uint32_t rowlen = bottom ? m0s : ms;
+					const uint8_t* vecs = blk + (bottom ? p.bb_idb : p.ub_idb + ms * 16);
+					for (uint32_t p0 = 0; p0 < rowlen; p0 += GI_SCORERS * 4) {
+						const uint32_t pos = p0 + team;
+						const bool in = pos < rowlen;
+						const uint32_t v = in ? __ldg(reinterpret_cast<const uint32_t*>(blk) + pos) : NO_VERTEX;
+						const float* pa = reinterpret_cast<const float*>(vecs) + (size_t)(in ? pos : 0) * d_pad + tl * 4;
+						float sa = 0.f;
 						for (int s0 = 0; s0 < nstep; s0 += 4) {
 							float4 xa[4];
 #pragma unroll
@@ -157,29 +225,39 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 								}
 						}
 #pragma unroll
-					for (int o = 4; o >= 1; o >>= 1) sa += __shfl_xor_sync(FULL, sa, o);
-					if (tl == 0 && in) {
-						uint32_t out = v;
-						if (bottom && v != NO_VERTEX) { // visited test-and-set (:596-605)
-							bool seen;
-							if (bits) seen = (atomicOr(bits + (v >> 5), 1u << (v & 31)) >> (v & 31)) & 1u;
-							else {
-								seen = vis[v] == ep8;
-								if (!seen) vis[v] = ep8;
+						for (int o = 4; o >= 1; o >>= 1) sa += __shfl_xor_sync(FULL, sa, o);
+						if (tl == 0 && in) {
+							uint64_t key = KEY_EMPTY;
+							if (v != NO_VERTEX) {
+								if (bottom) { // visited test-and-set (:596-605)
+									bool seen;
+									if (bits) seen = (atomicOr(bits + (v >> 5), 1u << (v & 31)) >> (v & 31)) & 1u;
+									else {
+										seen = vis[v] == ep8;
+										if (!seen) vis[v] = ep8;
+									}
+									if (!seen) key = beam_key(sa, v);
+								} else
+									key = ((uint64_t)f32_orderable(sa) << 32) | pos;
 							}
-							if (seen) out = NO_VERTEX;
-							// a fresh neighbour under the bound enters the beam and may be expanded — at once if it is the closest:
-							// its block starts its way into L2 now, before the controller has even seen the score
-							else if (p.prefetch && f32_orderable(sa) < thr_pub) bulk_prefetch_l2(p.blk_bottom + (size_t)v * p.bb_bytes, p.bb_bytes);
+							out[pos] = key;
 						}
-						rid[pos] = out;
-						rd[pos] = sa;
 					}
 				}
 				__syncwarp();
-				if (lane == 0) mbar_arrive(&bar_sc[par]);
+				if (lane == 0) GI_ARRIVE(&bar_sc[par]);
+				GI_S(4);
+				if (__any_sync(FULL, pfv != NO_VERTEX) && pfv != NO_VERTEX) bulk_prefetch_l2(p.blk_bottom + (size_t)pfv * p.bb_bytes, p.bb_bytes);
+				GI_S(5);
+#ifdef GI_PROFILE
+				sp_jobs++;
+#endif
 				++h;
 			}
+#ifdef GI_PROFILE
+			if (tid == 32 && (gi_prof_calls & 63u) == 40u)
+				printf("GISCORE jobs=%d wait_go=%lld issue+visit=%lld fma=%lld reduce=%lld store+arrive=%lld prefetch=%lld\n", sp_jobs, sp[0], sp[1], sp[2], sp[3], sp[4], sp[5]);
+#endif
 		} else {
 			// =============================== controller ===============================
 			uint32_t dc = 0;
@@ -187,12 +265,18 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 			long long pf[10] = { 0, 0, 0, 0, 0, 0, 0, 0, 0, 0 }, pf_t = clock64(), pf_t0 = pf_t;
 			int pf_hops = 0, pf_up = 0;
 #endif
-			auto publish = [&](uint32_t mode, const uint8_t* blk, uint32_t thr_pub = 0) { // job h for the scorers
+			auto publish = [&](uint32_t mode, const uint8_t* blk, uint32_t bound = 0) { // job h for the scorers
 				if (lane == 0) {
-					ctl[(h & 1) * 2] = reinterpret_cast<uint64_t>(blk);
-					ctl[(h & 1) * 2 + 1] = mode | ((uint64_t)thr_pub << 32);
-					mbar_arrive(&bar_go[h & 1]);
+					const uint64_t a = reinterpret_cast<uint64_t>(blk);
+					ctl[h & 1] = make_uint4((uint32_t)a, (uint32_t)(a >> 32), mode, bound);
+					GI_ARRIVE(&bar_go[h & 1]);
 				}
+			};
+			// all lanes: the smallest key of job h's scores
+			auto min_score = [&](uint32_t par, uint32_t rowlen) -> uint64_t {
+				uint64_t k = (uint32_t)lane < rowlen ? rk[par * GS_MAXNB + lane] : KEY_EMPTY;
+				for (uint32_t i = 32 + lane; i < rowlen; i += 32) k = min(k, rk[par * GS_MAXNB + i]);
+				return warp_min_u64(k);
 			};
 			// ---- upper layers: greedy descent (:878-893), one block per step
 			uint32_t ep = p.g.start, cu_ui = p.g.up_start_ui, cu_nl = p.g.up_start_nl;
@@ -218,28 +302,26 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 					if (layer >= 2) bulk_prefetch_l2(p.blk_upper + (size_t)(cu_ui + layer - 2) * p.ub_bytes, p.ub_bytes);
 					else bulk_prefetch_l2(p.blk_bottom + (size_t)ep * p.bb_bytes, p.bb_bytes);
 				}
+				const uint4 mt = (uint32_t)lane < ms ? __ldg(reinterpret_cast<const uint4*>(blk + p.ub_idb) + lane) : make_uint4(0, 0, 0, 0); // (rows of up to 32)
 				const uint32_t par = h & 1;
-				mbar_wait(&bar_sc[par], (h >> 1) & 1);
+				GI_WAIT(&bar_sc[par], h >> 1, (uint32_t)GI_SCORERS);
 				++h;
 				// first occurrence of the minimum, only if strictly better (:879-889)
-				uint32_t bk = 0xFFFFFFFFu, bi = 0xFFFFFFFFu, cnt = 0;
-				const uint32_t epk = f32_orderable(ep_dist);
-				for (uint32_t i0 = 0; i0 < ms; i0 += 32) {
-					const uint32_t i = i0 + lane;
-					const bool ok = i < ms && res_id[par * GS_MAXNB + i] != NO_VERTEX;
-					cnt += __popc(__ballot_sync(FULL, ok));
-					const uint32_t k32 = ok ? f32_orderable(res_d[par * GS_MAXNB + i]) : 0xFFFFFFFFu;
-					if (k32 < epk && k32 < bk) { bk = k32; bi = i; }
-				}
-				const uint32_t mn = __reduce_min_sync(FULL, bk);
+				uint32_t cnt = 0;
+				for (uint32_t i0 = 0; i0 < ms; i0 += 32) cnt += __popc(__ballot_sync(FULL, i0 + lane < ms && rk[par * GS_MAXNB + i0 + lane] != KEY_EMPTY));
 				dc += cnt;
-				if (mn != 0xFFFFFFFFu) {
-					const uint32_t besti = __reduce_min_sync(FULL, bk == mn ? bi : 0xFFFFFFFFu);
-					const uint4 mt = __ldg(reinterpret_cast<const uint4*>(blk + p.ub_idb) + besti);
-					cu_ui = mt.x;
-					cu_nl = mt.y;
-					ep = mt.z;
-					ep_dist = f32_from_orderable(mn);
+				const uint64_t mk = min_score(par, ms);
+				if ((uint32_t)(mk >> 32) < f32_orderable(ep_dist)) {
+					const uint32_t besti = (uint32_t)mk;
+					uint4 m;
+					if (ms <= 32) {
+						m.x = __shfl_sync(FULL, mt.x, besti); m.y = __shfl_sync(FULL, mt.y, besti); m.z = __shfl_sync(FULL, mt.z, besti);
+					} else
+						m = __ldg(reinterpret_cast<const uint4*>(blk + p.ub_idb) + besti);
+					cu_ui = m.x;
+					cu_nl = m.y;
+					ep = m.z;
+					ep_dist = f32_from_orderable((uint32_t)(mk >> 32));
 				} else
 					--layer;
 				while (layer > 0 && cu_nl <= layer) --layer;
@@ -256,60 +338,54 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 				bm[0] = beam_key(ep_dist, ep) | 1ull;
 			}
 			__syncwarp();
-			publish(2, p.blk_bottom + (size_t)ep * p.bb_bytes, ef == 1 ? f32_orderable(ep_dist) : 0xFFFFFFFFu);
-			WarpList<LPL> beam;
-			beam.init();
 			dc++; // the reference evaluates the entry vertex again on entering the bottom layer
-			beam.insert(beam_key(ep_dist, ep) | 1ull, lane);
-			int bsz = 1;
 			bool full = ef == 1;
 			uint32_t thr_hi = full ? f32_orderable(ep_dist) : 0xFFFFFFFFu; // orderable distance at position ef - 1
-			uint64_t r1 = KEY_EMPTY, r2 = KEY_EMPTY; // the two closest unexpanded entries among the first ef
-			int pos1 = -1;
-			__syncwarp();
+			publish(2, p.blk_bottom + (size_t)ep * p.bb_bytes, thr_hi);
+			WarpList<LPL> beam;
+			beam.init();
+			beam.insert(beam_key(ep_dist, ep) | 1ull, lane);
+			int bsz = 1, pos1 = -1;
+			uint64_t r1 = KEY_EMPTY, r2 = KEY_EMPTY; // the two closest unexpanded entries among the first ef (r1 at position pos1)
 			for (;;) {
 				const uint32_t par = h & 1;
-				mbar_wait(&bar_sc[par], (h >> 1) & 1);
+				GI_WAIT(&bar_sc[par], h >> 1, (uint32_t)GI_SCORERS);
 				++h;
 				GI_T(1);
-				const uint32_t* rid = res_id + par * GS_MAXNB;
-				const float* rd = res_d + par * GS_MAXNB;
 				// ---- which vertex does the next hop expand? The smaller of the closest fresh neighbour (if the beam admits it:
 				// then it is the smallest key admitted) and the closest unexpanded beam entry.
-				const uint32_t vv0 = (uint32_t)lane < m0s ? rid[lane] : NO_VERTEX;
-				const float dv0 = vv0 != NO_VERTEX ? rd[lane] : 0.f;
-				uint64_t fk = vv0 != NO_VERTEX ? beam_key(dv0, vv0) : KEY_EMPTY;
-				dc += __popc(__ballot_sync(FULL, vv0 != NO_VERTEX));
-				for (uint32_t i0 = 32; i0 < m0s; i0 += 32) {
-					const uint32_t i = i0 + lane;
-					const uint32_t vv = i < m0s ? rid[i] : NO_VERTEX;
-					if (vv != NO_VERTEX) fk = min(fk, beam_key(rd[i], vv));
-					dc += __popc(__ballot_sync(FULL, vv != NO_VERTEX));
-				}
+				const uint64_t* keys = rk + par * GS_MAXNB;
+				const uint64_t key0 = (uint32_t)lane < m0s ? keys[lane] : KEY_EMPTY;
+				uint64_t fk = key0;
+				for (uint32_t i = 32 + lane; i < m0s; i += 32) fk = min(fk, keys[i]);
 				fk = warp_min_u64(fk);
-				if (fk != KEY_EMPTY && full && (uint32_t)(fk >> 32) >= thr_hi) fk = KEY_EMPTY; // not admitted: then no neighbour is
+				if (full && (uint32_t)(fk >> 32) >= thr_hi) fk = KEY_EMPTY; // not admitted: then no neighbour is
 				const uint64_t nextk = min(fk, r1);
 				if (nextk == KEY_EMPTY) { // nothing left to expand (and nothing to admit): the search is over
 					publish(0, nullptr);
-					mbar_wait(&bar_sc[h & 1], (h >> 1) & 1);
+					for (uint32_t i0 = 0; i0 < m0s; i0 += 32) dc += __popc(__ballot_sync(FULL, i0 + lane < m0s && keys[i0 + lane] != KEY_EMPTY));
+					GI_WAIT(&bar_sc[h & 1], h >> 1, (uint32_t)GI_SCORERS);
 					++h;
 					break;
 				}
-				publish(2, p.blk_bottom + (size_t)((uint32_t)(nextk >> 1) & 0x7FFFFFFFu) * p.bb_bytes, thr_hi);
-				{ // the runner-up of the next hop is the likely vertex after it: its block goes to L2
+				{
+					// the runner-up of the next hop (unless one of this hop's other candidates is closer still): a neighbour the
+					// next hop finds under it — and under the beam's bound — is the vertex expanded after it, and the scorers ask
+					// for its block as soon as they have its distance; the runner-up's own block goes to L2 now
 					const uint64_t second = nextk == fk ? r1 : min(fk, r2);
+					publish(2, p.blk_bottom + (size_t)((uint32_t)(nextk >> 1) & 0x7FFFFFFFu) * p.bb_bytes, min((uint32_t)(second >> 32), thr_hi));
 					if (second != KEY_EMPTY && lane == 0) bulk_prefetch_l2(p.blk_bottom + (size_t)((uint32_t)(second >> 1) & 0x7FFFFFFFu) * p.bb_bytes, p.bb_bytes);
 				}
 				GI_T(2);
 #ifdef GI_PROFILE
 				pf_hops++;
 #endif
-				// ---- under the scorers' memory trip: admission (:666-676) of the whole row at once. Every fresh neighbour under
-				// the bound the hop started with is merged into the sorted beam by rank counting — candidate c lands at #beam keys
-				// below c (binary search in the shared-memory copy of the beam) + #candidates below c, a beam key moves up by
-				// #candidates below it (the round's candidates are staged in shared memory and read back as broadcasts). The
-				// vertex just published enters (or stays in) the beam as expanded.
-				if (nextk != fk) {
+				// ---- under the scorers' memory trip: admission (:666-676) of the hop's whole row at once. Every fresh neighbour
+				// under the bound the hop started with is merged into the sorted beam by rank counting — candidate c lands at
+				// #beam keys below c + #candidates below c, a beam key moves up by #candidates below it (the round's candidates
+				// are staged in shared memory and read back as broadcasts). The vertex just published enters (or stays in) the
+				// beam as expanded.
+				if (nextk == r1) {
 #pragma unroll
 					for (int s = 0; s < LPL; ++s)
 						if (s * 32 + lane == pos1) beam.e[s] |= 1ull;
@@ -318,36 +394,32 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 				const uint32_t thrh = thr_hi;
 				for (uint32_t i0 = 0; i0 < m0s; i0 += 32) {
 					const uint32_t i = i0 + lane;
-					const uint32_t vv = i0 == 0 ? vv0 : (i < m0s ? rid[i] : NO_VERTEX);
-					const float dv = i0 == 0 ? dv0 : (vv != NO_VERTEX ? rd[i] : 0.f);
-					const bool cand = vv != NO_VERTEX && (!fullh || f32_orderable(dv) < thrh);
+					uint64_t mykey = i0 == 0 ? key0 : (i < m0s ? keys[i] : KEY_EMPTY);
+					const bool cand = mykey != KEY_EMPTY && (!fullh || (uint32_t)(mykey >> 32) < thrh);
+					dc += __popc(__ballot_sync(FULL, mykey != KEY_EMPTY));
 					const unsigned mk = __ballot_sync(FULL, cand);
 					if (!mk) continue;
 					const int ncand = __popc(mk);
-					uint64_t mykey = cand ? beam_key(dv, vv) : KEY_EMPTY;
-					if (cand) ck[__popc(mk & ((1u << lane) - 1u))] = mykey;
+					if (!cand) mykey = KEY_EMPTY;
+					const int ci = cand ? __popc(mk & ((1u << lane) - 1u)) : -1; // my place among the round's candidates
+					if (cand) ck[ci] = mykey;
 					__syncwarp();
-					int myrank = 0, shift[LPL];
+					int myrank = 0, lo = 0, shift[LPL];
 #pragma unroll
 					for (int s = 0; s < LPL; ++s) shift[s] = 0;
-#pragma unroll 4
+#pragma unroll 2
 					for (int j = 0; j < ncand; ++j) {
 						const uint64_t kk = ck[j];
 						myrank += kk < mykey;
+						int below = 0; // beam keys below candidate j (expanded bits do not decide a comparison with a fresh vertex)
 #pragma unroll
-						for (int s = 0; s < LPL; ++s) shift[s] += kk < beam.e[s];
-					}
-					int lo = 0;
-					if (cand) { // beam keys below mine (expanded bits do not decide a comparison with a fresh vertex)
-						int hi = bsz;
-						while (lo < hi) {
-							const int mid = (lo + hi) >> 1;
-							if (bm[mid] < mykey) lo = mid + 1;
-							else hi = mid;
+						for (int s = 0; s < LPL; ++s) {
+							below += __popc(__ballot_sync(FULL, beam.e[s] < kk));
+							shift[s] += kk < beam.e[s];
 						}
-						if (mykey == nextk) mykey |= 1ull;
+						if (j == ci) lo = below;
 					}
-					__syncwarp();
+					if (cand && mykey == nextk) mykey |= 1ull;
 #pragma unroll
 					for (int s = 0; s < LPL; ++s) {
 						const int np = s * 32 + lane + shift[s];
@@ -360,8 +432,9 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 					for (int s = 0; s < LPL; ++s) beam.e[s] = s * 32 + lane < bsz ? bm[s * 32 + lane] : KEY_EMPTY;
 					__syncwarp();
 				}
+				// (bm is the beam as of the last merge; a mark set since then sits on an entry that is not read here)
 				full = bsz >= (int)ef;
-				if (full) thr_hi = (uint32_t)(beam.at(ef - 1) >> 32);
+				if (full) thr_hi = (uint32_t)(bm[ef - 1] >> 32);
 				{ // the two closest unexpanded entries among the first ef
 					int p1 = -1, p2 = -1;
 #pragma unroll
@@ -372,8 +445,8 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 						if (p1 >= 0 && p2 < 0 && mk) p2 = s * 32 + __ffs(mk) - 1;
 					}
 					pos1 = p1;
-					r1 = p1 >= 0 ? beam.at(p1) : KEY_EMPTY;
-					r2 = p2 >= 0 ? beam.at(p2) : KEY_EMPTY;
+					r1 = p1 >= 0 ? bm[p1] : KEY_EMPTY;
+					r2 = p2 >= 0 ? bm[p2] : KEY_EMPTY;
 				}
 				GI_T(3);
 			}
@@ -402,10 +475,8 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 		}
 		__syncthreads();
 	}
-	if (tid == 0) {
-		if (!bits) p.g.epoch[slot] = epoch;
-		if (p.g.distcomps && dc_total) atomicAdd(p.g.distcomps, dc_total);
-	}
+	if (tid == 0 && !bits) p.g.epoch[slot] = epoch;
+	if (tid == 0 && p.g.distcomps && dc_total) atomicAdd(p.g.distcomps, dc_total);
 }
 
 // ---- building the blocks (once, at build()): one warp per (block, entry)

@@ -261,3 +261,47 @@ def test_load_index_after_vectors_of_another_dimension(ex):
         got = e.query_k_batch(q, 10)
         e.close()
         assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+
+
+@pytest.mark.parametrize("n,d,M,M0,nq", [(6000, 128, 12, 32, 48), (3000, 96, 8, 24, 40), (2500, 100, 8, 48, 32),
+                                         (1500, 256, 8, 16, 16), (800, 20, 4, 8, 16)])
+def test_inline_blocks_identical(ex, n, d, M, M0, nq):
+    """the latency form on neighbourhood blocks (graph_inline, csrc/graph_inline.cuh) returns what the other forms
+    return, bit for bit — ids, distances, counts and the distance-evaluation counter — whether the visited set is the
+    shared-memory bitmap (1) or the bytes in HBM (2); rows of more than 32 neighbours, d that is not a multiple of 32
+    and d above 128 take the general path of the scorers"""
+    from expann_b200 import datasets
+    base, q = datasets.make("sift", n, nq, d, seed=5, variant="lowrank")
+    eng = {}
+    for inl in (0, 1, 2):
+        e = ex.GraphEngine()
+        e.set_option("graph_inline", inl)
+        e.store_many_vectors(base)
+        e.build_graph(M=M, M0=M0, K=2 * M0)
+        e.build()
+        eng[inl] = e
+    for ef in (1, 10, 33, 100, 250):
+        k = min(10, ef)
+        res = {}
+        for inl, e in eng.items():
+            e.set_ef_search(ef)
+            dc0 = e.stats()["distcomps"]
+            one = [e.query_k_batch(q[i:i + 1], k) for i in range(nq)]          # one CTA, one query per call
+            dc = e.stats()["distcomps"] - dc0
+            few = e.query_k_batch(q, k)                                          # one CTA per query, nq CTAs
+            res[inl] = (np.concatenate([o[0] for o in one]), np.concatenate([o[1] for o in one]),
+                        np.concatenate([o[2] for o in one]), few, dc)
+        for inl in (1, 2):
+            for a, b in zip(res[0][:3], res[inl][:3]):
+                assert np.array_equal(a, b), (ef, inl)
+            for a, b in zip(res[0][3], res[inl][3]):
+                assert np.array_equal(a, b), (ef, inl)
+            assert res[0][4] == res[inl][4], (ef, inl, res[0][4], res[inl][4])
+        # and the one-warp-per-query form agrees with all of them
+        eng[1].set_option("graph_cta_batch", 0)
+        warp = eng[1].query_k_batch(q, k)
+        eng[1].set_option("graph_cta_batch", -1)
+        for a, b in zip(res[1][3], warp):
+            assert np.array_equal(a, b), ef
+    for e in eng.values():
+        e.close()

@@ -17,4 +17,4 @@ for ef in (40,):
     print("ef", ef, (time.perf_counter() - t) / 400 * 1e6, "us per call")
 e.close()
 PY
-echo rc $?; grep -v "^GIPROF" gpurun_out/v.log | tail -5; grep "^GIPROF" gpurun_out/v.log | tail -8
+echo rc $?; grep -v "^GIPROF" gpurun_out/v.log | tail -5; grep "^GI" gpurun_out/v.log | tail -9
