@@ -160,7 +160,7 @@ int graph_load_index(expann_gpu* h, const char* path, std::vector<float>& vector
 }
 
 // shared memory of graph_search_inline_kernel next to its visited bitmap
-static size_t inline_fixed_smem(size_t d_pad) { return d_pad * 4 + 2 * GS_MAXNB * 8 + 256 * 8 + 32 * 8 + 2 * 16 + 4 * 8 + 128; }
+static size_t inline_fixed_smem(size_t d_pad) { return d_pad * 4 + 2 * GS_MAXNB * 8 + 256 * 8 + 32 * 8 + 6 * 16 + 6 * 8 + 128; }
 
 int graph_finalize(expann_gpu* h) {
 	HostGraph& g = h->graph;

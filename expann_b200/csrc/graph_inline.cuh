@@ -92,16 +92,19 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 	uint64_t* bm = rk + 2 * GS_MAXNB;                        // [32 * LPL] shared-memory copy of the beam
 	uint64_t* ck = bm + 256;                                 // [32] candidate keys of one admission round
 	uint4* ctl = reinterpret_cast<uint4*>(ck + 32);          // [2] job for the scorers: block pointer (lo, hi), mode (0 stop, 1 upper, 2 bottom), bound for their prefetch
-	uint64_t* bar_go = reinterpret_cast<uint64_t*>(ctl + 2); // [2] controller -> scorers
-	uint64_t* bar_sc = bar_go + 2;                           // [2] scorers -> controller
-	uint32_t* bits = p.bitmap_words ? reinterpret_cast<uint32_t*>(bar_sc + 2) : nullptr;
+	uint4* st = ctl + 2;                                     // [2][2] the beam after an admission: r1 (lo, hi), r2 (lo, hi) | bound, -, -, -
+	uint64_t* bar_go = reinterpret_cast<uint64_t*>(st + 4);  // [2] controller -> scorers: a job in ctl
+	uint64_t* bar_sc = bar_go + 2;                           // [2] scorers -> everybody: the scores of a job are in rk
+	uint64_t* bar_adm = bar_sc + 2;                          // [2] controller -> scorers: admission done, st written
+	uint32_t* bits = p.bitmap_words ? reinterpret_cast<uint32_t*>(bar_adm + 2) : nullptr;
 	uint8_t* vis = p.g.visited + (size_t)slot * p.g.vis_stride;
 	uint32_t epoch = p.g.epoch[slot];
 	unsigned long long dc_total = 0;
-	uint32_t h = 0; // jobs handed to the scorers so far: job h uses buffers / barriers h & 1, phase (h >> 1) & 1
+	uint32_t h = 0; // jobs scored so far: job h uses rk / bar_sc h & 1, phase (h >> 1) & 1
+	uint32_t Jg = 0, Jb = 0; // jobs handed over through ctl / decisions on the bottom layer so far (same counting in every warp)
 
 	if (tid == 0) {
-		for (int b = 0; b < 2; ++b) { GI_INIT(&bar_go[b], 1); GI_INIT(&bar_sc[b], GI_SCORERS); }
+		for (int b = 0; b < 2; ++b) { GI_INIT(&bar_go[b], 1); GI_INIT(&bar_sc[b], GI_SCORERS); GI_INIT(&bar_adm[b], 1); }
 #ifndef GI_POLL
 		mbar_fence_init();
 #endif
@@ -143,18 +146,22 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 #else
 #define GI_S(slot) do { } while (0)
 #endif
+			// The controller hands over the steps through the upper layers and the entry into the bottom layer (ctl / bar_go).
+			// From there on the scorers drive themselves: once a hop's scores are complete, every scorer warp works out the
+			// vertex of the next hop for itself (the same two-instruction minimum the controller computes for its admission)
+			// and starts its loads — no hand-over, no wake-up of another warp on the hop's path.
+			bool self = false;
+			uint4 job = make_uint4(0, 0, 0, 0);
 			for (;;) {
 				const uint32_t par = h & 1;
-				GI_WAIT(&bar_go[par], h >> 1, 1u);
+				if (!self) {
+					GI_WAIT(&bar_go[Jg & 1], Jg >> 1, 1u);
+					job = ctl[Jg & 1];
+					++Jg;
+				}
 				GI_S(0);
-				const uint4 job = ctl[par];
 				const uint8_t* blk = reinterpret_cast<const uint8_t*>(((uint64_t)job.y << 32) | job.x);
 				uint64_t* out = rk + par * GS_MAXNB;
-				if (job.z == 0) { // end of the query (the arrival keeps the two barriers' phases in step)
-					if (lane == 0) GI_ARRIVE(&bar_sc[par]);
-					++h;
-					break;
-				}
 				const bool bottom = job.z == 2;
 				uint32_t pfv = NO_VERTEX; // a neighbour likely to be expanded next: its block is asked into L2
 				if (NSTEP > 0 && one_round) {
@@ -253,6 +260,26 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 				sp_jobs++;
 #endif
 				++h;
+				if (bottom) {
+					// ---- which vertex does the next hop expand? The smaller of the closest fresh neighbour (if the beam admits
+					// it: then it is the smallest key admitted) and the closest unexpanded beam entry as of the last admission.
+					GI_WAIT(&bar_sc[par], (h - 1) >> 1, (uint32_t)GI_SCORERS);
+					GI_WAIT(&bar_adm[Jb & 1], Jb >> 1, 1u);
+					const uint4 a = st[(Jb & 1) * 2], b = st[(Jb & 1) * 2 + 1];
+					++Jb;
+					const uint64_t r1 = ((uint64_t)a.y << 32) | a.x, r2 = ((uint64_t)a.w << 32) | a.z;
+					uint64_t fk = (uint32_t)lane < m0s ? out[lane] : KEY_EMPTY;
+					for (uint32_t i = 32 + lane; i < m0s; i += 32) fk = min(fk, out[i]);
+					fk = warp_min_u64(fk);
+					if ((uint32_t)(fk >> 32) >= b.x) fk = KEY_EMPTY; // not admitted (b.x = 0xFFFFFFFF while the beam is not full)
+					const uint64_t nextk = min(fk, r1);
+					if (nextk == KEY_EMPTY) break; // the search is over
+					const uint64_t second = nextk == fk ? r1 : min(fk, r2);
+					const uint64_t addr = reinterpret_cast<uint64_t>(p.blk_bottom + (size_t)((uint32_t)(nextk >> 1) & 0x7FFFFFFFu) * p.bb_bytes);
+					job = make_uint4((uint32_t)addr, (uint32_t)(addr >> 32), 2u, min((uint32_t)(second >> 32), b.x));
+					self = true;
+					GI_S(5);
+				}
 			}
 #ifdef GI_PROFILE
 			if (tid == 32 && (gi_prof_calls & 63u) == 40u)
@@ -268,9 +295,10 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 			auto publish = [&](uint32_t mode, const uint8_t* blk, uint32_t bound = 0) { // job h for the scorers
 				if (lane == 0) {
 					const uint64_t a = reinterpret_cast<uint64_t>(blk);
-					ctl[h & 1] = make_uint4((uint32_t)a, (uint32_t)(a >> 32), mode, bound);
-					GI_ARRIVE(&bar_go[h & 1]);
+					ctl[Jg & 1] = make_uint4((uint32_t)a, (uint32_t)(a >> 32), mode, bound);
+					GI_ARRIVE(&bar_go[Jg & 1]);
 				}
+				++Jg;
 			};
 			// all lanes: the smallest key of job h's scores
 			auto min_score = [&](uint32_t par, uint32_t rowlen) -> uint64_t {
@@ -341,6 +369,11 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 			dc++; // the reference evaluates the entry vertex again on entering the bottom layer
 			bool full = ef == 1;
 			uint32_t thr_hi = full ? f32_orderable(ep_dist) : 0xFFFFFFFFu; // orderable distance at position ef - 1
+			if (lane == 0) { // what the first decision starts from
+				st[(Jb & 1) * 2] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+				st[(Jb & 1) * 2 + 1] = make_uint4(thr_hi, 0, 0, 0);
+				GI_ARRIVE(&bar_adm[Jb & 1]);
+			}
 			publish(2, p.blk_bottom + (size_t)ep * p.bb_bytes, thr_hi);
 			WarpList<LPL> beam;
 			beam.init();
@@ -361,19 +394,17 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 				fk = warp_min_u64(fk);
 				if (full && (uint32_t)(fk >> 32) >= thr_hi) fk = KEY_EMPTY; // not admitted: then no neighbour is
 				const uint64_t nextk = min(fk, r1);
-				if (nextk == KEY_EMPTY) { // nothing left to expand (and nothing to admit): the search is over
-					publish(0, nullptr);
+				++Jb;
+				if (nextk == KEY_EMPTY) { // nothing left to expand (and nothing to admit): the search is over, the scorers know too
 					for (uint32_t i0 = 0; i0 < m0s; i0 += 32) dc += __popc(__ballot_sync(FULL, i0 + lane < m0s && keys[i0 + lane] != KEY_EMPTY));
-					GI_WAIT(&bar_sc[h & 1], h >> 1, (uint32_t)GI_SCORERS);
-					++h;
 					break;
 				}
 				{
-					// the runner-up of the next hop (unless one of this hop's other candidates is closer still): a neighbour the
-					// next hop finds under it — and under the beam's bound — is the vertex expanded after it, and the scorers ask
-					// for its block as soon as they have its distance; the runner-up's own block goes to L2 now
+					// (the scorers have come to the same vertex and are loading its block.) The runner-up of the next hop, unless
+					// one of this hop's other candidates is closer still: a neighbour the next hop finds under it — and under the
+					// beam's bound — is the vertex expanded after it, and the scorers ask for its block as soon as they have its
+					// distance; the runner-up's own block goes to L2 now
 					const uint64_t second = nextk == fk ? r1 : min(fk, r2);
-					publish(2, p.blk_bottom + (size_t)((uint32_t)(nextk >> 1) & 0x7FFFFFFFu) * p.bb_bytes, min((uint32_t)(second >> 32), thr_hi));
 					if (second != KEY_EMPTY && lane == 0) bulk_prefetch_l2(p.blk_bottom + (size_t)((uint32_t)(second >> 1) & 0x7FFFFFFFu) * p.bb_bytes, p.bb_bytes);
 				}
 				GI_T(2);
@@ -447,6 +478,11 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 					pos1 = p1;
 					r1 = p1 >= 0 ? bm[p1] : KEY_EMPTY;
 					r2 = p2 >= 0 ? bm[p2] : KEY_EMPTY;
+				}
+				if (lane == 0) { // for the decision after the next hop's scores
+					st[(Jb & 1) * 2] = make_uint4((uint32_t)r1, (uint32_t)(r1 >> 32), (uint32_t)r2, (uint32_t)(r2 >> 32));
+					st[(Jb & 1) * 2 + 1] = make_uint4(full ? thr_hi : 0xFFFFFFFFu, 0, 0, 0);
+					GI_ARRIVE(&bar_adm[Jb & 1]);
 				}
 				GI_T(3);
 			}
