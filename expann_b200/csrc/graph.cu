@@ -313,7 +313,7 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 			h->fused = true;
 		}
 		cudaEvent_t t0 = timing_begin(h, st);
-		if (h->g_inline && p.width == 1 && !p.compressed) {
+		if (h->g_inline && h->opt_graph_inline != 0 && p.width == 1 && !p.compressed) {
 			// neighbourhood blocks (graph_inline.cuh): one bulk copy per hop
 			InlineParams ip{};
 			ip.g = p;

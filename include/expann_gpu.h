@@ -171,8 +171,8 @@ int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
  * measured recall >= at every beam width for 2 % more distance evaluations), "graph_upper_compact" (0/1, before build():
  * compact copy of the upper layers for the latency form, default 1), "graph_hash" (0/1, default 0: the one-warp-per-query form
  * keeps the visited set in a per-warp shared-memory hash, exact, moving to the per-vertex bytes in HBM when a query fills it;
- * measured 9-20 % slower than the bytes in HBM, which mostly hit L2), "graph_inline" (-1 automatic (default) | 0 | 1 | 2, before
- * build(): the latency form reads NEIGHBOURHOOD BLOCKS — per vertex the ids of its neighbours and copies of their vectors,
+ * measured 9-20 % slower than the bytes in HBM, which mostly hit L2), "graph_inline" (-1 automatic (default) | 0 | 1 | 2; before
+ * build() it decides whether the blocks are built, after it 0 / non-0 switches their use off and on: the latency form reads NEIGHBOURHOOD BLOCKS — per vertex the ids of its neighbours and copies of their vectors,
  * contiguous, n x (M0 x d x 4 + 128) bytes of HBM (16.5 GB per million vertices at M0 = 32, d = 128) — one memory round trip
  * per hop instead of two, same ids and distances bit for bit; automatic = built when the blocks take at most a third of the
  * free device memory, 1 = whenever they fit, 2 = as 1 with the visited set in HBM bytes instead of the shared-memory bitmap (the

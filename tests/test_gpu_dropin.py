@@ -31,7 +31,7 @@ def test_reference_harness_over_gpu_engines(tmp_path):
     if not os.path.exists(BIN):
         pytest.skip("oracle/_ref/expann_dropin was not built (needs /root/reference at build time)")
     prefix = str(tmp_path / "dropin") + "/"
-    r = subprocess.run([BIN, "4000", "100", "10", prefix], capture_output=True, text=True, timeout=600)
+    r = subprocess.run([BIN, "4000", "2000", "10", prefix], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     latest = json.load(open(prefix + "data/latest.json"))        # written by the reference's bench_data_manager
     assert len(latest) == 7

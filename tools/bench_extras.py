@@ -85,7 +85,8 @@ def graph_c3(device: int, steps: int, warmup: int, cpu: bool = True, n: int = 1_
             # the reference harness's own pattern: one query per call (src/basic_bench.h:82-126) -> latency form of K5
             one = (outp[0][:1], outp[1][:1], outp[2][:1])
             lat = {}
-            for width in (1, 2):
+            for name, inline, width in (("blocks_us_per_call", -1, 1), ("width1_us_per_call", 0, 1), ("width2_us_per_call", 0, 2)):
+                e.set_option("graph_inline", inline)
                 e.set_option("graph_cta_width", width)
                 for i in range(30):
                     e.query_k_batch(hq[i:i + 1], k, out=one)
@@ -93,10 +94,14 @@ def graph_c3(device: int, steps: int, warmup: int, cpu: bool = True, n: int = 1_
                 t1 = time.perf_counter()
                 for i in range(nq):
                     e.query_k_batch(hq[i:i + 1], k, out=one)
-                lat["width%d_us_per_call" % width] = (time.perf_counter() - t1) / nq * 1e6
+                lat[name] = (time.perf_counter() - t1) / nq * 1e6
             e.set_option("graph_cta_width", 1)
-            lat["note"] = ("expann_gpu_query with one query per call, graph_search_cta_kernel (one CTA per query); width1 = the "
-                           "reference's visit order (default), width2 = two vertices expanded per hop")
+            e.set_option("graph_inline", -1)
+            lat["note"] = ("expann_gpu_query with one query per call, one CTA per query; blocks = the default: "
+                           "graph_search_inline_kernel over neighbourhood blocks (ids + copies of the neighbours' vectors per "
+                           "vertex, one memory trip per hop; same ids and distances as width1); width1 = graph_search_cta_kernel "
+                           "over adjacency rows + gathered vectors, the reference's visit order; width2 = the same with two "
+                           "vertices expanded per hop")
             chosen["single_query_call"] = lat
     # the reference engine's own use_compression switch (src/antitopo_engine.h:197-199, 710-851): the SAME graph searched
     # over the 8-bit codes (128 B per gathered vector instead of 512 B; lossless on u8-valued rows) + fp32 re-rank
