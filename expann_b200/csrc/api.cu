@@ -552,6 +552,8 @@ int expann_gpu_set_option(expann_gpu_t* h, const char* name, int64_t value) {
 	} else if (nm == "graph_inline") {
 		if (value < -1 || value > 2) return fail(h, EXPANN_ERR_ARG, "graph_inline must be -1 (automatic), 0, 1 or 2");
 		h->opt_graph_inline = (int)value; // before build(): whether the blocks are built; after it: whether blocks that exist are used
+	} else if (nm == "graph_inline_batch") {
+		h->opt_graph_inline_batch = value != 0;
 	} else if (nm == "graph_upper_compact") {
 		h->opt_graph_upper_compact = value != 0;
 	} else if (nm == "tc_boot") {

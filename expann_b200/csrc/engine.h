@@ -114,6 +114,7 @@ struct expann_gpu {
 	expann::DevBuf g_blk_bottom, g_blk_upper;
 	uint32_t g_bb_bytes = 0, g_bb_idb = 0, g_ub_bytes = 0, g_ub_idb = 0;
 	bool g_inline = false; // the blocks are built
+	int opt_graph_inline_batch = 1; // the one-warp-per-query form reads the blocks too when they exist (+8-12 % QPS: one region of HBM per hop instead of scattered rows)
 	int opt_graph_inline = -1; // -1 automatic (built when the blocks take at most a third of the free HBM), 0 off, 1 whenever they fit, 2 = 1 with the visited set kept in HBM bytes (what graphs too large for the shared-memory bitmap get; tests); before build()
 	float build_ortho_factor = 0.5f, build_ortho_bias = 0.f;
 	uint64_t build_prune_overflow = 0, build_K = 0;

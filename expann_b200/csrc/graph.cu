@@ -373,6 +373,38 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 	}
 	const unsigned grid = (unsigned)std::min<size_t>(h->g_ctas, (m + GS_WARPS - 1) / GS_WARPS);
 	cudaEvent_t t0 = timing_begin(h, st);
+	if (h->g_inline && h->opt_graph_inline != 0 && h->opt_graph_inline_batch && !p.compressed && !p.hash) {
+		// the one-warp-per-query form over the neighbourhood blocks (graph_inline.cuh)
+		InlineParams ip{};
+		ip.g = p;
+		ip.blk_bottom = h->g_blk_bottom.as<uint8_t>();
+		ip.blk_upper = h->g_blk_upper.as<uint8_t>();
+		ip.bb_bytes = h->g_bb_bytes; ip.bb_idb = h->g_bb_idb; ip.ub_bytes = h->g_ub_bytes; ip.ub_idb = h->g_ub_idb;
+		const size_t smemb = ((size_t)h->d_pad * 4 + GS_MAXNB * 8) * GS_WARPS;
+#define GB_LAUNCH_B(L, B)                                                                                         \
+	do {                                                                                                          \
+		if (int rc_ = ensure_dyn_smem(h, (const void*)graph_search_blocks_kernel<L, B>, smemb)) return rc_;              \
+		graph_search_blocks_kernel<L, B><<<grid, 32 * GS_WARPS, smemb, st>>>(ip);                                \
+	} while (0)
+#define GB_LAUNCH(L)                                                                                              \
+	do {                                                                                                          \
+		const uint32_t occ = h->g_ctas / (uint32_t)std::max(1, sms);                                             \
+		if (occ >= 8) GB_LAUNCH_B(L, 8);                                                                         \
+		else if (occ >= 5) GB_LAUNCH_B(L, 5);                                                                    \
+		else if (occ >= 4) GB_LAUNCH_B(L, 4);                                                                    \
+		else GB_LAUNCH_B(L, 2);                                                                                  \
+	} while (0)
+		if (cap <= 32) GB_LAUNCH(1);
+		else if (cap <= 64) GB_LAUNCH(2);
+		else if (cap <= 128) GB_LAUNCH(4);
+		else GB_LAUNCH(8);
+#undef GB_LAUNCH
+#undef GB_LAUNCH_B
+		timing_end(h, t0, st);
+		EXPANN_CUDA(h, cudaGetLastError());
+		h->stats.graph_launches++;
+		return EXPANN_OK;
+	}
 #define GS_LAUNCH_B(L, B)                                                                                         \
 	do {                                                                                                          \
 		if (int rc_ = ensure_dyn_smem(h, (const void*)graph_search_kernel<L, B>, smem)) return rc_;                      \

@@ -515,6 +515,222 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 	if (tid == 0 && p.g.distcomps && dc_total) atomicAdd(p.g.distcomps, dc_total);
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// K5, batch form (one warp per query, graph_search_kernel) over the neighbourhood blocks. Same search, same results,
+// same prefetches (the runner-up's ids a hop early, the rows of the gather's later rounds when the ids are known); what
+// changes is where a hop's bytes come from: the ids and the vectors of the expanded vertex's neighbours are one contiguous
+// block (rows addressed by position), 16.5 KB in ONE region of HBM instead of ~26 rows scattered over the base: +8-12 % QPS
+// at every beam width (1M x 128: ef 40 5.77 -> 6.24 M QPS). MEASURED AND DROPPED: asking for whole blocks with
+// cp.async.bulk.prefetch.L2 when a vertex is chosen and for the runner-up (4.27 M QPS: the visited neighbours' rows and the
+// wrong guesses are paid for in DRAM bandwidth, which this form, unlike the one-query form, is short of); the first 4 KB of
+// the block's vectors asked for with the ids (no change).
+// ---------------------------------------------------------------------------------------------------------
+// gather_dist_f32 with the row numbers and the results in ONE array (io[i]: in = row of `rows`, out = distance bits)
+__device__ __forceinline__ void gather_dist_f32_inplace(const float* __restrict__ rows, uint32_t d_pad, const float* qsm, uint32_t* io, int cnt, int lane) {
+	const int team = lane >> 3, tl = lane & 7;
+	const int nstep = d_pad >> 5;
+	for (int i0 = 0; i0 < cnt; i0 += 8) {
+		const int ia = i0 + team, ib = i0 + 4 + team;
+		const uint32_t va = ia < cnt ? io[ia] : 0, vb = ib < cnt ? io[ib] : 0;
+		const float* pa = rows + (size_t)va * d_pad + tl * 4;
+		const float* pb = rows + (size_t)vb * d_pad + tl * 4;
+		float sa = 0.f, sb = 0.f;
+		for (int s0 = 0; s0 < nstep; s0 += 4) {
+			float4 xa[4], xb[4];
+#pragma unroll
+			for (int s = 0; s < 4; ++s)
+				if (s0 + s < nstep) { xa[s] = ldg128f(pa + (s0 + s) * 32); xb[s] = ldg128f(pb + (s0 + s) * 32); }
+#pragma unroll
+			for (int s = 0; s < 4; ++s)
+				if (s0 + s < nstep) { // same order of operations as gather_dist_f32
+					const float4 q = *reinterpret_cast<const float4*>(qsm + (s0 + s) * 32 + tl * 4);
+					float t;
+					t = q.x - xa[s].x; sa = fmaf(t, t, sa); t = q.y - xa[s].y; sa = fmaf(t, t, sa);
+					t = q.z - xa[s].z; sa = fmaf(t, t, sa); t = q.w - xa[s].w; sa = fmaf(t, t, sa);
+					t = q.x - xb[s].x; sb = fmaf(t, t, sb); t = q.y - xb[s].y; sb = fmaf(t, t, sb);
+					t = q.z - xb[s].z; sb = fmaf(t, t, sb); t = q.w - xb[s].w; sb = fmaf(t, t, sb);
+				}
+		}
+#pragma unroll
+		for (int o = 4; o >= 1; o >>= 1) { sa += __shfl_xor_sync(FULL, sa, o); sb += __shfl_xor_sync(FULL, sb, o); }
+		__syncwarp();
+		if (tl == 0) {
+			if (ia < cnt) io[ia] = __float_as_uint(sa);
+			if (ib < cnt) io[ib] = __float_as_uint(sb);
+		}
+	}
+	__syncwarp();
+}
+
+template <int LPL, int MINB>
+__global__ void __launch_bounds__(32 * GS_WARPS, MINB) graph_search_blocks_kernel(const InlineParams ip) {
+	extern __shared__ uint8_t gs_smem[];
+	const GraphParams& p = ip.g;
+	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+	const uint32_t slot = blockIdx.x * GS_WARPS + wib, nslots = gridDim.x * GS_WARPS;
+	// per-warp smem: query (d_pad floats) | nb ids (GS_MAXNB) | block rows in / distances out (GS_MAXNB)
+	const size_t per_warp = (size_t)p.d_pad * 4 + GS_MAXNB * 8;
+	uint8_t* wsm = gs_smem + per_warp * wib;
+	float* qsm = reinterpret_cast<float*>(wsm);
+	uint32_t* nb = reinterpret_cast<uint32_t*>(qsm + p.d_pad);
+	uint32_t* nio = nb + GS_MAXNB;
+	uint8_t* vis = p.visited + (size_t)slot * p.vis_stride;
+	uint32_t epoch = p.epoch[slot];
+	unsigned long long dc_total = 0;
+
+	for (uint32_t qi = slot; qi < p.m; qi += nslots) {
+		epoch++;
+		if ((epoch & 0xFF) == 0) {
+			epoch++;
+			for (size_t i = (size_t)lane * 16; i < p.vis_stride; i += 32 * 16)
+				*reinterpret_cast<uint4*>(vis + i) = make_uint4(0, 0, 0, 0);
+			__syncwarp();
+		}
+		const uint8_t ep8 = (uint8_t)(epoch & 0xFF);
+		for (uint32_t i = lane; i < p.d_pad; i += 32) qsm[i] = p.queries[(size_t)qi * p.d_pad + i];
+		__syncwarp();
+		uint32_t dc = 0;
+
+		// ---- upper layers: greedy descent (src/antitopo_engine.h:861-903), as in graph_search_kernel
+		uint32_t ep = p.start;
+		float ep_dist;
+		float* nbd = reinterpret_cast<float*>(nio);
+		if (lane == 0) nb[0] = ep;
+		__syncwarp();
+		gather_dist_f32(p.base, p.d_pad, qsm, nb, nbd, 1, lane);
+		ep_dist = nbd[0];
+		dc++;
+		for (uint32_t layer = p.max_layer > 0 ? p.max_layer - 1 : 0; layer > 0; --layer) {
+			bool changed = true;
+			while (changed) {
+				changed = false;
+				__syncwarp();
+				const uint32_t ui = p.upper_idx[ep];
+				if (ui == NO_VERTEX || p.upper_nl[ep] <= layer) break;
+				const uint32_t* row = p.upper + ((size_t)ui + (layer - 1)) * p.ms;
+				int cnt = 0;
+				for (uint32_t j0 = 0; j0 < p.ms; j0 += 32) {
+					const uint32_t v = j0 + lane < p.ms ? row[j0 + lane] : NO_VERTEX;
+					const unsigned mk = __ballot_sync(FULL, v != NO_VERTEX);
+					if (v != NO_VERTEX) nb[cnt + __popc(mk & ((1u << lane) - 1))] = v;
+					cnt += __popc(mk);
+				}
+				__syncwarp();
+				gather_dist_f32(p.base, p.d_pad, qsm, nb, nbd, cnt, lane);
+				dc += cnt;
+				float best = ep_dist;
+				int besti = -1;
+				for (int i = lane; i < cnt; i += 32)
+					if (nbd[i] < best) { best = nbd[i]; besti = i; }
+#pragma unroll
+				for (int o = 16; o >= 1; o >>= 1) {
+					const float ob = __shfl_xor_sync(FULL, best, o);
+					const int oi = __shfl_xor_sync(FULL, besti, o);
+					if (oi >= 0 && (ob < best || (ob == best && (besti < 0 || oi < besti)))) { best = ob; besti = oi; }
+				}
+				if (besti >= 0) { ep = nb[besti]; ep_dist = best; changed = true; }
+			}
+		}
+		if (lane == 0) bulk_prefetch_l2(ip.blk_bottom + (size_t)ep * ip.bb_bytes, ip.bb_bytes);
+
+		// ---- bottom layer beam search (src/antitopo_engine.h:495-708)
+		WarpList<LPL> beam;
+		beam.init();
+		dc++;
+		beam.insert(beam_key(ep_dist, ep), lane);
+		if (lane == 0) vis[ep] = ep8;
+		__syncwarp();
+		float thr = __int_as_float(0x7f800000); // distance at position ef-1 (inf while the beam is not full)
+		bool full = false;
+		if (p.ef == 1) { full = true; thr = ep_dist; }
+		for (;;) {
+			// closest unexpanded entry among the first ef
+			int pos = -1, pos2 = -1;
+#pragma unroll
+			for (int s = 0; s < LPL; ++s) {
+				const int i = s * 32 + lane;
+				unsigned mk = __ballot_sync(FULL, i < (int)p.ef && beam.e[s] != KEY_EMPTY && !(beam.e[s] & 1ull));
+				if (pos < 0 && mk) { pos = s * 32 + __ffs(mk) - 1; mk &= mk - 1; }
+				if (pos >= 0 && pos2 < 0 && mk) pos2 = s * 32 + __ffs(mk) - 1;
+			}
+			if (pos < 0) break;
+			const uint64_t ck = beam.at(pos);
+			const uint32_t cur = (uint32_t)(ck >> 1) & 0x7FFFFFFFu;
+			const uint8_t* blk = ip.blk_bottom + (size_t)cur * ip.bb_bytes;
+			const uint64_t rk2 = pos2 >= 0 ? beam.at(pos2) : KEY_EMPTY;
+			// the runner-up is the likely next vertex: the line with its neighbours' ids goes to L2 a hop early
+			if (rk2 != KEY_EMPTY && (uint32_t)lane * 32u < p.m0s) prefetch_l2(ip.blk_bottom + (size_t)((uint32_t)(rk2 >> 1) & 0x7FFFFFFFu) * ip.bb_bytes + lane * 128);
+#pragma unroll
+			for (int s = 0; s < LPL; ++s)
+				if (s * 32 + lane == pos) beam.e[s] |= 1ull;
+			// unvisited neighbours of cur (:595-607): ids from the block, fresh ones compacted with their row in the block
+			int cnt = 0;
+			__syncwarp();
+			for (uint32_t j0 = 0; j0 < p.m0s; j0 += 32) {
+				const uint32_t v = j0 + lane < p.m0s ? __ldg(reinterpret_cast<const uint32_t*>(blk) + j0 + lane) : NO_VERTEX;
+				bool fresh = false;
+				if (v != NO_VERTEX) {
+					fresh = vis[v] != ep8;
+					if (fresh) vis[v] = ep8;
+				}
+				const unsigned mk = __ballot_sync(FULL, fresh);
+				if (fresh) {
+					const int at = cnt + __popc(mk & ((1u << lane) - 1));
+					nb[at] = v;
+					nio[at] = j0 + lane;
+				}
+				cnt += __popc(mk);
+			}
+			__syncwarp();
+			if (cnt == 0) continue;
+			if (cnt > 8) { // rows of the gather's later rounds (8 per round) are asked for now: only the first round waits for DRAM
+				for (int i = 8 + lane; i < cnt; i += 32) {
+					const uint8_t* r = blk + ip.bb_idb + (size_t)nio[i] * p.d_pad * 4;
+					for (uint32_t o = 0; o < p.d_pad * 4; o += 128) prefetch_l2(r + o);
+				}
+			}
+			gather_dist_f32_inplace(reinterpret_cast<const float*>(blk + ip.bb_idb), p.d_pad, qsm, nio, cnt, lane);
+			dc += cnt;
+			// admission (:666-676): size < ef or d < worst
+			for (int i0 = 0; i0 < cnt; i0 += 32) {
+				const int i = i0 + lane;
+				const float dv = i < cnt ? __uint_as_float(nio[i]) : 0.f;
+				const uint32_t vv = i < cnt ? nb[i] : 0;
+				unsigned mk = __ballot_sync(FULL, i < cnt && (!full || dv < thr));
+				while (mk) {
+					const int src = __ffs(mk) - 1;
+					mk &= mk - 1;
+					const float dd = __shfl_sync(FULL, dv, src);
+					const uint32_t id = __shfl_sync(FULL, vv, src);
+					if (!full || dd < thr) {
+						beam.insert(beam_key(dd, id), lane);
+						const uint64_t tk = beam.at(p.ef - 1);
+						full = tk != KEY_EMPTY;
+						if (full) thr = f32_from_orderable((uint32_t)(tk >> 32));
+					}
+				}
+			}
+		}
+		// ---- output: first k of the ascending beam
+		uint64_t* dst = p.out_keys + (size_t)qi * p.k;
+#pragma unroll
+		for (int s = 0; s < LPL; ++s) {
+			const int i = s * 32 + lane;
+			if (i < (int)p.k) {
+				uint64_t e = beam.e[s];
+				if (i >= (int)p.ef) e = KEY_EMPTY;
+				dst[i] = e == KEY_EMPTY ? KEY_EMPTY : ((e >> 32) << 32) | (((uint32_t)(e >> 1) & 0x7FFFFFFFu) + p.id_add);
+			}
+		}
+		dc_total += dc;
+		__syncwarp();
+	}
+	if (lane == 0) {
+		p.epoch[slot] = epoch;
+		if (p.distcomps && dc_total) atomicAdd(p.distcomps, dc_total);
+	}
+}
+
 // ---- building the blocks (once, at build()): one warp per (block, entry)
 __global__ void build_bottom_blocks_kernel(const float* __restrict__ base, const uint32_t* __restrict__ bottom, uint8_t* __restrict__ blocks,
                                            uint32_t n, uint32_t m0s, uint32_t d_pad, uint32_t bb_bytes, uint32_t bb_idb) {

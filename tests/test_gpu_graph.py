@@ -297,11 +297,18 @@ def test_inline_blocks_identical(ex, n, d, M, M0, nq):
             for a, b in zip(res[0][3], res[inl][3]):
                 assert np.array_equal(a, b), (ef, inl)
             assert res[0][4] == res[inl][4], (ef, inl, res[0][4], res[inl][4])
-        # and the one-warp-per-query form agrees with all of them
-        eng[1].set_option("graph_cta_batch", 0)
-        warp = eng[1].query_k_batch(q, k)
-        eng[1].set_option("graph_cta_batch", -1)
-        for a, b in zip(res[1][3], warp):
-            assert np.array_equal(a, b), ef
+        # and the one-warp-per-query form agrees with all of them: over adjacency rows (engine 0), over the blocks (engine 1,
+        # graph_search_blocks_kernel), and over adjacency rows of an engine that has blocks (graph_inline_batch = 0)
+        for inl, batch in ((0, 1), (1, 1), (1, 0)):
+            eng[inl].set_option("graph_cta_batch", 0)
+            eng[inl].set_option("graph_inline_batch", batch)
+            dc0 = eng[inl].stats()["distcomps"]
+            warp = eng[inl].query_k_batch(q, k)
+            dc = eng[inl].stats()["distcomps"] - dc0
+            eng[inl].set_option("graph_cta_batch", -1)
+            eng[inl].set_option("graph_inline_batch", 1)
+            for a, b in zip(res[1][3], warp):
+                assert np.array_equal(a, b), (ef, inl, batch)
+            assert dc == res[0][4], (ef, inl, batch, dc, res[0][4])
     for e in eng.values():
         e.close()
