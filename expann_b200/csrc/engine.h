@@ -89,7 +89,7 @@ struct expann_gpu {
 	int opt_tc_pair = 1; // pair form of K3 (clusters of two CTAs, tcgen05.mma.cta_group::2)
 	int opt_tc_astream = 1; // pair form with the query operand streamed through the ring: 0 off, 1 when nothing else fits, 2 always
 	int opt_graph_occ = 5; // graph search: resident CTAs of 4 warps per SM (2, 4, 5 or 8); set before build()
-	int opt_graph_cta_batch = -1; // graph search: calls with at most this many queries take the one-CTA-per-query latency form (-1 = two waves: twice the SM count)
+	int opt_graph_cta_batch = -1; // graph search: calls with at most this many queries take the one-CTA-per-query latency form (-1 = two waves: twice the SM count; five waves over the neighbourhood blocks)
 	int opt_graph_cta_width = 1; // latency form: vertices expanded per hop (1 = the reference's order, the default; 2 = half the dependent hops, recall >= at every beam width measured, +2 % distance evaluations)
 	int opt_graph_hash = 0; // warp form of the search: visited set in a per-warp shared-memory hash (exact; falls back to the HBM bytes when full). Measured slower than the HBM bytes (5.28 vs 5.81 M QPS at ef 40): off by default
 	int opt_graph_upper_compact = 1; // latency form: upper layers in compact form (set before build())

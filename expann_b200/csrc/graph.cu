@@ -293,7 +293,10 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 	p.compressed = h->cfg.use_compression ? 1 : 0;
 	// automatic: up to two waves of one CTA per SM (measured on 1M x 128, ef 40: 128 queries 188 vs 394 us, 256 queries
 	// 320 vs 410 us, 512 queries 573 vs 419 us per call)
-	if (m <= (size_t)(h->opt_graph_cta_batch < 0 ? 2 * sms : h->opt_graph_cta_batch)) {
+	// (over the neighbourhood blocks the one-CTA-per-query form stays ahead for longer: 296 queries 183 vs 398 us, 592 queries
+	// 310 vs 408 us, 1024 queries 484 vs 426 us per call: automatic up to five waves)
+	const bool blocks_ok = h->g_inline && h->opt_graph_inline != 0 && !h->cfg.use_compression && !(h->opt_graph_cta_width == 2 && ef >= 2);
+	if (m <= (size_t)(h->opt_graph_cta_batch < 0 ? (blocks_ok ? 5 : 2) * sms : h->opt_graph_cta_batch)) {
 		// latency form: one CTA per query (few queries per call; nothing to hide the hops' round trips behind)
 		const size_t smem1 = (size_t)h->d_pad * 5 + GS_MAXNB * 8 + 16 + 256 * 8 + GS_MAXNB * 4; // query | u8 query | nb | nbd | ctl | beam copy
 		if (smem1 > 200 * 1024) return fail(h, EXPANN_ERR_UNSUPPORTED, "graph search: d too large");

@@ -166,7 +166,7 @@ int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
  * "qtile" (0 auto | 1 | 4 | 8), "nsplit" (0 auto | forced row splits per scan), "kprime" (QUANT_SCAN: survivors
  * re-ranked in fp32, 0 auto = min(128, 10k)), "graph_occ" (GRAPH: resident CTAs of 4 warps per SM, 2 | 4 | 5 | 8,
  * default 5, before build()), "graph_cta_batch" (GRAPH: calls with at most this many queries take the latency form
- * of the search, one CTA per query; -1 automatic = twice the SM count, 0 never), "graph_cta_width" (vertices the latency form expands per hop: 1 (default) =
+ * of the search, one CTA per query; -1 automatic = twice the SM count, five times with the neighbourhood blocks of "graph_inline"; 0 never), "graph_cta_width" (vertices the latency form expands per hop: 1 (default) =
  * exactly the reference's visit order, 2 = the two closest unexpanded beam entries together: half the dependent hops,
  * measured recall >= at every beam width for 2 % more distance evaluations), "graph_upper_compact" (0/1, before build():
  * compact copy of the upper layers for the latency form, default 1), "graph_hash" (0/1, default 0: the one-warp-per-query form
