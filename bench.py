@@ -766,7 +766,7 @@ def main():
             torch.cuda.empty_cache()
             g3 = bench_extras.graph_c3(local_rank, max(2, min(args.steps, 20)), args.warmup, cpu=not args.no_cpu, peak_gbs=peak)
             if "roofline" in g3:   # DRAM bytes per launch of the ef = 40 search from the committed ncu capture
-                g3["roofline"]["traffic"], g3["roofline"]["traffic_source"] = ncu_traffic("graph_search_kernel")
+                g3["roofline"]["traffic"], g3["roofline"]["traffic_source"] = ncu_traffic("graph_search_blocks_kernel")
             roof["graph"] = g3
             if g3.get("at_recall_0.95"):
                 out["graph_qps_at_recall_0_95"] = g3["at_recall_0.95"]["qps"]

@@ -129,7 +129,7 @@ def graph_c3(device: int, steps: int, warmup: int, cpu: bool = True, n: int = 1_
            "metric": "QPS @ smallest ef with recall@10 >= 0.95", "graph_build_s": build_s, "sweep": sweep, "at_recall_0.95": chosen,
            "compressed": compressed}
     if chosen:
-        out["roofline"] = {"bound": "hbm", "kernel": "graph_search_kernel", "achieved": chosen["gather_GBs"], "peak": peak_gbs,
+        out["roofline"] = {"bound": "hbm", "kernel": "graph_search_blocks_kernel (graph_search_kernel gathering from per-vertex neighbourhood blocks)", "achieved": chosen["gather_GBs"], "peak": peak_gbs,
                            "unit": "GB/s", "frac": chosen["gather_GBs"] / peak_gbs,
                            "note": "algorithmic bytes = distance evaluations x d x 4 (random 512 B row gathers); latency-bound"}
     if cpu and chosen:
