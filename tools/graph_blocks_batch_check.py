@@ -11,6 +11,7 @@ d = int(sys.argv[2]) if len(sys.argv) > 2 else 128
 m = int(sys.argv[3]) if len(sys.argv) > 3 else 10000
 base, q = datasets.make("sift", n, m, d, variant="lowrank")
 e = expann_b200.GraphEngine(); e.set_option("graph_inline", 1)
+if os.environ.get("GRAPH_OCC"): e.set_option("graph_occ", int(os.environ["GRAPH_OCC"]))
 e.store_many_vectors(base); e.build_graph(M=16, M0=32, K=64); e.build()
 dq = torch.from_numpy(q).cuda(); k = 10
 keys = {0: torch.empty((m, k), dtype=torch.int64, device="cuda"), 1: torch.empty((m, k), dtype=torch.int64, device="cuda")}
