@@ -312,3 +312,50 @@ def test_inline_blocks_identical(ex, n, d, M, M0, nq):
             assert dc == res[0][4], (ef, inl, batch, dc, res[0][4])
     for e in eng.values():
         e.close()
+
+
+@pytest.mark.parametrize("n,d,maxdeg,updeg,layers", [(900, 64, 200, 40, 3), (300, 128, 33, 8, 2), (64, 96, 5, 3, 1), (1, 128, 0, 0, 1)])
+def test_inline_blocks_handmade_graphs(ex, n, d, maxdeg, updeg, layers):
+    """hand-made CSR graphs (random edges; nothing about them is good, the forms only have to agree): bottom rows of up
+    to 200 neighbours and upper rows of more than 32 (the scorers' general path, several rounds per row), ragged
+    degrees, vertices without neighbours, a graph without upper layers, a one-vertex graph, k above what is reachable"""
+    rng = np.random.default_rng(n + d)
+    base = rng.integers(0, 256, (n, d)).astype(np.float32)
+    q = rng.integers(0, 256, (24, d)).astype(np.float32)
+    nl = np.ones(n, np.uint32)
+    if layers > 1:
+        top = rng.permutation(n)[:max(2, n // 6)]
+        nl[top] = rng.integers(2, layers + 1, top.size).astype(np.uint32)
+    start = int(np.argmax(nl))
+    offsets, edges = [0], []
+    for v in range(n):
+        for l in range(int(nl[v])):
+            pool = np.arange(n) if l == 0 else np.nonzero(nl > l)[0]
+            pool = pool[pool != v]
+            cap = maxdeg if l == 0 else updeg
+            deg = 0 if pool.size == 0 or cap == 0 else int(rng.integers(0 if v % 7 == 3 else 1, min(cap, pool.size) + 1))
+            edges += rng.choice(pool, deg, replace=False).tolist()
+            offsets.append(len(edges))
+    eng = {}
+    for inl in (0, 1, 2):
+        e = ex.GraphEngine()
+        e.set_option("graph_inline", inl)
+        e.store_many_vectors(base)
+        e.set_graph(nl, np.array(offsets, np.uint64), np.array(edges if edges else [0], np.uint32)[:len(edges)], start, int(nl.max()))
+        e.build()
+        eng[inl] = e
+    for ef, k in ((1, 1), (7, 5), (40, 10), (256, 100)):
+        res = {}
+        for inl, e in eng.items():
+            e.set_ef_search(ef)
+            one = [e.query_k_batch(q[i:i + 1], k) for i in range(len(q))]
+            res[inl] = [np.concatenate([o[j] for o in one]) for j in range(3)] + list(e.query_k_batch(q, k))
+        e = eng[1]
+        e.set_option("graph_cta_batch", 0)
+        res["warp"] = res[1][:3] + list(e.query_k_batch(q, k))
+        e.set_option("graph_cta_batch", -1)
+        for name in (1, 2, "warp"):
+            for a, b in zip(res[0], res[name]):
+                assert np.array_equal(a, b), (ef, k, name)
+    for e in eng.values():
+        e.close()
