@@ -14,13 +14,16 @@
 //   * the visited set is a bitmap of the whole vertex set in shared memory (n <= ~1.7 M: 1 bit per vertex, cleared per
 //     query in ~0.5 us) — no memory round trip; larger graphs keep the epoch-stamped bytes in HBM.
 //   * warp 0 is the CONTROLLER (owns the beam), warps 1..8 are SCORERS (32 teams of 8 lanes, one neighbour each). They
-//     meet on mbarriers, not bar.sync. As soon as the scores of hop h are in, the controller knows the vertex hop h+1
-//     expands WITHOUT touching the beam: it is the smaller of the closest fresh neighbour just scored (if the beam admits
-//     it) and the closest unexpanded beam entry — which was found at the end of the previous admission. It publishes that
-//     vertex, the scorers start their loads, and only then does the controller merge hop h's candidates into the beam and
-//     look up the next two unexpanded entries: that work runs under the scorers' memory trip.
+//     meet on mbarriers, not bar.sync. As soon as the scores of hop h are in, the vertex hop h+1 expands is known WITHOUT
+//     touching the beam: it is the smaller of the closest fresh neighbour just scored (if the beam admits it) and the
+//     closest unexpanded beam entry as of the previous admission — exactly what "admit, then take the closest unexpanded
+//     entry" yields. The controller drives the upper layers; on the bottom layer every scorer warp works that minimum out
+//     for itself (the scores and {r1, r2, bound} are in shared memory) and starts its loads, while the controller does the
+//     reference's own sequence one hop behind: merge hop h's candidates into the beam, mark the closest unexpanded entry
+//     (the vertex the scorers are on), leave the two after it and the new bound for the next decision. That work runs
+//     under the scorers' memory trip.
 //     The measured cost of a hop was instruction latency in the beam-owning warp, not memory (ncu: 233 k cycles per query,
-//     0.4 long-scoreboard stalls per issue); see profiles/r2_notes.md.
+//     0.4 long-scoreboard stalls per issue); see profiles/r2_notes.md section 12.
 #pragma once
 #include "graph_search.cuh"
 
@@ -254,7 +257,13 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 				__syncwarp();
 				if (lane == 0) GI_ARRIVE(&bar_sc[par]);
 				GI_S(4);
-				if (__any_sync(FULL, pfv != NO_VERTEX) && pfv != NO_VERTEX) bulk_prefetch_l2(p.blk_bottom + (size_t)pfv * p.bb_bytes, p.bb_bytes);
+				{ // one request per warp, with a warp-uniform address (per-lane operands make ptxas wrap the instruction in a loop)
+					const unsigned pm = __ballot_sync(FULL, pfv != NO_VERTEX);
+					if (pm) {
+						const uint32_t v1 = __shfl_sync(FULL, pfv, __ffs(pm) - 1);
+						if (lane == 0) bulk_prefetch_l2(p.blk_bottom + (size_t)v1 * p.bb_bytes, p.bb_bytes);
+					}
+				}
 				GI_S(5);
 #ifdef GI_PROFILE
 				sp_jobs++;
@@ -378,49 +387,25 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 			WarpList<LPL> beam;
 			beam.init();
 			beam.insert(beam_key(ep_dist, ep) | 1ull, lane);
-			int bsz = 1, pos1 = -1;
-			uint64_t r1 = KEY_EMPTY, r2 = KEY_EMPTY; // the two closest unexpanded entries among the first ef (r1 at position pos1)
+			int bsz = 1;
 			for (;;) {
 				const uint32_t par = h & 1;
 				GI_WAIT(&bar_sc[par], h >> 1, (uint32_t)GI_SCORERS);
 				++h;
 				GI_T(1);
-				// ---- which vertex does the next hop expand? The smaller of the closest fresh neighbour (if the beam admits it:
-				// then it is the smallest key admitted) and the closest unexpanded beam entry.
+				// ---- under the scorers' memory trip of the next hop (they have worked out its vertex themselves): admission
+				// (:666-676) of this hop's whole row at once. Every fresh neighbour under the bound the hop started with is merged
+				// into the sorted beam by rank counting — candidate c lands at #beam keys below c + #candidates below c, a beam key
+				// moves up by #candidates below it (the round's candidates are staged in shared memory and read back as
+				// broadcasts). Then the closest unexpanded entry — the vertex the scorers are on — is marked expanded, and the two
+				// after it are what the next decision starts from.
 				const uint64_t* keys = rk + par * GS_MAXNB;
 				const uint64_t key0 = (uint32_t)lane < m0s ? keys[lane] : KEY_EMPTY;
-				uint64_t fk = key0;
-				for (uint32_t i = 32 + lane; i < m0s; i += 32) fk = min(fk, keys[i]);
-				fk = warp_min_u64(fk);
-				if (full && (uint32_t)(fk >> 32) >= thr_hi) fk = KEY_EMPTY; // not admitted: then no neighbour is
-				const uint64_t nextk = min(fk, r1);
 				++Jb;
-				if (nextk == KEY_EMPTY) { // nothing left to expand (and nothing to admit): the search is over, the scorers know too
-					for (uint32_t i0 = 0; i0 < m0s; i0 += 32) dc += __popc(__ballot_sync(FULL, i0 + lane < m0s && keys[i0 + lane] != KEY_EMPTY));
-					break;
-				}
-				{
-					// (the scorers have come to the same vertex and are loading its block.) The runner-up of the next hop, unless
-					// one of this hop's other candidates is closer still: a neighbour the next hop finds under it — and under the
-					// beam's bound — is the vertex expanded after it, and the scorers ask for its block as soon as they have its
-					// distance; the runner-up's own block goes to L2 now
-					const uint64_t second = nextk == fk ? r1 : min(fk, r2);
-					if (second != KEY_EMPTY && lane == 0) bulk_prefetch_l2(p.blk_bottom + (size_t)((uint32_t)(second >> 1) & 0x7FFFFFFFu) * p.bb_bytes, p.bb_bytes);
-				}
 				GI_T(2);
 #ifdef GI_PROFILE
 				pf_hops++;
 #endif
-				// ---- under the scorers' memory trip: admission (:666-676) of the hop's whole row at once. Every fresh neighbour
-				// under the bound the hop started with is merged into the sorted beam by rank counting — candidate c lands at
-				// #beam keys below c + #candidates below c, a beam key moves up by #candidates below it (the round's candidates
-				// are staged in shared memory and read back as broadcasts). The vertex just published enters (or stays in) the
-				// beam as expanded.
-				if (nextk == r1) {
-#pragma unroll
-					for (int s = 0; s < LPL; ++s)
-						if (s * 32 + lane == pos1) beam.e[s] |= 1ull;
-				}
 				const bool fullh = full;
 				const uint32_t thrh = thr_hi;
 				for (uint32_t i0 = 0; i0 < m0s; i0 += 32) {
@@ -450,7 +435,6 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 						}
 						if (j == ci) lo = below;
 					}
-					if (cand && mykey == nextk) mykey |= 1ull;
 #pragma unroll
 					for (int s = 0; s < LPL; ++s) {
 						const int np = s * 32 + lane + shift[s];
@@ -466,18 +450,25 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 				// (bm is the beam as of the last merge; a mark set since then sits on an entry that is not read here)
 				full = bsz >= (int)ef;
 				if (full) thr_hi = (uint32_t)(bm[ef - 1] >> 32);
-				{ // the two closest unexpanded entries among the first ef
-					int p1 = -1, p2 = -1;
+				uint64_t r1, r2;
+				{ // the three closest unexpanded entries among the first ef: the first is being expanded, the others are r1, r2
+					int p0 = -1, p1 = -1, p2 = -1;
 #pragma unroll
 					for (int s = 0; s < LPL; ++s) {
 						const int i = s * 32 + lane;
 						unsigned mk = __ballot_sync(FULL, i < (int)ef && beam.e[s] != KEY_EMPTY && !(beam.e[s] & 1ull));
-						if (p1 < 0 && mk) { p1 = s * 32 + __ffs(mk) - 1; mk &= mk - 1; }
+						if (p0 < 0 && mk) { p0 = s * 32 + __ffs(mk) - 1; mk &= mk - 1; }
+						if (p0 >= 0 && p1 < 0 && mk) { p1 = s * 32 + __ffs(mk) - 1; mk &= mk - 1; }
 						if (p1 >= 0 && p2 < 0 && mk) p2 = s * 32 + __ffs(mk) - 1;
 					}
-					pos1 = p1;
+					if (p0 < 0) break; // nothing left to expand: the search is over (the scorers have seen the same)
+#pragma unroll
+					for (int s = 0; s < LPL; ++s)
+						if (s * 32 + lane == p0) beam.e[s] |= 1ull;
 					r1 = p1 >= 0 ? bm[p1] : KEY_EMPTY;
 					r2 = p2 >= 0 ? bm[p2] : KEY_EMPTY;
+					// the runner-up is the likely vertex after the one being scored: its block goes to L2
+					if (r1 != KEY_EMPTY && lane == 0) bulk_prefetch_l2(p.blk_bottom + (size_t)((uint32_t)(r1 >> 1) & 0x7FFFFFFFu) * p.bb_bytes, p.bb_bytes);
 				}
 				if (lane == 0) { // for the decision after the next hop's scores
 					st[(Jb & 1) * 2] = make_uint4((uint32_t)r1, (uint32_t)(r1 >> 32), (uint32_t)r2, (uint32_t)(r2 >> 32));
