@@ -514,7 +514,9 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 // at every beam width (1M x 128: ef 40 5.77 -> 6.24 M QPS). MEASURED AND DROPPED: asking for whole blocks with
 // cp.async.bulk.prefetch.L2 when a vertex is chosen and for the runner-up (4.27 M QPS: the visited neighbours' rows and the
 // wrong guesses are paid for in DRAM bandwidth, which this form, unlike the one-query form, is short of); the first 4 KB of
-// the block's vectors asked for with the ids (no change).
+// the block's vectors asked for with the ids (no change); scoring ALL rows of the block without waiting for the ids and the
+// visited bytes (first eight rows in the ids' memory trip, the rest out of L2, distances of visited vertices thrown away:
+// 4.44 M QPS — a fifth more bytes and FMAs cost more than the shorter chain saves).
 // ---------------------------------------------------------------------------------------------------------
 // gather_dist_f32 with the row numbers and the results in ONE array (io[i]: in = row of `rows`, out = distance bits)
 __device__ __forceinline__ void gather_dist_f32_inplace(const float* __restrict__ rows, uint32_t d_pad, const float* qsm, uint32_t* io, int cnt, int lane) {
