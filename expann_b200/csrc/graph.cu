@@ -327,16 +327,19 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 			const size_t bitmap = ((h->n + 127) / 128) * 16; // bytes, whole uint4s
 			ip.bitmap_words = fixed + bitmap <= lim && h->opt_graph_inline != 2 ? (uint32_t)(bitmap / 4) : 0;
 			const size_t smemi = fixed + (size_t)ip.bitmap_words * 4;
-#define GI_LAUNCH_N(L, N)                                                                                         \
+#define GI_LAUNCH_N(L, N, R)                                                                                      \
 	do {                                                                                                          \
-		if (int rc_ = ensure_dyn_smem(h, (const void*)graph_search_inline_kernel<L, N>, smemi)) return rc_;             \
-		graph_search_inline_kernel<L, N><<<grid1, GI_THREADS, smemi, st>>>(ip);                                  \
+		if (int rc_ = ensure_dyn_smem(h, (const void*)graph_search_inline_kernel<L, N, R>, smemi)) return rc_;          \
+		graph_search_inline_kernel<L, N, R><<<grid1, GI_THREADS, smemi, st>>>(ip);                               \
 	} while (0)
 #define GI_LAUNCH(L)                                                                                              \
 	do {                                                                                                          \
-		if (h->d_pad == 128) GI_LAUNCH_N(L, 4);                                                                  \
-		else if (h->d_pad == 96) GI_LAUNCH_N(L, 3);                                                              \
-		else GI_LAUNCH_N(L, 0);                                                                                  \
+		const bool wide = std::max(h->graph.m0s, h->graph.ms) > 32 && std::max(h->graph.m0s, h->graph.ms) <= 128; \
+		if (h->d_pad == 128 && wide) GI_LAUNCH_N(L, 4, 4);                                                       \
+		else if (h->d_pad == 128) GI_LAUNCH_N(L, 4, 1);                                                          \
+		else if (h->d_pad == 96 && wide) GI_LAUNCH_N(L, 3, 4);                                                   \
+		else if (h->d_pad == 96) GI_LAUNCH_N(L, 3, 1);                                                           \
+		else GI_LAUNCH_N(L, 0, 1);                                                                               \
 	} while (0)
 			if (cap <= 32) GI_LAUNCH(1);
 			else if (cap <= 64) GI_LAUNCH(2);

@@ -82,13 +82,13 @@ __device__ unsigned gi_prof_calls;
 // nearly alone on its scheduler), so the per-hop paths are specialised: NSTEP = d_pad / 32 (3 or 4: the lane's share of the
 // query lives in registers and the loads are issued unconditionally; 0 = any dimension), rows of at most 32 neighbours
 // (one per team) take a path without loops.
-template <int LPL, int NSTEP>
+template <int LPL, int NSTEP, int NR>
 __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const InlineParams p) {
 	extern __shared__ __align__(128) uint8_t gi_smem[];
 	const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
 	const uint32_t slot = blockIdx.x;
 	const uint32_t d_pad = p.g.d_pad, m0s = p.g.m0s, ms = p.g.ms, ef = p.g.ef;
-	const bool one_round = m0s <= 32 && ms <= 32;
+	const bool one_round = m0s <= 32u * NR && ms <= 32u * NR; // NR = 1: one neighbour per team; NR = 4: up to four (rows of up to 128, the reference's M0 = 120)
 	// shared memory: query | keys of a hop's scores x 2 | beam copy | staged candidates | ctl x 2 | state x 2 | barriers | bitmap
 	float* qsm = reinterpret_cast<float*>(gi_smem);
 	uint64_t* rk = reinterpret_cast<uint64_t*>(qsm + d_pad); // [2][GS_MAXNB] bottom: beam key of a fresh neighbour; upper: orderable(dist) << 32 | position; KEY_EMPTY
@@ -167,7 +167,67 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 				uint64_t* out = rk + par * GS_MAXNB;
 				const bool bottom = job.z == 2;
 				uint32_t pfv = NO_VERTEX; // a neighbour likely to be expanded next: its block is asked into L2
-				if (NSTEP > 0 && one_round) {
+				if (NSTEP > 0 && NR > 1 && one_round) {
+					// rows of up to 32 * NR neighbours: team t scores neighbours t, t + 32, ...; the loads of all its rounds are
+					// issued before the first is used
+					const uint32_t rowlen = bottom ? m0s : ms;
+					const uint8_t* pv = blk + (bottom ? off_b : off_u);
+					uint32_t v[NR];
+					float4 xa[NR][NSTEP > 0 ? NSTEP : 1];
+#pragma unroll
+					for (int r = 0; r < NR; ++r) {
+						v[r] = NO_VERTEX;
+						if (team + 32u * r < rowlen) {
+							v[r] = __ldg(reinterpret_cast<const uint32_t*>(blk) + team + 32 * r);
+#pragma unroll
+							for (int s = 0; s < NSTEP; ++s) xa[r][s] = __ldg(reinterpret_cast<const float4*>(pv + (size_t)r * 32 * d_pad * 4 + s * 128));
+						}
+					}
+					bool seen[NR];
+					uint8_t seenb[NR];
+#pragma unroll
+					for (int r = 0; r < NR; ++r) { // visited test-and-set (:596-605) as soon as the id is here, under the vector loads
+						seen[r] = false;
+						seenb[r] = 0;
+						if (tl == 0 && bottom && v[r] != NO_VERTEX) {
+							if (bits) seen[r] = (atomicOr(bits + (v[r] >> 5), 1u << (v[r] & 31)) >> (v[r] & 31)) & 1u;
+							else seenb[r] = vis[v[r]];
+						}
+					}
+					float sa[NR];
+#pragma unroll
+					for (int r = 0; r < NR; ++r) {
+						sa[r] = 0.f;
+						if (team + 32u * r < rowlen) {
+#pragma unroll
+							for (int s = 0; s < NSTEP; ++s) { // same order of operations as gather_dist_f32
+								float t;
+								t = qr[s].x - xa[r][s].x; sa[r] = fmaf(t, t, sa[r]); t = qr[s].y - xa[r][s].y; sa[r] = fmaf(t, t, sa[r]);
+								t = qr[s].z - xa[r][s].z; sa[r] = fmaf(t, t, sa[r]); t = qr[s].w - xa[r][s].w; sa[r] = fmaf(t, t, sa[r]);
+							}
+						}
+					}
+#pragma unroll
+					for (int o = 4; o >= 1; o >>= 1) {
+#pragma unroll
+						for (int r = 0; r < NR; ++r) sa[r] += __shfl_xor_sync(FULL, sa[r], o);
+					}
+#pragma unroll
+					for (int r = 0; r < NR; ++r) {
+						const uint32_t pos = team + 32u * r;
+						if (!bits && tl == 0 && bottom && v[r] != NO_VERTEX) {
+							seen[r] = seenb[r] == ep8;
+							if (!seen[r]) vis[v[r]] = ep8;
+						}
+						const bool fresh = v[r] != NO_VERTEX && !seen[r];
+						const uint32_t od = f32_orderable(sa[r]);
+						const uint64_t key = fresh ? ((uint64_t)od << 32) | (bottom ? v[r] << 1 : pos) : KEY_EMPTY; // bottom: beam_key(sa, v)
+						if (tl == 0 && pos < rowlen) {
+							out[pos] = key;
+							if (bottom && fresh && od < job.w && pfv == NO_VERTEX) pfv = v[r];
+						}
+					}
+				} else if (NSTEP > 0 && one_round) {
 					const bool in = bottom ? in_b : in_u;
 					const uint8_t* pv = blk + (bottom ? off_b : off_u);
 					uint32_t v = NO_VERTEX;
