@@ -359,3 +359,28 @@ def test_inline_blocks_handmade_graphs(ex, n, d, maxdeg, updeg, layers):
                 assert np.array_equal(a, b), (ef, k, name)
     for e in eng.values():
         e.close()
+
+
+def test_inline_blocks_several_queries_per_cta(ex):
+    """more queries than resident CTA slots: every CTA of the block form runs several queries one after the other (its
+    rendezvous counters, visited bitmap and scorer state carry over); results equal the one-warp-per-query form's"""
+    from expann_b200 import datasets
+    base, q = datasets.make("sift", 5000, 64, 128, seed=9, variant="lowrank")
+    rng = np.random.default_rng(3)
+    qq = np.ascontiguousarray(q[rng.integers(0, 64, 3000)] + rng.integers(0, 3, (3000, 128)).astype(np.float32))
+    for inl in (1, 2):
+        e = ex.GraphEngine()
+        e.set_option("graph_inline", inl)
+        e.set_option("graph_occ", 2)          # 2 x 148 CTAs x 4 slots = 1184 < 3000 queries
+        e.store_many_vectors(base)
+        e.build_graph(M=8, M0=24, K=48)
+        e.build()
+        for ef in (10, 40):
+            e.set_ef_search(ef)
+            e.set_option("graph_cta_batch", 10 ** 6)
+            a = e.query_k_batch(qq, 10)
+            e.set_option("graph_cta_batch", 0)
+            b = e.query_k_batch(qq, 10)
+            for x, y in zip(a, b):
+                assert np.array_equal(x, y), (inl, ef)
+        e.close()
