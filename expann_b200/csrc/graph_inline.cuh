@@ -483,7 +483,7 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 					int myrank = 0, lo = 0, shift[LPL];
 #pragma unroll
 					for (int s = 0; s < LPL; ++s) shift[s] = 0;
-#pragma unroll 2
+#pragma unroll 4
 					for (int j = 0; j < ncand; ++j) {
 						const uint64_t kk = ck[j];
 						myrank += kk < mykey;
