@@ -160,7 +160,7 @@ int graph_load_index(expann_gpu* h, const char* path, std::vector<float>& vector
 }
 
 // shared memory of graph_search_inline_kernel next to its visited bitmap
-static size_t inline_fixed_smem(size_t d_pad) { return d_pad * 4 + 2 * GS_MAXNB * 8 + 256 * 8 + 32 * 8 + 6 * 16 + 6 * 8 + 128; }
+static size_t inline_fixed_smem(size_t d_pad) { return d_pad * 5 + 2 * GS_MAXNB * 8 + 256 * 8 + 32 * 8 + 6 * 16 + 6 * 8 + 128; }
 
 int graph_finalize(expann_gpu* h) {
 	HostGraph& g = h->graph;
@@ -215,10 +215,18 @@ int graph_finalize(expann_gpu* h) {
 			h->g_nup = meta.size();
 		}
 	}
+	if (h->cfg.use_compression) {
+		const size_t total = h->n * h->d_pad;
+		EXPANN_CUDA(h, h->g_codes.ensure(total));
+		quantize_u8_kernel<<<(unsigned)std::min<size_t>(65535, (total + 255) / 256), 256, 0, st>>>(h->base, h->g_codes.as<uint8_t>(), total);
+		EXPANN_CUDA(h, cudaGetLastError());
+		h->stats.aux_launches++;
+	}
 	// neighbourhood blocks for the latency form (graph_inline.cuh): HBM capacity traded for one memory trip per hop
 	h->g_inline = false;
-	if (h->opt_graph_inline != 0 && !h->cfg.use_compression && (h->g_nup || g.max_layer <= 1)) {
-		const size_t bb_idb = (g.m0s * 4 + 127) / 128 * 128, bb = bb_idb + g.m0s * h->d_pad * 4;
+	if (h->opt_graph_inline != 0 && (h->g_nup || g.max_layer <= 1)) {
+		const bool comp = h->cfg.use_compression != 0; // compressed graphs: the bottom blocks hold the 8-bit codes
+		const size_t bb_idb = (g.m0s * 4 + 127) / 128 * 128, bb = comp ? (bb_idb + g.m0s * h->d_pad + 127) / 128 * 128 : bb_idb + g.m0s * h->d_pad * 4;
 		const size_t ub_idb = (g.ms * 4 + 127) / 128 * 128, ub = (ub_idb + g.ms * 16 + g.ms * h->d_pad * 4 + 127) / 128 * 128;
 		const size_t urows = h->g_nup ? g.upper.size() / g.ms : 0;
 		const size_t total = g.n * bb + urows * ub;
@@ -236,8 +244,12 @@ int graph_finalize(expann_gpu* h) {
 				}
 			h->g_bb_bytes = (uint32_t)bb; h->g_bb_idb = (uint32_t)bb_idb; h->g_ub_bytes = (uint32_t)ub; h->g_ub_idb = (uint32_t)ub_idb;
 			const size_t wb = g.n * g.m0s;
-			build_bottom_blocks_kernel<<<(unsigned)((wb * 32 + 255) / 256), 256, 0, st>>>(h->base, h->g_bottom.as<uint32_t>(), h->g_blk_bottom.as<uint8_t>(),
-			                                                                           (uint32_t)g.n, (uint32_t)g.m0s, (uint32_t)h->d_pad, (uint32_t)bb, (uint32_t)bb_idb);
+			if (comp)
+				build_bottom_code_blocks_kernel<<<(unsigned)((wb * 32 + 255) / 256), 256, 0, st>>>(h->g_codes.as<uint8_t>(), h->g_bottom.as<uint32_t>(), h->g_blk_bottom.as<uint8_t>(),
+				                                                                                (uint32_t)g.n, (uint32_t)g.m0s, (uint32_t)h->d_pad, (uint32_t)bb, (uint32_t)bb_idb);
+			else
+				build_bottom_blocks_kernel<<<(unsigned)((wb * 32 + 255) / 256), 256, 0, st>>>(h->base, h->g_bottom.as<uint32_t>(), h->g_blk_bottom.as<uint8_t>(),
+				                                                                           (uint32_t)g.n, (uint32_t)g.m0s, (uint32_t)h->d_pad, (uint32_t)bb, (uint32_t)bb_idb);
 			EXPANN_CUDA(h, cudaGetLastError());
 			if (urows) {
 				const size_t wu = urows * g.ms;
@@ -250,13 +262,6 @@ int graph_finalize(expann_gpu* h) {
 		}
 	}
 	if (!h->g_inline) { h->g_blk_bottom.release(); h->g_blk_upper.release(); }
-	if (h->cfg.use_compression) {
-		const size_t total = h->n * h->d_pad;
-		EXPANN_CUDA(h, h->g_codes.ensure(total));
-		quantize_u8_kernel<<<(unsigned)std::min<size_t>(65535, (total + 255) / 256), 256, 0, st>>>(h->base, h->g_codes.as<uint8_t>(), total);
-		EXPANN_CUDA(h, cudaGetLastError());
-		h->stats.aux_launches++;
-	}
 	EXPANN_CUDA(h, cudaStreamSynchronize(st));
 	return EXPANN_OK;
 }
@@ -295,7 +300,7 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 	// 320 vs 410 us, 512 queries 573 vs 419 us per call)
 	// (over the neighbourhood blocks the one-CTA-per-query form stays ahead for longer: 296 queries 183 vs 398 us, 592 queries
 	// 310 vs 408 us, 1024 queries 484 vs 426 us per call: automatic up to five waves)
-	const bool blocks_ok = h->g_inline && h->opt_graph_inline != 0 && !h->cfg.use_compression && !(h->opt_graph_cta_width == 2 && ef >= 2);
+	const bool blocks_ok = h->g_inline && h->opt_graph_inline != 0 && !(h->opt_graph_cta_width == 2 && ef >= 2);
 	if (m <= (size_t)(h->opt_graph_cta_batch < 0 ? (blocks_ok ? 5 : 2) * sms : h->opt_graph_cta_batch)) {
 		// latency form: one CTA per query (few queries per call; nothing to hide the hops' round trips behind)
 		const size_t smem1 = (size_t)h->d_pad * 5 + GS_MAXNB * 8 + 16 + 256 * 8 + GS_MAXNB * 4; // query | u8 query | nb | nbd | ctl | beam copy
@@ -316,7 +321,7 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 			h->fused = true;
 		}
 		cudaEvent_t t0 = timing_begin(h, st);
-		if (h->g_inline && h->opt_graph_inline != 0 && p.width == 1 && !p.compressed) {
+		if (h->g_inline && h->opt_graph_inline != 0 && p.width == 1) {
 			// neighbourhood blocks (graph_inline.cuh): one bulk copy per hop
 			InlineParams ip{};
 			ip.g = p;
@@ -327,19 +332,21 @@ int launch_graph_search(expann_gpu* h, const float* d_q, size_t m, size_t k, siz
 			const size_t bitmap = ((h->n + 127) / 128) * 16; // bytes, whole uint4s
 			ip.bitmap_words = fixed + bitmap <= lim && h->opt_graph_inline != 2 ? (uint32_t)(bitmap / 4) : 0;
 			const size_t smemi = fixed + (size_t)ip.bitmap_words * 4;
-#define GI_LAUNCH_N(L, N, R)                                                                                      \
+#define GI_LAUNCH_N(L, N, R, C)                                                                                   \
 	do {                                                                                                          \
-		if (int rc_ = ensure_dyn_smem(h, (const void*)graph_search_inline_kernel<L, N, R>, smemi)) return rc_;          \
-		graph_search_inline_kernel<L, N, R><<<grid1, GI_THREADS, smemi, st>>>(ip);                               \
+		if (int rc_ = ensure_dyn_smem(h, (const void*)graph_search_inline_kernel<L, N, R, C>, smemi)) return rc_;       \
+		graph_search_inline_kernel<L, N, R, C><<<grid1, GI_THREADS, smemi, st>>>(ip);                            \
 	} while (0)
 #define GI_LAUNCH(L)                                                                                              \
 	do {                                                                                                          \
 		const bool wide = std::max(h->graph.m0s, h->graph.ms) > 32 && std::max(h->graph.m0s, h->graph.ms) <= 128; \
-		if (h->d_pad == 128 && wide) GI_LAUNCH_N(L, 4, 4);                                                       \
-		else if (h->d_pad == 128) GI_LAUNCH_N(L, 4, 1);                                                          \
-		else if (h->d_pad == 96 && wide) GI_LAUNCH_N(L, 3, 4);                                                   \
-		else if (h->d_pad == 96) GI_LAUNCH_N(L, 3, 1);                                                           \
-		else GI_LAUNCH_N(L, 0, 1);                                                                               \
+		if (p.compressed && h->d_pad == 128) GI_LAUNCH_N(L, 4, 1, true);                                         \
+		else if (p.compressed) GI_LAUNCH_N(L, 0, 1, true);                                                       \
+		else if (h->d_pad == 128 && wide) GI_LAUNCH_N(L, 4, 4, false);                                           \
+		else if (h->d_pad == 128) GI_LAUNCH_N(L, 4, 1, false);                                                   \
+		else if (h->d_pad == 96 && wide) GI_LAUNCH_N(L, 3, 4, false);                                            \
+		else if (h->d_pad == 96) GI_LAUNCH_N(L, 3, 1, false);                                                    \
+		else GI_LAUNCH_N(L, 0, 1, false);                                                                        \
 	} while (0)
 			if (cap <= 32) GI_LAUNCH(1);
 			else if (cap <= 64) GI_LAUNCH(2);

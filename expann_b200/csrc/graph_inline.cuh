@@ -82,7 +82,7 @@ __device__ unsigned gi_prof_calls;
 // nearly alone on its scheduler), so the per-hop paths are specialised: NSTEP = d_pad / 32 (3 or 4: the lane's share of the
 // query lives in registers and the loads are issued unconditionally; 0 = any dimension), rows of at most 32 neighbours
 // (one per team) take a path without loops.
-template <int LPL, int NSTEP, int NR>
+template <int LPL, int NSTEP, int NR, bool COMP>
 __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const InlineParams p) {
 	extern __shared__ __align__(128) uint8_t gi_smem[];
 	const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
@@ -91,7 +91,8 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 	const bool one_round = m0s <= 32u * NR && ms <= 32u * NR; // NR = 1: one neighbour per team; NR = 4: up to four (rows of up to 128, the reference's M0 = 120)
 	// shared memory: query | keys of a hop's scores x 2 | beam copy | staged candidates | ctl x 2 | state x 2 | barriers | bitmap
 	float* qsm = reinterpret_cast<float*>(gi_smem);
-	uint64_t* rk = reinterpret_cast<uint64_t*>(qsm + d_pad); // [2][GS_MAXNB] bottom: beam key of a fresh neighbour; upper: orderable(dist) << 32 | position; KEY_EMPTY
+	uint8_t* qcs = reinterpret_cast<uint8_t*>(qsm + d_pad);  // [d_pad] the query truncated to u8 (compressed graphs: src/antitopo_engine.h:726-737)
+	uint64_t* rk = reinterpret_cast<uint64_t*>(qcs + d_pad); // [2][GS_MAXNB] bottom: beam key of a fresh neighbour; upper: orderable(dist) << 32 | position; KEY_EMPTY
 	uint64_t* bm = rk + 2 * GS_MAXNB;                        // [32 * LPL] shared-memory copy of the beam
 	uint64_t* ck = bm + 256;                                 // [32] candidate keys of one admission round
 	uint4* ctl = reinterpret_cast<uint4*>(ck + 32);          // [2] job for the scorers: block pointer (lo, hi), mode (0 stop, 1 upper, 2 bottom), bound for their prefetch
@@ -129,7 +130,11 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 		} else
 			for (uint32_t i = tid * 4; i < p.bitmap_words; i += GI_THREADS * 4) *reinterpret_cast<uint4*>(bits + i) = make_uint4(0, 0, 0, 0);
 		const uint8_t ep8 = (uint8_t)(epoch & 0xFF);
-		for (uint32_t i = tid; i < d_pad; i += GI_THREADS) qsm[i] = p.g.queries[(size_t)qi * d_pad + i];
+		for (uint32_t i = tid; i < d_pad; i += GI_THREADS) {
+			const float qv = p.g.queries[(size_t)qi * d_pad + i];
+			qsm[i] = qv;
+			if (COMP) qcs[i] = (uint8_t)(uint32_t)qv;
+		}
 		__syncthreads();
 
 		if (wib != 0) {
@@ -142,6 +147,9 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 			// where this lane reads in a block (rows of at most 32 neighbours: team t scores neighbour t)
 			const uint32_t off_b = p.bb_idb + team * d_pad * 4 + tl * 16, off_u = p.ub_idb + ms * 16 + team * d_pad * 4 + tl * 16;
 			const bool in_b = team < m0s, in_u = team < ms;
+			// compressed graphs: a bottom block holds 8-bit codes, d_pad bytes per row, one 16-byte chunk per lane for d_pad <= 128
+			const uint32_t nchunk = d_pad >> 4, off_c = p.bb_idb + team * d_pad + tl * 16;
+			const uint4 qcr = COMP && tl < nchunk ? *reinterpret_cast<const uint4*>(qcs + tl * 16) : make_uint4(0, 0, 0, 0);
 #ifdef GI_PROFILE
 			long long sp[6] = { 0, 0, 0, 0, 0, 0 }, sp_t = clock64();
 			int sp_jobs = 0;
@@ -167,7 +175,36 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 				uint64_t* out = rk + par * GS_MAXNB;
 				const bool bottom = job.z == 2;
 				uint32_t pfv = NO_VERTEX; // a neighbour likely to be expanded next: its block is asked into L2
-				if (NSTEP > 0 && NR > 1 && one_round) {
+				if (COMP && bottom && NSTEP > 0 && one_round) {
+					// dist2_compressed (src/antitopo_engine.h:38-61) on the block's 8-bit codes: one 16-byte load per lane
+					uint32_t v = NO_VERTEX;
+					uint4 xc = make_uint4(0, 0, 0, 0);
+					if (in_b) {
+						v = __ldg(reinterpret_cast<const uint32_t*>(blk) + team);
+						if (tl < nchunk) xc = __ldg(reinterpret_cast<const uint4*>(blk + off_c));
+					}
+					bool seen = false;
+					uint8_t seenb = 0;
+					if (tl == 0 && v != NO_VERTEX) { // visited test-and-set (:596-605) under the code loads
+						if (bits) seen = (atomicOr(bits + (v >> 5), 1u << (v & 31)) >> (v & 31)) & 1u;
+						else seenb = vis[v];
+					}
+					uint32_t sc = 0, t;
+					t = __vabsdiffu4(qcr.x, xc.x); sc = __dp4a(t, t, sc); t = __vabsdiffu4(qcr.y, xc.y); sc = __dp4a(t, t, sc);
+					t = __vabsdiffu4(qcr.z, xc.z); sc = __dp4a(t, t, sc); t = __vabsdiffu4(qcr.w, xc.w); sc = __dp4a(t, t, sc);
+#pragma unroll
+					for (int o = 4; o >= 1; o >>= 1) sc += __shfl_xor_sync(FULL, sc, o);
+					if (!bits && tl == 0 && v != NO_VERTEX) {
+						seen = seenb == ep8;
+						if (!seen) vis[v] = ep8;
+					}
+					const bool fresh = v != NO_VERTEX && !seen;
+					const uint32_t od = f32_orderable((float)(int32_t)sc); // the reference converts the int32 score to T = float (:738-743)
+					if (tl == 0 && in_b) {
+						out[team] = fresh ? ((uint64_t)od << 32) | (v << 1) : KEY_EMPTY;
+						if (fresh && od < job.w) pfv = v;
+					}
+				} else if (NSTEP > 0 && NR > 1 && one_round) {
 					// rows of up to 32 * NR neighbours: team t scores neighbours t, t + 32, ...; the loads of all its rounds are
 					// issued before the first is used
 					const uint32_t rowlen = bottom ? m0s : ms;
@@ -280,6 +317,20 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 						const uint32_t v = in ? __ldg(reinterpret_cast<const uint32_t*>(blk) + pos) : NO_VERTEX;
 						const float* pa = reinterpret_cast<const float*>(vecs) + (size_t)(in ? pos : 0) * d_pad + tl * 4;
 						float sa = 0.f;
+						if (COMP && bottom) { // 8-bit codes (rows of d_pad bytes)
+							const uint8_t* pc = vecs + (size_t)(in ? pos : 0) * d_pad;
+							uint32_t sc = 0;
+							for (uint32_t c = tl; c < nchunk; c += 8) {
+								const uint4 xc = __ldg(reinterpret_cast<const uint4*>(pc + c * 16));
+								const uint4 q = *reinterpret_cast<const uint4*>(qcs + c * 16);
+								uint32_t t;
+								t = __vabsdiffu4(q.x, xc.x); sc = __dp4a(t, t, sc); t = __vabsdiffu4(q.y, xc.y); sc = __dp4a(t, t, sc);
+								t = __vabsdiffu4(q.z, xc.z); sc = __dp4a(t, t, sc); t = __vabsdiffu4(q.w, xc.w); sc = __dp4a(t, t, sc);
+							}
+#pragma unroll
+							for (int o = 4; o >= 1; o >>= 1) sc += __shfl_xor_sync(FULL, sc, o);
+							sa = (float)(int32_t)sc;
+						} else {
 						for (int s0 = 0; s0 < nstep; s0 += 4) {
 							float4 xa[4];
 #pragma unroll
@@ -296,6 +347,7 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 						}
 #pragma unroll
 						for (int o = 4; o >= 1; o >>= 1) sa += __shfl_xor_sync(FULL, sa, o);
+						}
 						if (tl == 0 && in) {
 							uint64_t key = KEY_EMPTY;
 							if (v != NO_VERTEX) {
@@ -428,7 +480,16 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 #endif
 			}
 			GI_T(0);
-			// ---- bottom layer (:495-708). The entry vertex is the first to be expanded.
+			// ---- bottom layer (:495-708 / compressed :710-851). The entry vertex is the first to be expanded.
+			if (COMP) { // its key in the beam is its score on the codes
+				float* tmpd = reinterpret_cast<float*>(ck);
+				uint32_t* tmpi = reinterpret_cast<uint32_t*>(ck + 8);
+				if (lane == 0) tmpi[0] = ep;
+				__syncwarp();
+				gather_score_u8(p.g.codes, d_pad, qcs, tmpi, tmpd, 1, lane);
+				ep_dist = tmpd[0];
+				__syncwarp();
+			}
 			if (lane == 0) {
 				if (bits) atomicOr(bits + (ep >> 5), 1u << (ep & 31));
 				else vis[ep] = ep8;
@@ -540,6 +601,60 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 			// ---- output, as in the other forms
 			uint64_t* dst = p.g.out_keys + (size_t)qi * p.g.k;
 			uint32_t nres = 0;
+			if (COMP) {
+				// (:845-848) fp32 distances of the ef survivors; then — the deliberate deviation of the other forms, SURVEY 8(a)
+				// a13 — re-sorted by the fp32 key before the truncation to k. The scorers are idle: rk is scratch. Sorted by rank
+				// counting (every key against all others through shared memory), not by cnt insertions.
+				uint32_t* sid = reinterpret_cast<uint32_t*>(rk);
+				float* sd = reinterpret_cast<float*>(sid + GS_MAXNB);
+				uint64_t* sorted = rk + GS_MAXNB;
+				int cnt = 0;
+#pragma unroll
+				for (int s = 0; s < LPL; ++s) {
+					const int i = s * 32 + lane;
+					const bool ok = i < (int)ef && beam.e[s] != KEY_EMPTY;
+					const unsigned mk = __ballot_sync(FULL, ok);
+					if (ok) sid[cnt + __popc(mk & ((1u << lane) - 1))] = (uint32_t)(beam.e[s] >> 1) & 0x7FFFFFFFu;
+					cnt += __popc(mk);
+				}
+				__syncwarp();
+				for (int i = lane; i < cnt; i += 32) { // all survivors' rows are asked for at once: only the gather's first round waits for DRAM
+					const char* r = reinterpret_cast<const char*>(p.g.base + (size_t)sid[i] * d_pad);
+					for (uint32_t o = 0; o < d_pad * 4; o += 128) prefetch_l2(r + o);
+				}
+				gather_dist_f32(p.g.base, d_pad, qsm, sid, sd, cnt, lane);
+				uint64_t mine[LPL];
+#pragma unroll
+				for (int s = 0; s < LPL; ++s) {
+					const int i = s * 32 + lane;
+					mine[s] = i < cnt ? make_key(sd[i], sid[i]) : KEY_EMPTY;
+					if (i < cnt) bm[i] = mine[s];
+				}
+				__syncwarp();
+				int rank[LPL];
+#pragma unroll
+				for (int s = 0; s < LPL; ++s) rank[s] = 0;
+#pragma unroll 4
+				for (int j = 0; j < cnt; ++j) {
+					const uint64_t kk = bm[j];
+#pragma unroll
+					for (int s = 0; s < LPL; ++s) rank[s] += kk < mine[s];
+				}
+#pragma unroll
+				for (int s = 0; s < LPL; ++s)
+					if (mine[s] != KEY_EMPTY) sorted[rank[s]] = mine[s];
+				__syncwarp();
+#pragma unroll
+				for (int s = 0; s < LPL; ++s) {
+					const int i = s * 32 + lane;
+					uint64_t key = KEY_EMPTY;
+					if (i < (int)p.g.k) {
+						key = i < cnt ? sorted[i] + p.g.id_add : KEY_EMPTY;
+						dst[i] = key;
+					}
+					emit_decoded(p.g, qi, i, key, nres);
+				}
+			} else {
 #pragma unroll
 			for (int s = 0; s < LPL; ++s) {
 				const int i = s * 32 + lane;
@@ -551,6 +666,7 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 					dst[i] = key;
 				}
 				emit_decoded(p.g, qi, i, key, nres);
+			}
 			}
 			if (p.g.dec_counts && lane == 0) p.g.dec_counts[qi] = nres;
 			dc_total += dc;
@@ -799,6 +915,25 @@ __global__ void build_bottom_blocks_kernel(const float* __restrict__ base, const
 	float4* dst = reinterpret_cast<float4*>(blk + bb_idb + (size_t)j * d_pad * 4);
 	const float4* src = reinterpret_cast<const float4*>(base + (size_t)(nbv == NO_VERTEX ? 0 : nbv) * d_pad);
 	for (uint32_t i = lane; i < d_pad / 4; i += 32) dst[i] = nbv == NO_VERTEX ? make_float4(0.f, 0.f, 0.f, 0.f) : src[i];
+}
+
+// compressed graphs: block(v) = [ids | the neighbours' 8-bit codes, d_pad bytes each]
+__global__ void build_bottom_code_blocks_kernel(const uint8_t* __restrict__ codes, const uint32_t* __restrict__ bottom, uint8_t* __restrict__ blocks,
+                                                uint32_t n, uint32_t m0s, uint32_t d_pad, uint32_t bb_bytes, uint32_t bb_idb) {
+	const size_t w = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const uint32_t lane = threadIdx.x & 31;
+	if (w >= (size_t)n * m0s) return;
+	const uint32_t v = (uint32_t)(w / m0s), j = (uint32_t)(w % m0s);
+	uint8_t* blk = blocks + (size_t)v * bb_bytes;
+	const uint32_t nbv = bottom[(size_t)v * m0s + j];
+	if (lane == 0) reinterpret_cast<uint32_t*>(blk)[j] = nbv;
+	if (j == 0) {
+		for (uint32_t i = m0s + lane; i < bb_idb / 4; i += 32) reinterpret_cast<uint32_t*>(blk)[i] = NO_VERTEX;
+		for (uint32_t i = bb_idb + m0s * d_pad + lane; i < bb_bytes; i += 32) blk[i] = 0; // tail padding
+	}
+	uint4* dst = reinterpret_cast<uint4*>(blk + bb_idb + (size_t)j * d_pad);
+	const uint4* src = reinterpret_cast<const uint4*>(codes + (size_t)(nbv == NO_VERTEX ? 0 : nbv) * d_pad);
+	for (uint32_t i = lane; i < d_pad / 16; i += 32) dst[i] = nbv == NO_VERTEX ? make_uint4(0, 0, 0, 0) : src[i];
 }
 
 __global__ void build_upper_blocks_kernel(const float* __restrict__ up_vec, const uint4* __restrict__ up_meta, const uint32_t* __restrict__ upper_c,

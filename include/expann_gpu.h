@@ -176,7 +176,8 @@ int expann_gpu_stats(expann_gpu_t* h, expann_gpu_stats_t* out);
  * contiguous, n x (M0 x d x 4 + 128) bytes of HBM (16.5 GB per million vertices at M0 = 32, d = 128) — one memory round trip
  * per hop instead of two, same ids and distances bit for bit; automatic = built when the blocks take at most a third of the
  * free device memory, 1 = whenever they fit, 2 = as 1 with the visited set in HBM bytes instead of the shared-memory bitmap (the
- * form graphs above ~1.7 M vertices get; for tests); not used with use_compression or graph_cta_width 2), "graph_inline_batch"
+ * form graphs above ~1.7 M vertices get; for tests); with use_compression the bottom blocks hold the 8-bit codes (n x (M0 x d + 128)
+ * bytes) and only the one-CTA-per-query form reads them; not used with graph_cta_width 2), "graph_inline_batch"
  * (0/1, default 1: the one-warp-per-query form gathers from the blocks too when they exist — same results, +8-12 % QPS).
  * Tensor-core candidate filter of the brute-force engine: "tc" (0/1; operands are prepared by build(), so enabling
  * needs to precede it), "tc_min_batch" (default 5: measured crossover with the SIMT scan on 1M x 128), "tc_pair" (0/1:

@@ -384,3 +384,40 @@ def test_inline_blocks_several_queries_per_cta(ex):
             for x, y in zip(a, b):
                 assert np.array_equal(x, y), (inl, ef)
         e.close()
+
+
+@pytest.mark.parametrize("n,d,M,M0", [(6000, 128, 12, 32), (3000, 96, 8, 24), (2500, 100, 8, 48), (1500, 256, 8, 16)])
+def test_inline_code_blocks_identical(ex, n, d, M, M0):
+    """compressed graphs (use_compression: the bottom layer scored on 8-bit codes, fp32 re-rank of the ef survivors): the
+    block form over CODE blocks returns what the row forms return, bit for bit, with either visited-set form"""
+    from expann_b200 import datasets
+    base, q = datasets.make("sift", n, 40, d, seed=6, variant="lowrank")
+    eng = {}
+    for inl in (0, 1, 2):
+        e = ex.GraphEngine(use_compression=True)
+        e.set_option("graph_inline", inl)
+        e.store_many_vectors(base)
+        e.build_graph(M=M, M0=M0, K=2 * M0)
+        e.build()
+        eng[inl] = e
+    for ef in (1, 10, 40, 130):
+        k = min(10, ef)
+        res = {}
+        for inl, e in eng.items():
+            e.set_ef_search(ef)
+            dc0 = e.stats()["distcomps"]
+            one = [e.query_k_batch(q[i:i + 1], k) for i in range(len(q))]
+            dc = e.stats()["distcomps"] - dc0
+            res[inl] = [np.concatenate([o[j] for o in one]) for j in range(3)] + list(e.query_k_batch(q, k)) + [dc]
+        e = eng[0]
+        e.set_option("graph_cta_batch", 0)
+        warp = list(e.query_k_batch(q, k))
+        e.set_option("graph_cta_batch", -1)
+        for inl in (1, 2):
+            for a, b in zip(res[0][:6], res[inl][:6]):
+                assert np.array_equal(a, b), (ef, inl)
+            assert res[0][6] == res[inl][6], (ef, inl)
+            for a, b in zip(res[inl][3:6], warp):
+                assert np.array_equal(a, b), (ef, inl)
+    for e in eng.values():
+        e.close()

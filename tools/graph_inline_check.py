@@ -12,7 +12,7 @@ nq = 512
 base, q = datasets.make("sift", n, nq, d, variant="lowrank")
 eng = {}
 for inl in (0, 1):
-    e = expann_b200.GraphEngine()
+    e = expann_b200.GraphEngine(use_compression=bool(int(os.environ.get("COMPRESSED", "0"))))
     e.set_option("graph_inline", inl)
     e.store_many_vectors(base)
     t = time.time(); e.build_graph(M=16, M0=32, K=64); e.build(); tb = time.time() - t
