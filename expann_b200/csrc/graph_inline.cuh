@@ -394,7 +394,11 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 					fk = warp_min_u64(fk);
 					if ((uint32_t)(fk >> 32) >= b.x) fk = KEY_EMPTY; // not admitted (b.x = 0xFFFFFFFF while the beam is not full)
 					const uint64_t nextk = min(fk, r1);
-					if (nextk == KEY_EMPTY) break; // the search is over
+					if (nextk == KEY_EMPTY) { // the search is over
+						// (compressed graphs: the controller reuses rk for its re-rank; it may do so once every scorer is here)
+						if (COMP) asm volatile("bar.sync 1, %0;" ::"r"(GI_THREADS) : "memory");
+						break;
+					}
 					const uint64_t second = nextk == fk ? r1 : min(fk, r2);
 					const uint64_t addr = reinterpret_cast<uint64_t>(p.blk_bottom + (size_t)((uint32_t)(nextk >> 1) & 0x7FFFFFFFu) * p.bb_bytes);
 					job = make_uint4((uint32_t)addr, (uint32_t)(addr >> 32), 2u, min((uint32_t)(second >> 32), b.x));
@@ -602,6 +606,7 @@ __global__ void __launch_bounds__(GI_THREADS) graph_search_inline_kernel(const I
 			uint64_t* dst = p.g.out_keys + (size_t)qi * p.g.k;
 			uint32_t nres = 0;
 			if (COMP) {
+				asm volatile("bar.sync 1, %0;" ::"r"(GI_THREADS) : "memory"); // every scorer has read the last hop's scores
 				// (:845-848) fp32 distances of the ef survivors; then — the deliberate deviation of the other forms, SURVEY 8(a)
 				// a13 — re-sorted by the fp32 key before the truncation to k. The scorers are idle: rk is scratch. Sorted by rank
 				// counting (every key against all others through shared memory), not by cnt insertions.
