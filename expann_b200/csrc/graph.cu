@@ -236,12 +236,20 @@ int graph_finalize(expann_gpu* h) {
 		const bool fits_smem = inline_fixed_smem(h->d_pad) <= 200 * 1024;
 		const bool fits_hbm = h->opt_graph_inline >= 1 ? total + ((size_t)1 << 30) <= freeb : total <= freeb / 3;
 		if (fits_smem && fits_hbm && bb < ((size_t)1 << 31) && ub < ((size_t)1 << 31)) {
+			bool got = true;
 			for (auto pr : { std::make_pair(&h->g_blk_bottom, g.n * bb), std::make_pair(&h->g_blk_upper, std::max<size_t>(256, urows * ub)) })
-				if (pr.first->cap < pr.second) { // exact size: these are the largest allocations of the handle
+				if (got && pr.first->cap < pr.second) { // exact size: these are the largest allocations of the handle
 					pr.first->release();
-					EXPANN_CUDA(h, cudaMalloc(&pr.first->p, pr.second));
-					pr.first->cap = pr.second;
+					const cudaError_t e = cudaMalloc(&pr.first->p, pr.second);
+					if (e != cudaSuccess) { // (several engines building on one GPU at the same time may all have seen the same free memory)
+						(void)cudaGetLastError();
+						pr.first->p = nullptr;
+						got = false;
+						if (h->opt_graph_inline >= 1) return cuda_fail(h, e, "cudaMalloc of the neighbourhood blocks (graph_inline)");
+					} else
+						pr.first->cap = pr.second;
 				}
+			if (got) {
 			h->g_bb_bytes = (uint32_t)bb; h->g_bb_idb = (uint32_t)bb_idb; h->g_ub_bytes = (uint32_t)ub; h->g_ub_idb = (uint32_t)ub_idb;
 			const size_t wb = g.n * g.m0s;
 			if (comp)
@@ -259,6 +267,7 @@ int graph_finalize(expann_gpu* h) {
 			}
 			h->stats.aux_launches += 2;
 			h->g_inline = true;
+			} // (automatic mode without the memory: the row forms serve every call)
 		}
 	}
 	if (!h->g_inline) { h->g_blk_bottom.release(); h->g_blk_upper.release(); }
